@@ -1,0 +1,130 @@
+"""Generate tests/golden/vq_*.npz by running the reference's own compression/vq.py.
+
+Run in the build container (where /root/reference exists):
+
+    python -m oracle.make_golden
+
+The reference module is imported unchanged through oracle/ref_loader.py.  Its
+`vq_features` (compression/vq.py:49-87) is executed on CPU tensors with
+  * torch.cuda.synchronize / empty_cache patched to no-ops (no driver here),
+  * torch.randint, VectorQuantize.uniform_init and VectorQuantize.update wrapped by
+    recorders, so the fixture holds every random draw and every intermediate state.
+The fixtures pin the Python half of the path (weight normalisation, batch draw,
+update algebra, EMA order, eps, trace normalisation, final assignment).  The CUDA
+half (weighted_distance.cu) is pinned on the GPU box by oracle/make_golden_gpu.py.
+"""
+from __future__ import annotations
+
+import os
+import sys
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+sys.path.insert(0, ROOT)
+
+from oracle import ref_loader  # noqa: E402
+
+GOLDEN_DIR = os.path.join(ROOT, "tests", "golden")
+
+# name, N, D, K, vq_chunk, steps, scale_normalize, seed
+CASES = [
+    ("sh45", 1000, 45, 64, 256, 4, False, 0),       # BASELINE config 1/2 width
+    ("sh48", 1000, 48, 64, 256, 3, False, 1),       # fork default colour width (arguments/__init__.py:97)
+    ("shape7", 1500, 7, 96, 512, 4, False, 2),      # BASELINE config 3 width
+    ("cov6", 1500, 6, 96, 512, 4, True, 3),         # fork reality: 6-D covariance + trace normalise (vq.py:159-172)
+]
+
+
+def synth(n, d, seed, cov=False):
+    """Seeded CPU inputs: clustered features, heavy-tailed sensitivities."""
+    g = torch.Generator().manual_seed(seed)
+    centres = torch.randn(37, d, generator=g)
+    x = centres[torch.randint(0, 37, (n,), generator=g)] + 0.25 * torch.randn(n, d, generator=g)
+    if cov:
+        # symmetric positive-definite 3x3, upper triangle (xx,xy,xz,yy,yz,zz), trace-normalised like
+        # get_normalized_covariance(strip_sym=True) would give
+        a = torch.randn(n, 3, 3, generator=g)
+        m = a @ a.transpose(1, 2) + 0.05 * torch.eye(3)
+        m = m / m.diagonal(dim1=1, dim2=2).sum(-1)[:, None, None]
+        x = torch.stack([m[:, 0, 0], m[:, 0, 1], m[:, 0, 2], m[:, 1, 1], m[:, 1, 2], m[:, 2, 2]], 1)
+    w = torch.rand(n, generator=g) ** 4
+    return x.contiguous().float(), w.contiguous().float()
+
+
+def run_case(name, n, d, k, chunk, steps, scale_normalize, seed):
+    mod = ref_loader.load()
+    x, w = synth(n, d, seed, cov=scale_normalize)
+    rec = {"batches": [], "codebook0": None, "upd_x": [], "upd_w": [], "upd_dist": [], "upd_idx": [],
+           "cb_after": [], "ei_after": []}
+
+    VQ = mod.VectorQuantize
+    orig_init, orig_update = VQ.uniform_init, VQ.update
+    orig_randint = torch.randint
+    orig_sync, orig_empty = torch.cuda.synchronize, torch.cuda.empty_cache
+    orig_wd = mod.weightedDistance
+    last = {}
+
+    def wd(coefs, codebook):
+        dist, idx = orig_wd(coefs, codebook)
+        last["idx"] = idx.clone()
+        return dist, idx
+
+    def uniform_init(self, xx):
+        orig_init(self, xx)
+        rec["codebook0"] = self.codebook.data.clone()
+
+    def update(self, xx, importance):
+        out = orig_update(self, xx, importance)
+        rec["upd_dist"].append(out.clone())
+        rec["upd_idx"].append(last["idx"])
+        rec["cb_after"].append(self.codebook.data.clone())
+        rec["ei_after"].append(self.entry_importance.data.clone())
+        return out
+
+    def randint(*a, **kw):
+        r = orig_randint(*a, **kw)
+        rec["batches"].append(r.clone())
+        return r
+
+    torch.manual_seed(1000 + seed)
+    try:
+        VQ.uniform_init, VQ.update = uniform_init, update
+        mod.weightedDistance = wd
+        torch.randint = randint
+        torch.cuda.synchronize = lambda *a, **kw: None
+        torch.cuda.empty_cache = lambda *a, **kw: None
+        codebook, indices = mod.vq_features(x, w, k, chunk, steps, scale_normalize=scale_normalize, silent=True)
+    finally:
+        VQ.uniform_init, VQ.update = orig_init, orig_update
+        torch.randint = orig_randint
+        torch.cuda.synchronize, torch.cuda.empty_cache = orig_sync, orig_empty
+
+    # after cb_after was recorded the reference may have trace-normalised (vq.py:73-77); store both views
+    out = dict(
+        features=x.numpy(), importance=w.numpy(), codebook0=rec["codebook0"].numpy(),
+        batches=torch.stack(rec["batches"]).numpy(),
+        upd_dist=torch.stack(rec["upd_dist"]).numpy(), upd_idx=torch.stack(rec["upd_idx"]).numpy(),
+        cb_after_update=torch.stack(rec["cb_after"]).numpy(), ei_after_update=torch.stack(rec["ei_after"]).numpy(),
+        codebook=codebook.numpy(), indices=indices.numpy(),
+        meta=np.array([n, d, k, chunk, steps, int(scale_normalize), seed], np.int64),
+        decay=np.array(0.8), eps=np.array(1e-5),
+    )
+    os.makedirs(GOLDEN_DIR, exist_ok=True)
+    path = os.path.join(GOLDEN_DIR, f"vq_{name}.npz")
+    np.savez_compressed(path, **out)
+    return path
+
+
+def main():
+    if not ref_loader.available():
+        raise SystemExit("reference checkout not present; fixtures can only be generated in the build container")
+    for case in CASES:
+        p = run_case(*case)
+        print("wrote", p, os.path.getsize(p) // 1024, "KiB")
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,187 @@
+"""ctypes front-end of the CPU oracle (oracle/c3vq_oracle.c).
+
+TEST INFRASTRUCTURE ONLY — see the header of c3vq_oracle.c.  Imported by tests/,
+__graft_entry__.smoke() and bench.py's CPU-baseline legs; never by c3dgs_b200/.
+
+Works on numpy arrays (float32 / int64, C-contiguous).  Each function names the
+reference lines its C counterpart restates.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "libc3vq_oracle.so")
+_lib = None
+
+
+def build(force: bool = False) -> str:
+    """Compile the oracle with the recipe in oracle/Makefile."""
+    src = os.path.join(_HERE, "c3vq_oracle.c")
+    if force or not os.path.exists(_LIB_PATH) or os.path.getmtime(_LIB_PATH) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", _HERE, "libc3vq_oracle.so"], stdout=subprocess.DEVNULL)
+    return _LIB_PATH
+
+
+def lib() -> ctypes.CDLL:
+    global _lib
+    if _lib is None:
+        build()
+        L = ctypes.CDLL(_LIB_PATH)
+        f32p = ctypes.POINTER(ctypes.c_float)
+        f64p = ctypes.POINTER(ctypes.c_double)
+        i64p = ctypes.POINTER(ctypes.c_int64)
+        i64, i32, f64 = ctypes.c_int64, ctypes.c_int, ctypes.c_double
+        L.c3vq_oracle_num_threads.restype = i32
+        L.c3vq_oracle_set_threads.argtypes = [i32]
+        L.c3vq_oracle_distance.restype = ctypes.c_float
+        L.c3vq_oracle_distance.argtypes = [i32, f32p, f32p]
+        L.c3vq_oracle_assign.argtypes = [f32p, i64, i32, f32p, i32, f32p, i64p]
+        L.c3vq_oracle_scatter_sum.argtypes = [f32p, f32p, i64p, i64, i32, i32, f32p, f32p]
+        L.c3vq_oracle_scatter_sum_f64.argtypes = [f32p, f32p, i64p, i64, i32, i32, f64p, f64p]
+        L.c3vq_oracle_ema.argtypes = [f32p, f32p, f32p, f32p, i32, i32, f64, f64]
+        L.c3vq_oracle_trace_normalize.argtypes = [f32p, i32, i32]
+        L.c3vq_oracle_update.argtypes = [f32p, f32p, i64, i32, f32p, f32p, i32, f64, f64, f32p, i64p, f32p]
+        L.c3vq_oracle_gather.argtypes = [f32p, i64p, i64, i32, f32p]
+        _lib = L
+    return _lib
+
+
+def _f32(a) -> np.ndarray:
+    return np.ascontiguousarray(a, dtype=np.float32)
+
+
+def _i64(a) -> np.ndarray:
+    return np.ascontiguousarray(a, dtype=np.int64)
+
+
+def _p(a: np.ndarray, ty):
+    return a.ctypes.data_as(ctypes.POINTER(ty))
+
+
+def num_threads() -> int:
+    return int(lib().c3vq_oracle_num_threads())
+
+
+def set_threads(n: int) -> None:
+    lib().c3vq_oracle_set_threads(int(n))
+
+
+def distance(coefs, codeword) -> float:
+    """weighted_distance.cu:9-18."""
+    a, b = _f32(coefs), _f32(codeword)
+    return float(lib().c3vq_oracle_distance(a.shape[0], _p(a, ctypes.c_float), _p(b, ctypes.c_float)))
+
+
+def assign(x, codebook):
+    """weightedDistance(x, codebook) -> (min_dist f32[N], idx i64[N]).  weighted_distance.cu:20-93."""
+    x, cb = _f32(x), _f32(codebook)
+    if x.ndim != 2 or cb.ndim != 2:
+        raise RuntimeError("ceofs and codebook must have dimension 2")  # weighted_distance.cu:64-67
+    if x.shape[1] != cb.shape[1]:
+        raise RuntimeError("coefs and codebook must have same number of channels")  # :69-72
+    n, d = x.shape
+    k = cb.shape[0]
+    dist = np.zeros(n, np.float32)
+    idx = np.zeros(n, np.int64)
+    lib().c3vq_oracle_assign(_p(x, ctypes.c_float), n, d, _p(cb, ctypes.c_float), k,
+                             _p(dist, ctypes.c_float), _p(idx, ctypes.c_int64))
+    return dist, idx
+
+
+def scatter_sum(x, w, idx, k):
+    """vq.py:31,33 -> (sum_x f32[K,D], sum_w f32[K]); fp32, row order."""
+    x, idx = _f32(x), _i64(idx)
+    n, d = x.shape
+    wp = None
+    if w is not None:
+        w = _f32(w)
+        wp = _p(w, ctypes.c_float)
+    sx = np.zeros((k, d), np.float32)
+    sw = np.zeros(k, np.float32)
+    lib().c3vq_oracle_scatter_sum(_p(x, ctypes.c_float), wp, _p(idx, ctypes.c_int64), n, d, k,
+                                  _p(sx, ctypes.c_float), _p(sw, ctypes.c_float))
+    return sx, sw
+
+
+def scatter_sum_f64(x, w, idx, k):
+    x, idx = _f32(x), _i64(idx)
+    n, d = x.shape
+    wp = None
+    if w is not None:
+        w = _f32(w)
+        wp = _p(w, ctypes.c_float)
+    sx = np.zeros((k, d), np.float64)
+    sw = np.zeros(k, np.float64)
+    lib().c3vq_oracle_scatter_sum_f64(_p(x, ctypes.c_float), wp, _p(idx, ctypes.c_int64), n, d, k,
+                                      _p(sx, ctypes.c_double), _p(sw, ctypes.c_double))
+    return sx, sw
+
+
+def ema(codebook, entry_importance, sum_x, sum_w, decay, eps=1e-5):
+    """vq.py:32,34,45-46 — in place on float32 arrays."""
+    assert codebook.dtype == np.float32 and entry_importance.dtype == np.float32
+    k, d = codebook.shape
+    sx, sw = _f32(sum_x), _f32(sum_w)
+    lib().c3vq_oracle_ema(_p(codebook, ctypes.c_float), _p(entry_importance, ctypes.c_float),
+                          _p(sx, ctypes.c_float), _p(sw, ctypes.c_float), k, d, float(decay), float(eps))
+
+
+def trace_normalize(codebook):
+    """vq.py:76-77 — in place."""
+    assert codebook.dtype == np.float32 and codebook.flags.c_contiguous
+    k, d = codebook.shape
+    lib().c3vq_oracle_trace_normalize(_p(codebook, ctypes.c_float), k, d)
+
+
+def update(x, w, codebook, entry_importance, decay, eps=1e-5):
+    """VectorQuantize.update (vq.py:28-35): mutates codebook/entry_importance, returns (min_dists, idx)."""
+    x, w = _f32(x), _f32(w)
+    assert codebook.dtype == np.float32 and codebook.flags.c_contiguous
+    assert entry_importance.dtype == np.float32
+    n, d = x.shape
+    k = codebook.shape[0]
+    dist = np.zeros(n, np.float32)
+    idx = np.zeros(n, np.int64)
+    scratch = np.zeros(k * d + k, np.float32)
+    lib().c3vq_oracle_update(_p(x, ctypes.c_float), _p(w, ctypes.c_float), n, d,
+                             _p(codebook, ctypes.c_float), _p(entry_importance, ctypes.c_float), k,
+                             float(decay), float(eps),
+                             _p(dist, ctypes.c_float), _p(idx, ctypes.c_int64), _p(scratch, ctypes.c_float))
+    return dist, idx
+
+
+def gather(table, idx):
+    """codebook[idx] decode (vq.py:40-42, gaussian_model.py:220/240/257)."""
+    table, idx = _f32(table), _i64(idx)
+    d = int(np.prod(table.shape[1:])) if table.ndim > 1 else 1
+    out = np.zeros((idx.shape[0],) + table.shape[1:], np.float32)
+    lib().c3vq_oracle_gather(_p(table, ctypes.c_float), _p(idx, ctypes.c_int64), idx.shape[0], d,
+                             _p(out, ctypes.c_float))
+    return out
+
+
+def vq_features(features, importance, codebook0, batches, decay=0.8, scale_normalize=False, eps=1e-5):
+    """The vq_features loop (vq.py:49-87) with the random draws made explicit.
+
+    `codebook0` replaces uniform_init's device RNG (vq.py:24-26); `batches` is the list of
+    index arrays `torch.randint` would have produced (vq.py:69).  Returns
+    (codebook, entry_importance, final_idx, per-step (min_dists, idx))."""
+    features = _f32(features)
+    imp = _f32(importance)
+    imp_n = imp / imp.max()                                   # vq.py:59
+    cb = _f32(codebook0).copy()
+    ei = np.zeros(cb.shape[0], np.float32)                    # vq.py:21
+    trace = []
+    for b in batches:                                         # vq.py:68
+        b = _i64(b)
+        dist, idx = update(features[b], imp_n[b], cb, ei, decay, eps)   # vq.py:70-71
+        trace.append((dist, idx))
+        if scale_normalize:                                   # vq.py:73-77
+            trace_normalize(cb)
+    _, final_idx = assign(features, cb)                       # vq.py:82
+    return cb, ei, final_idx, trace
