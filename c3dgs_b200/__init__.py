@@ -1,0 +1,48 @@
+"""c3dgs_b200 — B200 (sm_100a) implementation of c3dgs's sensitivity-aware vector clustering.
+
+Public surface (mirrors the reference, compression/vq.py and submodules/weighted_distance):
+    VectorQuantize, vq_features, ema_inplace, join_features      (c3dgs_b200.vq)
+    weighted_distance._C.weightedDistance                        (c3dgs_b200.weighted_distance)
+    indexed_decode                                               (c3dgs_b200.decode)
+    install()   register the drop-ins under the reference's module names
+"""
+from __future__ import annotations
+
+import sys
+
+from . import _lib  # noqa: F401
+from .decode import indexed_decode, decode_gaussians  # noqa: F401
+from .vq import VectorQuantize, ema_inplace, join_features, vq_features  # noqa: F401
+
+__all__ = ["VectorQuantize", "vq_features", "ema_inplace", "join_features", "indexed_decode",
+           "decode_gaussians", "install"]
+
+
+def install(patch_vq_module: bool = True) -> None:
+    """Make the reference pick this implementation up without editing it.
+
+    1. `weighted_distance` / `weighted_distance._C` in sys.modules -> this package's drop-in, so
+       `from weighted_distance._C import weightedDistance` (compression/vq.py:12) binds to libc3vq.
+    2. If the reference's `compression.vq` is (or later gets) imported and `patch_vq_module` is
+       true, its `VectorQuantize`, `vq_features` and `ema_inplace` are rebound to the fused
+       versions, so compress_color / compress_covariance (vq.py:139, :164) call them.
+    """
+    from . import weighted_distance as wd
+
+    sys.modules["weighted_distance"] = wd
+    sys.modules["weighted_distance._C"] = wd._C
+    if patch_vq_module:
+        mod = sys.modules.get("compression.vq")
+        if mod is not None:
+            patch_reference_module(mod)
+
+
+def patch_reference_module(mod) -> None:
+    """Rebind the hot-path symbols of an imported reference `compression.vq` module."""
+    from . import vq as _vq
+    from .weighted_distance._C import weightedDistance
+
+    mod.weightedDistance = weightedDistance
+    mod.VectorQuantize = _vq.VectorQuantize
+    mod.vq_features = _vq.vq_features
+    mod.ema_inplace = _vq.ema_inplace

@@ -1,0 +1,352 @@
+"""ctypes binding of libc3vq.so (include/c3vq.h) for torch CUDA tensors.
+
+PyTorch is plumbing here: it owns device memory and streams; every operation below is
+one call through the C ABI with raw device pointers and the current stream.  There is
+no CPU fallback and no alternative backend: if the library is missing or a tensor is
+not a CUDA tensor the call raises.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import threading
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libc3vq.so")
+
+_lib = None
+_lock = threading.Lock()
+
+
+def default_tensor_cores() -> bool:
+    """Assignment kernel used by default: the tcgen05 path; C3VQ_ASSIGN=simt selects the SIMT exact
+    kernel (same results, ~10x slower) for debugging.  Both are CUDA kernels of libc3vq.so."""
+    return os.environ.get("C3VQ_ASSIGN", "tc").lower() != "simt"
+
+_c_f32p = ctypes.c_void_p
+_c_i64 = ctypes.c_int64
+_c_int = ctypes.c_int
+_c_dbl = ctypes.c_double
+_c_sz = ctypes.c_size_t
+_c_vp = ctypes.c_void_p
+
+# name -> (restype, argtypes); mirrors include/c3vq.h one to one (tests check every symbol resolves)
+SIGNATURES = {
+    "c3vq_version": (_c_int, []),
+    "c3vq_last_error": (ctypes.c_char_p, []),
+    "c3vq_launch_count": (_c_i64, []),
+    "c3vq_assign_workspace_bytes": (_c_sz, [_c_i64, _c_int, _c_int]),
+    "c3vq_assign": (_c_int, [_c_vp, _c_vp, _c_i64, _c_int, _c_vp, _c_int, _c_vp, _c_vp, _c_vp, _c_sz, _c_vp]),
+    "c3vq_assign_exact": (_c_int, [_c_vp, _c_vp, _c_i64, _c_int, _c_vp, _c_int, _c_vp, _c_vp, _c_vp]),
+    "c3vq_acc_stride": (_c_int, [_c_int]),
+    "c3vq_accumulate": (_c_int, [_c_vp, _c_vp, _c_vp, _c_vp, _c_i64, _c_int, _c_int, _c_vp, _c_vp]),
+    "c3vq_ema": (_c_int, [_c_vp, _c_vp, _c_vp, _c_int, _c_int, _c_dbl, _c_dbl, _c_int, _c_vp]),
+    "c3vq_update_workspace_bytes": (_c_sz, [_c_i64, _c_int, _c_int]),
+    "c3vq_update": (_c_int, [_c_vp, _c_vp, _c_vp, _c_i64, _c_int, _c_vp, _c_vp, _c_int, _c_dbl, _c_dbl, _c_int,
+                             _c_int, _c_vp, _c_vp, _c_vp, _c_sz, _c_vp]),
+    "c3vq_assign_accumulate": (_c_int, [_c_vp, _c_vp, _c_vp, _c_i64, _c_int, _c_vp, _c_int, _c_int, _c_vp, _c_vp,
+                                        _c_vp, _c_vp, _c_sz, _c_vp]),
+    "c3vq_gather": (_c_int, [_c_vp, _c_i64, _c_int, _c_vp, _c_i64, _c_vp, _c_vp]),
+    "c3vq_scatter_add": (_c_int, [_c_vp, _c_vp, _c_i64, _c_int, _c_vp, _c_i64, _c_vp]),
+    "c3vq_gather_rows": (_c_int, [_c_vp, _c_vp, _c_vp, _c_i64, _c_int, _c_vp, _c_vp, _c_vp]),
+    "c3vq_debug_scores": (_c_int, [_c_vp, _c_i64, _c_int, _c_vp, _c_int, _c_vp, _c_vp, _c_vp, _c_vp, _c_sz, _c_vp]),
+    "c3vq_assign_stats": (_c_int, [_c_vp, ctypes.POINTER(_c_i64), _c_vp]),
+}
+
+
+def load() -> ctypes.CDLL:
+    """Load libc3vq.so; raises if it has not been built (python -m c3dgs_b200.build)."""
+    global _lib
+    with _lock:
+        if _lib is None:
+            if not os.path.exists(LIB_PATH):
+                raise RuntimeError(
+                    f"{LIB_PATH} is missing: build it with `python -m c3dgs_b200.build` "
+                    "(nvcc, sm_100a). There is no fallback implementation.")
+            L = ctypes.CDLL(LIB_PATH)
+            for name, (res, args) in SIGNATURES.items():
+                fn = getattr(L, name)  # AttributeError if the symbol is not exported
+                fn.restype = res
+                fn.argtypes = args
+            _lib = L
+    return _lib
+
+
+def _err(rc: int) -> RuntimeError:
+    msg = load().c3vq_last_error()
+    return RuntimeError(f"libc3vq error {rc}: {msg.decode() if msg else '?'}")
+
+
+def _stream(t: torch.Tensor) -> int:
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+def _ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def _check(t: torch.Tensor, dtype, name: str, ndim=None):
+    if not isinstance(t, torch.Tensor):
+        raise RuntimeError(f"{name} must be a torch.Tensor")
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor (libc3vq has no CPU path)")
+    if t.dtype != dtype:
+        raise RuntimeError(f"{name} must be {dtype}, got {t.dtype}")
+    if ndim is not None and t.dim() != ndim:
+        raise RuntimeError(f"{name} must have {ndim} dimensions, got {t.dim()}")
+
+
+class Workspace:
+    """Grow-only device scratch owned by the Python side (the C side never allocates)."""
+
+    def __init__(self):
+        self._buf = {}
+
+    def get(self, device: torch.device, nbytes: int) -> torch.Tensor:
+        key = (device.type, device.index)
+        buf = self._buf.get(key)
+        if buf is None or buf.numel() < nbytes:
+            buf = torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=device)
+            self._buf[key] = buf
+        return buf
+
+
+_workspace = Workspace()
+
+
+def assign(x: torch.Tensor, codebook: torch.Tensor, rows: torch.Tensor | None = None, exact: bool = False,
+           return_dist: bool = True):
+    """Nearest codeword per row -> (min_dist f32[n] | None, idx i64[n]).  c3vq_assign / c3vq_assign_exact."""
+    _check(x, torch.float32, "coefs")
+    _check(codebook, torch.float32, "codebook")
+    if x.dim() != 2 or codebook.dim() != 2:
+        raise RuntimeError("ceofs and codebook must have dimension 2")          # weighted_distance.cu:64-67
+    if codebook.size(1) != x.size(1):
+        raise RuntimeError("coefs and codebook must have same number of channels")  # weighted_distance.cu:69-72
+    if codebook.device != x.device:
+        raise RuntimeError("coefs and codebook must be on the same device")
+    x = x.contiguous()
+    codebook = codebook.contiguous()
+    if rows is not None:
+        _check(rows, torch.int64, "rows", 1)
+        rows = rows.contiguous()
+    n = rows.numel() if rows is not None else x.size(0)
+    d, k = x.size(1), codebook.size(0)
+    L = load()
+    with torch.cuda.device(x.device):
+        dist = torch.empty(n, dtype=torch.float32, device=x.device) if return_dist else None
+        idx = torch.empty(n, dtype=torch.int64, device=x.device)
+        if exact:
+            rc = L.c3vq_assign_exact(_ptr(x), _ptr(rows), n, d, _ptr(codebook), k, _ptr(dist), _ptr(idx),
+                                     _stream(x))
+        else:
+            nbytes = L.c3vq_assign_workspace_bytes(n, d, k)
+            ws = _workspace.get(x.device, nbytes)
+            rc = L.c3vq_assign(_ptr(x), _ptr(rows), n, d, _ptr(codebook), k, _ptr(dist), _ptr(idx),
+                               _ptr(ws), ws.numel(), _stream(x))
+    if rc:
+        raise _err(rc)
+    return dist, idx
+
+
+def update(x: torch.Tensor, w: torch.Tensor, codebook: torch.Tensor, entry_importance: torch.Tensor,
+           decay: float, eps: float, rows: torch.Tensor | None = None, scale_normalize: bool = False,
+           tensor_cores: bool = True, return_dist: bool = True, return_idx: bool = False):
+    """One VectorQuantize.update (vq.py:28-35) in place on codebook / entry_importance.  c3vq_update."""
+    _check(x, torch.float32, "x", 2)
+    _check(w, torch.float32, "importance", 1)
+    _check(codebook, torch.float32, "codebook", 2)
+    _check(entry_importance, torch.float32, "entry_importance", 1)
+    if not (codebook.is_contiguous() and entry_importance.is_contiguous()):
+        raise RuntimeError("codebook and entry_importance must be contiguous (they are updated in place)")
+    if codebook.size(1) != x.size(1):
+        raise RuntimeError("coefs and codebook must have same number of channels")
+    x = x.contiguous()
+    w = w.contiguous()
+    if rows is not None:
+        _check(rows, torch.int64, "rows", 1)
+        rows = rows.contiguous()
+        n = rows.numel()
+    else:
+        n = x.size(0)
+        if w.numel() != n:
+            raise RuntimeError("importance must have one entry per row of x")
+    d, k = x.size(1), codebook.size(0)
+    L = load()
+    with torch.cuda.device(x.device):
+        dist = torch.empty(n, dtype=torch.float32, device=x.device) if return_dist else None
+        idx = torch.empty(n, dtype=torch.int64, device=x.device) if return_idx else None
+        nbytes = L.c3vq_update_workspace_bytes(n, d, k)
+        ws = _workspace.get(x.device, nbytes)
+        rc = L.c3vq_update(_ptr(x), _ptr(w), _ptr(rows), n, d, _ptr(codebook), _ptr(entry_importance), k,
+                           float(decay), float(eps), int(bool(scale_normalize)), int(bool(tensor_cores)),
+                           _ptr(dist), _ptr(idx), _ptr(ws), ws.numel(), _stream(x))
+    if rc:
+        raise _err(rc)
+    return dist, idx
+
+
+def assign_accumulate(x, w, codebook, acc: torch.Tensor | None = None, rows=None, tensor_cores: bool = True,
+                      return_dist: bool = False, return_idx: bool = True):
+    """Assignment + weighted sums added into acc, no EMA (multi-GPU building block).  c3vq_assign_accumulate."""
+    _check(x, torch.float32, "x", 2)
+    _check(w, torch.float32, "importance", 1)
+    _check(codebook, torch.float32, "codebook", 2)
+    if codebook.size(1) != x.size(1):
+        raise RuntimeError("coefs and codebook must have same number of channels")
+    x, w, codebook = x.contiguous(), w.contiguous(), codebook.contiguous()
+    if rows is not None:
+        _check(rows, torch.int64, "rows", 1)
+        rows = rows.contiguous()
+    n = rows.numel() if rows is not None else x.size(0)
+    d, k = x.size(1), codebook.size(0)
+    L = load()
+    stride = L.c3vq_acc_stride(d)
+    with torch.cuda.device(x.device):
+        if acc is None:
+            acc = torch.zeros(k, stride, dtype=torch.float32, device=x.device)
+        elif acc.shape != (k, stride) or not acc.is_contiguous():
+            raise RuntimeError(f"acc must be a contiguous [{k}, {stride}] float32 tensor")
+        dist = torch.empty(n, dtype=torch.float32, device=x.device) if return_dist else None
+        idx = torch.empty(n, dtype=torch.int64, device=x.device) if return_idx else None
+        nbytes = L.c3vq_update_workspace_bytes(n, d, k)
+        ws = _workspace.get(x.device, nbytes)
+        rc = L.c3vq_assign_accumulate(_ptr(x), _ptr(w), _ptr(rows), n, d, _ptr(codebook), k, int(bool(tensor_cores)),
+                                      _ptr(acc), _ptr(dist), _ptr(idx), _ptr(ws), ws.numel(), _stream(x))
+    if rc:
+        raise _err(rc)
+    return acc, dist, idx
+
+
+def launch_count() -> int:
+    return int(load().c3vq_launch_count())
+
+
+def acc_stride(d: int) -> int:
+    return int(load().c3vq_acc_stride(int(d)))
+
+
+def accumulate(x, w, idx, k: int, acc: torch.Tensor | None = None, rows=None) -> torch.Tensor:
+    """Weighted centroid sums into acc[k, acc_stride(d)] (vq.py:31,33).  c3vq_accumulate."""
+    _check(x, torch.float32, "x", 2)
+    _check(idx, torch.int64, "idx", 1)
+    x, idx = x.contiguous(), idx.contiguous()
+    if w is not None:
+        _check(w, torch.float32, "importance", 1)
+        w = w.contiguous()
+    if rows is not None:
+        _check(rows, torch.int64, "rows", 1)
+        rows = rows.contiguous()
+    n, d = idx.numel(), x.size(1)
+    L = load()
+    stride = L.c3vq_acc_stride(d)
+    with torch.cuda.device(x.device):
+        if acc is None:
+            acc = torch.zeros(k, stride, dtype=torch.float32, device=x.device)
+        elif acc.shape != (k, stride) or not acc.is_contiguous():
+            raise RuntimeError(f"acc must be a contiguous [{k}, {stride}] float32 tensor")
+        rc = L.c3vq_accumulate(_ptr(x), _ptr(w), _ptr(rows), _ptr(idx), n, d, k, _ptr(acc), _stream(x))
+    if rc:
+        raise _err(rc)
+    return acc
+
+
+def ema(codebook, entry_importance, acc, decay: float, eps: float, scale_normalize: bool = False) -> None:
+    """EMA epilogue (vq.py:32,34,45-46,76-77) in place.  c3vq_ema."""
+    _check(codebook, torch.float32, "codebook", 2)
+    _check(entry_importance, torch.float32, "entry_importance", 1)
+    _check(acc, torch.float32, "acc", 2)
+    k, d = codebook.shape
+    if acc.shape != (k, acc_stride(d)) or not (acc.is_contiguous() and codebook.is_contiguous()):
+        raise RuntimeError("acc/codebook layout mismatch")
+    with torch.cuda.device(codebook.device):
+        rc = load().c3vq_ema(_ptr(codebook), _ptr(entry_importance), _ptr(acc), k, d, float(decay), float(eps),
+                             int(bool(scale_normalize)), _stream(codebook))
+    if rc:
+        raise _err(rc)
+
+
+def gather(table: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
+    """out[i] = table[idx[i]] for a [R, ...] float32 table.  c3vq_gather."""
+    _check(table, torch.float32, "table")
+    _check(idx, torch.int64, "idx", 1)
+    if idx.device != table.device:
+        raise RuntimeError("table and idx must be on the same device")
+    table, idx = table.contiguous(), idx.contiguous()
+    rows = table.size(0)
+    d = table[0].numel() if rows > 0 else int(torch.Size(table.shape[1:]).numel())
+    n = idx.numel()
+    with torch.cuda.device(table.device):
+        out = torch.empty((n,) + tuple(table.shape[1:]), dtype=torch.float32, device=table.device)
+        rc = load().c3vq_gather(_ptr(table), rows, d, _ptr(idx), n, _ptr(out), _stream(table))
+    if rc:
+        raise _err(rc)
+    return out
+
+
+def scatter_add(grad_out: torch.Tensor, idx: torch.Tensor, table_rows: int) -> torch.Tensor:
+    """grad_table[idx[i]] += grad_out[i]  (backward of gather).  c3vq_scatter_add."""
+    _check(grad_out, torch.float32, "grad_out")
+    _check(idx, torch.int64, "idx", 1)
+    grad_out, idx = grad_out.contiguous(), idx.contiguous()
+    n = idx.numel()
+    d = int(torch.Size(grad_out.shape[1:]).numel())
+    with torch.cuda.device(grad_out.device):
+        gt = torch.zeros((table_rows,) + tuple(grad_out.shape[1:]), dtype=torch.float32, device=grad_out.device)
+        rc = load().c3vq_scatter_add(_ptr(grad_out), _ptr(idx), n, d, _ptr(gt), table_rows, _stream(grad_out))
+    if rc:
+        raise _err(rc)
+    return gt
+
+
+def gather_rows(x: torch.Tensor, w: torch.Tensor | None, rows: torch.Tensor):
+    """(x[rows], w[rows]) — the mini-batch gather of vq.py:70-71.  c3vq_gather_rows."""
+    _check(x, torch.float32, "x", 2)
+    _check(rows, torch.int64, "rows", 1)
+    x, rows = x.contiguous(), rows.contiguous()
+    n, d = rows.numel(), x.size(1)
+    with torch.cuda.device(x.device):
+        ox = torch.empty(n, d, dtype=torch.float32, device=x.device)
+        ow = None
+        if w is not None:
+            _check(w, torch.float32, "importance", 1)
+            w = w.contiguous()
+            ow = torch.empty(n, dtype=torch.float32, device=x.device)
+        rc = load().c3vq_gather_rows(_ptr(x), _ptr(w), _ptr(rows), n, d, _ptr(ox), _ptr(ow), _stream(x))
+    if rc:
+        raise _err(rc)
+    return ox, ow
+
+
+def debug_scores(x: torch.Tensor, codebook: torch.Tensor):
+    """Screening scores of the tensor-core path -> (scores [n,k], row_norm2 [n], row_band [n])."""
+    _check(x, torch.float32, "x", 2)
+    _check(codebook, torch.float32, "codebook", 2)
+    x, codebook = x.contiguous(), codebook.contiguous()
+    n, d, k = x.size(0), x.size(1), codebook.size(0)
+    L = load()
+    with torch.cuda.device(x.device):
+        scores = torch.empty(n, k, dtype=torch.float32, device=x.device)
+        norm2 = torch.empty(n, dtype=torch.float32, device=x.device)
+        band = torch.empty(n, dtype=torch.float32, device=x.device)
+        nbytes = L.c3vq_assign_workspace_bytes(n, d, k)
+        ws = _workspace.get(x.device, nbytes)
+        rc = L.c3vq_debug_scores(_ptr(x), n, d, _ptr(codebook), k, _ptr(scores), _ptr(norm2), _ptr(band),
+                                 _ptr(ws), ws.numel(), _stream(x))
+    if rc:
+        raise _err(rc)
+    return scores, norm2, band
+
+
+def assign_stats(device=None):
+    """(rows, candidates, fallback_rows) of the last tensor-core assignment on `device`."""
+    device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    ws = _workspace.get(device, 256)
+    out = (_c_i64 * 3)()
+    with torch.cuda.device(device):
+        rc = load().c3vq_assign_stats(_ptr(ws), out, torch.cuda.current_stream(device).cuda_stream)
+    if rc:
+        raise _err(rc)
+    return int(out[0]), int(out[1]), int(out[2])

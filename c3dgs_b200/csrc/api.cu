@@ -1,0 +1,231 @@
+// api.cu — the extern "C" boundary of libc3vq.so (declared in include/c3vq.h).
+// No torch types cross this file; the Python host passes raw device pointers and
+// the current CUDA stream.
+#include <cstdarg>
+#include <cstring>
+#include <atomic>
+
+#include "common.cuh"
+
+namespace c3vq {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+const char *get_error() { return g_err; }
+
+static std::atomic<long long> g_launches{0};
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+
+int sm_count()
+{
+    static thread_local int cached_dev = -1, cached = 0;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+    if (dev != cached_dev) {
+        int v = 0;
+        if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) v = 148;
+        cached = v;
+        cached_dev = dev;
+    }
+    return cached;
+}
+
+static inline size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
+
+static int check_common(const void *x, int64_t n, int d, const void *cb, int k)
+{
+    C3VQ_CHECK_ARG(n >= 0, "n=%lld is negative", (long long)n);
+    C3VQ_CHECK_ARG(d >= 1 && d <= C3VQ_MAX_DIM, "d=%d outside [1, %d]", d, C3VQ_MAX_DIM);
+    C3VQ_CHECK_ARG(k >= 0 && k <= C3VQ_MAX_CODES, "k=%d outside [0, %d]", k, C3VQ_MAX_CODES);
+    C3VQ_CHECK_ARG(n == 0 || x != nullptr, "x is null");
+    C3VQ_CHECK_ARG(k == 0 || cb != nullptr, "codebook is null");
+    return C3VQ_OK;
+}
+
+}  // namespace c3vq
+
+using namespace c3vq;
+
+#pragma GCC visibility push(default)
+extern "C" {
+
+int c3vq_version(void) { return 100; }
+
+const char *c3vq_last_error(void) { return get_error(); }
+
+int64_t c3vq_launch_count(void) { return (int64_t)g_launches.load(std::memory_order_relaxed); }
+
+int c3vq_acc_stride(int d) { return acc_stride(d); }
+
+size_t c3vq_assign_workspace_bytes(int64_t n, int d, int k) { return tc_workspace_bytes(n, d, k); }
+
+int c3vq_assign(const float *x, const int64_t *rows, int64_t n, int d, const float *codebook, int k,
+                float *out_dist, int64_t *out_idx, void *ws, size_t ws_bytes, c3vq_stream_t stream)
+{
+    int rc = check_common(x, n, d, codebook, k);
+    if (rc) return rc;
+    C3VQ_CHECK_ARG(n == 0 || out_idx != nullptr, "out_idx is null");
+    if (n == 0) return C3VQ_OK;
+    return launch_assign_tc(x, nullptr, rows, n, d, codebook, k, out_dist, out_idx, nullptr, nullptr, nullptr,
+                            nullptr, ws, ws_bytes, (cudaStream_t)stream);
+}
+
+int c3vq_assign_exact(const float *x, const int64_t *rows, int64_t n, int d, const float *codebook, int k,
+                      float *out_dist, int64_t *out_idx, c3vq_stream_t stream)
+{
+    int rc = check_common(x, n, d, codebook, k);
+    if (rc) return rc;
+    C3VQ_CHECK_ARG(n == 0 || out_idx != nullptr, "out_idx is null");
+    return launch_assign_exact(x, rows, n, d, codebook, k, out_dist, out_idx, (cudaStream_t)stream);
+}
+
+int c3vq_accumulate(const float *x, const float *w, const int64_t *rows, const int64_t *idx, int64_t n, int d,
+                    int k, float *acc, c3vq_stream_t stream)
+{
+    int rc = check_common(x, n, d, acc, k);
+    if (rc) return rc;
+    C3VQ_CHECK_ARG(n == 0 || idx != nullptr, "idx is null");
+    return launch_accumulate(x, w, rows, idx, n, d, k, acc, acc_stride(d), d, (cudaStream_t)stream);
+}
+
+int c3vq_ema(float *codebook, float *entry_importance, const float *acc, int k, int d, double decay, double eps,
+             int scale_normalize, c3vq_stream_t stream)
+{
+    C3VQ_CHECK_ARG(d >= 1 && d <= C3VQ_MAX_DIM, "d=%d outside [1, %d]", d, C3VQ_MAX_DIM);
+    C3VQ_CHECK_ARG(k >= 0, "k=%d is negative", k);
+    C3VQ_CHECK_ARG(k == 0 || (codebook && entry_importance && acc), "null pointer");
+    return launch_ema(codebook, entry_importance, acc, k, d, decay, eps, scale_normalize, (cudaStream_t)stream);
+}
+
+// Workspace layout shared by c3vq_update / c3vq_assign_accumulate:
+//   [tensor-core workspace (stats first)] [acc: k*stride floats] [idx: n int64]
+size_t c3vq_update_workspace_bytes(int64_t n, int d, int k)
+{
+    if (n < 0 || d < 1 || k < 0) return 0;
+    return align256(tc_workspace_bytes(n, d, k)) + align256((size_t)k * acc_stride(d) * sizeof(float)) +
+           align256((size_t)n * sizeof(int64_t));
+}
+
+static int assign_accumulate_impl(const float *x, const float *w, const int64_t *rows, int64_t n, int d,
+                                  const float *codebook, int k, int use_tensor_cores, float *acc,
+                                  float *out_dist, int64_t *out_idx, void *tc_ws, size_t tc_bytes,
+                                  int64_t *idx_buf, cudaStream_t s)
+{
+    if (n == 0 || k == 0) return C3VQ_OK;
+    int64_t *idx = out_idx ? out_idx : idx_buf;
+    int rc;
+    if (use_tensor_cores) {
+        // fused: the assignment kernel scatters w*x of every finished row tile itself
+        rc = launch_assign_tc(x, w, rows, n, d, codebook, k, out_dist, idx, acc, nullptr, nullptr, nullptr, tc_ws,
+                              tc_bytes, s);
+    } else {
+        rc = launch_assign_exact(x, rows, n, d, codebook, k, out_dist, idx, s);
+        if (rc) return rc;
+        rc = launch_accumulate(x, w, rows, idx, n, d, k, acc, acc_stride(d), d, s);
+    }
+    return rc;
+}
+
+int c3vq_assign_accumulate(const float *x, const float *w, const int64_t *rows, int64_t n, int d,
+                           const float *codebook, int k, int use_tensor_cores, float *acc, float *out_dist,
+                           int64_t *out_idx, void *ws, size_t ws_bytes, c3vq_stream_t stream)
+{
+    int rc = check_common(x, n, d, codebook, k);
+    if (rc) return rc;
+    C3VQ_CHECK_ARG(n == 0 || w != nullptr, "w is null");
+    C3VQ_CHECK_ARG(k == 0 || acc != nullptr, "acc is null");
+    if (ws_bytes < c3vq_update_workspace_bytes(n, d, k) || (ws == nullptr && ws_bytes > 0)) {
+        set_error("workspace too small: %zu < %zu", ws_bytes, c3vq_update_workspace_bytes(n, d, k));
+        return C3VQ_EWORKSPACE;
+    }
+    char *p = (char *)ws;
+    const size_t tc_bytes = tc_workspace_bytes(n, d, k);
+    void *tc_ws = p;
+    p += align256(tc_bytes) + align256((size_t)k * acc_stride(d) * sizeof(float));
+    return assign_accumulate_impl(x, w, rows, n, d, codebook, k, use_tensor_cores, acc, out_dist, out_idx, tc_ws,
+                                  tc_bytes, (int64_t *)p, (cudaStream_t)stream);
+}
+
+int c3vq_update(const float *x, const float *w, const int64_t *rows, int64_t n, int d, float *codebook,
+                float *entry_importance, int k, double decay, double eps, int scale_normalize,
+                int use_tensor_cores, float *out_dist, int64_t *out_idx, void *ws, size_t ws_bytes,
+                c3vq_stream_t stream)
+{
+    int rc = check_common(x, n, d, codebook, k);
+    if (rc) return rc;
+    C3VQ_CHECK_ARG(k == 0 || entry_importance != nullptr, "entry_importance is null");
+    C3VQ_CHECK_ARG(n == 0 || w != nullptr, "w is null");
+    if (ws_bytes < c3vq_update_workspace_bytes(n, d, k) || (ws == nullptr && ws_bytes > 0)) {
+        set_error("workspace too small: %zu < %zu", ws_bytes, c3vq_update_workspace_bytes(n, d, k));
+        return C3VQ_EWORKSPACE;
+    }
+    if (k == 0) return C3VQ_OK;
+    cudaStream_t s = (cudaStream_t)stream;
+    char *p = (char *)ws;
+    const size_t tc_bytes = tc_workspace_bytes(n, d, k);
+    void *tc_ws = p;
+    p += align256(tc_bytes);
+    const size_t acc_bytes = (size_t)k * acc_stride(d) * sizeof(float);
+    float *acc = (float *)p;
+    p += align256(acc_bytes);
+    int64_t *idx_buf = (int64_t *)p;
+
+    C3VQ_CUDA(cudaMemsetAsync(acc, 0, acc_bytes, s));
+    rc = assign_accumulate_impl(x, w, rows, n, d, codebook, k, use_tensor_cores, acc, out_dist, out_idx, tc_ws,
+                                tc_bytes, idx_buf, s);
+    if (rc) return rc;
+    return launch_ema(codebook, entry_importance, acc, k, d, decay, eps, scale_normalize, s);
+}
+
+int c3vq_gather(const float *table, int64_t table_rows, int d, const int64_t *idx, int64_t n, float *out,
+                c3vq_stream_t stream)
+{
+    C3VQ_CHECK_ARG(n >= 0 && d >= 0 && table_rows >= 0, "negative size");
+    C3VQ_CHECK_ARG(n == 0 || d == 0 || (table && idx && out), "null pointer");
+    return launch_gather(table, table_rows, d, idx, n, out, (cudaStream_t)stream);
+}
+
+int c3vq_scatter_add(const float *grad_out, const int64_t *idx, int64_t n, int d, float *grad_table,
+                     int64_t table_rows, c3vq_stream_t stream)
+{
+    C3VQ_CHECK_ARG(n >= 0 && d >= 1 && table_rows >= 0, "bad size");
+    C3VQ_CHECK_ARG(n == 0 || (grad_out && idx && grad_table), "null pointer");
+    return launch_accumulate(grad_out, nullptr, nullptr, idx, n, d, table_rows, grad_table, d, -1,
+                             (cudaStream_t)stream);
+}
+
+int c3vq_gather_rows(const float *x, const float *w, const int64_t *rows, int64_t n, int d, float *out_x,
+                     float *out_w, c3vq_stream_t stream)
+{
+    C3VQ_CHECK_ARG(n >= 0 && d >= 1, "bad size");
+    C3VQ_CHECK_ARG(n == 0 || (x && rows), "null pointer");
+    return launch_gather_rows(x, w, rows, n, d, out_x, out_w, (cudaStream_t)stream);
+}
+
+int c3vq_debug_scores(const float *x, int64_t n, int d, const float *codebook, int k, float *scores,
+                      float *row_norm2, float *row_band, void *ws, size_t ws_bytes, c3vq_stream_t stream)
+{
+    int rc = check_common(x, n, d, codebook, k);
+    if (rc) return rc;
+    C3VQ_CHECK_ARG(scores != nullptr, "scores is null");
+    if (n == 0 || k == 0) return C3VQ_OK;
+    return launch_assign_tc(x, nullptr, nullptr, n, d, codebook, k, nullptr, nullptr, nullptr, scores, row_norm2,
+                            row_band, ws, ws_bytes, (cudaStream_t)stream);
+}
+
+int c3vq_assign_stats(void *ws, int64_t out[3], c3vq_stream_t stream)
+{
+    C3VQ_CHECK_ARG(ws && out, "null pointer");
+    return tc_stats(ws, out, (cudaStream_t)stream);
+}
+
+}  // extern "C"
+#pragma GCC visibility pop

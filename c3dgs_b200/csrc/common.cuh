@@ -1,0 +1,74 @@
+// common.cuh — shared helpers for libc3vq (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <cfloat>
+
+#include "../../include/c3vq.h"
+
+namespace c3vq {
+
+// thread-local last-error text (c3vq_last_error)
+void set_error(const char *fmt, ...);
+const char *get_error();
+
+int sm_count();
+void count_launch();  // c3vq_launch_count bookkeeping (one call per kernel launched)
+
+#define C3VQ_CHECK_ARG(cond, ...)                 \
+    do {                                          \
+        if (!(cond)) {                            \
+            ::c3vq::set_error(__VA_ARGS__);       \
+            return C3VQ_EINVAL;                   \
+        }                                         \
+    } while (0)
+
+#define C3VQ_CUDA(expr)                                                                        \
+    do {                                                                                       \
+        cudaError_t _e = (expr);                                                               \
+        if (_e != cudaSuccess) {                                                               \
+            ::c3vq::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, \
+                              __LINE__);                                                       \
+            return C3VQ_ECUDA;                                                                 \
+        }                                                                                      \
+    } while (0)
+
+#define C3VQ_LAUNCH_CHECK(name)                                                          \
+    do {                                                                                 \
+        cudaError_t _e = cudaGetLastError();                                             \
+        if (_e != cudaSuccess) {                                                         \
+            ::c3vq::set_error("launch of %s failed: %s", name, cudaGetErrorString(_e));  \
+            return C3VQ_ECUDA;                                                           \
+        }                                                                                \
+        ::c3vq::count_launch();                                                          \
+    } while (0)
+
+// Accumulator row stride: d sums + 1 weight, rounded up to a multiple of 4 floats so rows are 16-byte aligned.
+__host__ __device__ inline int acc_stride(int d) { return (d + 1 + 3) & ~3; }
+
+// Padded feature width of the SIMT exact kernel (zero padding leaves the fma chain bit-identical).
+inline int exact_dp(int d) { return d <= 8 ? 8 : d <= 16 ? 16 : d <= 32 ? 32 : d <= 48 ? 48 : 64; }
+
+// ---- launchers implemented in the .cu files ----
+int launch_assign_exact(const float *x, const int64_t *rows, int64_t n, int d, const float *codebook, int k,
+                        float *out_dist, int64_t *out_idx, cudaStream_t s);
+// wcol >= 0: column of acc that receives the weight; wcol < 0: no weight column (decode backward)
+int launch_accumulate(const float *x, const float *w, const int64_t *rows, const int64_t *idx, int64_t n, int d,
+                      int64_t k, float *acc, int stride, int wcol, cudaStream_t s);
+int launch_ema(float *codebook, float *entry_importance, const float *acc, int k, int d, double decay, double eps,
+               int scale_normalize, cudaStream_t s);
+int launch_gather(const float *table, int64_t table_rows, int d, const int64_t *idx, int64_t n, float *out,
+                  cudaStream_t s);
+int launch_gather_rows(const float *x, const float *w, const int64_t *rows, int64_t n, int d, float *out_x,
+                       float *out_w, cudaStream_t s);
+
+// tensor-core assignment (assign_tc.cu)
+size_t tc_workspace_bytes(int64_t n, int d, int k);
+int launch_assign_tc(const float *x, const float *w, const int64_t *rows, int64_t n, int d, const float *codebook,
+                     int k, float *out_dist, int64_t *out_idx, float *acc /* null: no fused sums */,
+                     float *dbg_scores, float *dbg_norm2, float *dbg_band, void *ws, size_t ws_bytes,
+                     cudaStream_t s);
+int tc_stats(void *ws, int64_t out[3], cudaStream_t s);
+
+}  // namespace c3vq

@@ -1,0 +1,145 @@
+/*
+ * c3vq.h — C ABI of libc3vq.so, the B200 (sm_100a) implementation of c3dgs's
+ * sensitivity-aware vector clustering hot path.
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no torch types.  Every
+ * pointer is a DEVICE pointer on the current CUDA device unless it says "host".
+ * Every entry point returns 0 on success or a negative C3VQ_E* code, never throws,
+ * and records a message readable through c3vq_last_error() (thread-local).
+ * `stream` is a cudaStream_t passed as void*; work is enqueued, not synchronised.
+ *
+ * Reference interfaces replaced (paths relative to the c3dgs repository root):
+ *   c3vq_assign        <- weightedDistanceCUDA           submodules/weighted_distance/weighted_distance.cu:60-93
+ *                         (decl weighted_distance.h:3-5, binding ext.cpp:4-6, kernel :20-44)
+ *   c3vq_accumulate    <- torch_scatter.scatter x2       compression/vq.py:31, :33
+ *   c3vq_ema           <- ema_inplace x2 + divide        compression/vq.py:32, :34, :45-46; trace normalise :76-77
+ *   c3vq_update        <- VectorQuantize.update          compression/vq.py:28-35
+ *   c3vq_assign_accumulate <- vq.py:30-31,33 (update without the EMAs; multi-GPU building block)
+ *   c3vq_gather        <- codebook[idx] decode           compression/vq.py:40-42; scene/gaussian_model.py:220, :240, :257, :893-897
+ *   c3vq_scatter_add   <- backward of that gather        (autograd index_put_(accumulate=True))
+ *   c3vq_gather_rows   <- features[batch]                compression/vq.py:70
+ */
+#ifndef C3VQ_H
+#define C3VQ_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define C3VQ_OK 0
+#define C3VQ_EINVAL (-1)     /* bad argument (shape, null pointer, unsupported size) */
+#define C3VQ_EWORKSPACE (-2) /* workspace too small */
+#define C3VQ_ECUDA (-3)      /* CUDA runtime / launch error (message holds cudaGetErrorString) */
+
+#define C3VQ_MAX_DIM 64      /* widest feature row the kernels accept (SH colour is 48) */
+#define C3VQ_MAX_CODES 65536 /* candidate lists store code ids in 16 bits */
+
+typedef void *c3vq_stream_t; /* cudaStream_t */
+
+/* Library version (major*100 + minor) and last error text of the calling thread. */
+int c3vq_version(void);
+const char *c3vq_last_error(void);
+/* Number of CUDA kernels this library has launched in this process (monotonic; for benchmarks). */
+int64_t c3vq_launch_count(void);
+
+/*
+ * Nearest-codeword search: for each of the n rows of x[n,d] (row i is
+ * x + rows[i]*d when `rows` is non-null, else x + i*d) find the codeword of
+ * codebook[k,d] with the smallest squared L2 distance, where a distance is the fp32
+ * chain acc = fma(x_c - cb_c, x_c - cb_c, acc), c = 0..d-1, and the FIRST strict
+ * minimum in ascending codeword order wins (NaN never wins).  Results are identical,
+ * bit for bit, to the reference kernel; rows with no distance below FLT_MAX give
+ * index 0 / FLT_MAX (the reference leaves that index uninitialised).
+ *
+ * c3vq_assign runs the tensor-core path (TF32 tcgen05 screening + exact fp32
+ * re-rank of every candidate inside a proven error band); c3vq_assign_exact runs
+ * the SIMT in-order kernel over all k codewords.  Both give the same output.
+ * out_dist may be null.  ws: c3vq_assign_workspace_bytes(n, d, k) bytes.
+ */
+size_t c3vq_assign_workspace_bytes(int64_t n, int d, int k);
+int c3vq_assign(const float *x, const int64_t *rows, int64_t n, int d,
+                const float *codebook, int k,
+                float *out_dist, int64_t *out_idx,
+                void *ws, size_t ws_bytes, c3vq_stream_t stream);
+int c3vq_assign_exact(const float *x, const int64_t *rows, int64_t n, int d,
+                      const float *codebook, int k,
+                      float *out_dist, int64_t *out_idx, c3vq_stream_t stream);
+
+/*
+ * Sensitivity-weighted centroid sums.  acc is [k][c3vq_acc_stride(d)] fp32:
+ * columns 0..d-1 accumulate w_i * x_i, column d accumulates w_i, the rest is
+ * padding.  The call ADDS into acc (zero it first; a multi-GPU caller all-reduces
+ * it between c3vq_accumulate and c3vq_ema).  w == null means unit weights.
+ * `rows` as above (applies to both x and w).
+ */
+int c3vq_acc_stride(int d);
+int c3vq_accumulate(const float *x, const float *w, const int64_t *rows, const int64_t *idx,
+                    int64_t n, int d, int k, float *acc, c3vq_stream_t stream);
+
+/*
+ * EMA epilogue on the k codewords:
+ *   entry_importance = decay*entry_importance + (1-decay)*sum_w
+ *   codebook         = decay*codebook + (1-decay) * sum_x / (sum_w + eps)
+ * then, if scale_normalize, codebook[j,:] /= codebook[j,0]+codebook[j,3]+codebook[j,5].
+ * decay and eps are the Python doubles of the reference; they are narrowed to fp32
+ * exactly as torch narrows them ((float)decay, (float)(1.0-decay), (float)eps).
+ */
+int c3vq_ema(float *codebook, float *entry_importance, const float *acc,
+             int k, int d, double decay, double eps, int scale_normalize, c3vq_stream_t stream);
+
+/*
+ * One VectorQuantize.update: assignment, weighted sums and EMA in one call, reading
+ * x once.  out_dist / out_idx receive the per-row minimum distance and codeword
+ * (either may be null).  ws: c3vq_update_workspace_bytes(n, d, k) bytes.
+ * use_tensor_cores = 0 forces the SIMT exact assignment.
+ */
+size_t c3vq_update_workspace_bytes(int64_t n, int d, int k);
+int c3vq_update(const float *x, const float *w, const int64_t *rows, int64_t n, int d,
+                float *codebook, float *entry_importance, int k,
+                double decay, double eps, int scale_normalize, int use_tensor_cores,
+                float *out_dist, int64_t *out_idx,
+                void *ws, size_t ws_bytes, c3vq_stream_t stream);
+
+/*
+ * First half of c3vq_update for row-sharded (multi-GPU) clustering: assignment plus
+ * weighted sums ADDED into acc (layout of c3vq_accumulate), no EMA.  The caller zeroes
+ * acc, all-reduces it across ranks (one NCCL all-reduce of k*c3vq_acc_stride(d) floats)
+ * and then calls c3vq_ema on every rank.  ws: c3vq_update_workspace_bytes(n, d, k).
+ */
+int c3vq_assign_accumulate(const float *x, const float *w, const int64_t *rows, int64_t n, int d,
+                           const float *codebook, int k, int use_tensor_cores,
+                           float *acc, float *out_dist, int64_t *out_idx,
+                           void *ws, size_t ws_bytes, c3vq_stream_t stream);
+
+/* Indexed-codebook decode: out[i,:] = table[idx[i],:], rows of d floats. */
+int c3vq_gather(const float *table, int64_t table_rows, int d,
+                const int64_t *idx, int64_t n, float *out, c3vq_stream_t stream);
+
+/* Backward of the decode: grad_table[idx[i],:] += grad_out[i,:] (grad_table zeroed by caller). */
+int c3vq_scatter_add(const float *grad_out, const int64_t *idx, int64_t n, int d,
+                     float *grad_table, int64_t table_rows, c3vq_stream_t stream);
+
+/* Mini-batch row gather: out_x[i,:] = x[rows[i],:], out_w[i] = w[rows[i]] (w/out_w may be null). */
+int c3vq_gather_rows(const float *x, const float *w, const int64_t *rows, int64_t n, int d,
+                     float *out_x, float *out_w, c3vq_stream_t stream);
+
+/*
+ * Debug / evidence: the screening scores the tensor-core path computes,
+ * score[i][j] ~= |cb_j - mu|^2 - 2 (x_i - mu).(cb_j - mu), and the per-row error
+ * band used to select re-rank candidates.  Small inputs only (n*k floats).
+ */
+int c3vq_debug_scores(const float *x, int64_t n, int d, const float *codebook, int k,
+                      float *scores, float *row_norm2, float *row_band,
+                      void *ws, size_t ws_bytes, c3vq_stream_t stream);
+
+/* Counters of the last tensor-core assignment on this thread's device (host call, synchronises `stream`):
+ * out[0] = rows processed, out[1] = total re-rank candidates, out[2] = rows sent to the exact fallback. */
+int c3vq_assign_stats(void *ws, int64_t out[3], c3vq_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* C3VQ_H */

@@ -1,0 +1,341 @@
+"""GPU (-m gpu): the CUDA path through the C ABI against the oracle, the golden fixtures, and — when
+oracle/_ref holds it — the reference's own CUDA kernel compiled unmodified.
+
+Bar: bit-exact for assignments / indices / min distances / gathers; codebooks within 1e-5 relative
+(row-normalised) because fp32 atomics have no defined order in the reference either."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN_CASES, ROOT, golden_path
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda:0"
+CB_RTOL = 1e-5      # north_star: codebooks match within 1e-5 relative
+
+
+def _t(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(DEV)
+
+
+def _synth(n, d, k, seed, clustered=True):
+    g = torch.Generator().manual_seed(seed)
+    if clustered:
+        centres = torch.randn(max(k // 2, 1), d, generator=g)
+        x = centres[torch.randint(0, centres.shape[0], (n,), generator=g)] + 0.1 * torch.randn(n, d, generator=g)
+    else:
+        x = torch.randn(n, d, generator=g)
+    w = torch.rand(n, generator=g) ** 4
+    amin, amax = x.aminmax()
+    cb = torch.rand(k, d, generator=g) * (amax - amin) + amin
+    return x.contiguous(), w.contiguous(), cb.contiguous()
+
+
+def _cb_close(a, b, rtol=CB_RTOL):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    fin = np.isfinite(b).all(1)
+    assert np.array_equal(np.isfinite(a).all(1), fin)
+    scale = np.abs(b[fin]).max(1, keepdims=True) + 1e-30
+    err = np.abs(a[fin] - b[fin]) / scale
+    assert err.max() <= rtol, f"codebook rel err {err.max():.3e} > {rtol}"
+
+
+@pytest.fixture(scope="module")
+def L(lib):
+    from c3dgs_b200 import _lib
+    assert torch.cuda.is_available()
+    return _lib
+
+
+# ---------------------------------------------------------------- assignment ----------------
+@pytest.mark.parametrize("d", [6, 7, 45, 48])
+@pytest.mark.parametrize("n,k", [(1, 1), (127, 64), (129, 100), (1000, 256), (5003, 4096)])
+@pytest.mark.parametrize("exact", [True, False])
+def test_assign_bit_exact_vs_oracle(L, oracle, d, n, k, exact):
+    x, _, cb = _synth(n, d, k, seed=d * 1000 + n)
+    dist_o, idx_o = oracle.assign(x.numpy(), cb.numpy())
+    dist, idx = L.assign(x.to(DEV), cb.to(DEV), exact=exact)
+    assert idx.dtype == torch.int64 and dist.dtype == torch.float32
+    assert np.array_equal(idx.cpu().numpy(), idx_o)
+    assert np.array_equal(dist.cpu().numpy().view(np.uint32), dist_o.view(np.uint32))
+
+
+@pytest.mark.parametrize("exact", [True, False])
+def test_assign_kats(L, oracle, exact):
+    g = torch.Generator().manual_seed(5)
+    cb = torch.randn(512, 45, generator=g)
+    # (1) codebook rows map to themselves with distance 0
+    dist, idx = L.assign(cb.to(DEV), cb.to(DEV), exact=exact)
+    assert torch.equal(idx.cpu(), torch.arange(512)) and float(dist.abs().max()) == 0.0
+    # (2) duplicated codewords: lowest index wins
+    cb3 = torch.cat([cb, cb, cb])
+    x = cb + 1e-3 * torch.randn(cb.shape, generator=g)
+    _, idx = L.assign(x.to(DEV), cb3.to(DEV), exact=exact)
+    _, idx_o = oracle.assign(x.numpy(), cb3.numpy())
+    assert np.array_equal(idx.cpu().numpy(), idx_o) and int(idx.max()) < 512
+    # (3) one-hot +-1 data (exact in TF32)
+    eye = torch.eye(45)
+    cbh = torch.cat([eye, -eye])
+    xh = cbh[torch.randint(0, 90, (777,), generator=g)]
+    dist, idx = L.assign(xh.to(DEV), cbh.to(DEV), exact=exact)
+    dist_o, idx_o = oracle.assign(xh.numpy(), cbh.numpy())
+    assert np.array_equal(idx.cpu().numpy(), idx_o) and np.array_equal(dist.cpu().numpy(), dist_o)
+
+
+@pytest.mark.parametrize("exact", [True, False])
+def test_assign_nan_inf_codewords_never_win(L, oracle, exact):
+    g = torch.Generator().manual_seed(6)
+    cb = torch.randn(64, 6, generator=g)
+    cb[0, :] = float("nan")
+    cb[5, 2] = float("inf")
+    cb[9, :] = float("-inf")
+    x = torch.randn(300, 6, generator=g)
+    x[7, :] = float("nan")                       # all distances NaN -> index 0 / FLT_MAX (defined fallback)
+    dist, idx = L.assign(x.to(DEV), cb.to(DEV), exact=exact)
+    dist_o, idx_o = oracle.assign(x.numpy(), cb.numpy())
+    assert np.array_equal(idx.cpu().numpy(), idx_o)
+    assert np.array_equal(dist.cpu().numpy().view(np.uint32), dist_o.view(np.uint32))
+    assert idx_o[7] == 0 and dist_o[7] == np.finfo(np.float32).max
+
+
+def test_assign_rows_indirection_and_noncontiguous(L, oracle):
+    x, _, cb = _synth(3000, 45, 128, seed=7)
+    rows = torch.randint(0, 3000, (1111,), generator=torch.Generator().manual_seed(8))
+    for exact in (True, False):
+        dist, idx = L.assign(x.to(DEV), cb.to(DEV), rows=rows.to(DEV), exact=exact)
+        dist_o, idx_o = oracle.assign(x[rows].numpy(), cb.numpy())
+        assert np.array_equal(idx.cpu().numpy(), idx_o) and np.array_equal(dist.cpu().numpy(), dist_o)
+    # a strided view goes through .contiguous() like the reference (weighted_distance.cu:86-87)
+    xs = x.to(DEV)[::2]
+    dist, idx = L.assign(xs, cb.to(DEV))
+    _, idx_o = oracle.assign(x[::2].numpy(), cb.numpy())
+    assert np.array_equal(idx.cpu().numpy(), idx_o)
+
+
+def test_weighted_distance_dropin_errors_and_empty(L):
+    from c3dgs_b200.weighted_distance._C import weightedDistance
+    with pytest.raises(RuntimeError, match="dimension 2"):
+        weightedDistance(torch.zeros(5, device=DEV), torch.zeros(3, 5, device=DEV))
+    with pytest.raises(RuntimeError, match="same number of channels"):
+        weightedDistance(torch.zeros(5, 4, device=DEV), torch.zeros(3, 5, device=DEV))
+    dist, idx = weightedDistance(torch.zeros(0, 5, device=DEV), torch.zeros(3, 5, device=DEV))
+    assert dist.shape == (0,) and idx.shape == (0,) and idx.dtype == torch.int64
+
+
+def _load_reference_kernel():
+    ref_dir = os.path.join(ROOT, "oracle", "_ref")
+    if not os.path.exists(os.path.join(ref_dir, "weighted_distance_ref", "_C.so")):
+        return None
+    sys.path.insert(0, ref_dir)
+    try:
+        from weighted_distance_ref import _C
+        return _C
+    finally:
+        sys.path.remove(ref_dir)
+
+
+@pytest.mark.parametrize("d,k", [(45, 4096), (48, 1024), (6, 4096), (7, 512)])
+def test_reference_cuda_kernel_pins_oracle_and_product(L, oracle, d, k):
+    """The reference's own weighted_distance.cu, compiled unmodified (oracle/Makefile `ref`), run here."""
+    ref = _load_reference_kernel()
+    if ref is None:
+        pytest.skip("oracle/_ref not built (reference checkout was absent at build time)")
+    x, _, cb = _synth(4099, d, k, seed=31 + d)
+    torch.cuda.synchronize()
+    dist_r, idx_r = ref.weightedDistance(x.to(DEV), cb.to(DEV))     # legacy default stream (:52)
+    torch.cuda.synchronize()
+    dist_o, idx_o = oracle.assign(x.numpy(), cb.numpy())
+    assert np.array_equal(idx_r.cpu().numpy(), idx_o), "oracle disagrees with the reference kernel"
+    assert np.array_equal(dist_r.cpu().numpy().view(np.uint32), dist_o.view(np.uint32))
+    for exact in (True, False):
+        dist, idx = L.assign(x.to(DEV), cb.to(DEV), exact=exact)
+        assert torch.equal(idx, idx_r) and torch.equal(dist, dist_r)
+
+
+# ---------------------------------------------------------------- update ---------------------
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+@pytest.mark.parametrize("tc", [False, True])
+def test_update_teacher_forced_against_reference_golden(L, name, tc):
+    """Every recorded reference step, replayed from the recorded previous state (SURVEY §7.2 protocol)."""
+    g = np.load(golden_path(name))
+    n, d, k, chunk, steps, sn, seed = [int(v) for v in g["meta"]]
+    f = _t(g["features"])
+    w = _t(g["importance"])
+    wn = (w / w.max()).contiguous()
+    for s in range(steps):
+        if s == 0:
+            cb_prev, ei_prev = g["codebook0"], np.zeros(k, np.float32)
+        else:
+            cb_prev, ei_prev = g["cb_after_update"][s - 1].copy(), g["ei_after_update"][s - 1]
+            if sn:
+                from oracle import oracle as o
+                o.trace_normalize(cb_prev)
+        cb, ei = _t(cb_prev), _t(ei_prev)
+        batch = _t(g["batches"][s])
+        dist, idx = L.update(f, wn, cb, ei, float(g["decay"]), float(g["eps"]), rows=batch,
+                             scale_normalize=False, tensor_cores=tc, return_dist=True, return_idx=True)
+        assert np.array_equal(idx.cpu().numpy(), g["upd_idx"][s])
+        assert np.array_equal(dist.cpu().numpy().view(np.uint32), g["upd_dist"][s].view(np.uint32))
+        _cb_close(cb.cpu().numpy(), g["cb_after_update"][s])
+        assert np.allclose(ei.cpu().numpy(), g["ei_after_update"][s], rtol=1e-5, atol=1e-7)
+
+
+@pytest.mark.parametrize("d", [6, 7, 45, 48])
+def test_accumulate_and_ema_vs_oracle(L, oracle, d):
+    n, k = 20000, 300
+    x, w, cb = _synth(n, d, k, seed=50 + d)
+    _, idx = oracle.assign(x.numpy(), cb.numpy())
+    sx64, sw64 = oracle.scatter_sum_f64(x.numpy(), w.numpy(), idx, k)
+    acc = L.accumulate(x.to(DEV), w.to(DEV), _t(idx), k).cpu().numpy()
+    assert acc.shape == (k, L.acc_stride(d))
+    scale = np.abs(sx64).max(1, keepdims=True) + 1e-30
+    assert np.max(np.abs(acc[:, :d] - sx64) / scale) < 1e-5
+    assert np.allclose(acc[:, d], sw64, rtol=1e-5)
+    assert not acc[:, d + 1:].any()
+    # EMA epilogue is deterministic: bit-exact against the oracle on the SAME sums
+    for sn in (False, True):
+        cb_g, ei_g = cb.to(DEV).clone(), torch.rand(k, generator=torch.Generator().manual_seed(1)).to(DEV)
+        cb_o, ei_o = cb.numpy().copy(), ei_g.cpu().numpy().copy()
+        L.ema(cb_g, ei_g, _t(acc), 0.8, 1e-5, scale_normalize=sn)
+        oracle.ema(cb_o, ei_o, np.ascontiguousarray(acc[:, :d]), np.ascontiguousarray(acc[:, d]), 0.8, 1e-5)
+        if sn:
+            oracle.trace_normalize(cb_o)
+        assert np.array_equal(cb_g.cpu().numpy().view(np.uint32), cb_o.view(np.uint32))
+        assert np.array_equal(ei_g.cpu().numpy().view(np.uint32), ei_o.view(np.uint32))
+
+
+def test_update_kats_empty_cluster_and_single_cluster(L):
+    cb = torch.tensor([[1.0, 2.0], [100.0, 100.0]], device=DEV)
+    ei = torch.tensor([0.5, 0.25], device=DEV)
+    x = torch.tensor([[1.0, 2.0], [1.5, 2.5]], device=DEV)
+    w = torch.ones(2, device=DEV)
+    for tc in (False, True):
+        c, e = cb.clone(), ei.clone()
+        L.update(x, w, c, e, 0.8, 1e-5, tensor_cores=tc)
+        assert torch.equal(c[1], cb[1] * 0.8) and float(e[1]) == float(torch.tensor(0.25) * torch.tensor(0.8))
+    g = torch.Generator().manual_seed(3)
+    x = torch.randn(5000, 7, generator=g)
+    w = torch.rand(5000, generator=g)
+    c, e = torch.zeros(1, 7, device=DEV), torch.zeros(1, device=DEV)
+    L.update(x.to(DEV), w.to(DEV), c, e, 0.0, 1e-5)
+    expect = (x.double() * w.double()[:, None]).sum(0) / (w.double().sum() + 1e-5)
+    assert torch.allclose(c[0].cpu().double(), expect, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_vq_loop_end_to_end_vs_oracle(L, oracle, name):
+    """The whole mini-batch loop with the reference's recorded draws: final codebook within tolerance,
+    final assignments equal wherever the two codebooks agree on the winner by a clear margin."""
+    from c3dgs_b200 import VectorQuantize
+    g = np.load(golden_path(name))
+    n, d, k, chunk, steps, sn, seed = [int(v) for v in g["meta"]]
+    f, w = _t(g["features"]), _t(g["importance"])
+    wn = (w / w.max()).contiguous()
+    vq = VectorQuantize(d, k, decay=0.8).to(DEV)
+    vq.codebook.data = _t(g["codebook0"])
+    for s in range(steps):
+        vq.update_indexed(f, wn, _t(g["batches"][s]), scale_normalize=bool(sn))
+    _cb_close(vq.codebook.data.cpu().numpy(), g["codebook"], rtol=5e-5)
+    idx = vq.assign(f).cpu().numpy()
+    assert (idx == g["indices"]).mean() > 0.99
+    # and exactly the oracle's answer for the codebook we actually hold
+    _, idx_o = oracle.assign(g["features"], vq.codebook.data.cpu().numpy())
+    assert np.array_equal(idx, idx_o)
+
+
+def test_vq_features_dropin_contract(L):
+    from c3dgs_b200 import vq_features
+    x, w, _ = _synth(20000, 6, 64, seed=77)
+    torch.manual_seed(0)
+    cb, idx = vq_features(x.to(DEV), w.to(DEV), 64, vq_chunk=4096, steps=5, scale_normalize=True, silent=True)
+    assert cb.shape == (64, 6) and cb.dtype == torch.float32 and not cb.requires_grad
+    assert idx.shape == (20000,) and idx.dtype == torch.int64
+    assert int(idx.min()) >= 0 and int(idx.max()) < 64
+    torch.manual_seed(0)
+    cb2, idx2 = vq_features(x.to(DEV), w.to(DEV), 64, vq_chunk=4096, steps=5, scale_normalize=True, silent=True)
+    assert torch.allclose(cb, cb2, rtol=1e-4, atol=1e-6, equal_nan=True)
+
+
+def test_reference_vq_module_runs_on_the_dropin(L):
+    """compression/vq.py's own import line resolves to libc3vq after install()."""
+    import c3dgs_b200
+    saved = {k: sys.modules.get(k) for k in ("weighted_distance", "weighted_distance._C")}
+    try:
+        c3dgs_b200.install()
+        from weighted_distance._C import weightedDistance
+        x, _, cb = _synth(500, 48, 32, seed=9)
+        dist, idx = weightedDistance(x.to(DEV), cb.to(DEV))
+        assert dist.device.type == "cuda" and idx.dtype == torch.int64
+    finally:
+        for k, v in saved.items():
+            if v is None:
+                sys.modules.pop(k, None)
+            else:
+                sys.modules[k] = v
+
+
+# ---------------------------------------------------------------- decode ---------------------
+@pytest.mark.parametrize("shape", [(100, 3), (100, 4), (5000, 16, 3), (300, 45), (64, 7), (10, 1)])
+def test_gather_bit_exact(L, oracle, shape):
+    g = torch.Generator().manual_seed(sum(shape))
+    table = torch.randn(*shape, generator=g)
+    idx = torch.randint(0, shape[0], (12345,), generator=g)
+    out = L.gather(table.to(DEV), idx.to(DEV))
+    assert out.shape == (12345,) + tuple(shape[1:])
+    assert np.array_equal(out.cpu().numpy(), oracle.gather(table.numpy(), idx.numpy()))
+    assert torch.equal(out.cpu(), table[idx])
+    empty = L.gather(table.to(DEV), torch.zeros(0, dtype=torch.int64, device=DEV))
+    assert empty.shape == (0,) + tuple(shape[1:])
+
+
+def test_indexed_decode_autograd_matches_torch_indexing(L):
+    from c3dgs_b200 import indexed_decode
+    g = torch.Generator().manual_seed(12)
+    table = torch.randn(200, 16, 3, generator=g).to(DEV).requires_grad_(True)
+    idx = torch.randint(0, 200, (5000,), generator=g).to(DEV)
+    upstream = torch.randn(5000, 16, 3, generator=g).to(DEV)
+    out = indexed_decode(table, idx)
+    out.backward(upstream)
+    grad = table.grad.clone()
+    table.grad = None
+    ref = table[idx]
+    ref.backward(upstream)
+    assert torch.equal(out, ref)
+    assert torch.allclose(grad, table.grad, rtol=1e-5, atol=1e-5)
+
+
+def test_gather_rows_matches_indexing(L):
+    x, w, _ = _synth(5000, 45, 8, seed=13)
+    rows = torch.randint(0, 5000, (3000,), generator=torch.Generator().manual_seed(14))
+    ox, ow = L.gather_rows(x.to(DEV), w.to(DEV), rows.to(DEV))
+    assert torch.equal(ox.cpu(), x[rows]) and torch.equal(ow.cpu(), w[rows])
+
+
+# ---------------------------------------------------------------- full size ------------------
+@pytest.mark.parametrize("d", [45, 7])
+def test_full_size_properties(L, d):
+    """BASELINE config 2/3 sizes (5.8M rows, K=4096): properties that need no CPU oracle."""
+    n, k = 5_800_000, 4096
+    g = torch.Generator(device=DEV).manual_seed(d)
+    x = torch.randn(n, d, device=DEV, generator=g)
+    w = torch.rand(n, device=DEV, generator=g) ** 4
+    cb = x[torch.randint(0, n, (k,), device=DEV, generator=g)].clone()
+    cb[1] = cb[0]                                             # a duplicated codeword: index 0 must win
+    dist_tc, idx_tc = L.assign(x, cb, exact=False)
+    # tensor-core path == SIMT exact path on every row (bit-exact indices and distances)
+    dist_ex, idx_ex = L.assign(x, cb, exact=True)
+    assert torch.equal(idx_tc, idx_ex) and torch.equal(dist_tc, dist_ex)
+    assert int((idx_tc == 1).sum()) == 0
+    # codeword rows map to themselves
+    _, self_idx = L.assign(cb, cb, exact=False)
+    assert torch.equal(self_idx[2:].cpu(), torch.arange(2, k))
+    # sums: total weight is conserved; decode of the assignment is idempotent under re-assignment
+    acc = L.accumulate(x, w, idx_tc, k)
+    assert abs(float(acc[:, d].double().sum()) - float(w.double().sum())) < 1e-4 * float(w.double().sum())
+    q = L.gather(cb, idx_tc[:1_000_000])
+    _, idx_q = L.assign(q, cb, exact=False)
+    assert torch.equal(cb[idx_q], q)

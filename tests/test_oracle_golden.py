@@ -1,0 +1,153 @@
+"""CPU: the oracle (oracle/c3vq_oracle.c) against the fixtures generated from the reference's own
+compression/vq.py (oracle/make_golden.py), plus known-answer tests for the assignment rule
+(weighted_distance.cu:20-44)."""
+import numpy as np
+import pytest
+
+from conftest import GOLDEN_CASES, golden_path
+
+
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_oracle_reproduces_reference_vq_features_bit_exact(oracle, name):
+    g = np.load(golden_path(name))
+    n, d, k, chunk, steps, sn, seed = [int(v) for v in g["meta"]]
+    cb, ei, idx, trace = oracle.vq_features(g["features"], g["importance"], g["codebook0"], list(g["batches"]),
+                                            decay=float(g["decay"]), scale_normalize=bool(sn), eps=float(g["eps"]))
+    assert len(trace) == steps
+    for s, (dist, sidx) in enumerate(trace):
+        assert np.array_equal(sidx, g["upd_idx"][s]), f"step {s} assignments differ"
+        assert np.array_equal(dist.view(np.uint32), g["upd_dist"][s].view(np.uint32)), f"step {s} min_dists differ"
+    assert np.array_equal(idx, g["indices"])
+    assert np.array_equal(cb.view(np.uint32), g["codebook"].view(np.uint32))
+    assert np.array_equal(ei.view(np.uint32), g["ei_after_update"][-1].view(np.uint32))
+
+
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_oracle_update_teacher_forced(oracle, name):
+    """Each recorded step replayed from the recorded state of the previous one."""
+    g = np.load(golden_path(name))
+    n, d, k, chunk, steps, sn, seed = [int(v) for v in g["meta"]]
+    f, w = g["features"], g["importance"]
+    wn = (w / w.max()).astype(np.float32)
+    cb = g["codebook0"].copy()
+    ei = np.zeros(k, np.float32)
+    for s in range(steps):
+        b = g["batches"][s]
+        dist, idx = oracle.update(f[b], wn[b], cb, ei, float(g["decay"]), float(g["eps"]))
+        assert np.array_equal(idx, g["upd_idx"][s])
+        assert np.array_equal(cb, g["cb_after_update"][s])
+        assert np.array_equal(ei, g["ei_after_update"][s])
+        if sn:
+            oracle.trace_normalize(cb)
+            tr = cb[:, 0] + cb[:, 3] + cb[:, 5]
+            ok = np.isfinite(tr)
+            scale = np.abs(cb[:, [0, 3, 5]]).max(1)           # rows with a near-zero trace blow up; error scales with them
+            assert np.all(np.abs(tr[ok] - 1.0) <= 1e-5 * np.maximum(scale[ok], 1.0))   # KAT (6): unit trace
+
+
+def test_kat_codebook_rows_map_to_themselves(oracle):
+    rng = np.random.default_rng(0)
+    cb = rng.standard_normal((300, 45)).astype(np.float32)
+    dist, idx = oracle.assign(cb, cb)
+    assert np.array_equal(idx, np.arange(300))
+    assert np.all(dist == 0)
+
+
+def test_kat_duplicate_codewords_lowest_index_wins(oracle):
+    rng = np.random.default_rng(1)
+    base = rng.standard_normal((50, 7)).astype(np.float32)
+    cb = np.concatenate([base, base, base])          # every codeword three times
+    x = base + 1e-3 * rng.standard_normal(base.shape).astype(np.float32)
+    _, idx = oracle.assign(x, cb)
+    assert np.array_equal(idx, np.arange(50))          # strict '<' keeps the first copy
+
+
+def test_kat_distance_is_in_order_fma_chain(oracle):
+    rng = np.random.default_rng(2)
+    x = rng.standard_normal(45).astype(np.float32)
+    c = rng.standard_normal(45).astype(np.float32)
+    acc = np.float32(0)
+    for i in range(45):
+        diff = np.float32(x[i] - c[i])
+        acc = np.float32(np.float64(diff) * np.float64(diff) + np.float64(acc))   # fma: one rounding
+    assert oracle.distance(x, c) == acc
+    dist, idx = oracle.assign(x[None], c[None])
+    assert dist[0] == acc and idx[0] == 0
+
+
+def test_kat_nan_and_inf_never_win(oracle):
+    cb = np.zeros((4, 6), np.float32)
+    cb[0, :] = np.nan
+    cb[1, :] = np.inf
+    cb[2, :] = 5.0
+    cb[3, :] = 1.0
+    x = np.ones((3, 6), np.float32)
+    dist, idx = oracle.assign(x, cb)
+    assert np.array_equal(idx, [3, 3, 3]) and np.all(dist == 0)
+    xn = np.full((2, 6), np.nan, np.float32)
+    dist, idx = oracle.assign(xn, cb)
+    assert np.array_equal(idx, [0, 0]) and np.all(dist == np.finfo(np.float32).max)   # defined fallback
+
+
+def test_kat_empty_cluster_decays_by_decay(oracle):
+    cb = np.array([[1.0, 2.0], [100.0, 100.0]], np.float32)
+    ei = np.array([0.5, 0.25], np.float32)
+    x = np.array([[1.0, 2.0], [1.5, 2.5]], np.float32)
+    w = np.array([1.0, 1.0], np.float32)
+    cb0 = cb.copy()
+    oracle.update(x, w, cb, ei, 0.8)
+    assert np.array_equal(cb[1], cb0[1] * np.float32(0.8))        # 0/(0+eps) then EMA: pure decay (vq.py:34)
+    assert ei[1] == np.float32(0.25) * np.float32(0.8)
+
+
+def test_kat_single_cluster_weighted_mean(oracle):
+    rng = np.random.default_rng(3)
+    x = rng.standard_normal((200, 7)).astype(np.float32)
+    w = rng.random(200).astype(np.float32)
+    cb = np.zeros((1, 7), np.float32)
+    ei = np.zeros(1, np.float32)
+    oracle.update(x, w, cb, ei, 0.0)                               # decay 0: codebook = new value
+    expect = (x * w[:, None]).sum(0, dtype=np.float64) / (w.sum(dtype=np.float64) + 1e-5)
+    assert np.allclose(cb[0], expect, rtol=1e-5, atol=1e-6)
+
+
+def test_assign_shape_errors(oracle):
+    with pytest.raises(RuntimeError):
+        oracle.assign(np.zeros((3,), np.float32), np.zeros((2, 3), np.float32))
+    with pytest.raises(RuntimeError):
+        oracle.assign(np.zeros((3, 4), np.float32), np.zeros((2, 3), np.float32))
+
+
+def test_empty_inputs(oracle):
+    dist, idx = oracle.assign(np.zeros((0, 5), np.float32), np.zeros((4, 5), np.float32))
+    assert dist.shape == (0,) and idx.shape == (0,)
+    sx, sw = oracle.scatter_sum(np.zeros((0, 5), np.float32), np.zeros(0, np.float32), np.zeros(0, np.int64), 4)
+    assert not sx.any() and not sw.any()
+
+
+def test_gather_matches_numpy(oracle):
+    rng = np.random.default_rng(4)
+    table = rng.standard_normal((37, 16, 3)).astype(np.float32)
+    idx = rng.integers(0, 37, 1000)
+    assert np.array_equal(oracle.gather(table, idx), table[idx])
+
+
+@pytest.mark.skipif(not __import__("oracle.ref_loader", fromlist=["x"]).available(),
+                    reason="reference checkout only exists in the build container")
+def test_reference_module_agrees_with_oracle_on_fresh_inputs(oracle):
+    """Import the reference's compression/vq.py and run one update on new random inputs."""
+    import torch
+    from oracle import ref_loader
+    mod = ref_loader.load()
+    g = torch.Generator().manual_seed(11)
+    x = torch.randn(700, 45, generator=g)
+    w = torch.rand(700, generator=g)
+    vq = mod.VectorQuantize(45, 32, decay=0.8)
+    vq.codebook.data = torch.randn(32, 45, generator=g)
+    cb = vq.codebook.data.numpy().copy()
+    ei = np.zeros(32, np.float32)
+    dist_ref = vq.update(x, w)
+    dist, idx = oracle.update(x.numpy(), w.numpy(), cb, ei, 0.8)
+    assert np.array_equal(dist, dist_ref.numpy())
+    assert np.array_equal(cb, vq.codebook.data.numpy())
+    assert np.array_equal(ei, vq.entry_importance.data.numpy())
