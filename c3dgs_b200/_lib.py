@@ -14,7 +14,7 @@ import threading
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libc3vq.so")
+LIB_PATH = os.environ.get("C3VQ_LIB") or os.path.join(_HERE, "libc3vq.so")   # C3VQ_LIB: developer builds
 
 _lib = None
 _lock = threading.Lock()

@@ -60,3 +60,14 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
 if __name__ == "__main__":
     print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+
+
+def build_dev(defines, out_name="libc3vq_dev.so") -> str:
+    """Developer build with extra -D flags (e.g. C3VQ_TC_SINGLE, C3VQ_TC_PROF); load it with C3VQ_LIB=<path>."""
+    out = os.path.join(HERE, out_name)
+    cmd = [nvcc(), "-ccbin", "/usr/bin/g++"] + NVCC_FLAGS + ["-D" + d for d in defines] + \
+          [os.path.join(CSRC, s) for s in SOURCES] + ["-o", out]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
+    return out

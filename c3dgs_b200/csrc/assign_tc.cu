@@ -35,6 +35,16 @@ namespace c3vq {
 
 using namespace ptx;
 
+#ifdef C3VQ_TC_PROF
+#define PROF_DECL unsigned long long prof_t = clock64(); unsigned long long prof_a[8] = {0, 0, 0, 0, 0, 0, 0, 0}
+#define PROF(i) do { const unsigned long long _n = clock64(); prof_a[i] += _n - prof_t; prof_t = _n; } while (0)
+#define PROF_FLUSH(base, cond) do { if (cond) { for (int _i = 0; _i < 8; _i++) atomicAdd(&p.hdr->prof[(base) + _i], prof_a[_i]); } } while (0)
+#else
+#define PROF_DECL
+#define PROF(i)
+#define PROF_FLUSH(base, cond)
+#endif
+
 constexpr int TC_BM = 128;            // rows per UMMA tile
 constexpr int TC_PR = 2 * TC_BM;      // rows per CTA pass ("pair" of tiles)
 constexpr int TC_BN = 256;            // codes per stage / per MMA
@@ -59,6 +69,7 @@ struct TcHeader {
     int cmax_bits;                  // max |c'_j| over finite codes, float bits (non-negative)
     int live;                       // number of finite codes
     float mu_sum[72];               // column sums over finite codes
+    unsigned long long prof[32];    // developer build (C3VQ_TC_PROF): cycle counters per role/phase
 };
 
 __host__ __device__ inline int tc_dp(int d) { return (d + 2 + 7) & ~7; }          // padded K extent
@@ -87,23 +98,28 @@ struct TcParams {
 
 // ------------------------------------------------------------------------------------------------
 // prep 1: column sums over finite codes (for the centre mu)
-__global__ void k_tc_prep_mean(const float *__restrict__ cb, int k, int d, TcHeader *hdr)
+__global__ void __launch_bounds__(256) k_tc_prep_mean(const float *__restrict__ cb, int k, int d, TcHeader *hdr)
 {
+    // warp per code (lanes over columns, coalesced row reads), 128 codes per block
     __shared__ float ssum[72];
     __shared__ int slive;
     if (threadIdx.x < 72) ssum[threadIdx.x] = 0.f;
     if (threadIdx.x == 0) slive = 0;
     __syncthreads();
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j < k) {
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    float s0 = 0.f, s1 = 0.f;
+    int live = 0;
+    const int j0 = blockIdx.x * 128;
+    for (int j = j0 + wib; j < min(k, j0 + 128); j += 8) {
         const float *row = cb + (size_t)j * d;
-        bool fin = true;
-        for (int c = 0; c < d; c++) fin = fin && isfinite(row[c]);
-        if (fin) {
-            for (int c = 0; c < d; c++) atomicAdd(&ssum[c], row[c]);
-            atomicAdd(&slive, 1);
-        }
+        const float v0 = lane < d ? row[lane] : 0.f;
+        const float v1 = lane + 32 < d ? row[lane + 32] : 0.f;
+        const bool fin = __all_sync(0xffffffffu, isfinite(v0) && isfinite(v1));
+        if (fin) { s0 += v0; s1 += v1; live++; }
     }
+    if (lane < d) atomicAdd(&ssum[lane], s0);
+    if (lane + 32 < d) atomicAdd(&ssum[lane + 32], s1);
+    if (lane == 0) atomicAdd(&slive, live);
     __syncthreads();
     if (threadIdx.x < d) atomicAdd(&hdr->mu_sum[threadIdx.x], ssum[threadIdx.x]);
     if (threadIdx.x == 0) atomicAdd(&hdr->live, slive);
@@ -271,16 +287,20 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
         // ===================== codebook stage producer (TMA engine, 1-D bulk copies) =====================
         if (lane == 0) {
             uint32_t g = 0;
+            PROF_DECL;
             for (int64_t pair = blockIdx.x; pair < p.npairs; pair += gridDim.x) {
                 for (int s = 0; s < nsteps; s++, g++) {
                     const int stage = g % S;
                     const uint32_t u = g / S;
-                    mbar_wait(B_EMPTY(stage), (u & 1) ^ 1);
+                    PROF(0);
+                    mbar_wait_backoff(B_EMPTY(stage), (u & 1) ^ 1);
+                    PROF(1);   // prof[1]: TMA wait B_EMPTY
                     mbar_arrive_expect_tx(B_FULL(stage), L::BSTAGE);
                     bulk_g2s(smem_u32(sB + (size_t)stage * L::BSTAGE), p.bimg + (size_t)s * (TC_BN * DP), L::BSTAGE,
                              B_FULL(stage));
                 }
             }
+            PROF_FLUSH(0, true);
         }
     } else if (warp == 1) {
         // ===================== MMA issuer =====================
@@ -288,18 +308,25 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             constexpr uint32_t IDESC = idesc_tf32(TC_BM, TC_BN);
             const uint32_t a_addr = smem_u32(sA);
             uint32_t g = 0, pi = 0;
+            PROF_DECL;
             for (int64_t pair = blockIdx.x; pair < p.npairs; pair += gridDim.x, pi++) {
+                PROF(0);
                 mbar_wait(A_FULL, pi & 1);
+                PROF(1);   // prof[8+1]: MMA wait A_FULL
                 tc_fence_after();
                 for (int s = 0; s < nsteps; s++, g++) {
                     const int stage = g % S;
                     const uint32_t u = g / S;
+                    PROF(0);
                     mbar_wait(B_FULL(stage), u & 1);
+                    PROF(2);   // prof[8+2]: MMA wait B_FULL
                     tc_fence_after();
                     const uint32_t b_addr = smem_u32(sB + (size_t)stage * L::BSTAGE);
 #pragma unroll
                     for (int t = 0; t < 2; t++) {
+                        PROF(0);
                         mbar_wait(ACC_EMPTY(t), (g & 1) ^ 1);
+                        PROF(3);   // prof[8+3]: MMA wait ACC_EMPTY
                         tc_fence_after();
 #pragma unroll
                         for (int ks = 0; ks < KSTEPS; ks++) {
@@ -313,6 +340,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                 }
                 umma_commit(A_EMPTY);
             }
+            PROF(0);       // prof[8+0]: MMA issue + everything else
+            PROF_FLUSH(8, true);
         }
     } else if (warp >= TC_PROD_WARP0) {
         // ===================== feature producers (256 threads) =====================
@@ -325,95 +354,82 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             for (int kk = D; kk < DP; kk++)
                 *reinterpret_cast<float *>(base + (kk >> 2) * TC_LBO_A + (kk & 3) * 4) = (kk < D + NC) ? 1.0f : 0.f;
         }
-        if (ptid < D) sMu[ptid] = p.mu[ptid];
-        const float cmax = __int_as_float(p.hdr->cmax_bits);
-        const bool force_fb = p.hdr->force_fallback != 0;
-        named_bar_sync(1, TC_PR);
-
         // Mapping: producer warp pw owns rows pw*32 .. pw*32+31 of the pass, lane <-> column (kk = lane + 32*h).
         // Loads are coalesced per row, every smem offset below is a per-thread base plus an immediate, and
         // with the 16-byte skew of TC_LBO_A the 32 lanes of a store hit 32 different banks.
-        constexpr int NH = DP > 32 ? 2 : 1;                       // D <= 32 needs one column group
+        constexpr int NH = DP > 32 ? 2 : 1;                       // D <= 30 needs one column group
         const int pw = warp - TC_PROD_WARP0;
         float xr[32 * NH];
         auto prefetch = [&](int64_t pair) {
             const int64_t r0 = pair * TC_PR + pw * 32;
+            if (p.rows == nullptr && r0 + 32 <= p.n) {
+                // common case: 32 contiguous full rows -> one base pointer, immediate offsets
+                const float *xp = p.x + r0 * D + lane;
 #pragma unroll
-            for (int r = 0; r < 32; r++) {
-                const int64_t gi = r0 + r;
-                const bool valid = gi < p.n;
-                const int64_t src = valid ? (p.rows ? p.rows[gi] : gi) : 0;
-                const float *xp = p.x + src * D;
+                for (int r = 0; r < 32; r++) {
 #pragma unroll
-                for (int h = 0; h < NH; h++) {
-                    const int kk = lane + 32 * h;
-                    xr[r * NH + h] = (valid && kk < D) ? xp[kk] : 0.f;
+                    for (int h = 0; h < NH; h++) xr[r * NH + h] = (lane + 32 * h < D) ? xp[r * D + 32 * h] : 0.f;
+                }
+            } else {
+#pragma unroll
+                for (int r = 0; r < 32; r++) {
+                    const int64_t gi = r0 + r;
+                    const bool valid = gi < p.n;
+                    const int64_t src = valid ? (p.rows ? p.rows[gi] : gi) : 0;
+                    const float *xp = p.x + src * D + lane;
+#pragma unroll
+                    for (int h = 0; h < NH; h++) xr[r * NH + h] = (valid && lane + 32 * h < D) ? xp[32 * h] : 0.f;
                 }
             }
         };
-        if ((int64_t)blockIdx.x < p.npairs) prefetch(blockIdx.x);
         float mu_l[NH];
         uint32_t koff[NH];
 #pragma unroll
         for (int h = 0; h < NH; h++) {
             const int kk = lane + 32 * h;
-            mu_l[h] = kk < D ? sMu[kk] : 0.f;
+            mu_l[h] = kk < D ? p.mu[kk] : 0.f;
             koff[h] = (kk >> 2) * TC_LBO_A + (kk & 3) * 4;
         }
         uint8_t *a_base = sA + (pw >> 2) * L::ATILE + (pw & 3) * 4 * 128;   // row pw*32 of the pass
         uint32_t pi = 0;
-        for (int64_t pair = blockIdx.x; pair < p.npairs; pair += gridDim.x, pi++) {
-            const int64_t r0 = pair * TC_PR + pw * 32;
-            mbar_wait(A_EMPTY, (pi & 1) ^ 1);          // previous pass' MMAs no longer read A
-#pragma unroll
-            for (int r = 0; r < 32; r++) {
-                float X = 0.f;
-#pragma unroll
-                for (int h = 0; h < NH; h++) {
-                    const int kk = lane + 32 * h;
-                    if (kk < D) {
-                        const uint32_t bits = to_tf32(xr[r * NH + h] - mu_l[h]);
-                        *reinterpret_cast<uint32_t *>(a_base + (r >> 3) * 128 + (r & 7) * 16 + koff[h]) = bits;
-                        const float vr = __uint_as_float(bits);
-                        X = fmaf(vr, vr, X);
-                    }
-                }
-                // row norm of the rounded, centred row -> error band
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1) X += __shfl_xor_sync(0xffffffffu, X, o);
-                if (lane == (r & 31)) {
-                    // E bounds |score + X - true distance| for every code
-                    const float C1 = 1.002f * 0.001953125f + 7.62939453125e-6f;   // 2^-9 * 1.002 + 2^-17
-                    const float C2 = 3.814697265625e-6f + 4.76837158203125e-7f;   // 2^-18 + 2^-21
-                    const float E = C1 * sqrtf(X) * cmax + C2 * cmax * cmax;
-                    float band = 1.01f * (2.f * E + p.gamma2 * X) + 3.0e-36f;
-                    const bool valid = (r0 + r) < p.n;
-                    if (!(X < TC_HUGE2 * 0.0625f) || force_fb || !(band < TC_BIG))
-                        band = __int_as_float(0x7fc00000);                        // NaN: exact fallback
-                    if (!valid) band = -1.f;
-                    sInfo[pw * 32 + r] = band;
-                    if (p.dbg_norm2 && valid) {
-                        p.dbg_norm2[r0 + r] = X;
-                        p.dbg_band[r0 + r] = band;
-                    }
-                }
-            }
-            fence_proxy_async_smem();
-            mbar_arrive(A_FULL);
-            if (RAW) {
-                mbar_wait(RAW_FREE, (pi & 1) ^ 1);     // epilogue finished re-ranking the previous pass
+        PROF_DECL;
+        // software pipeline with ONE prefetch call site: iteration -1 only prefetches the first pass
+        for (int64_t pair = (int64_t)blockIdx.x - gridDim.x;; pair += gridDim.x) {
+            if (pair >= 0) {
+                PROF(0);   // prof[16+0]: producer prefetch issue
+                mbar_wait_backoff(A_EMPTY, (pi & 1) ^ 1);  // previous pass' MMAs no longer read A
+                PROF(1);   // prof[16+1]: producer wait A_EMPTY
 #pragma unroll
                 for (int r = 0; r < 32; r++) {
 #pragma unroll
                     for (int h = 0; h < NH; h++) {
-                        const int kk = lane + 32 * h;
-                        if (kk < D) sRaw[(pw * 32 + r) * RS + kk] = xr[r * NH + h];
+                        if (lane + 32 * h < D)
+                            *reinterpret_cast<uint32_t *>(a_base + (r >> 3) * 128 + (r & 7) * 16 + koff[h]) =
+                                to_tf32(xr[r * NH + h] - mu_l[h]);
                     }
                 }
-                mbar_arrive(RAW_FULL);
+                fence_proxy_async_smem();
+                mbar_arrive(A_FULL);
+                PROF(2);   // prof[16+2]: producer convert + store A (includes waiting for the prefetched loads)
+                if (RAW) {
+                    mbar_wait_backoff(RAW_FREE, (pi & 1) ^ 1);   // epilogue finished re-ranking the previous pass
+                    PROF(3);   // prof[16+3]: producer wait RAW_FREE
+                    float *rp = sRaw + (pw * 32) * RS + lane;
+#pragma unroll
+                    for (int r = 0; r < 32; r++) {
+#pragma unroll
+                        for (int h = 0; h < NH; h++)
+                            if (lane + 32 * h < D) rp[r * RS + 32 * h] = xr[r * NH + h];
+                    }
+                    mbar_arrive(RAW_FULL);
+                    PROF(4);   // prof[16+4]: producer raw store
+                }
+                pi++;
             }
-            if (pair + gridDim.x < p.npairs) prefetch(pair + gridDim.x);
+            if (pair + gridDim.x >= p.npairs) break;
+            prefetch(pair + gridDim.x);
         }
+        PROF_FLUSH(16, lane == 0 && pw == 0);
     } else if (warp >= TC_EPI_WARP0) {
         // ===================== epilogue: scan, candidate lists, re-rank, outputs =====================
         const int lr = tid - TC_EPI_WARP0 * 32;        // local row 0..255
@@ -421,18 +437,52 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
         const int q = warp & 3;                         // TMEM lane quarter this warp may access
         const uint32_t tsrc = tmem_base + ((uint32_t)(q * 32) << 16) + t * TC_BN;
         const bool need_dist = p.out_dist != nullptr;
+        const float cmax = __int_as_float(p.hdr->cmax_bits);
+        const bool force_fb = p.hdr->force_fallback != 0;
         unsigned long long st_rows = 0, st_cands = 0, st_fb = 0;
         uint32_t g = 0, pi = 0;
+        PROF_DECL;
         for (int64_t pair = blockIdx.x; pair < p.npairs; pair += gridDim.x, pi++) {
             const int64_t gi = pair * TC_PR + lr;
+            PROF(0);
             mbar_wait(A_FULL, pi & 1);
-            const float band = sInfo[lr];
+            PROF(1);       // prof[24+1]: epilogue wait A_FULL
+            float band;
+            {
+                // row norm of the rounded, centred row (read back from the A tile) -> error band
+                const int r = lr & 127;
+                const uint8_t *base = sA + t * L::ATILE + (r >> 3) * 128 + (r & 7) * 16;
+                float X = 0.f;
+#pragma unroll
+                for (int c4 = 0; c4 < DP / 4; c4++) {
+                    const float4 xv = *reinterpret_cast<const float4 *>(base + c4 * TC_LBO_A);
+                    if (4 * c4 + 0 < D) X = fmaf(xv.x, xv.x, X);
+                    if (4 * c4 + 1 < D) X = fmaf(xv.y, xv.y, X);
+                    if (4 * c4 + 2 < D) X = fmaf(xv.z, xv.z, X);
+                    if (4 * c4 + 3 < D) X = fmaf(xv.w, xv.w, X);
+                }
+                // E bounds |score + X - true distance| for every code
+                const float C1 = 1.002f * 0.001953125f + 7.62939453125e-6f;   // 2^-9 * 1.002 + 2^-17
+                const float C2 = 3.814697265625e-6f + 4.76837158203125e-7f;   // 2^-18 + 2^-21
+                const float E = C1 * sqrtf(X) * cmax + C2 * cmax * cmax;
+                band = 1.01f * (2.f * E + p.gamma2 * X) + 3.0e-36f;
+                if (!(X < TC_HUGE2 * 0.0625f) || force_fb || !(band < TC_BIG))
+                    band = __int_as_float(0x7fc00000);                        // NaN: exact fallback
+                if (gi >= p.n) band = -1.f;
+                if (p.dbg_norm2 && gi < p.n) {
+                    p.dbg_norm2[gi] = X;
+                    p.dbg_band[gi] = band;
+                }
+            }
             float m = 3.0e38f;
             float thr = (band >= 0.f) ? __int_as_float(0x7f800000) : __int_as_float(0xff800000);  // +inf / -inf
             int cnt = 0;
             bool ovf = false;
+            PROF(2);       // prof[24+2]: epilogue band
             for (int s = 0; s < nsteps; s++, g++) {
+                PROF(4);   // prof[24+4]: epilogue drain (LDTM + min + lists)
                 mbar_wait(ACC_FULL(t), g & 1);
+                PROF(3);   // prof[24+3]: epilogue wait ACC_FULL
                 tc_fence_after();
 #pragma unroll 1
                 for (int c = 0; c < TC_BN / 32; c++) {
@@ -454,30 +504,37 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                             m = cm;
                             thr = m + p.gamma2 * fabsf(m) + band;
                         }
+                        uint32_t mask = 0;
 #pragma unroll
-                        for (int j = 0; j < 32; j++) {
-                            if (v[j] <= thr) {
-                                if (cnt == TC_LCAP) {   // full: drop entries the tighter threshold excludes
-                                    int wpos = 0;
-                                    for (int e = 0; e < TC_LCAP; e++) {
-                                        const uint32_t ent = sList[e * TC_PR + lr];
-                                        if (entry_score(ent) <= thr) sList[(wpos++) * TC_PR + lr] = ent;
-                                    }
-                                    cnt = wpos;
+                        for (int j = 0; j < 32; j++) mask |= (v[j] <= thr) ? (1u << j) : 0u;
+                        // every entry of this chunk carries the chunk minimum as its (lower-bound) score: enough
+                        // to prune it later, and no dynamic indexing of the register tile is needed
+                        const uint32_t sc = pack_entry(cm, 0u);
+                        while (mask) {
+                            const int j = __ffs(mask) - 1;
+                            mask &= mask - 1;
+                            if (cnt == TC_LCAP) {           // full: drop entries the tighter threshold excludes
+                                int wpos = 0;
+                                for (int e = 0; e < TC_LCAP; e++) {
+                                    const uint32_t ent = sList[e * TC_PR + lr];
+                                    if (entry_score(ent) <= thr) sList[(wpos++) * TC_PR + lr] = ent;
                                 }
-                                if (cnt < TC_LCAP) {
-                                    sList[cnt * TC_PR + lr] = pack_entry(v[j], (uint32_t)(code0 + j));
-                                    cnt++;
-                                } else {
-                                    ovf = true;
-                                }
+                                cnt = wpos;
+                            }
+                            if (cnt < TC_LCAP) {
+                                sList[cnt * TC_PR + lr] = sc | (uint32_t)(code0 + j);
+                                cnt++;
+                            } else {
+                                ovf = true;
                             }
                         }
                     }
                 }
             }
             // ---- re-rank with the reference arithmetic ----
+            PROF(4);
             if (RAW) mbar_wait(RAW_FULL, pi & 1);
+            PROF(5);       // prof[24+5]: epilogue wait RAW_FULL
             if (gi < p.n) {
                 st_rows++;
                 const int64_t src = p.rows ? p.rows[gi] : gi;
@@ -537,7 +594,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                 }
             }
             if (RAW) mbar_arrive(RAW_FREE);
+            PROF(6);       // prof[24+6]: epilogue re-rank + outputs + scatter
         }
+        PROF_FLUSH(24, tid == TC_EPI_WARP0 * 32);
         // stats: one atomic per warp
         for (int o = 16; o > 0; o >>= 1) {
             st_rows += __shfl_xor_sync(0xffffffffu, st_rows, o);
@@ -679,7 +738,7 @@ int launch_assign_tc(const float *x, const float *w, const int64_t *rows, int64_
     unsigned int *fb = (unsigned int *)(base + l.off_fb);
 
     C3VQ_CUDA(cudaMemsetAsync(hdr, 0, sizeof(TcHeader), s));
-    k_tc_prep_mean<<<(k + 255) / 256, 256, 0, s>>>(codebook, k, d, hdr);
+    k_tc_prep_mean<<<(k + 127) / 128, 256, 0, s>>>(codebook, k, d, hdr);
     C3VQ_LAUNCH_CHECK("k_tc_prep_mean");
     k_tc_prep_image<<<(l.k_pad + 127) / 128, 128, 0, s>>>(codebook, k, l.k_pad, d, l.dp, l.nc, l.dpc, hdr, mu, bimg,
                                                         cbp);

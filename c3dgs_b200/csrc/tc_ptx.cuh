@@ -47,6 +47,12 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
     }
 }
 
+// for waiters that are not on the critical path (producers running ahead): do not burn issue slots
+__device__ __forceinline__ void mbar_wait_backoff(uint32_t bar, uint32_t parity)
+{
+    while (!mbar_try_wait(bar, parity)) __nanosleep(128);
+}
+
 // ---------------------------------------------------------------- proxies / bulk copy
 // generic-proxy shared-memory writes -> visible to the async proxy (UMMA operand reads)
 __device__ __forceinline__ void fence_proxy_async_smem()

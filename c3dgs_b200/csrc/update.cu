@@ -110,25 +110,39 @@ int launch_accumulate(const float *x, const float *w, const int64_t *rows, const
     return C3VQ_OK;
 }
 
-// One thread per codeword; K is a few thousand, so this launch is latency only.
+// One warp per codeword, lanes over columns (coalesced); K is a few thousand, so this launch is latency only.
 // Arithmetic mirrors torch: mul_(decay) rounds, add_(new, alpha) is fma(alpha, new, self).
-__global__ void k_ema(float *__restrict__ cb, float *__restrict__ ei, const float *__restrict__ acc, int k, int d,
-                      int stride, float decay, float alpha, float eps, int scale_normalize)
+__global__ void __launch_bounds__(256)
+k_ema(float *__restrict__ cb, float *__restrict__ ei, const float *__restrict__ acc, int k, int d, int stride,
+      float decay, float alpha, float eps, int scale_normalize)
 {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    const int j = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (j >= k) return;
     const float *a = acc + (size_t)j * stride;
     const float sw = a[d];
-    ei[j] = fmaf(alpha, sw, __fmul_rn(ei[j], decay));               // vq.py:32
-    const float denom = __fadd_rn(sw, eps);                          // vq.py:34
+    if (lane == 0) ei[j] = fmaf(alpha, sw, __fmul_rn(ei[j], decay));   // vq.py:32
+    const float denom = __fadd_rn(sw, eps);                             // vq.py:34
     float *row = cb + (size_t)j * d;
-    for (int c = 0; c < d; c++) {
-        const float nw = __fdiv_rn(a[c], denom);
-        row[c] = fmaf(alpha, nw, __fmul_rn(row[c], decay));
+    float v[2];
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+        const int c = lane + 32 * h;
+        v[h] = 0.f;
+        if (c < d) v[h] = fmaf(alpha, __fdiv_rn(a[c], denom), __fmul_rn(row[c], decay));
     }
-    if (scale_normalize && d >= 6) {                                 // vq.py:76-77
-        const float tr = __fadd_rn(__fadd_rn(row[0], row[3]), row[5]);
-        for (int c = 0; c < d; c++) row[c] = __fdiv_rn(row[c], tr);
+    if (scale_normalize && d >= 6) {                                    // vq.py:76-77
+        const float r0 = __shfl_sync(0xffffffffu, v[0], 0);
+        const float r3 = __shfl_sync(0xffffffffu, v[0], 3);
+        const float r5 = __shfl_sync(0xffffffffu, v[0], 5);
+        const float tr = __fadd_rn(__fadd_rn(r0, r3), r5);
+        v[0] = __fdiv_rn(v[0], tr);
+        v[1] = __fdiv_rn(v[1], tr);
+    }
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+        const int c = lane + 32 * h;
+        if (c < d) row[c] = v[h];
     }
 }
 
@@ -136,7 +150,7 @@ int launch_ema(float *codebook, float *entry_importance, const float *acc, int k
                int scale_normalize, cudaStream_t s)
 {
     if (k == 0) return C3VQ_OK;
-    k_ema<<<(k + 127) / 128, 128, 0, s>>>(codebook, entry_importance, acc, k, d, acc_stride(d), (float)decay,
+    k_ema<<<(k + 7) / 8, 256, 0, s>>>(codebook, entry_importance, acc, k, d, acc_stride(d), (float)decay,
                                           (float)(1.0 - decay), (float)eps, scale_normalize);
     C3VQ_LAUNCH_CHECK("k_ema");
     return C3VQ_OK;

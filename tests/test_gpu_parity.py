@@ -332,7 +332,8 @@ def test_full_size_properties(L, d):
     assert int((idx_tc == 1).sum()) == 0
     # codeword rows map to themselves
     _, self_idx = L.assign(cb, cb, exact=False)
-    assert torch.equal(self_idx[2:].cpu(), torch.arange(2, k))
+    assert torch.equal(cb[self_idx], cb)                      # sampled rows may repeat: the copy with the
+    assert bool((self_idx <= torch.arange(k, device=DEV)).all())   # lowest index wins, never a later one
     # sums: total weight is conserved; decode of the assignment is idempotent under re-assignment
     acc = L.accumulate(x, w, idx_tc, k)
     assert abs(float(acc[:, d].double().sum()) - float(w.double().sum())) < 1e-4 * float(w.double().sum())
