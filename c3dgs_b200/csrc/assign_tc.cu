@@ -9,25 +9,29 @@
 //      x' = x - mu, c' = c - mu (mu = codebook mean; a distance-preserving shift that shrinks the
 //      cancellation error).  Operands are rounded to TF32 by us (cvt.rna), |c'|^2 rides along as 2-3
 //      extra K columns (hi/mid/lo TF32 pieces against a 1.0 in the A operand), so the epilogue is a
-//      pure min: one FMNMX3 per two scores plus one compare per 32.
-//   2. BAND    every code whose score is within band_i of the row minimum is a candidate, where
-//      band_i = 2*E_i + slack bounds the worst-case screening error (TF32 input rounding 2^-11 per
-//      operand, tensor-core accumulation, norm split) plus the reference chain's own rounding; the
-//      fp32 argmin of the reference is therefore always among the candidates.
-//   3. RE-RANK candidates with the reference arithmetic (in-order fma chain, first index wins ties).
-//      Rows whose candidate list overflows, or whose magnitudes break the error model, go to an exact
-//      warp-per-row scan (k_assign_fallback).
+//      pure min: one FMNMX3 per two scores.
+//   2. BAND    every GROUP of 4 consecutive codes whose minimum score is within band_i of the running
+//      row minimum is recorded, where band_i = 2*E_i + slack bounds the worst-case screening error
+//      (TF32 input rounding 2^-11 per operand, tensor-core accumulation, norm split) plus the
+//      reference chain's own rounding; the fp32 argmin of the reference is therefore always inside a
+//      recorded group.
+//   3. RE-RANK all codes of the surviving groups with the reference arithmetic (in-order fma chain,
+//      first index wins ties).  Rows whose group list overflows, or whose magnitudes break the error
+//      model, go to an exact warp-per-row scan (k_assign_fallback).
 //
 // Kernel organisation (persistent, one CTA per SM, 640 threads, warp specialised):
 //   warp 0      bulk-copy (TMA engine, cp.async.bulk) producer: codebook image stages -> smem ring
-//   warp 1      MMA issuer: per stage 2 x KSTEPS tcgen05.mma (M=128, N=256, K=8), commits to mbarriers
-//   warp 2      TMEM allocator (512 columns = two 128x256 fp32 accumulators, one per row tile)
-//   warps 4-11  epilogue: tcgen05.ld 32 columns at a time, running min + candidate list per row
-//               (one thread owns one row for all K codes), then re-rank + outputs + red.global.add.v4
-//   warps 12-19 feature producers: coalesced prefetch of the next 256 rows into registers, centre,
-//               round to TF32, store into the UMMA canonical K-major layout, row norms -> error band
-// While the tensor core fills the accumulator of row tile 0 the epilogue drains row tile 1 and vice
-// versa, so each codebook stage (256 codes) is used for 256 rows: 32 B/cycle/SM of L2 traffic.
+//   warp 1      MMA issuer: per stage 2 x KSTEPS tcgen05.mma (M=128, N=128, K=8), commits to mbarriers
+//   warp 2      TMEM allocator (512 columns = four 128x128 fp32 accumulators: 2 row tiles x 2 ring slots)
+//   warps 4-11  drain: tcgen05.ld 16 columns at a time (double buffered), running min + group list per
+//               row (one thread owns one row for all K codes); at the end of a pass the surviving
+//               groups are pushed into a work queue
+//   warps 12-19 feature producers AND re-rankers: store the prefetched next 256 rows (centred, TF32,
+//               UMMA canonical K-major layout); then, while the tensor core and the drain warps work on
+//               that pass, re-rank the previous pass' queue (4 lanes per group, shared-memory 64-bit
+//               atomicMin per row), write idx/dist, red.global.add.v4 the weighted rows; then prefetch.
+// A pass is 256 rows x all K codes.  Accumulator slot (tile t, step parity b) is refilled by the MMA warp
+// as soon as its 128 drain threads have read it, so MMA, drain and re-rank all overlap.
 #include "common.cuh"
 #include "tc_ptx.cuh"
 
@@ -47,10 +51,12 @@ using namespace ptx;
 
 constexpr int TC_BM = 128;            // rows per UMMA tile
 constexpr int TC_PR = 2 * TC_BM;      // rows per CTA pass ("pair" of tiles)
-constexpr int TC_BN = 256;            // codes per stage / per MMA
-constexpr int TC_LCAP = 16;           // candidate list capacity per row
+constexpr int TC_BN = 128;            // codes per stage / per MMA
+constexpr int TC_LCAP = 8;            // group-list capacity per row
+constexpr int TC_QCAP = 1024;         // re-rank queue capacity per pass (groups of 4 codes)
+constexpr int TC_MAXSTAGES = 6;
 constexpr int TC_THREADS = 640;
-constexpr int TC_EPI_WARP0 = 4;
+constexpr int TC_DRAIN_WARP0 = 4;
 constexpr int TC_PROD_WARP0 = 12;
 constexpr uint32_t TC_LBO_A = TC_BM * 16 + 16;   // skewed by 16 B: conflict-free scattered stores
 constexpr uint32_t TC_LBO_B = TC_BN * 16;
@@ -62,7 +68,7 @@ constexpr int TC_SMEM_LIMIT = 227 * 1024;
 // Workspace header (device memory, zeroed per call).
 struct TcHeader {
     unsigned long long rows;        // stats: rows processed by the tensor-core kernel
-    unsigned long long cands;       // stats: candidates that survived pruning (re-rank evaluations)
+    unsigned long long cands;       // stats: codes re-ranked exactly (4 per surviving group)
     unsigned long long fb_rows;     // stats: rows sent to the exact fallback
     unsigned int fb_count;          // fallback list length
     unsigned int force_fallback;    // set by prep when a finite code breaks the magnitude limit
@@ -82,7 +88,7 @@ struct TcParams {
     int64_t n;
     int d, k, nsteps, nstages;
     int64_t npairs;
-    const float *bimg;      // [k_pad/256][dp/4][256][4] tf32 image of -2c' and the norm pieces
+    const float *bimg;      // [k_pad/128][dp/4][128][4] tf32 image of -2c' and the norm pieces
     const float *cbp;       // [k][dpc] raw codebook, zero padded to a multiple of 4 columns
     int dpc;
     const float *mu;        // [d] centre
@@ -134,7 +140,7 @@ __global__ void k_tc_prep_image(const float *__restrict__ cb, int k, int k_pad, 
     if (j >= k_pad) return;
     const int live = hdr->live;
     const float inv = live > 0 ? 1.f / (float)live : 0.f;
-    float *img = bimg + (size_t)(j >> 8) * (TC_BN * dp) + (size_t)(j & 255) * 4;   // + chunk*1024 + (kk&3)
+    float *img = bimg + (size_t)(j / TC_BN) * (TC_BN * dp) + (size_t)(j % TC_BN) * 4;   // + chunk*BN*4 + (kk&3)
     bool fin = j < k;
     double n2 = 0.0;
     if (j < k) {
@@ -176,52 +182,35 @@ __global__ void k_tc_prep_image(const float *__restrict__ cb, int k, int k_pad, 
 }
 
 // ------------------------------------------------------------------------------------------------
+// Shared-memory plan of k_assign_tc (bytes; every region 16-byte aligned, sB/sA 128-byte aligned)
 template <int DP>
 struct TcSmem {
     static constexpr int KSTEPS = DP / 8;
     static constexpr uint32_t BSTAGE = TC_BN * DP * 4;
     static constexpr uint32_t ATILE = (DP / 4) * TC_LBO_A;
-    static constexpr bool RAW = DP <= 48;                 // raw fp32 rows kept in smem for the re-rank
-    static constexpr int RS_MAX = DP - 1;                 // row stride (floats), odd
-    static constexpr uint32_t RAW_BYTES = RAW ? (uint32_t)TC_PR * RS_MAX * 4 : 0;
-    static constexpr uint32_t LIST_BYTES = TC_PR * TC_LCAP * 4;
-    static constexpr uint32_t FIXED = 2 * ATILE + RAW_BYTES + LIST_BYTES + TC_PR * 4 /*rowinfo*/ + 80 * 4 /*mu*/ +
-                                      256 /*barriers, tmem ptr*/ + 128 /*alignment*/;
+    static constexpr uint32_t LIST_BYTES = 2u * TC_PR * TC_LCAP * 4;       // score words + payload words
+    static constexpr uint32_t QUEUE_BYTES = 2u * TC_QCAP * 4;              // two passes in flight
+    static constexpr uint32_t BEST_BYTES = TC_PR * 8;
+    static constexpr uint32_t FLAG_BYTES = 2u * TC_PR;                     // per-row status, two passes in flight
+    static constexpr uint32_t MISC_BYTES = 80 * 4 /*mu*/ + 64 /*counters, tmem ptr*/ + 40 * 8 /*barriers*/;
+    static constexpr uint32_t FIXED = 2 * ATILE + LIST_BYTES + QUEUE_BYTES + BEST_BYTES + FLAG_BYTES + MISC_BYTES +
+                                      128 /*alignment*/;
     static int stages()
     {
         int s = (TC_SMEM_LIMIT - (int)FIXED) / (int)BSTAGE;
-        return s > 4 ? 4 : s;
+        return s > TC_MAXSTAGES ? TC_MAXSTAGES : s;
     }
     static size_t bytes(int s) { return (size_t)FIXED + (size_t)s * BSTAGE; }
 };
 
-__device__ __forceinline__ float min32(const float (&v)[32])
+// minimum of 4 consecutive scores: FMNMX3 + FMNMX
+__device__ __forceinline__ float min4(uint32_t a, uint32_t b, uint32_t c, uint32_t d)
 {
-    float m0 = fminf(fminf(v[0], v[1]), v[2]);
-    float m1 = fminf(fminf(v[3], v[4]), v[5]);
-    float m2 = fminf(fminf(v[6], v[7]), v[8]);
-    float m3 = fminf(fminf(v[9], v[10]), v[11]);
-    m0 = fminf(fminf(m0, v[12]), v[13]);
-    m1 = fminf(fminf(m1, v[14]), v[15]);
-    m2 = fminf(fminf(m2, v[16]), v[17]);
-    m3 = fminf(fminf(m3, v[18]), v[19]);
-    m0 = fminf(fminf(m0, v[20]), v[21]);
-    m1 = fminf(fminf(m1, v[22]), v[23]);
-    m2 = fminf(fminf(m2, v[24]), v[25]);
-    m3 = fminf(fminf(m3, v[26]), v[27]);
-    m0 = fminf(fminf(m0, v[28]), v[29]);
-    m1 = fminf(fminf(m1, v[30]), v[31]);
-    return fminf(fminf(m0, m1), fminf(m2, m3));
+    return fminf(fminf(fminf(__uint_as_float(a), __uint_as_float(b)), __uint_as_float(c)), __uint_as_float(d));
 }
 
-// score rounded DOWN to 16 significant bits, packed with the 16-bit code id
-__device__ __forceinline__ uint32_t pack_entry(float s, uint32_t code)
-{
-    uint32_t b = __float_as_uint(s);
-    if (b & 0x80000000u) b += 0xFFFFu;   // negative: grow the magnitude
-    return (b & 0xFFFF0000u) | code;
-}
-__device__ __forceinline__ float entry_score(uint32_t e) { return __uint_as_float(e & 0xFFFF0000u); }
+// row status handed from the drain warps to the re-rank warps
+constexpr uint8_t ROW_OK = 0, ROW_FALLBACK = 1, ROW_SKIP = 2;
 
 // DCONST > 0: feature width known at compile time (6, 7, 45, 48); DCONST == 0: runtime width p.d <= DP - 2.
 template <int DP, int DCONST>
@@ -229,47 +218,53 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
 {
     using L = TcSmem<DP>;
     constexpr int KSTEPS = L::KSTEPS;
-    constexpr bool RAW = L::RAW;
     extern __shared__ __align__(128) uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
 
     const int D = DCONST > 0 ? DCONST : p.d;
-    const int RS = D | 1;                                      // raw row stride (odd -> conflict free)
     const int S = p.nstages;
     uint8_t *sB = smem;                                        // S * BSTAGE
     uint8_t *sA = sB + (size_t)S * L::BSTAGE;                  // 2 * ATILE
-    float *sRaw = reinterpret_cast<float *>(sA + 2 * L::ATILE);
-    uint32_t *sList = reinterpret_cast<uint32_t *>(reinterpret_cast<uint8_t *>(sRaw) + L::RAW_BYTES);
-    float *sInfo = reinterpret_cast<float *>(sList + TC_PR * TC_LCAP);
-    float *sMu = sInfo + TC_PR;
-    uint64_t *sBar = reinterpret_cast<uint64_t *>(sMu + 80);
+    uint32_t *sListS = reinterpret_cast<uint32_t *>(sA + 2 * L::ATILE);     // [LCAP][PR] score bits
+    uint32_t *sListP = sListS + TC_PR * TC_LCAP;                            // [LCAP][PR] (chunk16 << 4) | group mask
+    uint32_t *sQueue = sListP + TC_PR * TC_LCAP;                            // [2][QCAP] (row << 16) | group
+    unsigned long long *sBest = reinterpret_cast<unsigned long long *>(sQueue + 2 * TC_QCAP);   // [PR]
+    uint8_t *sFlag = reinterpret_cast<uint8_t *>(sBest + TC_PR);            // [2][PR]
+    float *sMu = reinterpret_cast<float *>(sFlag + 2 * TC_PR);              // [80]
+    uint32_t *sQCount = reinterpret_cast<uint32_t *>(sMu + 80);             // [2]
+    uint32_t *sTmem = sQCount + 2;
+    uint64_t *sBar = reinterpret_cast<uint64_t *>(sQCount + 16);
     // barrier indices
     const uint32_t bar0 = smem_u32(sBar);
     auto B_FULL = [&](int s) { return bar0 + 8u * s; };
-    auto B_EMPTY = [&](int s) { return bar0 + 8u * (4 + s); };
-    const uint32_t A_FULL = bar0 + 8u * 8, A_EMPTY = bar0 + 8u * 9;
-    auto ACC_FULL = [&](int t) { return bar0 + 8u * (10 + t); };
-    auto ACC_EMPTY = [&](int t) { return bar0 + 8u * (12 + t); };
-    const uint32_t RAW_FULL = bar0 + 8u * 14, RAW_FREE = bar0 + 8u * 15;
-    uint32_t *sTmem = reinterpret_cast<uint32_t *>(sBar + 16);
+    auto B_EMPTY = [&](int s) { return bar0 + 8u * (TC_MAXSTAGES + s); };
+    const uint32_t A_FULL = bar0 + 8u * (2 * TC_MAXSTAGES), A_EMPTY = A_FULL + 8u;
+    auto ACC_FULL = [&](int t, int b) { return A_EMPTY + 8u * (1 + t * 2 + b); };
+    auto ACC_EMPTY = [&](int t, int b) { return A_EMPTY + 8u * (5 + t * 2 + b); };
+    auto Q_FULL = [&](int b) { return A_EMPTY + 8u * (9 + b); };
+    auto Q_EMPTY = [&](int b) { return A_EMPTY + 8u * (11 + b); };
 
     const int tid = threadIdx.x;
     const int warp = tid >> 5;
     const int lane = tid & 31;
 
     if (warp == 0 && lane == 0) {
-        for (int s = 0; s < 4; s++) {
+        for (int s = 0; s < TC_MAXSTAGES; s++) {
             mbar_init(B_FULL(s), 1);
             mbar_init(B_EMPTY(s), 1);
         }
         mbar_init(A_FULL, TC_PR);
         mbar_init(A_EMPTY, 1);
-        for (int t = 0; t < 2; t++) {
-            mbar_init(ACC_FULL(t), 1);
-            mbar_init(ACC_EMPTY(t), TC_BM);
+        for (int t = 0; t < 2; t++)
+            for (int b = 0; b < 2; b++) {
+                mbar_init(ACC_FULL(t, b), 1);
+                mbar_init(ACC_EMPTY(t, b), TC_BM);
+            }
+        for (int b = 0; b < 2; b++) {
+            mbar_init(Q_FULL(b), TC_PR);
+            mbar_init(Q_EMPTY(b), TC_PR);
+            sQCount[b] = 0;
         }
-        mbar_init(RAW_FULL, TC_PR);
-        mbar_init(RAW_FREE, TC_PR);
         fence_mbar_init();
     }
     if (warp == 2) {
@@ -322,19 +317,21 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                     PROF(2);   // prof[8+2]: MMA wait B_FULL
                     tc_fence_after();
                     const uint32_t b_addr = smem_u32(sB + (size_t)stage * L::BSTAGE);
+                    const int b = g & 1;                 // accumulator ring slot
+                    const uint32_t use = g >> 1;         // how often this slot has been used before
 #pragma unroll
                     for (int t = 0; t < 2; t++) {
                         PROF(0);
-                        mbar_wait(ACC_EMPTY(t), (g & 1) ^ 1);
+                        mbar_wait(ACC_EMPTY(t, b), (use & 1) ^ 1);
                         PROF(3);   // prof[8+3]: MMA wait ACC_EMPTY
                         tc_fence_after();
 #pragma unroll
                         for (int ks = 0; ks < KSTEPS; ks++) {
                             const uint64_t ad = smem_desc(a_addr + t * L::ATILE + ks * 2 * TC_LBO_A, TC_LBO_A, TC_SBO);
                             const uint64_t bd = smem_desc(b_addr + ks * 2 * TC_LBO_B, TC_LBO_B, TC_SBO);
-                            umma_tf32(tmem_base + t * TC_BN, ad, bd, IDESC, ks > 0 ? 1u : 0u);
+                            umma_tf32(tmem_base + (t * 2 + b) * TC_BN, ad, bd, IDESC, ks > 0 ? 1u : 0u);
                         }
-                        umma_commit(ACC_FULL(t));
+                        umma_commit(ACC_FULL(t, b));
                     }
                     umma_commit(B_EMPTY(stage));
                 }
@@ -344,7 +341,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             PROF_FLUSH(8, true);
         }
     } else if (warp >= TC_PROD_WARP0) {
-        // ===================== feature producers (256 threads) =====================
+        // ===================== feature producers + re-rankers (256 threads) =====================
         const int ptid = tid - TC_PROD_WARP0 * 32;
         const int NC = DP - D < 3 ? DP - D : 3;
         // constant padding columns of both A tiles: 1.0 against the norm pieces, 0 elsewhere
@@ -391,62 +388,159 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             koff[h] = (kk >> 2) * TC_LBO_A + (kk & 3) * 4;
         }
         uint8_t *a_base = sA + (pw >> 2) * L::ATILE + (pw & 3) * 4 * 128;   // row pw*32 of the pass
-        uint32_t pi = 0;
-        PROF_DECL;
-        // software pipeline with ONE prefetch call site: iteration -1 only prefetches the first pass
-        for (int64_t pair = (int64_t)blockIdx.x - gridDim.x;; pair += gridDim.x) {
-            if (pair >= 0) {
-                PROF(0);   // prof[16+0]: producer prefetch issue
-                mbar_wait_backoff(A_EMPTY, (pi & 1) ^ 1);  // previous pass' MMAs no longer read A
-                PROF(1);   // prof[16+1]: producer wait A_EMPTY
+        const bool need_dist = p.out_dist != nullptr;
+        unsigned long long st_rows = 0, st_cands = 0, st_fb = 0;
+
+        // ---- re-rank of one finished pass: queue -> exact distances -> per-row minimum -> outputs ----
+        auto rerank = [&](int64_t pair, uint32_t rp) {
+            const int qb = rp & 1;
+            mbar_wait_backoff(Q_FULL(qb), (rp >> 1) & 1);
+            sBest[ptid] = ((unsigned long long)__float_as_uint(FLT_MAX)) << 32;      // (FLT_MAX, code 0)
+            named_bar_sync(1, TC_PR);
+            const uint32_t nq = min(sQCount[qb], (uint32_t)TC_QCAP);
+            const uint32_t *queue = sQueue + qb * TC_QCAP;
+            const uint32_t gmask = 0xFu << (lane & ~3);
+            for (uint32_t u = ptid >> 2; u < nq; u += TC_PR / 4) {
+                const uint32_t item = queue[u];
+                const int lr = item >> 16;
+                const int code = (int)(item & 0xFFFFu) * 4 + (lane & 3);
+                const int64_t gi = pair * TC_PR + lr;
+                const int64_t src = p.rows ? p.rows[gi] : gi;
+                const float *xg = p.x + src * D;
+                unsigned long long key = ~0ull;
+                if (code < p.k) {
+                    const float4 *cp = reinterpret_cast<const float4 *>(p.cbp + (size_t)code * p.dpc);
+                    float a = 0.f;
+                    if (DCONST > 0) {
 #pragma unroll
-                for (int r = 0; r < 32; r++) {
-#pragma unroll
-                    for (int h = 0; h < NH; h++) {
-                        if (lane + 32 * h < D)
-                            *reinterpret_cast<uint32_t *>(a_base + (r >> 3) * 128 + (r & 7) * 16 + koff[h]) =
-                                to_tf32(xr[r * NH + h] - mu_l[h]);
+                        for (int c4 = 0; c4 < (DCONST + 3) / 4; c4++) {
+                            const float4 cv = __ldg(cp + c4);
+                            float df;
+                            if (4 * c4 + 0 < D) { df = __ldg(xg + 4 * c4 + 0) - cv.x; a = fmaf(df, df, a); }
+                            if (4 * c4 + 1 < D) { df = __ldg(xg + 4 * c4 + 1) - cv.y; a = fmaf(df, df, a); }
+                            if (4 * c4 + 2 < D) { df = __ldg(xg + 4 * c4 + 2) - cv.z; a = fmaf(df, df, a); }
+                            if (4 * c4 + 3 < D) { df = __ldg(xg + 4 * c4 + 3) - cv.w; a = fmaf(df, df, a); }
+                        }
+                    } else {
+                        for (int c4 = 0; c4 < p.dpc / 4; c4++) {
+                            const float4 cv = __ldg(cp + c4);
+                            float df;
+                            if (4 * c4 + 0 < D) { df = __ldg(xg + 4 * c4 + 0) - cv.x; a = fmaf(df, df, a); }
+                            if (4 * c4 + 1 < D) { df = __ldg(xg + 4 * c4 + 1) - cv.y; a = fmaf(df, df, a); }
+                            if (4 * c4 + 2 < D) { df = __ldg(xg + 4 * c4 + 2) - cv.z; a = fmaf(df, df, a); }
+                            if (4 * c4 + 3 < D) { df = __ldg(xg + 4 * c4 + 3) - cv.w; a = fmaf(df, df, a); }
+                        }
                     }
+                    // distances are sums of squares from +0: non-negative or NaN; as unsigned bit patterns
+                    // smaller distance <=> smaller key, NaN/inf sort above FLT_MAX, ties -> lower code
+                    key = ((unsigned long long)__float_as_uint(a) << 32) | (unsigned int)code;
                 }
-                fence_proxy_async_smem();
-                mbar_arrive(A_FULL);
-                PROF(2);   // prof[16+2]: producer convert + store A (includes waiting for the prefetched loads)
-                if (RAW) {
-                    mbar_wait_backoff(RAW_FREE, (pi & 1) ^ 1);   // epilogue finished re-ranking the previous pass
-                    PROF(3);   // prof[16+3]: producer wait RAW_FREE
-                    float *rp = sRaw + (pw * 32) * RS + lane;
-#pragma unroll
-                    for (int r = 0; r < 32; r++) {
-#pragma unroll
-                        for (int h = 0; h < NH; h++)
-                            if (lane + 32 * h < D) rp[r * RS + 32 * h] = xr[r * NH + h];
-                    }
-                    mbar_arrive(RAW_FULL);
-                    PROF(4);   // prof[16+4]: producer raw store
-                }
-                pi++;
+                unsigned long long o = __shfl_xor_sync(gmask, key, 1);
+                key = o < key ? o : key;
+                o = __shfl_xor_sync(gmask, key, 2);
+                key = o < key ? o : key;
+                if ((lane & 3) == 0) atomicMin(&sBest[lr], key);
             }
-            if (pair + gridDim.x >= p.npairs) break;
-            prefetch(pair + gridDim.x);
+            named_bar_sync(1, TC_PR);
+            st_cands += 4ull * nq;      // counted once per thread, divided out below
+            // ---- outputs: two rows per warp step (half warp each), lanes over 16-byte accumulator chunks ----
+            const int half = lane >> 4, hl = lane & 15;
+            const int nchunk = p.acc_stride >> 2;
+#pragma unroll 1
+            for (int rr = 0; rr < 32; rr += 2) {
+                const int lr = pw * 32 + rr + half;
+                const uint8_t status = sFlag[qb * TC_PR + lr];
+                const int64_t gi = pair * TC_PR + lr;
+                if (status == ROW_OK) {
+                    const unsigned long long best = sBest[lr];
+                    const int bj = (int)(best & 0xFFFFFFFFu);
+                    const int64_t src = p.rows ? p.rows[gi] : gi;
+                    if (hl == 0) {
+                        st_rows++;
+                        if (p.out_idx) p.out_idx[gi] = bj;
+                        if (need_dist) p.out_dist[gi] = __uint_as_float((unsigned int)(best >> 32));
+                    }
+                    if (p.acc) {
+                        const float wv = p.w ? __ldg(p.w + src) : 1.f;
+                        const float *xg = p.x + src * D;
+                        float *ap = p.acc + (size_t)bj * p.acc_stride;
+                        for (int ch = hl; ch < nchunk; ch += 16) {
+                            float e4[4];
+#pragma unroll
+                            for (int i = 0; i < 4; i++) {
+                                const int kk = 4 * ch + i;
+                                e4[i] = kk < D ? __fmul_rn(__ldg(xg + kk), wv) : (kk == D ? wv : 0.f);
+                            }
+                            red_add_v4(ap + 4 * ch, e4[0], e4[1], e4[2], e4[3]);
+                        }
+                    }
+                } else if (status == ROW_FALLBACK && hl == 0) {
+                    st_rows++;
+                    st_fb++;
+                    const unsigned int pos = atomicAdd(&p.hdr->fb_count, 1u);
+                    p.fb_list[pos] = (unsigned int)gi;
+                }
+            }
+            __syncwarp();
+            if (ptid == 0) sQCount[qb] = 0;       // every thread has read nq (barrier above)
+            mbar_arrive(Q_EMPTY(qb));
+        };
+
+        uint32_t pi = 0;
+        int64_t prev_pair = -1;
+        PROF_DECL;
+        if ((int64_t)blockIdx.x < p.npairs) prefetch(blockIdx.x);
+        for (int64_t pair = blockIdx.x; pair < p.npairs; pair += gridDim.x, pi++) {
+            PROF(0);
+            mbar_wait_backoff(A_EMPTY, (pi & 1) ^ 1);  // previous pass' MMAs no longer read A
+            PROF(1);   // prof[16+1]: producer wait A_EMPTY
+#pragma unroll
+            for (int r = 0; r < 32; r++) {
+#pragma unroll
+                for (int h = 0; h < NH; h++) {
+                    if (lane + 32 * h < D)
+                        *reinterpret_cast<uint32_t *>(a_base + (r >> 3) * 128 + (r & 7) * 16 + koff[h]) =
+                            to_tf32(xr[r * NH + h] - mu_l[h]);
+                }
+            }
+            fence_proxy_async_smem();
+            mbar_arrive(A_FULL);
+            PROF(2);   // prof[16+2]: producer convert + store A (includes waiting for the prefetched loads)
+            if (prev_pair >= 0) rerank(prev_pair, pi - 1);
+            PROF(3);   // prof[16+3]: re-rank + outputs of the previous pass (includes waiting for its queue)
+            prev_pair = pair;
+            if (pair + gridDim.x < p.npairs) prefetch(pair + gridDim.x);
+            PROF(4);   // prof[16+4]: prefetch issue
         }
+        if (prev_pair >= 0) rerank(prev_pair, pi - 1);
+        PROF(5);       // prof[16+5]: last re-rank
         PROF_FLUSH(16, lane == 0 && pw == 0);
-    } else if (warp >= TC_EPI_WARP0) {
-        // ===================== epilogue: scan, candidate lists, re-rank, outputs =====================
-        const int lr = tid - TC_EPI_WARP0 * 32;        // local row 0..255
+        // stats: one atomic per warp (st_cands was counted by every thread of the 256)
+        for (int o = 16; o > 0; o >>= 1) {
+            st_rows += __shfl_xor_sync(0xffffffffu, st_rows, o);
+            st_fb += __shfl_xor_sync(0xffffffffu, st_fb, o);
+        }
+        if (lane == 0) {
+            atomicAdd(&p.hdr->rows, st_rows);
+            atomicAdd(&p.hdr->fb_rows, st_fb);
+            if (pw == 0) atomicAdd(&p.hdr->cands, st_cands);
+        }
+    } else if (warp >= TC_DRAIN_WARP0) {
+        // ===================== drain: TMEM scan, running minimum, group lists, work queue =====================
+        const int lr = tid - TC_DRAIN_WARP0 * 32;      // local row 0..255
         const int t = lr >> 7;
         const int q = warp & 3;                         // TMEM lane quarter this warp may access
-        const uint32_t tsrc = tmem_base + ((uint32_t)(q * 32) << 16) + t * TC_BN;
-        const bool need_dist = p.out_dist != nullptr;
+        const uint32_t tsrc = tmem_base + ((uint32_t)(q * 32) << 16) + t * 2 * TC_BN;
         const float cmax = __int_as_float(p.hdr->cmax_bits);
         const bool force_fb = p.hdr->force_fallback != 0;
-        unsigned long long st_rows = 0, st_cands = 0, st_fb = 0;
+        uint32_t *listS = sListS + lr, *listP = sListP + lr;
         uint32_t g = 0, pi = 0;
         PROF_DECL;
         for (int64_t pair = blockIdx.x; pair < p.npairs; pair += gridDim.x, pi++) {
             const int64_t gi = pair * TC_PR + lr;
             PROF(0);
             mbar_wait(A_FULL, pi & 1);
-            PROF(1);       // prof[24+1]: epilogue wait A_FULL
+            PROF(1);       // prof[24+1]: drain wait A_FULL
             float band;
             {
                 // row norm of the rounded, centred row (read back from the A tile) -> error band
@@ -461,7 +555,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                     if (4 * c4 + 2 < D) X = fmaf(xv.z, xv.z, X);
                     if (4 * c4 + 3 < D) X = fmaf(xv.w, xv.w, X);
                 }
-                // E bounds |score + X - true distance| for every code (DESIGN.md §4)
+                // E bounds |score + X - true distance| for every code (DESIGN.md §4.1)
                 const float C1 = 1.002f * 0.001953125f + 7.62939453125e-6f;   // 2^-9 * 1.002 + 2^-17
                 const float C2 = 3.814697265625e-6f + 4.76837158203125e-7f;   // 2^-18 + 2^-21
                 const float E = C1 * sqrtf(X) * cmax + C2 * cmax * cmax;
@@ -478,136 +572,117 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             float thr = (band >= 0.f) ? __int_as_float(0x7f800000) : __int_as_float(0xff800000);  // +inf / -inf
             int cnt = 0;
             bool ovf = false;
-            PROF(2);       // prof[24+2]: epilogue band
-            for (int s = 0; s < nsteps; s++, g++) {
-                PROF(4);   // prof[24+4]: epilogue drain (LDTM + min + lists)
-                mbar_wait(ACC_FULL(t), g & 1);
-                PROF(3);   // prof[24+3]: epilogue wait ACC_FULL
-                tc_fence_after();
-#pragma unroll 1
-                for (int c = 0; c < TC_BN / 32; c++) {
-                    float v[32];
-                    tmem_ld32(tsrc + c * 32, v);
-                    if (c == TC_BN / 32 - 1) {          // accumulator fully read: hand it back to the MMA warp
-                        tc_fence_before();
-                        mbar_arrive(ACC_EMPTY(t));
+            PROF(2);       // prof[24+2]: drain band
+
+            // one 16-column chunk: four group minima, then (rarely per row, often per warp) the list append
+            auto process = [&](const uint32_t (&v)[16], int code0) {
+                const float g0 = min4(v[0], v[1], v[2], v[3]);
+                const float g1 = min4(v[4], v[5], v[6], v[7]);
+                const float g2 = min4(v[8], v[9], v[10], v[11]);
+                const float g3 = min4(v[12], v[13], v[14], v[15]);
+                const float cm = fminf(fminf(fminf(g0, g1), g2), g3);
+                if (cm <= thr && cm < 0.5f * TC_BIG) {   // dead / padding codes (score 2^126) never enter
+                    if (cm < m) {
+                        m = cm;
+                        thr = m + p.gamma2 * fabsf(m) + band;
                     }
-                    const int code0 = s * TC_BN + c * 32;
+                    const uint32_t gm = (g0 <= thr ? 1u : 0u) | (g1 <= thr ? 2u : 0u) | (g2 <= thr ? 4u : 0u) |
+                                        (g3 <= thr ? 8u : 0u);
+                    if (cnt == TC_LCAP) {               // full: drop entries the tighter threshold excludes
+                        int wpos = 0;
+                        for (int e = 0; e < TC_LCAP; e++) {
+                            const uint32_t es = listS[e * TC_PR], ep = listP[e * TC_PR];
+                            if (__uint_as_float(es) <= thr) {
+                                listS[wpos * TC_PR] = es;
+                                listP[wpos * TC_PR] = ep;
+                                wpos++;
+                            }
+                        }
+                        cnt = wpos;
+                    }
+                    if (cnt < TC_LCAP) {
+                        listS[cnt * TC_PR] = __float_as_uint(cm);
+                        listP[cnt * TC_PR] = ((uint32_t)(code0 >> 4) << 4) | gm;
+                        cnt++;
+                    } else {
+                        ovf = true;
+                    }
+                }
+            };
+
+            for (int s = 0; s < nsteps; s++, g++) {
+                const int b = g & 1;
+                const uint32_t use = g >> 1;
+                PROF(4);   // prof[24+4]: drain (LDTM + min + lists)
+                mbar_wait(ACC_FULL(t, b), use & 1);
+                PROF(3);   // prof[24+3]: drain wait ACC_FULL
+                tc_fence_after();
+                const uint32_t ta = tsrc + b * TC_BN;
+                const int code_s = s * TC_BN;
+                uint32_t va[16], vb[16];
+                tmem_ld16_async(ta, va);
+#pragma unroll
+                for (int c = 0; c < TC_BN / 32; c++) {
+                    tmem_wait_ld16(va);
+                    tmem_ld16_async(ta + c * 32 + 16, vb);
                     if (p.dbg_scores && gi < p.n) {
 #pragma unroll
-                        for (int j = 0; j < 32; j++)
-                            if (code0 + j < p.k) p.dbg_scores[gi * p.k + code0 + j] = v[j];
+                        for (int j = 0; j < 16; j++)
+                            if (code_s + c * 32 + j < p.k)
+                                p.dbg_scores[gi * p.k + code_s + c * 32 + j] = __uint_as_float(va[j]);
                     }
-                    const float cm = min32(v);
-                    if (cm <= thr && cm < 0.5f * TC_BIG) {   // dead / padding codes (score 2^126) never lower the minimum
-                        if (cm < m) {
-                            m = cm;
-                            thr = m + p.gamma2 * fabsf(m) + band;
-                        }
-                        uint32_t mask = 0;
+                    process(va, code_s + c * 32);
+                    tmem_wait_ld16(vb);
+                    if (c + 1 < TC_BN / 32) {
+                        tmem_ld16_async(ta + (c + 1) * 32, va);
+                    } else {                            // accumulator slot fully read: hand it back to the MMA warp
+                        tc_fence_before();
+                        mbar_arrive(ACC_EMPTY(t, b));
+                    }
+                    if (p.dbg_scores && gi < p.n) {
 #pragma unroll
-                        for (int j = 0; j < 32; j++) mask |= (v[j] <= thr) ? (1u << j) : 0u;
-                        // every entry of this chunk carries the chunk minimum as its (lower-bound) score: enough
-                        // to prune it later, and no dynamic indexing of the register tile is needed
-                        const uint32_t sc = pack_entry(cm, 0u);
-                        while (mask) {
-                            const int j = __ffs(mask) - 1;
-                            mask &= mask - 1;
-                            if (cnt == TC_LCAP) {           // full: drop entries the tighter threshold excludes
-                                int wpos = 0;
-                                for (int e = 0; e < TC_LCAP; e++) {
-                                    const uint32_t ent = sList[e * TC_PR + lr];
-                                    if (entry_score(ent) <= thr) sList[(wpos++) * TC_PR + lr] = ent;
-                                }
-                                cnt = wpos;
-                            }
-                            if (cnt < TC_LCAP) {
-                                sList[cnt * TC_PR + lr] = sc | (uint32_t)(code0 + j);
-                                cnt++;
-                            } else {
-                                ovf = true;
-                            }
-                        }
+                        for (int j = 0; j < 16; j++)
+                            if (code_s + c * 32 + 16 + j < p.k)
+                                p.dbg_scores[gi * p.k + code_s + c * 32 + 16 + j] = __uint_as_float(vb[j]);
                     }
+                    process(vb, code_s + c * 32 + 16);
                 }
             }
-            // ---- re-rank with the reference arithmetic ----
             PROF(4);
-            if (RAW) mbar_wait(RAW_FULL, pi & 1);
-            PROF(5);       // prof[24+5]: epilogue wait RAW_FULL
-            if (gi < p.n) {
-                st_rows++;
-                const int64_t src = p.rows ? p.rows[gi] : gi;
-                const float *xg = p.x + src * D;
-                auto getx = [&](int kk) -> float { return RAW ? sRaw[lr * RS + kk] : xg[kk]; };
-                const bool fallback = !(band >= 0.f) || ovf;
-                if (!fallback) {
-                    const float thrF = m + p.gamma2 * fabsf(m) + band;
-                    int ns = 0, sole = 0;
-                    for (int e = 0; e < cnt; e++) {
-                        const uint32_t ent = sList[e * TC_PR + lr];
-                        const int j = ent & 0xFFFF;
-                        if (entry_score(ent) <= thrF && j < p.k) { ns++; sole = j; }
-                    }
-                    st_cands += ns;
-                    float best = FLT_MAX;
-                    int bj = 0;
-                    if (ns == 1 && !need_dist) {
-                        bj = sole;
-                    } else {
-                        for (int e = 0; e < cnt; e++) {
-                            const uint32_t ent = sList[e * TC_PR + lr];
-                            const int j = ent & 0xFFFF;
-                            if (!(entry_score(ent) <= thrF && j < p.k)) continue;
-                            const float4 *cp = reinterpret_cast<const float4 *>(p.cbp + (size_t)j * p.dpc);
-                            float a = 0.f;
-                            for (int c4 = 0; c4 < p.dpc / 4; c4++) {
-                                const float4 cv = __ldg(cp + c4);
-                                float df;
-                                if (4 * c4 + 0 < D) { df = getx(4 * c4 + 0) - cv.x; a = fmaf(df, df, a); }
-                                if (4 * c4 + 1 < D) { df = getx(4 * c4 + 1) - cv.y; a = fmaf(df, df, a); }
-                                if (4 * c4 + 2 < D) { df = getx(4 * c4 + 2) - cv.z; a = fmaf(df, df, a); }
-                                if (4 * c4 + 3 < D) { df = getx(4 * c4 + 3) - cv.w; a = fmaf(df, df, a); }
-                            }
-                            if (a < best || (a == best && j < bj)) { best = a; bj = j; }
+            // ---- hand the surviving groups of this pass to the re-rank warps ----
+            const int qb = pi & 1;
+            mbar_wait(Q_EMPTY(qb), ((pi >> 1) & 1) ^ 1);     // the pass that used this queue slot is finished
+            PROF(5);       // prof[24+5]: drain wait Q_EMPTY
+            uint8_t status = ROW_OK;
+            if (gi >= p.n) {
+                status = ROW_SKIP;
+            } else if (!(band >= 0.f) || ovf) {
+                status = ROW_FALLBACK;
+            } else {
+                uint32_t *queue = sQueue + qb * TC_QCAP;
+                for (int e = 0; e < cnt; e++) {
+                    if (!(__uint_as_float(listS[e * TC_PR]) <= thr)) continue;
+                    const uint32_t ep = listP[e * TC_PR];
+                    uint32_t gm = ep & 0xFu;
+                    const uint32_t grp0 = (ep >> 4) * 4;         // first group (code / 4) of the chunk
+                    while (gm) {
+                        const int bit = __ffs(gm) - 1;
+                        gm &= gm - 1;
+                        if ((int)(grp0 + bit) * 4 < p.k) {
+                            const uint32_t pos = atomicAdd(&sQCount[qb], 1u);
+                            if (pos < (uint32_t)TC_QCAP)
+                                queue[pos] = ((uint32_t)lr << 16) | (grp0 + bit);
+                            else
+                                status = ROW_FALLBACK;
                         }
                     }
-                    if (p.out_idx) p.out_idx[gi] = bj;
-                    if (need_dist) p.out_dist[gi] = best;
-                    if (p.acc) {
-                        const float wv = p.w ? p.w[src] : 1.f;
-                        float *ap = p.acc + (size_t)bj * p.acc_stride;
-                        for (int c4 = 0; c4 < p.acc_stride / 4; c4++) {
-                            float e4[4];
-#pragma unroll
-                            for (int i = 0; i < 4; i++) {
-                                const int kk = 4 * c4 + i;
-                                e4[i] = kk < D ? __fmul_rn(getx(kk), wv) : (kk == D ? wv : 0.f);
-                            }
-                            red_add_v4(ap + 4 * c4, e4[0], e4[1], e4[2], e4[3]);
-                        }
-                    }
-                } else {
-                    st_fb++;
-                    const unsigned int pos = atomicAdd(&p.hdr->fb_count, 1u);
-                    p.fb_list[pos] = (unsigned int)gi;
                 }
             }
-            if (RAW) mbar_arrive(RAW_FREE);
-            PROF(6);       // prof[24+6]: epilogue re-rank + outputs + scatter
+            sFlag[qb * TC_PR + lr] = status;
+            mbar_arrive(Q_FULL(qb));
+            PROF(6);       // prof[24+6]: drain queue push
         }
-        PROF_FLUSH(24, tid == TC_EPI_WARP0 * 32);
-        // stats: one atomic per warp
-        for (int o = 16; o > 0; o >>= 1) {
-            st_rows += __shfl_xor_sync(0xffffffffu, st_rows, o);
-            st_cands += __shfl_xor_sync(0xffffffffu, st_cands, o);
-            st_fb += __shfl_xor_sync(0xffffffffu, st_fb, o);
-        }
-        if (lane == 0) {
-            atomicAdd(&p.hdr->rows, st_rows);
-            atomicAdd(&p.hdr->cands, st_cands);
-            atomicAdd(&p.hdr->fb_rows, st_fb);
-        }
+        PROF_FLUSH(24, tid == TC_DRAIN_WARP0 * 32);
     }
 
     tc_fence_before();

@@ -20,10 +20,10 @@ ei = torch.zeros(4096, device=dev)
 acc = torch.zeros(4096, _lib.acc_stride(d), device=dev)
 names = {0: "tma other", 1: "tma wait B_EMPTY",
          8: "mma issue/other", 9: "mma wait A_FULL", 10: "mma wait B_FULL", 11: "mma wait ACC_EMPTY",
-         16: "prod prefetch issue", 17: "prod wait A_EMPTY", 18: "prod convert+store A", 19: "prod wait RAW_FREE",
-         20: "prod raw store",
-         24: "epi other", 25: "epi wait A_FULL", 26: "epi band", 27: "epi wait ACC_FULL", 28: "epi drain",
-         29: "epi wait RAW_FULL", 30: "epi rerank+scatter"}
+         16: "prod other", 17: "prod wait A_EMPTY", 18: "prod convert+store A", 19: "prod rerank(prev pass)",
+         20: "prod prefetch issue", 21: "prod last rerank",
+         24: "drain other", 25: "drain wait A_FULL", 26: "drain band", 27: "drain wait ACC_FULL",
+         28: "drain LDTM+min+lists", 29: "drain wait Q_EMPTY", 30: "drain queue push"}
 for it in range(3):
     acc.zero_()
     a = torch.cuda.Event(enable_timing=True); b = torch.cuda.Event(enable_timing=True)
