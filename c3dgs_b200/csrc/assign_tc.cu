@@ -19,14 +19,15 @@
 //      first index wins ties).  Rows whose group list overflows, or whose magnitudes break the error
 //      model, go to an exact warp-per-row scan (k_assign_fallback).
 //
-// Kernel organisation (persistent, one CTA per SM, 640 threads, warp specialised):
+// Kernel organisation (persistent, one CTA per SM, 896 threads, warp specialised, setmaxnreg per role):
 //   warp 0      bulk-copy (TMA engine, cp.async.bulk) producer: codebook image stages -> smem ring
 //   warp 1      MMA issuer: per stage 2 x KSTEPS tcgen05.mma (M=128, N=128, K=8), commits to mbarriers
 //   warp 2      TMEM allocator (512 columns = four 128x128 fp32 accumulators: 2 row tiles x 2 ring slots)
-//   warps 4-11  drain: tcgen05.ld 16 columns at a time (double buffered), running min + group list per
-//               row (one thread owns one row for all K codes); at the end of a pass the surviving
-//               groups are pushed into a work queue
-//   warps 12-19 feature producers AND re-rankers: store the prefetched next 256 rows (centred, TF32,
+//   warps 4-19  drain: tcgen05.ld 16 columns at a time, running min + group list per row; two threads per
+//               row (one per 64-column half of every accumulator slot: a warp reads TMEM at only ~19 B/cycle,
+//               measured, so 16 warps are needed to keep up with the tensor core); at the end of a pass the
+//               halves exchange minima and push the surviving groups into a work queue
+//   warps 20-27 feature producers AND re-rankers: store the prefetched next 256 rows (centred, TF32,
 //               UMMA canonical K-major layout); then, while the tensor core and the drain warps work on
 //               that pass, re-rank the previous pass' queue (4 lanes per group, shared-memory 64-bit
 //               atomicMin per row), write idx/dist, red.global.add.v4 the weighted rows; then prefetch.
@@ -55,9 +56,13 @@ constexpr int TC_BN = 128;            // codes per stage / per MMA
 constexpr int TC_LCAP = 8;            // group-list capacity per row
 constexpr int TC_QCAP = 1024;         // re-rank queue capacity per pass (groups of 4 codes)
 constexpr int TC_MAXSTAGES = 6;
-constexpr int TC_THREADS = 640;
 constexpr int TC_DRAIN_WARP0 = 4;
-constexpr int TC_PROD_WARP0 = 12;
+constexpr int TC_NDRAIN = 16;          // drain warps: (tile t, lane quarter q, column half h)
+constexpr int TC_DT = TC_NDRAIN * 32; // drain threads
+constexpr int TC_PROD_WARP0 = TC_DRAIN_WARP0 + TC_NDRAIN;
+constexpr int TC_THREADS = (TC_PROD_WARP0 + 8) * 32;   // 896
+// register budgets per role (setmaxnreg): 896 threads start at 72; 4*32*(72-40) + 16*32*(72-64) = 8192 = 8*32*(104-72)
+constexpr int TC_REGS_MISC = 40, TC_REGS_DRAIN = 64, TC_REGS_PROD = 104;
 constexpr uint32_t TC_LBO_A = TC_BM * 16 + 16;   // skewed by 16 B: conflict-free scattered stores
 constexpr uint32_t TC_LBO_B = TC_BN * 16;
 constexpr uint32_t TC_SBO = 128;
@@ -187,13 +192,19 @@ template <int DP>
 struct TcSmem {
     static constexpr int KSTEPS = DP / 8;
     static constexpr uint32_t BSTAGE = TC_BN * DP * 4;
-    static constexpr uint32_t ATILE = (DP / 4) * TC_LBO_A;
-    static constexpr uint32_t LIST_BYTES = 2u * TC_PR * TC_LCAP * 4;       // score words + payload words
+    static constexpr int XS = DP + 1;                                      // transposition scratch row stride (odd)
+    static constexpr uint32_t XS_BYTES = (uint32_t)TC_PR * XS * 4;
+    static constexpr uint32_t BAND_BYTES = 2u * TC_PR * 4;                 // per-row error band, two passes in flight
+    // TMEM columns: NSLOT accumulator slots of 128, then the A operand of both row tiles (DP columns each)
+    static constexpr int NSLOT = (512 - 2 * DP) / TC_BN >= 3 ? 3 : 2;
+    static constexpr uint32_t ACOL = NSLOT * TC_BN;
+    static constexpr uint32_t LIST_BYTES = 2u * TC_DT * TC_LCAP * 4;       // score words + payload words
     static constexpr uint32_t QUEUE_BYTES = 2u * TC_QCAP * 4;              // two passes in flight
     static constexpr uint32_t BEST_BYTES = TC_PR * 8;
-    static constexpr uint32_t FLAG_BYTES = 2u * TC_PR;                     // per-row status, two passes in flight
+    static constexpr uint32_t FLAG_BYTES = 4u * TC_PR;                     // per-row, per-half status, two passes in flight
+    static constexpr uint32_t XCHG_BYTES = 4u * TC_PR * 4;                 // running minima exchanged between column halves
     static constexpr uint32_t MISC_BYTES = 80 * 4 /*mu*/ + 64 /*counters, tmem ptr*/ + 40 * 8 /*barriers*/;
-    static constexpr uint32_t FIXED = 2 * ATILE + LIST_BYTES + QUEUE_BYTES + BEST_BYTES + FLAG_BYTES + MISC_BYTES +
+    static constexpr uint32_t FIXED = XS_BYTES + BAND_BYTES + LIST_BYTES + QUEUE_BYTES + BEST_BYTES + FLAG_BYTES + XCHG_BYTES + MISC_BYTES +
                                       128 /*alignment*/;
     static int stages()
     {
@@ -224,13 +235,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
     const int D = DCONST > 0 ? DCONST : p.d;
     const int S = p.nstages;
     uint8_t *sB = smem;                                        // S * BSTAGE
-    uint8_t *sA = sB + (size_t)S * L::BSTAGE;                  // 2 * ATILE
-    uint32_t *sListS = reinterpret_cast<uint32_t *>(sA + 2 * L::ATILE);     // [LCAP][PR] score bits
-    uint32_t *sListP = sListS + TC_PR * TC_LCAP;                            // [LCAP][PR] (chunk16 << 4) | group mask
-    uint32_t *sQueue = sListP + TC_PR * TC_LCAP;                            // [2][QCAP] (row << 16) | group
+    float *sX = reinterpret_cast<float *>(sB + (size_t)S * L::BSTAGE);     // [PR][XS] centred tf32 rows (transposition)
+    float *sBand = sX + TC_PR * L::XS;                                      // [2][PR]
+    uint32_t *sListS = reinterpret_cast<uint32_t *>(sBand + 2 * TC_PR);     // [LCAP][DT] score bits
+    uint32_t *sListP = sListS + TC_DT * TC_LCAP;                            // [LCAP][DT] (chunk16 << 4) | group mask
+    uint32_t *sQueue = sListP + TC_DT * TC_LCAP;                            // [2][QCAP] (row << 16) | group
     unsigned long long *sBest = reinterpret_cast<unsigned long long *>(sQueue + 2 * TC_QCAP);   // [PR]
-    uint8_t *sFlag = reinterpret_cast<uint8_t *>(sBest + TC_PR);            // [2][PR]
-    float *sMu = reinterpret_cast<float *>(sFlag + 2 * TC_PR);              // [80]
+    uint8_t *sFlag = reinterpret_cast<uint8_t *>(sBest + TC_PR);            // [2 passes][2 halves][PR]
+    float *sXchg = reinterpret_cast<float *>(sFlag + 4 * TC_PR);            // [2 passes][2 halves][PR]
+    float *sMu = sXchg + 4 * TC_PR;                                         // [80]
     uint32_t *sQCount = reinterpret_cast<uint32_t *>(sMu + 80);             // [2]
     uint32_t *sTmem = sQCount + 2;
     uint64_t *sBar = reinterpret_cast<uint64_t *>(sQCount + 16);
@@ -239,8 +252,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
     auto B_FULL = [&](int s) { return bar0 + 8u * s; };
     auto B_EMPTY = [&](int s) { return bar0 + 8u * (TC_MAXSTAGES + s); };
     const uint32_t A_FULL = bar0 + 8u * (2 * TC_MAXSTAGES), A_EMPTY = A_FULL + 8u;
-    auto ACC_FULL = [&](int t, int b) { return A_EMPTY + 8u * (1 + t * 2 + b); };
-    auto ACC_EMPTY = [&](int t, int b) { return A_EMPTY + 8u * (5 + t * 2 + b); };
+    auto ACC_FULL = [&](int sl) { return A_EMPTY + 8u * (1 + sl); };
+    auto ACC_EMPTY = [&](int sl) { return A_EMPTY + 8u * (5 + sl); };
     auto Q_FULL = [&](int b) { return A_EMPTY + 8u * (9 + b); };
     auto Q_EMPTY = [&](int b) { return A_EMPTY + 8u * (11 + b); };
 
@@ -255,13 +268,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
         }
         mbar_init(A_FULL, TC_PR);
         mbar_init(A_EMPTY, 1);
-        for (int t = 0; t < 2; t++)
-            for (int b = 0; b < 2; b++) {
-                mbar_init(ACC_FULL(t, b), 1);
-                mbar_init(ACC_EMPTY(t, b), TC_BM);
-            }
+        for (int sl = 0; sl < 4; sl++) {
+            mbar_init(ACC_FULL(sl), 1);
+            mbar_init(ACC_EMPTY(sl), 2 * TC_BM);
+        }
         for (int b = 0; b < 2; b++) {
-            mbar_init(Q_FULL(b), TC_PR);
+            mbar_init(Q_FULL(b), TC_DT);
             mbar_init(Q_EMPTY(b), TC_PR);
             sQCount[b] = 0;
         }
@@ -278,6 +290,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
 
     const int nsteps = p.nsteps;
 
+    if (warp < TC_DRAIN_WARP0) setmaxnreg_dec<TC_REGS_MISC>();
     if (warp == 0) {
         // ===================== codebook stage producer (TMA engine, 1-D bulk copies) =====================
         if (lane == 0) {
@@ -301,7 +314,6 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
         // ===================== MMA issuer =====================
         if (lane == 0) {
             constexpr uint32_t IDESC = idesc_tf32(TC_BM, TC_BN);
-            const uint32_t a_addr = smem_u32(sA);
             uint32_t g = 0, pi = 0;
             PROF_DECL;
             for (int64_t pair = blockIdx.x; pair < p.npairs; pair += gridDim.x, pi++) {
@@ -317,21 +329,23 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                     PROF(2);   // prof[8+2]: MMA wait B_FULL
                     tc_fence_after();
                     const uint32_t b_addr = smem_u32(sB + (size_t)stage * L::BSTAGE);
-                    const int b = g & 1;                 // accumulator ring slot
-                    const uint32_t use = g >> 1;         // how often this slot has been used before
 #pragma unroll
                     for (int t = 0; t < 2; t++) {
+                        const uint32_t job = 2 * g + t;                  // (step, row tile) jobs share a ring of NSLOT slots
+                        const uint32_t sl = job % L::NSLOT, use = job / L::NSLOT;
                         PROF(0);
-                        mbar_wait(ACC_EMPTY(t, b), (use & 1) ^ 1);
+                        mbar_wait(ACC_EMPTY(sl), (use & 1) ^ 1);
                         PROF(3);   // prof[8+3]: MMA wait ACC_EMPTY
                         tc_fence_after();
 #pragma unroll
                         for (int ks = 0; ks < KSTEPS; ks++) {
-                            const uint64_t ad = smem_desc(a_addr + t * L::ATILE + ks * 2 * TC_LBO_A, TC_LBO_A, TC_SBO);
                             const uint64_t bd = smem_desc(b_addr + ks * 2 * TC_LBO_B, TC_LBO_B, TC_SBO);
-                            umma_tf32(tmem_base + (t * 2 + b) * TC_BN, ad, bd, IDESC, ks > 0 ? 1u : 0u);
+                            umma_tf32_ts(tmem_base + sl * TC_BN, tmem_base + L::ACOL + t * DP + ks * 8, bd, IDESC,
+                                         ks > 0 ? 1u : 0u);
                         }
-                        umma_commit(ACC_FULL(t, b));
+                        PROF(4);   // prof[8+4]: MMA issue of one job (KSTEPS instructions)
+                        umma_commit(ACC_FULL(sl));
+                        PROF(5);   // prof[8+5]: commit
                     }
                     umma_commit(B_EMPTY(stage));
                 }
@@ -342,15 +356,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
         }
     } else if (warp >= TC_PROD_WARP0) {
         // ===================== feature producers + re-rankers (256 threads) =====================
+        setmaxnreg_inc<TC_REGS_PROD>();
         const int ptid = tid - TC_PROD_WARP0 * 32;
         const int NC = DP - D < 3 ? DP - D : 3;
-        // constant padding columns of both A tiles: 1.0 against the norm pieces, 0 elsewhere
-        {
-            const int t = ptid >> 7, r = ptid & 127;
-            uint8_t *base = sA + t * L::ATILE + (r >> 3) * 128 + (r & 7) * 16;
-            for (int kk = D; kk < DP; kk++)
-                *reinterpret_cast<float *>(base + (kk >> 2) * TC_LBO_A + (kk & 3) * 4) = (kk < D + NC) ? 1.0f : 0.f;
-        }
         // Mapping: producer warp pw owns rows pw*32 .. pw*32+31 of the pass, lane <-> column (kk = lane + 32*h).
         // Loads are coalesced per row, every smem offset below is a per-thread base plus an immediate, and
         // with the 16-byte skew of TC_LBO_A the 32 lanes of a store hit 32 different banks.
@@ -380,21 +388,23 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             }
         };
         float mu_l[NH];
-        uint32_t koff[NH];
 #pragma unroll
-        for (int h = 0; h < NH; h++) {
-            const int kk = lane + 32 * h;
-            mu_l[h] = kk < D ? p.mu[kk] : 0.f;
-            koff[h] = (kk >> 2) * TC_LBO_A + (kk & 3) * 4;
-        }
-        uint8_t *a_base = sA + (pw >> 2) * L::ATILE + (pw & 3) * 4 * 128;   // row pw*32 of the pass
+        for (int h = 0; h < NH; h++) mu_l[h] = lane + 32 * h < D ? p.mu[lane + 32 * h] : 0.f;
+        // warp pw owns rows pw*32..+31 of the pass in both mappings: lane <-> column for the global loads and the
+        // scratch stores, lane <-> row (= TMEM lane, this warp's quarter pw & 3 of tile pw >> 2) for the A operand
+        float *xs_w = sX + (pw * 32) * L::XS;
+        const uint32_t a_tmem = tmem_base + ((uint32_t)((pw & 3) * 32) << 16) + L::ACOL + (pw >> 2) * DP;
+        const float cmax = __int_as_float(p.hdr->cmax_bits);
+        const bool force_fb = p.hdr->force_fallback != 0;
         const bool need_dist = p.out_dist != nullptr;
         unsigned long long st_rows = 0, st_cands = 0, st_fb = 0;
 
+        PROF_DECL;
         // ---- re-rank of one finished pass: queue -> exact distances -> per-row minimum -> outputs ----
         auto rerank = [&](int64_t pair, uint32_t rp) {
             const int qb = rp & 1;
             mbar_wait_backoff(Q_FULL(qb), (rp >> 1) & 1);
+            PROF(6);   // prof[16+6]: re-rank wait Q_FULL
             sBest[ptid] = ((unsigned long long)__float_as_uint(FLT_MAX)) << 32;      // (FLT_MAX, code 0)
             named_bar_sync(1, TC_PR);
             const uint32_t nq = min(sQCount[qb], (uint32_t)TC_QCAP);
@@ -449,7 +459,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
 #pragma unroll 1
             for (int rr = 0; rr < 32; rr += 2) {
                 const int lr = pw * 32 + rr + half;
-                const uint8_t status = sFlag[qb * TC_PR + lr];
+                const uint8_t st0 = sFlag[(qb * 2 + 0) * TC_PR + lr], st1 = sFlag[(qb * 2 + 1) * TC_PR + lr];
+                const uint8_t status = st0 > st1 ? st0 : st1;
                 const int64_t gi = pair * TC_PR + lr;
                 if (status == ROW_OK) {
                     const unsigned long long best = sBest[lr];
@@ -488,28 +499,69 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
 
         uint32_t pi = 0;
         int64_t prev_pair = -1;
-        PROF_DECL;
-        if ((int64_t)blockIdx.x < p.npairs) prefetch(blockIdx.x);
-        for (int64_t pair = blockIdx.x; pair < p.npairs; pair += gridDim.x, pi++) {
+        // software pipeline with ONE prefetch call site (two would make the 64 prefetch registers spill):
+        // iteration -1 only prefetches the first pass
+        for (int64_t pair = (int64_t)blockIdx.x - gridDim.x;; pair += gridDim.x) {
+          if (pair >= 0) {
             PROF(0);
-            mbar_wait_backoff(A_EMPTY, (pi & 1) ^ 1);  // previous pass' MMAs no longer read A
-            PROF(1);   // prof[16+1]: producer wait A_EMPTY
+            // transpose through shared memory: centred, TF32-rounded values, row stride XS (odd: conflict free both ways)
+            __syncwarp();
 #pragma unroll
             for (int r = 0; r < 32; r++) {
 #pragma unroll
-                for (int h = 0; h < NH; h++) {
+                for (int h = 0; h < NH; h++)
                     if (lane + 32 * h < D)
-                        *reinterpret_cast<uint32_t *>(a_base + (r >> 3) * 128 + (r & 7) * 16 + koff[h]) =
-                            to_tf32(xr[r * NH + h] - mu_l[h]);
-                }
+                        xs_w[r * L::XS + lane + 32 * h] = __uint_as_float(to_tf32(xr[r * NH + h] - mu_l[h]));
             }
-            fence_proxy_async_smem();
+            __syncwarp();
+            uint32_t av[DP];
+            float X = 0.f;                       // |x'|^2 of the rounded, centred row -> error band
+#pragma unroll
+            for (int kk = 0; kk < DP; kk++) {
+                float v = (kk < D + NC) ? 1.0f : 0.f;        // 1.0 against the norm pieces, 0 beyond
+                if (kk < D) {
+                    v = xs_w[lane * L::XS + kk];
+                    X = fmaf(v, v, X);
+                }
+                av[kk] = __float_as_uint(v);
+            }
+            {
+                const int64_t gi = pair * TC_PR + ptid;
+                // E bounds |score + X - true distance| for every code (DESIGN.md §4.1)
+                const float C1 = 1.002f * 0.001953125f + 7.62939453125e-6f;   // 2^-9 * 1.002 + 2^-17
+                const float C2 = 3.814697265625e-6f + 4.76837158203125e-7f;   // 2^-18 + 2^-21
+                const float E = C1 * sqrtf(X) * cmax + C2 * cmax * cmax;
+                float band = 1.01f * (2.f * E + p.gamma2 * X) + 3.0e-36f;
+                if (!(X < TC_HUGE2 * 0.0625f) || force_fb || !(band < TC_BIG))
+                    band = __int_as_float(0x7fc00000);                        // NaN: exact fallback
+                if (gi >= p.n) band = -1.f;
+                if (p.dbg_norm2 && gi < p.n) {
+                    p.dbg_norm2[gi] = X;
+                    p.dbg_band[gi] = band;
+                }
+                sBand[(pi & 1) * TC_PR + ptid] = band;
+            }
+            PROF(2);   // prof[16+2]: producer convert + transpose + band
+            mbar_wait_backoff(A_EMPTY, (pi & 1) ^ 1);  // previous pass' MMAs no longer read the A operand in TMEM
+            PROF(1);   // prof[16+1]: producer wait A_EMPTY
+            tc_fence_after();
+#pragma unroll
+            for (int c8 = 0; c8 < DP / 8; c8++) {
+                const uint32_t r8[8] = {av[c8 * 8 + 0], av[c8 * 8 + 1], av[c8 * 8 + 2], av[c8 * 8 + 3],
+                                        av[c8 * 8 + 4], av[c8 * 8 + 5], av[c8 * 8 + 6], av[c8 * 8 + 7]};
+                tmem_st8(a_tmem + c8 * 8, r8);
+            }
+            tmem_wait_st();
+            tc_fence_before();
             mbar_arrive(A_FULL);
-            PROF(2);   // prof[16+2]: producer convert + store A (includes waiting for the prefetched loads)
+            PROF(7);   // prof[16+7]: A operand -> TMEM
             if (prev_pair >= 0) rerank(prev_pair, pi - 1);
             PROF(3);   // prof[16+3]: re-rank + outputs of the previous pass (includes waiting for its queue)
             prev_pair = pair;
-            if (pair + gridDim.x < p.npairs) prefetch(pair + gridDim.x);
+            pi++;
+          }
+            if (pair + gridDim.x >= p.npairs) break;
+            prefetch(pair + gridDim.x);
             PROF(4);   // prof[16+4]: prefetch issue
         }
         if (prev_pair >= 0) rerank(prev_pair, pi - 1);
@@ -527,13 +579,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
         }
     } else if (warp >= TC_DRAIN_WARP0) {
         // ===================== drain: TMEM scan, running minimum, group lists, work queue =====================
-        const int lr = tid - TC_DRAIN_WARP0 * 32;      // local row 0..255
-        const int t = lr >> 7;
+        setmaxnreg_dec<TC_REGS_DRAIN>();
+        const int dw = warp - TC_DRAIN_WARP0;           // 0..15
         const int q = warp & 3;                         // TMEM lane quarter this warp may access
-        const uint32_t tsrc = tmem_base + ((uint32_t)(q * 32) << 16) + t * 2 * TC_BN;
-        const float cmax = __int_as_float(p.hdr->cmax_bits);
-        const bool force_fb = p.hdr->force_fallback != 0;
-        uint32_t *listS = sListS + lr, *listP = sListP + lr;
+        const int t = (dw >> 2) & 1;                    // row tile
+        const int h = dw >> 3;                          // column half of every accumulator slot
+        const int lr = t * TC_BM + q * 32 + lane;       // local row 0..255 (shared with the other half's thread)
+        const int dl = dw * 32 + lane;                  // drain thread 0..511 (list column)
+        const uint32_t tsrc = tmem_base + ((uint32_t)(q * 32) << 16) + h * (TC_BN / 2);
+        uint32_t *listS = sListS + dl, *listP = sListP + dl;
         uint32_t g = 0, pi = 0;
         PROF_DECL;
         for (int64_t pair = blockIdx.x; pair < p.npairs; pair += gridDim.x, pi++) {
@@ -541,33 +595,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             PROF(0);
             mbar_wait(A_FULL, pi & 1);
             PROF(1);       // prof[24+1]: drain wait A_FULL
-            float band;
-            {
-                // row norm of the rounded, centred row (read back from the A tile) -> error band
-                const int r = lr & 127;
-                const uint8_t *base = sA + t * L::ATILE + (r >> 3) * 128 + (r & 7) * 16;
-                float X = 0.f;
-#pragma unroll
-                for (int c4 = 0; c4 < DP / 4; c4++) {
-                    const float4 xv = *reinterpret_cast<const float4 *>(base + c4 * TC_LBO_A);
-                    if (4 * c4 + 0 < D) X = fmaf(xv.x, xv.x, X);
-                    if (4 * c4 + 1 < D) X = fmaf(xv.y, xv.y, X);
-                    if (4 * c4 + 2 < D) X = fmaf(xv.z, xv.z, X);
-                    if (4 * c4 + 3 < D) X = fmaf(xv.w, xv.w, X);
-                }
-                // E bounds |score + X - true distance| for every code (DESIGN.md §4.1)
-                const float C1 = 1.002f * 0.001953125f + 7.62939453125e-6f;   // 2^-9 * 1.002 + 2^-17
-                const float C2 = 3.814697265625e-6f + 4.76837158203125e-7f;   // 2^-18 + 2^-21
-                const float E = C1 * sqrtf(X) * cmax + C2 * cmax * cmax;
-                band = 1.01f * (2.f * E + p.gamma2 * X) + 3.0e-36f;
-                if (!(X < TC_HUGE2 * 0.0625f) || force_fb || !(band < TC_BIG))
-                    band = __int_as_float(0x7fc00000);                        // NaN: exact fallback
-                if (gi >= p.n) band = -1.f;
-                if (p.dbg_norm2 && gi < p.n) {
-                    p.dbg_norm2[gi] = X;
-                    p.dbg_band[gi] = band;
-                }
-            }
+            const float band = sBand[(pi & 1) * TC_PR + lr];      // computed by the producer of this row
             float m = 3.0e38f;
             float thr = (band >= 0.f) ? __int_as_float(0x7f800000) : __int_as_float(0xff800000);  // +inf / -inf
             int cnt = 0;
@@ -591,18 +619,18 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                     if (cnt == TC_LCAP) {               // full: drop entries the tighter threshold excludes
                         int wpos = 0;
                         for (int e = 0; e < TC_LCAP; e++) {
-                            const uint32_t es = listS[e * TC_PR], ep = listP[e * TC_PR];
+                            const uint32_t es = listS[e * TC_DT], ep = listP[e * TC_DT];
                             if (__uint_as_float(es) <= thr) {
-                                listS[wpos * TC_PR] = es;
-                                listP[wpos * TC_PR] = ep;
+                                listS[wpos * TC_DT] = es;
+                                listP[wpos * TC_DT] = ep;
                                 wpos++;
                             }
                         }
                         cnt = wpos;
                     }
                     if (cnt < TC_LCAP) {
-                        listS[cnt * TC_PR] = __float_as_uint(cm);
-                        listP[cnt * TC_PR] = ((uint32_t)(code0 >> 4) << 4) | gm;
+                        listS[cnt * TC_DT] = __float_as_uint(cm);
+                        listP[cnt * TC_DT] = ((uint32_t)(code0 >> 4) << 4) | gm;
                         cnt++;
                     } else {
                         ovf = true;
@@ -611,18 +639,18 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             };
 
             for (int s = 0; s < nsteps; s++, g++) {
-                const int b = g & 1;
-                const uint32_t use = g >> 1;
+                const uint32_t job = 2 * g + t;
+                const uint32_t sl = job % L::NSLOT, use = job / L::NSLOT;
                 PROF(4);   // prof[24+4]: drain (LDTM + min + lists)
-                mbar_wait(ACC_FULL(t, b), use & 1);
+                mbar_wait(ACC_FULL(sl), use & 1);
                 PROF(3);   // prof[24+3]: drain wait ACC_FULL
                 tc_fence_after();
-                const uint32_t ta = tsrc + b * TC_BN;
-                const int code_s = s * TC_BN;
+                const uint32_t ta = tsrc + sl * TC_BN;
+                const int code_s = s * TC_BN + h * (TC_BN / 2);
                 uint32_t va[16], vb[16];
                 tmem_ld16_async(ta, va);
 #pragma unroll
-                for (int c = 0; c < TC_BN / 32; c++) {
+                for (int c = 0; c < TC_BN / 64; c++) {
                     tmem_wait_ld16(va);
                     tmem_ld16_async(ta + c * 32 + 16, vb);
                     if (p.dbg_scores && gi < p.n) {
@@ -633,11 +661,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                     }
                     process(va, code_s + c * 32);
                     tmem_wait_ld16(vb);
-                    if (c + 1 < TC_BN / 32) {
+                    if (c + 1 < TC_BN / 64) {
                         tmem_ld16_async(ta + (c + 1) * 32, va);
                     } else {                            // accumulator slot fully read: hand it back to the MMA warp
                         tc_fence_before();
-                        mbar_arrive(ACC_EMPTY(t, b));
+                        mbar_arrive(ACC_EMPTY(sl));
                     }
                     if (p.dbg_scores && gi < p.n) {
 #pragma unroll
@@ -654,15 +682,20 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             mbar_wait(Q_EMPTY(qb), ((pi >> 1) & 1) ^ 1);     // the pass that used this queue slot is finished
             PROF(5);       // prof[24+5]: drain wait Q_EMPTY
             uint8_t status = ROW_OK;
-            if (gi >= p.n) {
+            if (gi >= p.n)
                 status = ROW_SKIP;
-            } else if (!(band >= 0.f) || ovf) {
+            else if (!(band >= 0.f) || ovf)
                 status = ROW_FALLBACK;
-            } else {
+            // the two column halves of a row exchange their running minima: both filter with the row's threshold
+            sXchg[(qb * 2 + h) * TC_PR + lr] = m;             // double buffered: one barrier per pass is enough
+            named_bar_sync(2, TC_DT);
+            m = fminf(m, sXchg[(qb * 2 + (h ^ 1)) * TC_PR + lr]);
+            if (status == ROW_OK) {
+                thr = m + p.gamma2 * fabsf(m) + band;
                 uint32_t *queue = sQueue + qb * TC_QCAP;
                 for (int e = 0; e < cnt; e++) {
-                    if (!(__uint_as_float(listS[e * TC_PR]) <= thr)) continue;
-                    const uint32_t ep = listP[e * TC_PR];
+                    if (!(__uint_as_float(listS[e * TC_DT]) <= thr)) continue;
+                    const uint32_t ep = listP[e * TC_DT];
                     uint32_t gm = ep & 0xFu;
                     const uint32_t grp0 = (ep >> 4) * 4;         // first group (code / 4) of the chunk
                     while (gm) {
@@ -678,7 +711,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                     }
                 }
             }
-            sFlag[qb * TC_PR + lr] = status;
+            sFlag[(qb * 2 + h) * TC_PR + lr] = status;
             mbar_arrive(Q_FULL(qb));
             PROF(6);       // prof[24+6]: drain queue push
         }

@@ -19,9 +19,9 @@ cb = init_codebook(x, 4096, 99)
 ei = torch.zeros(4096, device=dev)
 acc = torch.zeros(4096, _lib.acc_stride(d), device=dev)
 names = {0: "tma other", 1: "tma wait B_EMPTY",
-         8: "mma issue/other", 9: "mma wait A_FULL", 10: "mma wait B_FULL", 11: "mma wait ACC_EMPTY",
-         16: "prod other", 17: "prod wait A_EMPTY", 18: "prod convert+store A", 19: "prod rerank(prev pass)",
-         20: "prod prefetch issue", 21: "prod last rerank",
+         8: "mma issue/other", 9: "mma wait A_FULL", 10: "mma wait B_FULL", 11: "mma wait ACC_EMPTY", 12: "mma issue 6 MMAs", 13: "mma commit",
+         16: "prod other", 17: "prod wait A_EMPTY", 18: "prod convert+transpose+band", 19: "prod rerank(prev pass) work",
+         20: "prod prefetch issue", 21: "prod last rerank", 22: "prod rerank wait Q_FULL", 23: "prod A -> TMEM",
          24: "drain other", 25: "drain wait A_FULL", 26: "drain band", 27: "drain wait ACC_FULL",
          28: "drain LDTM+min+lists", 29: "drain wait Q_EMPTY", 30: "drain queue push"}
 for it in range(3):
