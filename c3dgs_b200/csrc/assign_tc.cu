@@ -56,11 +56,12 @@ constexpr int TC_BN = 128;            // codes per stage / per MMA
 constexpr int TC_LCAP = 8;            // group-list capacity per row
 constexpr int TC_QCAP = 1024;         // re-rank queue capacity per pass (groups of 4 codes)
 constexpr int TC_MAXSTAGES = 6;
-constexpr int TC_DRAIN_WARP0 = 4;
+constexpr int TC_DRAIN_WARP0 = 0;    // warp order = issue priority on B200 (highest warp id first): misc warps last
 constexpr int TC_NDRAIN = 16;          // drain warps: (tile t, lane quarter q, column half h)
 constexpr int TC_DT = TC_NDRAIN * 32; // drain threads
 constexpr int TC_PROD_WARP0 = TC_DRAIN_WARP0 + TC_NDRAIN;
-constexpr int TC_THREADS = (TC_PROD_WARP0 + 8) * 32;   // 896
+constexpr int TC_MISC_WARP0 = TC_PROD_WARP0 + 8;        // TMA producer, MMA issuer, TMEM allocator, spare
+constexpr int TC_THREADS = (TC_MISC_WARP0 + 4) * 32;   // 896
 // register budgets per role (setmaxnreg): 896 threads start at 72; 4*32*(72-40) + 16*32*(72-64) = 8192 = 8*32*(104-72)
 constexpr int TC_REGS_MISC = 40, TC_REGS_DRAIN = 64, TC_REGS_PROD = 104;
 constexpr uint32_t TC_LBO_A = TC_BM * 16 + 16;   // skewed by 16 B: conflict-free scattered stores
@@ -261,7 +262,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
     const int warp = tid >> 5;
     const int lane = tid & 31;
 
-    if (warp == 0 && lane == 0) {
+    if (warp == TC_MISC_WARP0 && lane == 0) {
         for (int s = 0; s < TC_MAXSTAGES; s++) {
             mbar_init(B_FULL(s), 1);
             mbar_init(B_EMPTY(s), 1);
@@ -279,7 +280,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
         }
         fence_mbar_init();
     }
-    if (warp == 2) {
+    if (warp == TC_MISC_WARP0 + 2) {
         tmem_alloc(smem_u32(sTmem), 512);
         tmem_relinquish();
     }
@@ -290,8 +291,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
 
     const int nsteps = p.nsteps;
 
-    if (warp < TC_DRAIN_WARP0) setmaxnreg_dec<TC_REGS_MISC>();
-    if (warp == 0) {
+    if (warp >= TC_MISC_WARP0) setmaxnreg_dec<TC_REGS_MISC>();
+    if (warp == TC_MISC_WARP0) {
         // ===================== codebook stage producer (TMA engine, 1-D bulk copies) =====================
         if (lane == 0) {
             uint32_t g = 0;
@@ -310,9 +311,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             }
             PROF_FLUSH(0, true);
         }
-    } else if (warp == 1) {
+    } else if (warp == TC_MISC_WARP0 + 1) {
         // ===================== MMA issuer =====================
-        if (lane == 0) {
+        // The whole warp runs the loop convergently (so addresses and descriptors live in uniform registers and
+        // the waits are warp-wide); one elected lane issues the tcgen05 instructions.
+        {
             constexpr uint32_t IDESC = idesc_tf32(TC_BM, TC_BN);
             uint32_t g = 0, pi = 0;
             PROF_DECL;
@@ -337,23 +340,29 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                         mbar_wait(ACC_EMPTY(sl), (use & 1) ^ 1);
                         PROF(3);   // prof[8+3]: MMA wait ACC_EMPTY
                         tc_fence_after();
+                        if (elect_one()) {
 #pragma unroll
-                        for (int ks = 0; ks < KSTEPS; ks++) {
-                            const uint64_t bd = smem_desc(b_addr + ks * 2 * TC_LBO_B, TC_LBO_B, TC_SBO);
-                            umma_tf32_ts(tmem_base + sl * TC_BN, tmem_base + L::ACOL + t * DP + ks * 8, bd, IDESC,
-                                         ks > 0 ? 1u : 0u);
+                            for (int ks = 0; ks < KSTEPS; ks++) {
+                                const uint64_t bd = smem_desc(b_addr + ks * 2 * TC_LBO_B, TC_LBO_B, TC_SBO);
+                                umma_tf32_ts(tmem_base + sl * TC_BN, tmem_base + L::ACOL + t * DP + ks * 8, bd, IDESC,
+                                             ks > 0 ? 1u : 0u);
+                            }
+                            umma_commit(ACC_FULL(sl));
                         }
-                        PROF(4);   // prof[8+4]: MMA issue of one job (KSTEPS instructions)
-                        umma_commit(ACC_FULL(sl));
-                        PROF(5);   // prof[8+5]: commit
+                        __syncwarp();
+                        PROF(4);   // prof[8+4]: MMA issue of one job (KSTEPS instructions + commit)
                     }
-                    umma_commit(B_EMPTY(stage));
+                    if (elect_one()) umma_commit(B_EMPTY(stage));
+                    __syncwarp();
                 }
-                umma_commit(A_EMPTY);
+                if (elect_one()) umma_commit(A_EMPTY);
+                __syncwarp();
             }
             PROF(0);       // prof[8+0]: MMA issue + everything else
-            PROF_FLUSH(8, true);
+            PROF_FLUSH(8, lane == 0);
         }
+    } else if (warp >= TC_MISC_WARP0) {
+        // TMEM allocator warp and the spare warp: nothing to do until teardown
     } else if (warp >= TC_PROD_WARP0) {
         // ===================== feature producers + re-rankers (256 threads) =====================
         setmaxnreg_inc<TC_REGS_PROD>();
@@ -577,7 +586,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             atomicAdd(&p.hdr->fb_rows, st_fb);
             if (pw == 0) atomicAdd(&p.hdr->cands, st_cands);
         }
-    } else if (warp >= TC_DRAIN_WARP0) {
+    } else {
         // ===================== drain: TMEM scan, running minimum, group lists, work queue =====================
         setmaxnreg_dec<TC_REGS_DRAIN>();
         const int dw = warp - TC_DRAIN_WARP0;           // 0..15
@@ -720,7 +729,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
 
     tc_fence_before();
     __syncthreads();
-    if (warp == 2) {
+    if (warp == TC_MISC_WARP0 + 2) {
         tc_fence_after();
         tmem_dealloc(tmem_base, 512);
     }
