@@ -597,6 +597,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
         const int dl = dw * 32 + lane;                  // drain thread 0..511 (list column)
         const uint32_t tsrc = tmem_base + ((uint32_t)(q * 32) << 16) + h * (TC_BN / 2);
         uint32_t *listS = sListS + dl, *listP = sListP + dl;
+        const uint32_t lS = smem_u32(listS), lP = smem_u32(listP);
+        constexpr uint32_t LIST_STRIDE = TC_DT * 4, LIST_END = TC_LCAP * LIST_STRIDE;
+        static_assert(TC_BN == 128, "the drain reads two 32-column chunks per half slot");
         uint32_t g = 0, pi = 0;
         PROF_DECL;
         for (int64_t pair = blockIdx.x; pair < p.npairs; pair += gridDim.x, pi++) {
@@ -606,44 +609,63 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             PROF(1);       // prof[24+1]: drain wait A_FULL
             const float band = sBand[(pi & 1) * TC_PR + lr];      // computed by the producer of this row
             float m = 3.0e38f;
-            float thr = (band >= 0.f) ? __int_as_float(0x7f800000) : __int_as_float(0xff800000);  // +inf / -inf
-            int cnt = 0;
+            // valid rows start at 2^124: above every real score, below the 2^126 of dead / padding codes
+            float thr = (band >= 0.f) ? 0.25f * TC_BIG : __int_as_float(0xff800000);
+            uint32_t cnt_off = 0;                       // byte offset of the next free list entry
             bool ovf = false;
+            const bool dbg = p.dbg_scores != nullptr && gi < p.n;
             PROF(2);       // prof[24+2]: drain band
 
-            // one 16-column chunk: four group minima, then (rarely per row, often per warp) the list append
-            auto process = [&](const uint32_t (&v)[16], int code0) {
-                const float g0 = min4(v[0], v[1], v[2], v[3]);
-                const float g1 = min4(v[4], v[5], v[6], v[7]);
-                const float g2 = min4(v[8], v[9], v[10], v[11]);
-                const float g3 = min4(v[12], v[13], v[14], v[15]);
-                const float cm = fminf(fminf(fminf(g0, g1), g2), g3);
-                if (cm <= thr && cm < 0.5f * TC_BIG) {   // dead / padding codes (score 2^126) never enter
-                    if (cm < m) {
-                        m = cm;
+            // eight group minima of a 32-column chunk (FMNMX3 + FMNMX per group)
+            auto groups = [&](const uint32_t (&a)[16], const uint32_t (&b)[16], float (&gm)[8]) {
+                gm[0] = min4(a[0], a[1], a[2], a[3]);
+                gm[1] = min4(a[4], a[5], a[6], a[7]);
+                gm[2] = min4(a[8], a[9], a[10], a[11]);
+                gm[3] = min4(a[12], a[13], a[14], a[15]);
+                gm[4] = min4(b[0], b[1], b[2], b[3]);
+                gm[5] = min4(b[4], b[5], b[6], b[7]);
+                gm[6] = min4(b[8], b[9], b[10], b[11]);
+                gm[7] = min4(b[12], b[13], b[14], b[15]);
+            };
+            // chunk minimum against the running threshold; the append path is entered per WARP (uniform branch)
+            auto process = [&](const float (&gv)[8], int code0) {
+                const float cm = fminf(fminf(fminf(fminf(gv[0], gv[1]), gv[2]), fminf(fminf(gv[3], gv[4]), gv[5])),
+                                       fminf(gv[6], gv[7]));
+                const bool flag = cm <= thr;
+                if (__any_sync(0xffffffffu, flag)) {
+                    if (flag) {
+                        m = fminf(m, cm);
                         thr = m + p.gamma2 * fabsf(m) + band;
-                    }
-                    const uint32_t gm = (g0 <= thr ? 1u : 0u) | (g1 <= thr ? 2u : 0u) | (g2 <= thr ? 4u : 0u) |
-                                        (g3 <= thr ? 8u : 0u);
-                    if (cnt == TC_LCAP) {               // full: drop entries the tighter threshold excludes
-                        int wpos = 0;
-                        for (int e = 0; e < TC_LCAP; e++) {
-                            const uint32_t es = listS[e * TC_DT], ep = listP[e * TC_DT];
-                            if (__uint_as_float(es) <= thr) {
-                                listS[wpos * TC_DT] = es;
-                                listP[wpos * TC_DT] = ep;
-                                wpos++;
+                        uint32_t gm = 0;
+#pragma unroll
+                        for (int i = 0; i < 8; i++) gm |= (gv[i] <= thr) ? (1u << i) : 0u;
+                        if (cnt_off == LIST_END) {      // full: drop entries the tighter threshold excludes
+                            uint32_t wpos = 0;
+                            for (uint32_t e = 0; e < LIST_END; e += LIST_STRIDE) {
+                                const uint32_t es = ld_shared_u32(lS + e), ep = ld_shared_u32(lP + e);
+                                if (__uint_as_float(es) <= thr) {
+                                    st_shared_u32(lS + wpos, es);
+                                    st_shared_u32(lP + wpos, ep);
+                                    wpos += LIST_STRIDE;
+                                }
                             }
+                            cnt_off = wpos;
                         }
-                        cnt = wpos;
+                        if (cnt_off < LIST_END) {
+                            st_shared_u32(lS + cnt_off, __float_as_uint(cm));
+                            st_shared_u32(lP + cnt_off, ((uint32_t)(code0 >> 5) << 8) | gm);
+                            cnt_off += LIST_STRIDE;
+                        } else {
+                            ovf = true;
+                        }
                     }
-                    if (cnt < TC_LCAP) {
-                        listS[cnt * TC_DT] = __float_as_uint(cm);
-                        listP[cnt * TC_DT] = ((uint32_t)(code0 >> 4) << 4) | gm;
-                        cnt++;
-                    } else {
-                        ovf = true;
-                    }
+                }
+            };
+            auto dump = [&](const uint32_t (&a)[16], const uint32_t (&b)[16], int code0) {   // debug only
+#pragma unroll
+                for (int jj = 0; jj < 16; jj++) {
+                    if (code0 + jj < p.k) p.dbg_scores[gi * p.k + code0 + jj] = __uint_as_float(a[jj]);
+                    if (code0 + 16 + jj < p.k) p.dbg_scores[gi * p.k + code0 + 16 + jj] = __uint_as_float(b[jj]);
                 }
             };
 
@@ -651,40 +673,31 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                 const uint32_t job = 2 * g + t;
                 const uint32_t sl = job % L::NSLOT, use = job / L::NSLOT;
                 PROF(4);   // prof[24+4]: drain (LDTM + min + lists)
-                mbar_wait(ACC_FULL(sl), use & 1);
+                mbar_wait_hint(ACC_FULL(sl), use & 1);
                 PROF(3);   // prof[24+3]: drain wait ACC_FULL
                 tc_fence_after();
                 const uint32_t ta = tsrc + sl * TC_BN;
                 const int code_s = s * TC_BN + h * (TC_BN / 2);
                 uint32_t va[16], vb[16];
+                float gv[8];
                 tmem_ld16_async(ta, va);
-#pragma unroll
-                for (int c = 0; c < TC_BN / 64; c++) {
-                    tmem_wait_ld16(va);
-                    tmem_ld16_async(ta + c * 32 + 16, vb);
-                    if (p.dbg_scores && gi < p.n) {
-#pragma unroll
-                        for (int j = 0; j < 16; j++)
-                            if (code_s + c * 32 + j < p.k)
-                                p.dbg_scores[gi * p.k + code_s + c * 32 + j] = __uint_as_float(va[j]);
-                    }
-                    process(va, code_s + c * 32);
-                    tmem_wait_ld16(vb);
-                    if (c + 1 < TC_BN / 64) {
-                        tmem_ld16_async(ta + (c + 1) * 32, va);
-                    } else {                            // accumulator slot fully read: hand it back to the MMA warp
-                        tc_fence_before();
-                        mbar_arrive(ACC_EMPTY(sl));
-                    }
-                    if (p.dbg_scores && gi < p.n) {
-#pragma unroll
-                        for (int j = 0; j < 16; j++)
-                            if (code_s + c * 32 + 16 + j < p.k)
-                                p.dbg_scores[gi * p.k + code_s + c * 32 + 16 + j] = __uint_as_float(vb[j]);
-                    }
-                    process(vb, code_s + c * 32 + 16);
-                }
+                tmem_ld16_async(ta + 16, vb);
+                tmem_wait_ld16(va);
+                tmem_wait_ld16(vb);
+                if (dbg) dump(va, vb, code_s);
+                groups(va, vb, gv);
+                tmem_ld16_async(ta + 32, va);           // second chunk in flight while the first is judged
+                tmem_ld16_async(ta + 48, vb);
+                process(gv, code_s);
+                tmem_wait_ld16(va);
+                tmem_wait_ld16(vb);
+                tc_fence_before();                      // accumulator slot fully read: hand it back to the MMA warp
+                mbar_arrive(ACC_EMPTY(sl));
+                if (dbg) dump(va, vb, code_s + 32);
+                groups(va, vb, gv);
+                process(gv, code_s + 32);
             }
+            const int cnt = (int)(cnt_off / LIST_STRIDE);
             PROF(4);
             // ---- hand the surviving groups of this pass to the re-rank warps ----
             const int qb = pi & 1;
@@ -705,8 +718,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                 for (int e = 0; e < cnt; e++) {
                     if (!(__uint_as_float(listS[e * TC_DT]) <= thr)) continue;
                     const uint32_t ep = listP[e * TC_DT];
-                    uint32_t gm = ep & 0xFu;
-                    const uint32_t grp0 = (ep >> 4) * 4;         // first group (code / 4) of the chunk
+                    uint32_t gm = ep & 0xFFu;
+                    const uint32_t grp0 = (ep >> 8) * 8;         // first group (code / 4) of the 32-column chunk
                     while (gm) {
                         const int bit = __ffs(gm) - 1;
                         gm &= gm - 1;

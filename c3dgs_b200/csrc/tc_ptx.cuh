@@ -47,6 +47,32 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
     }
 }
 
+// critical-path waiters: let the hardware park the thread (up to the hint, in ns) instead of spinning through
+// try_wait/branch pairs that compete for issue slots with the working warps
+__device__ __forceinline__ void mbar_wait_hint(uint32_t bar, uint32_t parity)
+{
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok)
+            : "r"(bar), "r"(parity), "r"(20000u)
+            : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void st_shared_u32(uint32_t addr, uint32_t v)
+{
+    asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_shared_u32(uint32_t addr)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+    return v;
+}
+
 // for waiters that are not on the critical path (producers running ahead): do not burn issue slots
 __device__ __forceinline__ void mbar_wait_backoff(uint32_t bar, uint32_t parity)
 {
