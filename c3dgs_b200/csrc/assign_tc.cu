@@ -20,19 +20,20 @@
 //      model, go to an exact warp-per-row scan (k_assign_fallback).
 //
 // Kernel organisation (persistent, one CTA per SM, 896 threads, warp specialised, setmaxnreg per role):
-//   warp 0      bulk-copy (TMA engine, cp.async.bulk) producer: codebook image stages -> smem ring
-//   warp 1      MMA issuer: per stage 2 x KSTEPS tcgen05.mma (M=128, N=128, K=8), commits to mbarriers
-//   warp 2      TMEM allocator (512 columns = four 128x128 fp32 accumulators: 2 row tiles x 2 ring slots)
-//   warps 4-19  drain: tcgen05.ld 16 columns at a time, running min + group list per row; two threads per
-//               row (one per 64-column half of every accumulator slot: a warp reads TMEM at only ~19 B/cycle,
-//               measured, so 16 warps are needed to keep up with the tensor core); at the end of a pass the
-//               halves exchange minima and push the surviving groups into a work queue
-//   warps 20-27 feature producers AND re-rankers: store the prefetched next 256 rows (centred, TF32,
-//               UMMA canonical K-major layout); then, while the tensor core and the drain warps work on
-//               that pass, re-rank the previous pass' queue (4 lanes per group, shared-memory 64-bit
-//               atomicMin per row), write idx/dist, red.global.add.v4 the weighted rows; then prefetch.
-// A pass is 256 rows x all K codes.  Accumulator slot (tile t, step parity b) is refilled by the MMA warp
-// as soon as its 128 drain threads have read it, so MMA, drain and re-rank all overlap.
+//   warps 0-15  drain: tcgen05.ld 16 columns at a time, running min + group list per row; two threads per
+//               row (one per column half of every accumulator slot); at the end of a pass the halves
+//               exchange minima and push the surviving groups into a work queue
+//   warps 16-23 feature producers AND re-rankers: stage the prefetched next 256 raw rows in shared memory
+//               (double buffered), write them centred + TF32-rounded into TMEM as the A operand; then,
+//               while the tensor core and the drain warps work on that pass, re-rank the previous pass'
+//               queue from the staged rows (4 lanes per group, shared-memory 64-bit atomicMin per row),
+//               write idx/dist, red.global.add.v4 the weighted rows; then prefetch.
+//   warp 24     bulk-copy (TMA engine, cp.async.bulk) producer: codebook image stages -> smem ring
+//   warp 25     MMA issuer: per stage 2 x KSTEPS tcgen05.mma (M=128, N=BN, K=8), commits to mbarriers
+//   warp 26     TMEM allocator (512 columns: four 128 x BN fp32 accumulator slots, two per row tile, then the
+//               A operand of both row tiles)
+// A pass is 256 rows x all K codes.  Each row tile owns two accumulator slots, so the MMA warp fills one while
+// the tile's 256 drain threads read the other: MMA, drain and re-rank all overlap.
 #include "common.cuh"
 #include "tc_ptx.cuh"
 
@@ -52,8 +53,9 @@ using namespace ptx;
 
 constexpr int TC_BM = 128;            // rows per UMMA tile
 constexpr int TC_PR = 2 * TC_BM;      // rows per CTA pass ("pair" of tiles)
-constexpr int TC_BN = 128;            // codes per stage / per MMA
-constexpr int TC_LCAP = 8;            // group-list capacity per row
+// codes per stage / per MMA: four accumulator slots plus the A operand of both row tiles share the 512 TMEM columns
+__host__ __device__ constexpr int tc_bn(int dp) { return dp <= 64 ? 96 : 64; }
+__host__ __device__ constexpr int tc_lcap(int dp) { return dp <= 56 ? 8 : 4; }   // chunk-list capacity per drain thread
 constexpr int TC_QCAP = 1024;         // re-rank queue capacity per pass (groups of 4 codes)
 constexpr int TC_MAXSTAGES = 6;
 constexpr int TC_DRAIN_WARP0 = 0;    // warp order = issue priority on B200 (highest warp id first): misc warps last
@@ -62,10 +64,8 @@ constexpr int TC_DT = TC_NDRAIN * 32; // drain threads
 constexpr int TC_PROD_WARP0 = TC_DRAIN_WARP0 + TC_NDRAIN;
 constexpr int TC_MISC_WARP0 = TC_PROD_WARP0 + 8;        // TMA producer, MMA issuer, TMEM allocator, spare
 constexpr int TC_THREADS = (TC_MISC_WARP0 + 4) * 32;   // 896
-// register budgets per role (setmaxnreg): 896 threads start at 72; 4*32*(72-40) + 16*32*(72-64) = 8192 = 8*32*(104-72)
-constexpr int TC_REGS_MISC = 40, TC_REGS_DRAIN = 64, TC_REGS_PROD = 104;
-constexpr uint32_t TC_LBO_A = TC_BM * 16 + 16;   // skewed by 16 B: conflict-free scattered stores
-constexpr uint32_t TC_LBO_B = TC_BN * 16;
+// register budgets per role (setmaxnreg): the CTA owns 896 * 72 = 64512 registers = 4*32*40 + 16*32*72 + 8*32*88
+constexpr int TC_REGS_MISC = 40, TC_REGS_DRAIN = 72, TC_REGS_PROD = 88;
 constexpr uint32_t TC_SBO = 128;
 constexpr float TC_BIG = 8.507059173023462e37f;  // 2^126: score of dead / padding codes
 constexpr float TC_HUGE2 = 1.2676506002282294e30f;  // 2^100: squared-norm limit of the error model
@@ -139,14 +139,14 @@ __global__ void __launch_bounds__(256) k_tc_prep_mean(const float *__restrict__ 
 
 // prep 2: one thread per (padded) code: centre, norms, TF32 image, padded raw copy, Cmax
 __global__ void k_tc_prep_image(const float *__restrict__ cb, int k, int k_pad, int d, int dp, int nc, int dpc,
-                                TcHeader *hdr, float *__restrict__ mu_out, float *__restrict__ bimg,
+                                int bn, TcHeader *hdr, float *__restrict__ mu_out, float *__restrict__ bimg,
                                 float *__restrict__ cbp)
 {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= k_pad) return;
     const int live = hdr->live;
     const float inv = live > 0 ? 1.f / (float)live : 0.f;
-    float *img = bimg + (size_t)(j / TC_BN) * (TC_BN * dp) + (size_t)(j % TC_BN) * 4;   // + chunk*BN*4 + (kk&3)
+    float *img = bimg + (size_t)(j / bn) * (bn * dp) + (size_t)(j % bn) * 4;   // + chunk*BN*4 + (kk&3)
     bool fin = j < k;
     double n2 = 0.0;
     if (j < k) {
@@ -183,7 +183,7 @@ __global__ void k_tc_prep_image(const float *__restrict__ cb, int k, int k_pad, 
         } else if (c == d) {
             v = TC_BIG;                  // dead or padding code: score 2^126, never inside any band
         }
-        img[(size_t)(c >> 2) * (TC_BN * 4) + (c & 3)] = v;
+        img[(size_t)(c >> 2) * (bn * 4) + (c & 3)] = v;
     }
 }
 
@@ -192,21 +192,27 @@ __global__ void k_tc_prep_image(const float *__restrict__ cb, int k, int k_pad, 
 template <int DP>
 struct TcSmem {
     static constexpr int KSTEPS = DP / 8;
-    static constexpr uint32_t BSTAGE = TC_BN * DP * 4;
-    static constexpr int XS = DP + 1;                                      // transposition scratch row stride (odd)
-    static constexpr uint32_t XS_BYTES = (uint32_t)TC_PR * XS * 4;
+    static constexpr int BN = tc_bn(DP);                                   // codes per stage / per MMA
+    static constexpr int NG = BN / 8;                                      // groups of 4 codes per drain thread and job
+    static constexpr int LCAP = tc_lcap(DP);
+    static constexpr uint32_t LBO_B = BN * 16;
+    static constexpr uint32_t BSTAGE = BN * DP * 4;
+    static constexpr int XS = DP + 1;                                      // staged row stride in floats (odd)
+    static constexpr uint32_t XS_BYTES = 2u * TC_PR * XS * 4;              // raw rows, two passes in flight
+    static constexpr uint32_t W_BYTES = 2u * TC_PR * 4;                    // row weights, two passes in flight
     static constexpr uint32_t BAND_BYTES = 2u * TC_PR * 4;                 // per-row error band, two passes in flight
-    // TMEM columns: NSLOT accumulator slots of 128, then the A operand of both row tiles (DP columns each)
-    static constexpr int NSLOT = (512 - 2 * DP) / TC_BN >= 3 ? 3 : 2;
-    static constexpr uint32_t ACOL = NSLOT * TC_BN;
-    static constexpr uint32_t LIST_BYTES = 2u * TC_DT * TC_LCAP * 4;       // score words + payload words
+    // TMEM columns: NSLOT accumulator slots of BN (two per row tile), then the A operand of both row tiles
+    static constexpr int NSLOT = 4;
+    static constexpr uint32_t ACOL = NSLOT * BN;
+    static_assert(ACOL + 2 * DP <= 512, "TMEM budget");
+    static constexpr uint32_t LIST_BYTES = 2u * TC_DT * LCAP * 4;          // score words + payload words
     static constexpr uint32_t QUEUE_BYTES = 2u * TC_QCAP * 4;              // two passes in flight
     static constexpr uint32_t BEST_BYTES = TC_PR * 8;
     static constexpr uint32_t FLAG_BYTES = 4u * TC_PR;                     // per-row, per-half status, two passes in flight
     static constexpr uint32_t XCHG_BYTES = 4u * TC_PR * 4;                 // running minima exchanged between column halves
     static constexpr uint32_t MISC_BYTES = 80 * 4 /*mu*/ + 64 /*counters, tmem ptr*/ + 40 * 8 /*barriers*/;
-    static constexpr uint32_t FIXED = XS_BYTES + BAND_BYTES + LIST_BYTES + QUEUE_BYTES + BEST_BYTES + FLAG_BYTES + XCHG_BYTES + MISC_BYTES +
-                                      128 /*alignment*/;
+    static constexpr uint32_t FIXED = XS_BYTES + W_BYTES + BAND_BYTES + LIST_BYTES + QUEUE_BYTES + BEST_BYTES + FLAG_BYTES +
+                                      XCHG_BYTES + MISC_BYTES + 128 /*alignment*/;
     static int stages()
     {
         int s = (TC_SMEM_LIMIT - (int)FIXED) / (int)BSTAGE;
@@ -225,22 +231,24 @@ __device__ __forceinline__ float min4(uint32_t a, uint32_t b, uint32_t c, uint32
 constexpr uint8_t ROW_OK = 0, ROW_FALLBACK = 1, ROW_SKIP = 2;
 
 // DCONST > 0: feature width known at compile time (6, 7, 45, 48); DCONST == 0: runtime width p.d <= DP - 2.
-template <int DP, int DCONST>
+template <int DP, int DCONST, bool DBG>
 __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
 {
     using L = TcSmem<DP>;
     constexpr int KSTEPS = L::KSTEPS;
+    constexpr int BN = L::BN;
     extern __shared__ __align__(128) uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
 
     const int D = DCONST > 0 ? DCONST : p.d;
     const int S = p.nstages;
     uint8_t *sB = smem;                                        // S * BSTAGE
-    float *sX = reinterpret_cast<float *>(sB + (size_t)S * L::BSTAGE);     // [PR][XS] centred tf32 rows (transposition)
-    float *sBand = sX + TC_PR * L::XS;                                      // [2][PR]
-    uint32_t *sListS = reinterpret_cast<uint32_t *>(sBand + 2 * TC_PR);     // [LCAP][DT] score bits
-    uint32_t *sListP = sListS + TC_DT * TC_LCAP;                            // [LCAP][DT] (chunk16 << 4) | group mask
-    uint32_t *sQueue = sListP + TC_DT * TC_LCAP;                            // [2][QCAP] (row << 16) | group
+    float *sX = reinterpret_cast<float *>(sB + (size_t)S * L::BSTAGE);     // [2][PR][XS] raw rows of two passes
+    float *sW = sX + 2 * TC_PR * L::XS;                                     // [2][PR] row weights
+    float *sBand = sW + 2 * TC_PR;                                          // [2][PR]
+    uint32_t *sListS = reinterpret_cast<uint32_t *>(sBand + 2 * TC_PR);     // [LCAP][DT] chunk-minimum score bits
+    uint32_t *sListP = sListS + TC_DT * L::LCAP;                            // [LCAP][DT] (chunk << 12) | group mask
+    uint32_t *sQueue = sListP + TC_DT * L::LCAP;                            // [2][QCAP] (row << 16) | group
     unsigned long long *sBest = reinterpret_cast<unsigned long long *>(sQueue + 2 * TC_QCAP);   // [PR]
     uint8_t *sFlag = reinterpret_cast<uint8_t *>(sBest + TC_PR);            // [2 passes][2 halves][PR]
     float *sXchg = reinterpret_cast<float *>(sFlag + 4 * TC_PR);            // [2 passes][2 halves][PR]
@@ -253,8 +261,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
     auto B_FULL = [&](int s) { return bar0 + 8u * s; };
     auto B_EMPTY = [&](int s) { return bar0 + 8u * (TC_MAXSTAGES + s); };
     const uint32_t A_FULL = bar0 + 8u * (2 * TC_MAXSTAGES), A_EMPTY = A_FULL + 8u;
-    auto ACC_FULL = [&](int sl) { return A_EMPTY + 8u * (1 + sl); };
-    auto ACC_EMPTY = [&](int sl) { return A_EMPTY + 8u * (5 + sl); };
+    auto ACC_FULL = [&](uint32_t sl) { return A_EMPTY + 8u * (1 + sl); };
+    auto ACC_EMPTY = [&](uint32_t sl) { return A_EMPTY + 8u * (5 + sl); };
     auto Q_FULL = [&](int b) { return A_EMPTY + 8u * (9 + b); };
     auto Q_EMPTY = [&](int b) { return A_EMPTY + 8u * (11 + b); };
 
@@ -267,15 +275,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             mbar_init(B_FULL(s), 1);
             mbar_init(B_EMPTY(s), 1);
         }
-        mbar_init(A_FULL, TC_PR);
+        mbar_init(A_FULL, 8);                      // one arrival per producer warp
         mbar_init(A_EMPTY, 1);
         for (int sl = 0; sl < 4; sl++) {
             mbar_init(ACC_FULL(sl), 1);
-            mbar_init(ACC_EMPTY(sl), 2 * TC_BM);
+            mbar_init(ACC_EMPTY(sl), 4);           // one arrival per drain warp of the tile/parity
         }
         for (int b = 0; b < 2; b++) {
-            mbar_init(Q_FULL(b), TC_DT);
-            mbar_init(Q_EMPTY(b), TC_PR);
+            mbar_init(Q_FULL(b), TC_NDRAIN);
+            mbar_init(Q_EMPTY(b), 8);
             sQCount[b] = 0;
         }
         fence_mbar_init();
@@ -284,40 +292,48 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
         tmem_alloc(smem_u32(sTmem), 512);
         tmem_relinquish();
     }
+    if (tid < 80) sMu[tid] = tid < D ? p.mu[tid] : 0.f;
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    const uint32_t tmem_base = *sTmem;
 
     const int nsteps = p.nsteps;
 
-    if (warp >= TC_MISC_WARP0) setmaxnreg_dec<TC_REGS_MISC>();
-    if (warp == TC_MISC_WARP0) {
+    // setmaxnreg sits inside each warpgroup's own branch (ptxas applies a dec to all code reachable from it) and is
+    // executed by all four warps of the warpgroup at ONE site (.aligned)
+    if (warp >= TC_MISC_WARP0) {
+      setmaxnreg_dec<TC_REGS_MISC>();
+      if (warp == TC_MISC_WARP0) {
         // ===================== codebook stage producer (TMA engine, 1-D bulk copies) =====================
         if (lane == 0) {
-            uint32_t g = 0;
+            uint32_t stage = 0, phase = 1;              // ring position; parity of the "empty" phase to wait for
+            const uint32_t sb0 = smem_u32(sB);
             PROF_DECL;
             for (int64_t pair = blockIdx.x; pair < p.npairs; pair += gridDim.x) {
-                for (int s = 0; s < nsteps; s++, g++) {
-                    const int stage = g % S;
-                    const uint32_t u = g / S;
+                const float *src = p.bimg;
+                for (int s = 0; s < nsteps; s++, src += BN * DP) {
                     PROF(0);
-                    mbar_wait_backoff(B_EMPTY(stage), (u & 1) ^ 1);
+                    mbar_wait_backoff(B_EMPTY(stage), phase);
                     PROF(1);   // prof[1]: TMA wait B_EMPTY
                     mbar_arrive_expect_tx(B_FULL(stage), L::BSTAGE);
-                    bulk_g2s(smem_u32(sB + (size_t)stage * L::BSTAGE), p.bimg + (size_t)s * (TC_BN * DP), L::BSTAGE,
-                             B_FULL(stage));
+                    bulk_g2s(sb0 + stage * L::BSTAGE, src, L::BSTAGE, B_FULL(stage));
+                    if (++stage == (uint32_t)S) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
                 }
             }
             PROF_FLUSH(0, true);
         }
-    } else if (warp == TC_MISC_WARP0 + 1) {
+      } else if (warp == TC_MISC_WARP0 + 1) {
         // ===================== MMA issuer =====================
         // The whole warp runs the loop convergently (so addresses and descriptors live in uniform registers and
         // the waits are warp-wide); one elected lane issues the tcgen05 instructions.
         {
-            constexpr uint32_t IDESC = idesc_tf32(TC_BM, TC_BN);
-            uint32_t g = 0, pi = 0;
+            constexpr uint32_t IDESC = idesc_tf32(TC_BM, BN);
+            const uint32_t tmem_b = *(volatile uint32_t *)sTmem;     // role-local copy (the kernel-wide one is spilled)
+            const uint32_t sb0 = smem_u32(sB);
+            uint32_t g = 0, pi = 0, stage = 0, phase = 0;
             PROF_DECL;
             for (int64_t pair = blockIdx.x; pair < p.npairs; pair += gridDim.x, pi++) {
                 PROF(0);
@@ -325,26 +341,24 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                 PROF(1);   // prof[8+1]: MMA wait A_FULL
                 tc_fence_after();
                 for (int s = 0; s < nsteps; s++, g++) {
-                    const int stage = g % S;
-                    const uint32_t u = g / S;
                     PROF(0);
-                    mbar_wait(B_FULL(stage), u & 1);
+                    mbar_wait(B_FULL(stage), phase);
                     PROF(2);   // prof[8+2]: MMA wait B_FULL
                     tc_fence_after();
-                    const uint32_t b_addr = smem_u32(sB + (size_t)stage * L::BSTAGE);
+                    const uint32_t b_addr = sb0 + stage * L::BSTAGE;
 #pragma unroll
                     for (int t = 0; t < 2; t++) {
-                        const uint32_t job = 2 * g + t;                  // (step, row tile) jobs share a ring of NSLOT slots
-                        const uint32_t sl = job % L::NSLOT, use = job / L::NSLOT;
+                        // row tile t owns slots 2t and 2t+1 and alternates between them step by step
+                        const uint32_t sl = 2 * t + (g & 1);
                         PROF(0);
-                        mbar_wait(ACC_EMPTY(sl), (use & 1) ^ 1);
+                        mbar_wait(ACC_EMPTY(sl), ((g >> 1) & 1) ^ 1);
                         PROF(3);   // prof[8+3]: MMA wait ACC_EMPTY
                         tc_fence_after();
                         if (elect_one()) {
 #pragma unroll
                             for (int ks = 0; ks < KSTEPS; ks++) {
-                                const uint64_t bd = smem_desc(b_addr + ks * 2 * TC_LBO_B, TC_LBO_B, TC_SBO);
-                                umma_tf32_ts(tmem_base + sl * TC_BN, tmem_base + L::ACOL + t * DP + ks * 8, bd, IDESC,
+                                const uint64_t bd = smem_desc(b_addr + ks * 2 * L::LBO_B, L::LBO_B, TC_SBO);
+                                umma_tf32_ts(tmem_b + sl * BN, tmem_b + L::ACOL + t * DP + ks * 8, bd, IDESC,
                                              ks > 0 ? 1u : 0u);
                             }
                             umma_commit(ACC_FULL(sl));
@@ -354,6 +368,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                     }
                     if (elect_one()) umma_commit(B_EMPTY(stage));
                     __syncwarp();
+                    if (++stage == (uint32_t)S) {
+                        stage = 0;
+                        phase ^= 1;
+                    }
                 }
                 if (elect_one()) umma_commit(A_EMPTY);
                 __syncwarp();
@@ -361,19 +379,19 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             PROF(0);       // prof[8+0]: MMA issue + everything else
             PROF_FLUSH(8, lane == 0);
         }
-    } else if (warp >= TC_MISC_WARP0) {
-        // TMEM allocator warp and the spare warp: nothing to do until teardown
+      }
+      // TMEM allocator warp and the spare warp: nothing to do until teardown
     } else if (warp >= TC_PROD_WARP0) {
         // ===================== feature producers + re-rankers (256 threads) =====================
         setmaxnreg_inc<TC_REGS_PROD>();
         const int ptid = tid - TC_PROD_WARP0 * 32;
         const int NC = DP - D < 3 ? DP - D : 3;
         // Mapping: producer warp pw owns rows pw*32 .. pw*32+31 of the pass, lane <-> column (kk = lane + 32*h).
-        // Loads are coalesced per row, every smem offset below is a per-thread base plus an immediate, and
-        // with the 16-byte skew of TC_LBO_A the 32 lanes of a store hit 32 different banks.
-        constexpr int NH = DP > 32 ? 2 : 1;                       // D <= 30 needs one column group
+        // Global loads are coalesced per row and every smem offset below is a per-thread base plus an immediate.
+        constexpr int NH = DP > 32 ? 2 : 1;                       // column groups of 32 (D <= 64)
         const int pw = warp - TC_PROD_WARP0;
         float xr[32 * NH];
+        float wr = 0.f;
         auto prefetch = [&](int64_t pair) {
             const int64_t r0 = pair * TC_PR + pw * 32;
             if (p.rows == nullptr && r0 + 32 <= p.n) {
@@ -384,6 +402,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
 #pragma unroll
                     for (int h = 0; h < NH; h++) xr[r * NH + h] = (lane + 32 * h < D) ? xp[r * D + 32 * h] : 0.f;
                 }
+                wr = p.w ? p.w[r0 + lane] : 1.f;
             } else {
 #pragma unroll
                 for (int r = 0; r < 32; r++) {
@@ -394,15 +413,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
 #pragma unroll
                     for (int h = 0; h < NH; h++) xr[r * NH + h] = (valid && lane + 32 * h < D) ? xp[32 * h] : 0.f;
                 }
+                const int64_t gl = r0 + lane;
+                wr = 0.f;
+                if (gl < p.n) {
+                    const int64_t src = p.rows ? p.rows[gl] : gl;
+                    wr = p.w ? p.w[src] : 1.f;
+                }
             }
         };
-        float mu_l[NH];
-#pragma unroll
-        for (int h = 0; h < NH; h++) mu_l[h] = lane + 32 * h < D ? p.mu[lane + 32 * h] : 0.f;
         // warp pw owns rows pw*32..+31 of the pass in both mappings: lane <-> column for the global loads and the
-        // scratch stores, lane <-> row (= TMEM lane, this warp's quarter pw & 3 of tile pw >> 2) for the A operand
-        float *xs_w = sX + (pw * 32) * L::XS;
-        const uint32_t a_tmem = tmem_base + ((uint32_t)((pw & 3) * 32) << 16) + L::ACOL + (pw >> 2) * DP;
+        // staging stores, lane <-> row (= TMEM lane, this warp's quarter pw & 3 of tile pw >> 2) for the A operand
+        const uint32_t a_tmem = *(volatile uint32_t *)sTmem + ((uint32_t)((pw & 3) * 32) << 16) + L::ACOL + (pw >> 2) * DP;
         const float cmax = __int_as_float(p.hdr->cmax_bits);
         const bool force_fb = p.hdr->force_fallback != 0;
         const bool need_dist = p.out_dist != nullptr;
@@ -412,42 +433,47 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
         // ---- re-rank of one finished pass: queue -> exact distances -> per-row minimum -> outputs ----
         auto rerank = [&](int64_t pair, uint32_t rp) {
             const int qb = rp & 1;
+            const float *xq = sX + qb * (TC_PR * L::XS);                    // the staged raw rows of that pass
             mbar_wait_backoff(Q_FULL(qb), (rp >> 1) & 1);
             PROF(6);   // prof[16+6]: re-rank wait Q_FULL
             sBest[ptid] = ((unsigned long long)__float_as_uint(FLT_MAX)) << 32;      // (FLT_MAX, code 0)
             named_bar_sync(1, TC_PR);
+#ifdef C3VQ_TC_EXP_NORERANK   // experiment: no exact re-rank, no outputs (results are garbage)
+            const uint32_t nq = 0;
+#else
             const uint32_t nq = min(sQCount[qb], (uint32_t)TC_QCAP);
+#endif
             const uint32_t *queue = sQueue + qb * TC_QCAP;
             const uint32_t gmask = 0xFu << (lane & ~3);
             for (uint32_t u = ptid >> 2; u < nq; u += TC_PR / 4) {
                 const uint32_t item = queue[u];
                 const int lr = item >> 16;
                 const int code = (int)(item & 0xFFFFu) * 4 + (lane & 3);
-                const int64_t gi = pair * TC_PR + lr;
-                const int64_t src = p.rows ? p.rows[gi] : gi;
-                const float *xg = p.x + src * D;
+                const float *xg = xq + lr * L::XS;
                 unsigned long long key = ~0ull;
                 if (code < p.k) {
                     const float4 *cp = reinterpret_cast<const float4 *>(p.cbp + (size_t)code * p.dpc);
                     float a = 0.f;
                     if (DCONST > 0) {
+                        float4 cv[DCONST > 0 ? (DCONST + 3) / 4 : 1];
+#pragma unroll
+                        for (int c4 = 0; c4 < (DCONST + 3) / 4; c4++) cv[c4] = __ldg(cp + c4);
 #pragma unroll
                         for (int c4 = 0; c4 < (DCONST + 3) / 4; c4++) {
-                            const float4 cv = __ldg(cp + c4);
                             float df;
-                            if (4 * c4 + 0 < D) { df = __ldg(xg + 4 * c4 + 0) - cv.x; a = fmaf(df, df, a); }
-                            if (4 * c4 + 1 < D) { df = __ldg(xg + 4 * c4 + 1) - cv.y; a = fmaf(df, df, a); }
-                            if (4 * c4 + 2 < D) { df = __ldg(xg + 4 * c4 + 2) - cv.z; a = fmaf(df, df, a); }
-                            if (4 * c4 + 3 < D) { df = __ldg(xg + 4 * c4 + 3) - cv.w; a = fmaf(df, df, a); }
+                            if (4 * c4 + 0 < D) { df = xg[4 * c4 + 0] - cv[c4].x; a = fmaf(df, df, a); }
+                            if (4 * c4 + 1 < D) { df = xg[4 * c4 + 1] - cv[c4].y; a = fmaf(df, df, a); }
+                            if (4 * c4 + 2 < D) { df = xg[4 * c4 + 2] - cv[c4].z; a = fmaf(df, df, a); }
+                            if (4 * c4 + 3 < D) { df = xg[4 * c4 + 3] - cv[c4].w; a = fmaf(df, df, a); }
                         }
                     } else {
                         for (int c4 = 0; c4 < p.dpc / 4; c4++) {
                             const float4 cv = __ldg(cp + c4);
                             float df;
-                            if (4 * c4 + 0 < D) { df = __ldg(xg + 4 * c4 + 0) - cv.x; a = fmaf(df, df, a); }
-                            if (4 * c4 + 1 < D) { df = __ldg(xg + 4 * c4 + 1) - cv.y; a = fmaf(df, df, a); }
-                            if (4 * c4 + 2 < D) { df = __ldg(xg + 4 * c4 + 2) - cv.z; a = fmaf(df, df, a); }
-                            if (4 * c4 + 3 < D) { df = __ldg(xg + 4 * c4 + 3) - cv.w; a = fmaf(df, df, a); }
+                            if (4 * c4 + 0 < D) { df = xg[4 * c4 + 0] - cv.x; a = fmaf(df, df, a); }
+                            if (4 * c4 + 1 < D) { df = xg[4 * c4 + 1] - cv.y; a = fmaf(df, df, a); }
+                            if (4 * c4 + 2 < D) { df = xg[4 * c4 + 2] - cv.z; a = fmaf(df, df, a); }
+                            if (4 * c4 + 3 < D) { df = xg[4 * c4 + 3] - cv.w; a = fmaf(df, df, a); }
                         }
                     }
                     // distances are sums of squares from +0: non-negative or NaN; as unsigned bit patterns
@@ -465,8 +491,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             // ---- outputs: two rows per warp step (half warp each), lanes over 16-byte accumulator chunks ----
             const int half = lane >> 4, hl = lane & 15;
             const int nchunk = p.acc_stride >> 2;
-#pragma unroll 1
+#ifdef C3VQ_TC_EXP_NORERANK
+            for (int rr = 32; rr < 32; rr += 2) {
+#else
+#pragma unroll 4
             for (int rr = 0; rr < 32; rr += 2) {
+#endif
                 const int lr = pw * 32 + rr + half;
                 const uint8_t st0 = sFlag[(qb * 2 + 0) * TC_PR + lr], st1 = sFlag[(qb * 2 + 1) * TC_PR + lr];
                 const uint8_t status = st0 > st1 ? st0 : st1;
@@ -474,22 +504,21 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                 if (status == ROW_OK) {
                     const unsigned long long best = sBest[lr];
                     const int bj = (int)(best & 0xFFFFFFFFu);
-                    const int64_t src = p.rows ? p.rows[gi] : gi;
                     if (hl == 0) {
                         st_rows++;
                         if (p.out_idx) p.out_idx[gi] = bj;
                         if (need_dist) p.out_dist[gi] = __uint_as_float((unsigned int)(best >> 32));
                     }
                     if (p.acc) {
-                        const float wv = p.w ? __ldg(p.w + src) : 1.f;
-                        const float *xg = p.x + src * D;
+                        const float wv = sW[qb * TC_PR + lr];
+                        const float *xg = xq + lr * L::XS;
                         float *ap = p.acc + (size_t)bj * p.acc_stride;
                         for (int ch = hl; ch < nchunk; ch += 16) {
                             float e4[4];
 #pragma unroll
                             for (int i = 0; i < 4; i++) {
                                 const int kk = 4 * ch + i;
-                                e4[i] = kk < D ? __fmul_rn(__ldg(xg + kk), wv) : (kk == D ? wv : 0.f);
+                                e4[i] = kk < D ? __fmul_rn(xg[kk], wv) : (kk == D ? wv : 0.f);
                             }
                             red_add_v4(ap + 4 * ch, e4[0], e4[1], e4[2], e4[3]);
                         }
@@ -503,25 +532,29 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             }
             __syncwarp();
             if (ptid == 0) sQCount[qb] = 0;       // every thread has read nq (barrier above)
-            mbar_arrive(Q_EMPTY(qb));
+            if (lane == 0) mbar_arrive(Q_EMPTY(qb));
         };
 
         uint32_t pi = 0;
         int64_t prev_pair = -1;
-        // software pipeline with ONE prefetch call site (two would make the 64 prefetch registers spill):
+        // software pipeline with ONE prefetch call site (two would make the prefetch registers spill):
         // iteration -1 only prefetches the first pass
         for (int64_t pair = (int64_t)blockIdx.x - gridDim.x;; pair += gridDim.x) {
           if (pair >= 0) {
             PROF(0);
-            // transpose through shared memory: centred, TF32-rounded values, row stride XS (odd: conflict free both ways)
+            // stage the raw rows (exact fp32: the re-rank and the weighted sums of this pass read them back);
+            // row stride XS is odd, so both the lane <-> column stores and the lane <-> row loads are conflict free.
+            // Buffer pi & 1 was last read by the re-rank of pass pi - 2, which every producer warp has left
+            // (its second named barrier) before any warp arrives here.
+            float *xs_w = sX + ((pi & 1) * TC_PR + pw * 32) * L::XS;
             __syncwarp();
 #pragma unroll
             for (int r = 0; r < 32; r++) {
 #pragma unroll
                 for (int h = 0; h < NH; h++)
-                    if (lane + 32 * h < D)
-                        xs_w[r * L::XS + lane + 32 * h] = __uint_as_float(to_tf32(xr[r * NH + h] - mu_l[h]));
+                    if (lane + 32 * h < D) xs_w[r * L::XS + lane + 32 * h] = xr[r * NH + h];
             }
+            sW[(pi & 1) * TC_PR + ptid] = wr;
             __syncwarp();
             uint32_t av[DP];
             float X = 0.f;                       // |x'|^2 of the rounded, centred row -> error band
@@ -529,7 +562,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             for (int kk = 0; kk < DP; kk++) {
                 float v = (kk < D + NC) ? 1.0f : 0.f;        // 1.0 against the norm pieces, 0 beyond
                 if (kk < D) {
-                    v = xs_w[lane * L::XS + kk];
+                    v = __uint_as_float(to_tf32(xs_w[lane * L::XS + kk] - sMu[kk]));
                     X = fmaf(v, v, X);
                 }
                 av[kk] = __float_as_uint(v);
@@ -544,14 +577,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                 if (!(X < TC_HUGE2 * 0.0625f) || force_fb || !(band < TC_BIG))
                     band = __int_as_float(0x7fc00000);                        // NaN: exact fallback
                 if (gi >= p.n) band = -1.f;
-                if (p.dbg_norm2 && gi < p.n) {
+                if (DBG && gi < p.n) {
                     p.dbg_norm2[gi] = X;
                     p.dbg_band[gi] = band;
                 }
                 sBand[(pi & 1) * TC_PR + ptid] = band;
             }
-            PROF(2);   // prof[16+2]: producer convert + transpose + band
-            mbar_wait_backoff(A_EMPTY, (pi & 1) ^ 1);  // previous pass' MMAs no longer read the A operand in TMEM
+            PROF(2);   // prof[16+2]: producer stage + convert + band
+            mbar_wait(A_EMPTY, (pi & 1) ^ 1);          // previous pass' MMAs no longer read the A operand in TMEM
             PROF(1);   // prof[16+1]: producer wait A_EMPTY
             tc_fence_after();
 #pragma unroll
@@ -562,7 +595,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             }
             tmem_wait_st();
             tc_fence_before();
-            mbar_arrive(A_FULL);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(A_FULL);
             PROF(7);   // prof[16+7]: A operand -> TMEM
             if (prev_pair >= 0) rerank(prev_pair, pi - 1);
             PROF(3);   // prof[16+3]: re-rank + outputs of the previous pass (includes waiting for its queue)
@@ -587,50 +621,53 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             if (pw == 0) atomicAdd(&p.hdr->cands, st_cands);
         }
     } else {
-        // ===================== drain: TMEM scan, running minimum, group lists, work queue =====================
-        setmaxnreg_dec<TC_REGS_DRAIN>();
+        // ===================== drain: TMEM scan, running minimum, chunk lists, work queue =====================
+        // Warp (tile t, lane quarter q, parity b) reads every column of slot 2t + b, i.e. the steps with
+        // (global step & 1) == b: two threads per row, each seeing every other BN-code block of the codebook.
+        if (TC_REGS_DRAIN < 72) setmaxnreg_dec<TC_REGS_DRAIN < 72 ? TC_REGS_DRAIN : 64>();
+        constexpr int NGH = BN / 8;                     // groups of 4 codes per half job (12 or 8)
         const int dw = warp - TC_DRAIN_WARP0;           // 0..15
         const int q = warp & 3;                         // TMEM lane quarter this warp may access
         const int t = (dw >> 2) & 1;                    // row tile
-        const int h = dw >> 3;                          // column half of every accumulator slot
-        const int lr = t * TC_BM + q * 32 + lane;       // local row 0..255 (shared with the other half's thread)
+        const int h = dw >> 3;                          // step parity served by this warp
+        const int lr = t * TC_BM + q * 32 + lane;       // local row 0..255 (shared with the other parity's thread)
         const int dl = dw * 32 + lane;                  // drain thread 0..511 (list column)
-        const uint32_t tsrc = tmem_base + ((uint32_t)(q * 32) << 16) + h * (TC_BN / 2);
+        const uint32_t tsrc = *(volatile uint32_t *)sTmem + ((uint32_t)(q * 32) << 16) + (2 * t + h) * BN;
+        const uint32_t acc_full = ACC_FULL(2 * t + h), acc_empty = ACC_EMPTY(2 * t + h);
         uint32_t *listS = sListS + dl, *listP = sListP + dl;
         const uint32_t lS = smem_u32(listS), lP = smem_u32(listP);
-        constexpr uint32_t LIST_STRIDE = TC_DT * 4, LIST_END = TC_LCAP * LIST_STRIDE;
-        static_assert(TC_BN == 128, "the drain reads two 32-column chunks per half slot");
-        uint32_t g = 0, pi = 0;
+        constexpr uint32_t LIST_STRIDE = TC_DT * 4, LIST_END = L::LCAP * LIST_STRIDE;
+        uint32_t g0 = 0, pi = 0;                        // g0: global step counter at the start of the pass
         PROF_DECL;
-        for (int64_t pair = blockIdx.x; pair < p.npairs; pair += gridDim.x, pi++) {
+        for (int64_t pair = blockIdx.x; pair < p.npairs; pair += gridDim.x, pi++, g0 += nsteps) {
             const int64_t gi = pair * TC_PR + lr;
             PROF(0);
             mbar_wait(A_FULL, pi & 1);
             PROF(1);       // prof[24+1]: drain wait A_FULL
-            const float band = sBand[(pi & 1) * TC_PR + lr];      // computed by the producer of this row
+            float band = sBand[(pi & 1) * TC_PR + lr];            // computed by the producer of this row
             float m = 3.0e38f;
             // valid rows start at 2^124: above every real score, below the 2^126 of dead / padding codes
             float thr = (band >= 0.f) ? 0.25f * TC_BIG : __int_as_float(0xff800000);
             uint32_t cnt_off = 0;                       // byte offset of the next free list entry
-            bool ovf = false;
-            const bool dbg = p.dbg_scores != nullptr && gi < p.n;
             PROF(2);       // prof[24+2]: drain band
 
-            // eight group minima of a 32-column chunk (FMNMX3 + FMNMX per group)
-            auto groups = [&](const uint32_t (&a)[16], const uint32_t (&b)[16], float (&gm)[8]) {
+            // group minima of a 16-column chunk (FMNMX3 + FMNMX per group)
+            auto groups = [&](const uint32_t (&a)[16], float *gm) {
                 gm[0] = min4(a[0], a[1], a[2], a[3]);
                 gm[1] = min4(a[4], a[5], a[6], a[7]);
                 gm[2] = min4(a[8], a[9], a[10], a[11]);
                 gm[3] = min4(a[12], a[13], a[14], a[15]);
-                gm[4] = min4(b[0], b[1], b[2], b[3]);
-                gm[5] = min4(b[4], b[5], b[6], b[7]);
-                gm[6] = min4(b[8], b[9], b[10], b[11]);
-                gm[7] = min4(b[12], b[13], b[14], b[15]);
             };
-            // chunk minimum against the running threshold; the append path is entered per WARP (uniform branch)
-            auto process = [&](const float (&gv)[8], int code0) {
-                const float cm = fminf(fminf(fminf(fminf(gv[0], gv[1]), gv[2]), fminf(fminf(gv[3], gv[4]), gv[5])),
-                                       fminf(gv[6], gv[7]));
+            // half-job minimum against the running threshold; the append path is entered per WARP (uniform branch)
+            auto process = [&](const float (&gv)[NGH], uint32_t chunk) {
+                float cm = fminf(fminf(gv[0], gv[1]), gv[2]);
+#pragma unroll
+                for (int i = 3; i + 1 < NGH; i += 2) cm = fminf(fminf(cm, gv[i]), gv[i + 1]);
+                if (NGH % 2 == 0) cm = fminf(cm, gv[NGH - 1]);
+#ifdef C3VQ_TC_EXP_NOPROC     // experiment: running minimum only, no candidate lists (results are garbage)
+                m = fminf(m, cm);
+                return;
+#endif
                 const bool flag = cm <= thr;
                 if (__any_sync(0xffffffffu, flag)) {
                     if (flag) {
@@ -638,7 +675,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                         thr = m + p.gamma2 * fabsf(m) + band;
                         uint32_t gm = 0;
 #pragma unroll
-                        for (int i = 0; i < 8; i++) gm |= (gv[i] <= thr) ? (1u << i) : 0u;
+                        for (int i = 0; i < NGH; i++) gm |= (gv[i] <= thr) ? (1u << i) : 0u;
                         if (cnt_off == LIST_END) {      // full: drop entries the tighter threshold excludes
                             uint32_t wpos = 0;
                             for (uint32_t e = 0; e < LIST_END; e += LIST_STRIDE) {
@@ -653,49 +690,76 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                         }
                         if (cnt_off < LIST_END) {
                             st_shared_u32(lS + cnt_off, __float_as_uint(cm));
-                            st_shared_u32(lP + cnt_off, ((uint32_t)(code0 >> 5) << 8) | gm);
+                            st_shared_u32(lP + cnt_off, (chunk << 12) | gm);
                             cnt_off += LIST_STRIDE;
                         } else {
-                            ovf = true;
+                            band = __int_as_float(0x7fc00000);   // overflow: NaN band = exact fallback for this row
+                            thr = band;                          // and nothing is appended any more
                         }
                     }
                 }
             };
-            auto dump = [&](const uint32_t (&a)[16], const uint32_t (&b)[16], int code0) {   // debug only
+            auto dump = [&](const uint32_t (&a)[16], int code0) {   // debug build of the kernel only
 #pragma unroll
-                for (int jj = 0; jj < 16; jj++) {
-                    if (code0 + jj < p.k) p.dbg_scores[gi * p.k + code0 + jj] = __uint_as_float(a[jj]);
-                    if (code0 + 16 + jj < p.k) p.dbg_scores[gi * p.k + code0 + 16 + jj] = __uint_as_float(b[jj]);
-                }
+                for (int jj = 0; jj < 16; jj++)
+                    if (gi < p.n && code0 + jj < p.k) p.dbg_scores[gi * p.k + code0 + jj] = __uint_as_float(a[jj]);
             };
 
-            for (int s = 0; s < nsteps; s++, g++) {
-                const uint32_t job = 2 * g + t;
-                const uint32_t sl = job % L::NSLOT, use = job / L::NSLOT;
+            for (int s = (int)((g0 ^ (uint32_t)h) & 1u); s < nsteps; s += 2) {
+                const uint32_t use = (g0 + (uint32_t)s) >> 1;
                 PROF(4);   // prof[24+4]: drain (LDTM + min + lists)
-                mbar_wait_hint(ACC_FULL(sl), use & 1);
+                mbar_wait_hint(acc_full, use & 1);
                 PROF(3);   // prof[24+3]: drain wait ACC_FULL
                 tc_fence_after();
-                const uint32_t ta = tsrc + sl * TC_BN;
-                const int code_s = s * TC_BN + h * (TC_BN / 2);
+                const int code_s = s * BN;
+#ifdef C3VQ_TC_EXP_NODRAIN   // experiment: hand the slot straight back (results are garbage)
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(acc_empty);
+                continue;
+#endif
                 uint32_t va[16], vb[16];
-                float gv[8];
-                tmem_ld16_async(ta, va);
-                tmem_ld16_async(ta + 16, vb);
+                float gv[NGH];
+                tmem_ld16_async(tsrc, va);
+                tmem_ld16_async(tsrc + 16, vb);
                 tmem_wait_ld16(va);
                 tmem_wait_ld16(vb);
-                if (dbg) dump(va, vb, code_s);
-                groups(va, vb, gv);
-                tmem_ld16_async(ta + 32, va);           // second chunk in flight while the first is judged
-                tmem_ld16_async(ta + 48, vb);
-                process(gv, code_s);
-                tmem_wait_ld16(va);
-                tmem_wait_ld16(vb);
-                tc_fence_before();                      // accumulator slot fully read: hand it back to the MMA warp
-                mbar_arrive(ACC_EMPTY(sl));
-                if (dbg) dump(va, vb, code_s + 32);
-                groups(va, vb, gv);
-                process(gv, code_s + 32);
+                if (DBG) { dump(va, code_s); dump(vb, code_s + 16); }
+                groups(va, gv);
+                tmem_ld16_async(tsrc + 32, va);
+                groups(vb, gv + 4);
+                if (BN == 96) {
+                    tmem_ld16_async(tsrc + 48, vb);
+                    tmem_wait_ld16(va);
+                    tmem_wait_ld16(vb);
+                    if (DBG) { dump(va, code_s + 32); dump(vb, code_s + 48); }
+                    groups(va, gv + 8);
+                    tmem_ld16_async(tsrc + 64, va);
+                    process(gv, (uint32_t)(2 * s));
+                    groups(vb, gv);
+                    tmem_ld16_async(tsrc + 80, vb);
+                    tmem_wait_ld16(va);
+                    tmem_wait_ld16(vb);
+                    tc_fence_before();                  // accumulator slot fully read: hand it back to the MMA warp
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(acc_empty);
+                    if (DBG) { dump(va, code_s + 64); dump(vb, code_s + 80); }
+                    groups(va, gv + 4);
+                    groups(vb, gv + 8);
+                    process(gv, (uint32_t)(2 * s + 1));
+                } else {                                // BN == 64: two half jobs of 32 columns
+                    tmem_ld16_async(tsrc + 48, vb);
+                    process(gv, (uint32_t)(2 * s));
+                    tmem_wait_ld16(va);
+                    tmem_wait_ld16(vb);
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(acc_empty);
+                    if (DBG) { dump(va, code_s + 32); dump(vb, code_s + 48); }
+                    groups(va, gv);
+                    groups(vb, gv + 4);
+                    process(gv, (uint32_t)(2 * s + 1));
+                }
             }
             const int cnt = (int)(cnt_off / LIST_STRIDE);
             PROF(4);
@@ -706,9 +770,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             uint8_t status = ROW_OK;
             if (gi >= p.n)
                 status = ROW_SKIP;
-            else if (!(band >= 0.f) || ovf)
+            else if (!(band >= 0.f))
                 status = ROW_FALLBACK;
-            // the two column halves of a row exchange their running minima: both filter with the row's threshold
+            // the two threads of a row exchange their running minima: both filter with the row's threshold
             sXchg[(qb * 2 + h) * TC_PR + lr] = m;             // double buffered: one barrier per pass is enough
             named_bar_sync(2, TC_DT);
             m = fminf(m, sXchg[(qb * 2 + (h ^ 1)) * TC_PR + lr]);
@@ -718,8 +782,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                 for (int e = 0; e < cnt; e++) {
                     if (!(__uint_as_float(listS[e * TC_DT]) <= thr)) continue;
                     const uint32_t ep = listP[e * TC_DT];
-                    uint32_t gm = ep & 0xFFu;
-                    const uint32_t grp0 = (ep >> 8) * 8;         // first group (code / 4) of the 32-column chunk
+                    uint32_t gm = ep & 0xFFFu;
+                    const uint32_t grp0 = (ep >> 12) * NGH;      // first group (code / 4) of the half job
                     while (gm) {
                         const int bit = __ffs(gm) - 1;
                         gm &= gm - 1;
@@ -734,7 +798,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                 }
             }
             sFlag[(qb * 2 + h) * TC_PR + lr] = status;
-            mbar_arrive(Q_FULL(qb));
+            __syncwarp();
+            if (lane == 0) mbar_arrive(Q_FULL(qb));
             PROF(6);       // prof[24+6]: drain queue push
         }
         PROF_FLUSH(24, tid == TC_DRAIN_WARP0 * 32);
@@ -744,7 +809,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
     __syncthreads();
     if (warp == TC_MISC_WARP0 + 2) {
         tc_fence_after();
-        tmem_dealloc(tmem_base, 512);
+        tmem_dealloc(*(volatile uint32_t *)sTmem, 512);
     }
 }
 
@@ -800,7 +865,7 @@ static inline size_t al256(size_t v) { return (v + 255) & ~(size_t)255; }
 
 struct TcLayout {
     size_t off_mu, off_bimg, off_cbp, off_fb, total;
-    int dp, nc, dpc, k_pad;
+    int dp, nc, dpc, k_pad, bn;
 };
 
 static TcLayout tc_layout(int64_t n, int d, int k)
@@ -809,8 +874,9 @@ static TcLayout tc_layout(int64_t n, int d, int k)
     l.dp = tc_dp(d);
     l.nc = tc_nc(d);
     l.dpc = (d + 3) & ~3;
-    l.k_pad = (k + TC_BN - 1) / TC_BN * TC_BN;
-    if (l.k_pad == 0) l.k_pad = TC_BN;
+    l.bn = tc_bn(l.dp);
+    l.k_pad = (k + l.bn - 1) / l.bn * l.bn;
+    if (l.k_pad == 0) l.k_pad = l.bn;
     size_t o = al256(sizeof(TcHeader));
     l.off_mu = o;
     o += al256(80 * sizeof(float));
@@ -830,9 +896,10 @@ size_t tc_workspace_bytes(int64_t n, int d, int k)
     return tc_layout(n, d, k).total;
 }
 
-template <int DP, int DCONST>
+template <int DP, int DCONST, bool DBG = false>
 static int launch_tc_t(const TcParams &p, int grid, cudaStream_t s)
 {
+    if (!DBG && DCONST == 0 && p.dbg_scores != nullptr) return launch_tc_t<DP, 0, true>(p, grid, s);
     using L = TcSmem<DP>;
     TcParams q = p;
     q.nstages = L::stages();
@@ -841,8 +908,8 @@ static int launch_tc_t(const TcParams &p, int grid, cudaStream_t s)
         return C3VQ_EINVAL;
     }
     const size_t smem = L::bytes(q.nstages);
-    C3VQ_CUDA(cudaFuncSetAttribute(k_assign_tc<DP, DCONST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_assign_tc<DP, DCONST><<<grid, TC_THREADS, smem, s>>>(q);
+    C3VQ_CUDA(cudaFuncSetAttribute(k_assign_tc<DP, DCONST, DBG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_assign_tc<DP, DCONST, DBG><<<grid, TC_THREADS, smem, s>>>(q);
     C3VQ_LAUNCH_CHECK("k_assign_tc");
     return C3VQ_OK;
 }
@@ -870,13 +937,13 @@ int launch_assign_tc(const float *x, const float *w, const int64_t *rows, int64_
     C3VQ_CUDA(cudaMemsetAsync(hdr, 0, sizeof(TcHeader), s));
     k_tc_prep_mean<<<(k + 127) / 128, 256, 0, s>>>(codebook, k, d, hdr);
     C3VQ_LAUNCH_CHECK("k_tc_prep_mean");
-    k_tc_prep_image<<<(l.k_pad + 127) / 128, 128, 0, s>>>(codebook, k, l.k_pad, d, l.dp, l.nc, l.dpc, hdr, mu, bimg,
-                                                        cbp);
+    k_tc_prep_image<<<(l.k_pad + 127) / 128, 128, 0, s>>>(codebook, k, l.k_pad, d, l.dp, l.nc, l.dpc, l.bn, hdr, mu,
+                                                        bimg, cbp);
     C3VQ_LAUNCH_CHECK("k_tc_prep_image");
 
     TcParams p{};
     p.x = x; p.w = w; p.rows = rows; p.n = n; p.d = d; p.k = k;
-    p.nsteps = l.k_pad / TC_BN;
+    p.nsteps = l.k_pad / l.bn;
     p.npairs = (n + TC_PR - 1) / TC_PR;
     p.bimg = bimg; p.cbp = cbp; p.dpc = l.dpc; p.mu = mu; p.hdr = hdr;
     p.out_dist = out_dist; p.out_idx = out_idx; p.acc = acc; p.acc_stride = acc_stride(d);
@@ -890,7 +957,7 @@ int launch_assign_tc(const float *x, const float *w, const int64_t *rows, int64_
 #ifdef C3VQ_TC_SINGLE   // developer build: one instantiation only (fast compile, SASS inspection)
     rc = launch_tc_t<48, 45>(p, grid, s);
 #else
-    switch (d) {
+    switch (dbg_scores ? -1 : d) {      // the debug build of the kernel exists for the generic widths only
         case 6: rc = launch_tc_t<8, 6>(p, grid, s); break;
         case 7: rc = launch_tc_t<16, 7>(p, grid, s); break;
         case 45: rc = launch_tc_t<48, 45>(p, grid, s); break;
