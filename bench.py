@@ -195,6 +195,8 @@ def main():
     ap.add_argument("--rows", type=int, default=5_800_000, help="rows per GPU (default: configs[1])")
     ap.add_argument("--dim", type=int, default=45)
     ap.add_argument("--simt", action="store_true", help="use the SIMT exact assignment instead of tensor cores")
+    ap.add_argument("--sums", default="sorted", choices=["sorted", "fused"],
+                    help="centroid sums: sorted segmented sum after the assignment (default) or fused bulk reduce-adds")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
 
@@ -229,10 +231,11 @@ def main():
     wn = (w / wmax).contiguous()
     cb0 = init_codebook(x, K, 99)                       # same seed on every rank -> identical replicas
     ops = CudaOps()
-    ops.tensor_cores = not args.simt
+    ops.tensor_cores = False if args.simt else ("fused" if args.sums == "fused" else True)
     vq = ShardedVectorQuantize(d, K, DECAY, device=dev, ops=ops)
 
     ev_pairs = []
+    split = (not args.simt) and args.sums == "sorted"
 
     def job(record: bool):
         """10 iterations of update over all local rows; the dominant kernel is bracketed by events."""
@@ -243,9 +246,18 @@ def main():
             if record:
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 e0.record()
-            ops.assign_accumulate(x, wn, vq.codebook, vq._acc)
+            if split:
+                # the same kernels c3vq_assign_accumulate launches, as two calls so that the assignment
+                # (prep + k_assign_tc + fallback scan) can be bracketed on its own
+                idx = _lib.assign(x, vq.codebook, return_dist=False)[1]
+                if record:
+                    e1.record()
+                _lib.accumulate(x, wn, idx, K, acc=vq._acc, sorted_path=True)
+            else:
+                ops.assign_accumulate(x, wn, vq.codebook, vq._acc)
+                if record:
+                    e1.record()
             if record:
-                e1.record()
                 ev_pairs.append((e0, e1))
             vq._all_reduce(vq._acc)
             ops.ema(vq.codebook, vq.entry_importance, vq._acc, DECAY, EPS, False)
@@ -288,7 +300,9 @@ def main():
     achieved = flops / (kern_ms * 1e-3) / 1e12
     roofline = {"bound": "tensor", "achieved": achieved, "peak": tf32_peak, "unit": "TFLOP/s",
                 "frac": achieved / tf32_peak, "traffic": None,
-                "kernel": "k_assign_exact+k_accumulate (SIMT)" if args.simt else "k_assign_tc (fused assign+sums)",
+                "kernel": "k_assign_exact+k_accumulate (SIMT)" if args.simt else
+                          ("k_assign_tc (assignment; sums by the sorted segmented-sum kernels)" if split
+                           else "k_assign_tc (fused assign+sums)"),
                 "kernel_ms": kern_ms, "kernel_share_of_step": kern_ms * ITERS / ms_per_step,
                 "peak_source": f"{pk['source']}: bf16_tflops_sustained/2 (TF32 dense = half bf16)",
                 "algorithmic_flops_per_launch": flops}
@@ -349,7 +363,8 @@ def main():
                        "decay": DECAY, "parallelism": f"rows sharded x{world}, codebook replicated, "
                                                       "1 all-reduce of K x (D+1) sums per iteration",
                        "l2": "inputs (1.04 GB per GPU) exceed the 126 MB L2; no explicit flush",
-                       "assignment": "simt-exact" if args.simt else "tcgen05-tf32+rerank"},
+                       "assignment": "simt-exact" if args.simt else "tcgen05-tf32+rerank",
+                       "sums": "atomic" if args.simt else args.sums},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
             "clocks": clocks,
         }

@@ -25,6 +25,18 @@ def default_tensor_cores() -> bool:
     kernel (same results, ~10x slower) for debugging.  Both are CUDA kernels of libc3vq.so."""
     return os.environ.get("C3VQ_ASSIGN", "tc").lower() != "simt"
 
+
+def _tc_mode(tensor_cores) -> int:
+    """use_tensor_cores argument of c3vq_update / c3vq_assign_accumulate: 0 = SIMT exact assignment + atomic sums,
+    1 = tcgen05 assignment + sorted segmented sums (default), 2 = tcgen05 assignment with the sums fused into
+    the kernel (one bulk reduce-add per row; x read once).  C3VQ_SUMS=fused selects 2 wherever True is passed."""
+    if tensor_cores == "fused" or tensor_cores == 2:
+        return 2
+    if not tensor_cores:
+        return 0
+    return 2 if os.environ.get("C3VQ_SUMS", "sorted").lower() == "fused" else 1
+
+
 _c_f32p = ctypes.c_void_p
 _c_i64 = ctypes.c_int64
 _c_int = ctypes.c_int
@@ -42,6 +54,8 @@ SIGNATURES = {
     "c3vq_assign_exact": (_c_int, [_c_vp, _c_vp, _c_i64, _c_int, _c_vp, _c_int, _c_vp, _c_vp, _c_vp]),
     "c3vq_acc_stride": (_c_int, [_c_int]),
     "c3vq_accumulate": (_c_int, [_c_vp, _c_vp, _c_vp, _c_vp, _c_i64, _c_int, _c_int, _c_vp, _c_vp]),
+    "c3vq_accumulate_sorted_workspace_bytes": (_c_sz, [_c_i64, _c_int]),
+    "c3vq_accumulate_sorted": (_c_int, [_c_vp, _c_vp, _c_vp, _c_vp, _c_i64, _c_int, _c_int, _c_vp, _c_vp, _c_sz, _c_vp]),
     "c3vq_ema": (_c_int, [_c_vp, _c_vp, _c_vp, _c_int, _c_int, _c_dbl, _c_dbl, _c_int, _c_vp]),
     "c3vq_update_workspace_bytes": (_c_sz, [_c_i64, _c_int, _c_int]),
     "c3vq_update": (_c_int, [_c_vp, _c_vp, _c_vp, _c_i64, _c_int, _c_vp, _c_vp, _c_int, _c_dbl, _c_dbl, _c_int,
@@ -181,7 +195,7 @@ def update(x: torch.Tensor, w: torch.Tensor, codebook: torch.Tensor, entry_impor
         nbytes = L.c3vq_update_workspace_bytes(n, d, k)
         ws = _workspace.get(x.device, nbytes)
         rc = L.c3vq_update(_ptr(x), _ptr(w), _ptr(rows), n, d, _ptr(codebook), _ptr(entry_importance), k,
-                           float(decay), float(eps), int(bool(scale_normalize)), int(bool(tensor_cores)),
+                           float(decay), float(eps), int(bool(scale_normalize)), _tc_mode(tensor_cores),
                            _ptr(dist), _ptr(idx), _ptr(ws), ws.numel(), _stream(x))
     if rc:
         raise _err(rc)
@@ -213,7 +227,7 @@ def assign_accumulate(x, w, codebook, acc: torch.Tensor | None = None, rows=None
         idx = torch.empty(n, dtype=torch.int64, device=x.device) if return_idx else None
         nbytes = L.c3vq_update_workspace_bytes(n, d, k)
         ws = _workspace.get(x.device, nbytes)
-        rc = L.c3vq_assign_accumulate(_ptr(x), _ptr(w), _ptr(rows), n, d, _ptr(codebook), k, int(bool(tensor_cores)),
+        rc = L.c3vq_assign_accumulate(_ptr(x), _ptr(w), _ptr(rows), n, d, _ptr(codebook), k, _tc_mode(tensor_cores),
                                       _ptr(acc), _ptr(dist), _ptr(idx), _ptr(ws), ws.numel(), _stream(x))
     if rc:
         raise _err(rc)
@@ -228,8 +242,9 @@ def acc_stride(d: int) -> int:
     return int(load().c3vq_acc_stride(int(d)))
 
 
-def accumulate(x, w, idx, k: int, acc: torch.Tensor | None = None, rows=None) -> torch.Tensor:
-    """Weighted centroid sums into acc[k, acc_stride(d)] (vq.py:31,33).  c3vq_accumulate."""
+def accumulate(x, w, idx, k: int, acc: torch.Tensor | None = None, rows=None, sorted_path: bool = False) -> torch.Tensor:
+    """Weighted centroid sums into acc[k, acc_stride(d)] (vq.py:31,33).  c3vq_accumulate, or with
+    sorted_path the atomic-free c3vq_accumulate_sorted (counting sort by codeword + segmented sum)."""
     _check(x, torch.float32, "x", 2)
     _check(idx, torch.int64, "idx", 1)
     x, idx = x.contiguous(), idx.contiguous()
@@ -247,7 +262,13 @@ def accumulate(x, w, idx, k: int, acc: torch.Tensor | None = None, rows=None) ->
             acc = torch.zeros(k, stride, dtype=torch.float32, device=x.device)
         elif acc.shape != (k, stride) or not acc.is_contiguous():
             raise RuntimeError(f"acc must be a contiguous [{k}, {stride}] float32 tensor")
-        rc = L.c3vq_accumulate(_ptr(x), _ptr(w), _ptr(rows), _ptr(idx), n, d, k, _ptr(acc), _stream(x))
+        if sorted_path:
+            nbytes = L.c3vq_accumulate_sorted_workspace_bytes(n, k)
+            ws = _workspace.get(x.device, nbytes)
+            rc = L.c3vq_accumulate_sorted(_ptr(x), _ptr(w), _ptr(rows), _ptr(idx), n, d, k, _ptr(acc), _ptr(ws),
+                                          nbytes, _stream(x))
+        else:
+            rc = L.c3vq_accumulate(_ptr(x), _ptr(w), _ptr(rows), _ptr(idx), n, d, k, _ptr(acc), _stream(x))
     if rc:
         raise _err(rc)
     return acc

@@ -96,6 +96,18 @@ int c3vq_accumulate(const float *x, const float *w, const int64_t *rows, const i
     return launch_accumulate(x, w, rows, idx, n, d, k, acc, acc_stride(d), d, (cudaStream_t)stream);
 }
 
+size_t c3vq_accumulate_sorted_workspace_bytes(int64_t n, int k) { return n < 0 || k < 0 ? 0 : seg_workspace_bytes(n, k); }
+
+int c3vq_accumulate_sorted(const float *x, const float *w, const int64_t *rows, const int64_t *idx, int64_t n, int d,
+                           int k, float *acc, void *ws, size_t ws_bytes, c3vq_stream_t stream)
+{
+    int rc = check_common(x, n, d, acc, k);
+    if (rc) return rc;
+    C3VQ_CHECK_ARG(n == 0 || idx != nullptr, "idx is null");
+    return launch_accumulate_sorted(x, w, rows, idx, n, d, k, acc, acc_stride(d), d, ws, ws_bytes,
+                                    (cudaStream_t)stream);
+}
+
 int c3vq_ema(float *codebook, float *entry_importance, const float *acc, int k, int d, double decay, double eps,
              int scale_normalize, c3vq_stream_t stream)
 {
@@ -106,12 +118,12 @@ int c3vq_ema(float *codebook, float *entry_importance, const float *acc, int k, 
 }
 
 // Workspace layout shared by c3vq_update / c3vq_assign_accumulate:
-//   [tensor-core workspace (stats first)] [acc: k*stride floats] [idx: n int64]
+//   [tensor-core workspace (stats first)] [acc: k*stride floats] [idx: n int64] [sorted-sum workspace]
 size_t c3vq_update_workspace_bytes(int64_t n, int d, int k)
 {
     if (n < 0 || d < 1 || k < 0) return 0;
     return align256(tc_workspace_bytes(n, d, k)) + align256((size_t)k * acc_stride(d) * sizeof(float)) +
-           align256((size_t)n * sizeof(int64_t));
+           align256((size_t)n * sizeof(int64_t)) + align256(seg_workspace_bytes(n, k));
 }
 
 static int assign_accumulate_impl(const float *x, const float *w, const int64_t *rows, int64_t n, int d,
@@ -122,10 +134,19 @@ static int assign_accumulate_impl(const float *x, const float *w, const int64_t 
     if (n == 0 || k == 0) return C3VQ_OK;
     int64_t *idx = out_idx ? out_idx : idx_buf;
     int rc;
-    if (use_tensor_cores) {
-        // fused: the assignment kernel scatters w*x of every finished row tile itself
+    if (use_tensor_cores == 2) {
+        // fused: the assignment kernel adds w*x of every finished row itself (one bulk reduce per row); reads x
+        // once, but is bounded by the L2's fp32 reduction rate for wide rows
         rc = launch_assign_tc(x, w, rows, n, d, codebook, k, out_dist, idx, acc, nullptr, nullptr, nullptr, tc_ws,
                               tc_bytes, s);
+    } else if (use_tensor_cores) {
+        // tensor-core assignment, then the atomic-free sorted segmented sum (second pass over x)
+        rc = launch_assign_tc(x, nullptr, rows, n, d, codebook, k, out_dist, idx, nullptr, nullptr, nullptr, nullptr,
+                              tc_ws, tc_bytes, s);
+        if (rc) return rc;
+        void *seg_ws = (char *)idx_buf + align256((size_t)n * sizeof(int64_t));
+        rc = launch_accumulate_sorted(x, w, rows, idx, n, d, k, acc, acc_stride(d), d, seg_ws,
+                                      seg_workspace_bytes(n, k), s);
     } else {
         rc = launch_assign_exact(x, rows, n, d, codebook, k, out_dist, idx, s);
         if (rc) return rc;

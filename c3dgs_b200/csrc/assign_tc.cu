@@ -55,7 +55,7 @@ constexpr int TC_BM = 128;            // rows per UMMA tile
 constexpr int TC_PR = 2 * TC_BM;      // rows per CTA pass ("pair" of tiles)
 // codes per stage / per MMA: four accumulator slots plus the A operand of both row tiles share the 512 TMEM columns
 __host__ __device__ constexpr int tc_bn(int dp) { return dp <= 64 ? 96 : 64; }
-__host__ __device__ constexpr int tc_lcap(int dp) { return dp <= 56 ? 8 : 4; }   // chunk-list capacity per drain thread
+__host__ __device__ constexpr int tc_lcap(int dp) { return dp <= 48 ? 6 : 4; }   // chunk-list capacity per drain thread
 constexpr int TC_QCAP = 1024;         // re-rank queue capacity per pass (groups of 4 codes)
 constexpr int TC_MAXSTAGES = 6;
 constexpr int TC_DRAIN_WARP0 = 0;    // warp order = issue priority on B200 (highest warp id first): misc warps last
@@ -197,7 +197,9 @@ struct TcSmem {
     static constexpr int LCAP = tc_lcap(DP);
     static constexpr uint32_t LBO_B = BN * 16;
     static constexpr uint32_t BSTAGE = BN * DP * 4;
-    static constexpr int XS = DP + 1;                                      // staged row stride in floats (odd)
+    // staged row stride in floats: rows are 16-byte aligned (bulk reduce source) and XS / 4 is odd, which keeps the
+    // lane <-> row accesses at 4-way bank conflicts (lane <-> column accesses are conflict free)
+    static constexpr int XS = DP + 4;
     static constexpr uint32_t XS_BYTES = 2u * TC_PR * XS * 4;              // raw rows, two passes in flight
     static constexpr uint32_t W_BYTES = 2u * TC_PR * 4;                    // row weights, two passes in flight
     static constexpr uint32_t BAND_BYTES = 2u * TC_PR * 4;                 // per-row error band, two passes in flight
@@ -438,7 +440,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             PROF(6);   // prof[16+6]: re-rank wait Q_FULL
             sBest[ptid] = ((unsigned long long)__float_as_uint(FLT_MAX)) << 32;      // (FLT_MAX, code 0)
             named_bar_sync(1, TC_PR);
-#ifdef C3VQ_TC_EXP_NORERANK   // experiment: no exact re-rank, no outputs (results are garbage)
+#if defined(C3VQ_TC_EXP_NORERANK) || defined(C3VQ_TC_EXP_NOQUEUE)   // experiment: no exact re-rank (results are garbage)
             const uint32_t nq = 0;
 #else
             const uint32_t nq = min(sQCount[qb], (uint32_t)TC_QCAP);
@@ -488,48 +490,53 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             }
             named_bar_sync(1, TC_PR);
             st_cands += 4ull * nq;      // counted once per thread, divided out below
-            // ---- outputs: two rows per warp step (half warp each), lanes over 16-byte accumulator chunks ----
-            const int half = lane >> 4, hl = lane & 15;
-            const int nchunk = p.acc_stride >> 2;
-#ifdef C3VQ_TC_EXP_NORERANK
-            for (int rr = 32; rr < 32; rr += 2) {
-#else
-#pragma unroll 4
-            for (int rr = 0; rr < 32; rr += 2) {
-#endif
-                const int lr = pw * 32 + rr + half;
+            // ---- outputs (lane <-> row): idx / dist, fallback list, then the weighted row into the centroid sums ----
+#ifndef C3VQ_TC_EXP_NORERANK
+            {
+                const int lr = pw * 32 + lane;
                 const uint8_t st0 = sFlag[(qb * 2 + 0) * TC_PR + lr], st1 = sFlag[(qb * 2 + 1) * TC_PR + lr];
                 const uint8_t status = st0 > st1 ? st0 : st1;
                 const int64_t gi = pair * TC_PR + lr;
+                const unsigned long long best = sBest[lr];
+                const int bj = (int)(best & 0xFFFFFFFFu);
                 if (status == ROW_OK) {
-                    const unsigned long long best = sBest[lr];
-                    const int bj = (int)(best & 0xFFFFFFFFu);
-                    if (hl == 0) {
-                        st_rows++;
-                        if (p.out_idx) p.out_idx[gi] = bj;
-                        if (need_dist) p.out_dist[gi] = __uint_as_float((unsigned int)(best >> 32));
-                    }
-                    if (p.acc) {
-                        const float wv = sW[qb * TC_PR + lr];
-                        const float *xg = xq + lr * L::XS;
-                        float *ap = p.acc + (size_t)bj * p.acc_stride;
-                        for (int ch = hl; ch < nchunk; ch += 16) {
-                            float e4[4];
-#pragma unroll
-                            for (int i = 0; i < 4; i++) {
-                                const int kk = 4 * ch + i;
-                                e4[i] = kk < D ? __fmul_rn(xg[kk], wv) : (kk == D ? wv : 0.f);
-                            }
-                            red_add_v4(ap + 4 * ch, e4[0], e4[1], e4[2], e4[3]);
-                        }
-                    }
-                } else if (status == ROW_FALLBACK && hl == 0) {
+                    st_rows++;
+                    if (p.out_idx) p.out_idx[gi] = bj;
+                    if (need_dist) p.out_dist[gi] = __uint_as_float((unsigned int)(best >> 32));
+                } else if (status == ROW_FALLBACK) {
                     st_rows++;
                     st_fb++;
                     const unsigned int pos = atomicAdd(&p.hdr->fb_count, 1u);
                     p.fb_list[pos] = (unsigned int)gi;
                 }
+#ifndef C3VQ_TC_EXP_NORED
+                if (p.acc) {
+                    // scale this warp's 32 staged rows in place (lane <-> column): [w*x (D) | w | 0 ...] = one
+                    // accumulator row, then ONE bulk reduce-add per row (TMA engine, f32 adds at the L2)
+                    float *xw = sX + (qb * TC_PR + pw * 32) * L::XS;
+                    const float *ww = sW + qb * TC_PR + pw * 32;
+#pragma unroll 8
+                    for (int r = 0; r < 32; r++) {
+                        const float wv = ww[r];
+#pragma unroll
+                        for (int h = 0; h < NH; h++) {
+                            const int col = lane + 32 * h;
+                            if (col < p.acc_stride) {
+                                const float v = col < D ? __fmul_rn(xw[r * L::XS + col], wv) : (col == D ? wv : 0.f);
+                                xw[r * L::XS + col] = v;
+                            }
+                        }
+                    }
+                    fence_proxy_async_smem();
+                    __syncwarp();
+                    if (status == ROW_OK)
+                        bulk_reduce_add_f32(p.acc + (size_t)bj * p.acc_stride, smem_u32(xw + lane * L::XS),
+                                            (uint32_t)p.acc_stride * 4u);
+                    bulk_commit_group();
+                }
+#endif
             }
+#endif
             __syncwarp();
             if (ptid == 0) sQCount[qb] = 0;       // every thread has read nq (barrier above)
             if (lane == 0) mbar_arrive(Q_EMPTY(qb));
@@ -545,8 +552,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             // stage the raw rows (exact fp32: the re-rank and the weighted sums of this pass read them back);
             // row stride XS is odd, so both the lane <-> column stores and the lane <-> row loads are conflict free.
             // Buffer pi & 1 was last read by the re-rank of pass pi - 2, which every producer warp has left
-            // (its second named barrier) before any warp arrives here.
+            // (its second named barrier) before any warp arrives here; the bulk reduces of that pass read only
+            // this warp's own rows and are waited for below.
             float *xs_w = sX + ((pi & 1) * TC_PR + pw * 32) * L::XS;
+            bulk_wait_group_read<1>();           // this thread's bulk reduce of pass pi - 2 no longer reads the buffer
             __syncwarp();
 #pragma unroll
             for (int r = 0; r < 32; r++) {
@@ -608,6 +617,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             PROF(4);   // prof[16+4]: prefetch issue
         }
         if (prev_pair >= 0) rerank(prev_pair, pi - 1);
+        bulk_wait_group<0>();                    // every bulk reduce of this thread has been performed
         PROF(5);       // prof[16+5]: last re-rank
         PROF_FLUSH(16, lane == 0 && pw == 0);
         // stats: one atomic per warp (st_cands was counted by every thread of the 256)
@@ -633,14 +643,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
         const int lr = t * TC_BM + q * 32 + lane;       // local row 0..255 (shared with the other parity's thread)
         const int dl = dw * 32 + lane;                  // drain thread 0..511 (list column)
         const uint32_t tsrc = *(volatile uint32_t *)sTmem + ((uint32_t)(q * 32) << 16) + (2 * t + h) * BN;
-        const uint32_t acc_full = ACC_FULL(2 * t + h), acc_empty = ACC_EMPTY(2 * t + h);
+        const uint32_t acc_full = ACC_FULL(2 * t + h);  // ACC_EMPTY of the same slot is 32 bytes further
+        constexpr uint32_t ACC_E_OFF = 32;
         uint32_t *listS = sListS + dl, *listP = sListP + dl;
-        const uint32_t lS = smem_u32(listS), lP = smem_u32(listP);
-        constexpr uint32_t LIST_STRIDE = TC_DT * 4, LIST_END = L::LCAP * LIST_STRIDE;
+        const uint32_t lS = smem_u32(listS);            // the payload plane is LIST_PLANE bytes further
+        constexpr uint32_t LIST_STRIDE = TC_DT * 4, LIST_END = L::LCAP * LIST_STRIDE, LIST_PLANE = LIST_END;
         uint32_t g0 = 0, pi = 0;                        // g0: global step counter at the start of the pass
         PROF_DECL;
         for (int64_t pair = blockIdx.x; pair < p.npairs; pair += gridDim.x, pi++, g0 += nsteps) {
-            const int64_t gi = pair * TC_PR + lr;
             PROF(0);
             mbar_wait(A_FULL, pi & 1);
             PROF(1);       // prof[24+1]: drain wait A_FULL
@@ -679,10 +689,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                         if (cnt_off == LIST_END) {      // full: drop entries the tighter threshold excludes
                             uint32_t wpos = 0;
                             for (uint32_t e = 0; e < LIST_END; e += LIST_STRIDE) {
-                                const uint32_t es = ld_shared_u32(lS + e), ep = ld_shared_u32(lP + e);
+                                const uint32_t es = ld_shared_u32(lS + e), ep = ld_shared_u32(lS + LIST_PLANE + e);
                                 if (__uint_as_float(es) <= thr) {
                                     st_shared_u32(lS + wpos, es);
-                                    st_shared_u32(lP + wpos, ep);
+                                    st_shared_u32(lS + LIST_PLANE + wpos, ep);
                                     wpos += LIST_STRIDE;
                                 }
                             }
@@ -690,7 +700,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                         }
                         if (cnt_off < LIST_END) {
                             st_shared_u32(lS + cnt_off, __float_as_uint(cm));
-                            st_shared_u32(lP + cnt_off, (chunk << 12) | gm);
+                            st_shared_u32(lS + LIST_PLANE + cnt_off, (chunk << 12) | gm);
                             cnt_off += LIST_STRIDE;
                         } else {
                             band = __int_as_float(0x7fc00000);   // overflow: NaN band = exact fallback for this row
@@ -702,7 +712,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             auto dump = [&](const uint32_t (&a)[16], int code0) {   // debug build of the kernel only
 #pragma unroll
                 for (int jj = 0; jj < 16; jj++)
-                    if (gi < p.n && code0 + jj < p.k) p.dbg_scores[gi * p.k + code0 + jj] = __uint_as_float(a[jj]);
+                    if (pair * TC_PR + lr < p.n && code0 + jj < p.k)
+                        p.dbg_scores[(pair * TC_PR + lr) * p.k + code0 + jj] = __uint_as_float(a[jj]);
             };
 
             for (int s = (int)((g0 ^ (uint32_t)h) & 1u); s < nsteps; s += 2) {
@@ -715,11 +726,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
 #ifdef C3VQ_TC_EXP_NODRAIN   // experiment: hand the slot straight back (results are garbage)
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(acc_empty);
+                if (lane == 0) mbar_arrive(acc_full + ACC_E_OFF);
                 continue;
 #endif
                 uint32_t va[16], vb[16];
-                float gv[NGH];
+                float gv[NGH], gw[NGH];
+                // all loads first (two 16-column chunks in flight), the slot goes back to the MMA warp as soon as
+                // the last one has landed; the threshold test / list append of both half jobs comes after that
                 tmem_ld16_async(tsrc, va);
                 tmem_ld16_async(tsrc + 16, vb);
                 tmem_wait_ld16(va);
@@ -728,38 +741,33 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                 groups(va, gv);
                 tmem_ld16_async(tsrc + 32, va);
                 groups(vb, gv + 4);
+                tmem_ld16_async(tsrc + 48, vb);
+                tmem_wait_ld16(va);
+                tmem_wait_ld16(vb);
+                if (DBG) { dump(va, code_s + 32); dump(vb, code_s + 48); }
                 if (BN == 96) {
-                    tmem_ld16_async(tsrc + 48, vb);
-                    tmem_wait_ld16(va);
-                    tmem_wait_ld16(vb);
-                    if (DBG) { dump(va, code_s + 32); dump(vb, code_s + 48); }
                     groups(va, gv + 8);
                     tmem_ld16_async(tsrc + 64, va);
-                    process(gv, (uint32_t)(2 * s));
-                    groups(vb, gv);
+                    groups(vb, gw);
                     tmem_ld16_async(tsrc + 80, vb);
+                    process(gv, (uint32_t)(2 * s));     // first half job judged while the last two chunks land
                     tmem_wait_ld16(va);
                     tmem_wait_ld16(vb);
                     tc_fence_before();                  // accumulator slot fully read: hand it back to the MMA warp
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(acc_empty);
+                    if (lane == 0) mbar_arrive(acc_full + ACC_E_OFF);
                     if (DBG) { dump(va, code_s + 64); dump(vb, code_s + 80); }
-                    groups(va, gv + 4);
-                    groups(vb, gv + 8);
-                    process(gv, (uint32_t)(2 * s + 1));
+                    groups(va, gw + 4);
+                    groups(vb, gw + 8);
                 } else {                                // BN == 64: two half jobs of 32 columns
-                    tmem_ld16_async(tsrc + 48, vb);
-                    process(gv, (uint32_t)(2 * s));
-                    tmem_wait_ld16(va);
-                    tmem_wait_ld16(vb);
                     tc_fence_before();
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(acc_empty);
-                    if (DBG) { dump(va, code_s + 32); dump(vb, code_s + 48); }
-                    groups(va, gv);
-                    groups(vb, gv + 4);
-                    process(gv, (uint32_t)(2 * s + 1));
+                    if (lane == 0) mbar_arrive(acc_full + ACC_E_OFF);
+                    groups(va, gw);
+                    groups(vb, gw + 4);
+                    process(gv, (uint32_t)(2 * s));
                 }
+                process(gw, (uint32_t)(2 * s + 1));
             }
             const int cnt = (int)(cnt_off / LIST_STRIDE);
             PROF(4);
@@ -768,7 +776,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             mbar_wait(Q_EMPTY(qb), ((pi >> 1) & 1) ^ 1);     // the pass that used this queue slot is finished
             PROF(5);       // prof[24+5]: drain wait Q_EMPTY
             uint8_t status = ROW_OK;
-            if (gi >= p.n)
+            if (pair * TC_PR + lr >= p.n)
                 status = ROW_SKIP;
             else if (!(band >= 0.f))
                 status = ROW_FALLBACK;

@@ -56,6 +56,10 @@ int launch_assign_exact(const float *x, const int64_t *rows, int64_t n, int d, c
 // wcol >= 0: column of acc that receives the weight; wcol < 0: no weight column (decode backward)
 int launch_accumulate(const float *x, const float *w, const int64_t *rows, const int64_t *idx, int64_t n, int d,
                       int64_t k, float *acc, int stride, int wcol, cudaStream_t s);
+// atomic-free variant: counting sort by codeword + segmented sum; ws = seg_workspace_bytes(n, k)
+size_t seg_workspace_bytes(int64_t n, int k);
+int launch_accumulate_sorted(const float *x, const float *w, const int64_t *rows, const int64_t *idx, int64_t n, int d,
+                             int k, float *acc, int stride, int wcol, void *ws, size_t ws_bytes, cudaStream_t s);
 int launch_ema(float *codebook, float *entry_importance, const float *acc, int k, int d, double decay, double eps,
                int scale_normalize, cudaStream_t s);
 int launch_gather(const float *table, int64_t table_rows, int d, const int64_t *idx, int64_t n, float *out,

@@ -94,6 +94,29 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst_smem, const void *src_gmem
                  : "memory");
 }
 
+// Bulk reduction shared -> global through the TMA engine: dst[i] += src[i] for bytes/4 floats, performed as
+// f32 adds at the L2 (SASS: UBLKRED).  One instruction per row instead of one red.global per 16 bytes and lane.
+// Addresses and size are multiples of 16 bytes; completion is tracked per thread with bulk async-groups.
+__device__ __forceinline__ void bulk_reduce_add_f32(float *dst_gmem, uint32_t src_smem, uint32_t bytes)
+{
+    asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;" ::"l"(dst_gmem),
+                 "r"(src_smem), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_commit_group() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// wait until at most N of this thread's bulk groups still READ their shared-memory source
+template <int N>
+__device__ __forceinline__ void bulk_wait_group_read()
+{
+    asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+// wait until at most N of this thread's bulk groups are incomplete (writes performed)
+template <int N>
+__device__ __forceinline__ void bulk_wait_group()
+{
+    asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
+}
+
 // ---------------------------------------------------------------- tcgen05
 __device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols)
 {

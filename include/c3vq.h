@@ -80,6 +80,17 @@ int c3vq_accumulate(const float *x, const float *w, const int64_t *rows, const i
                     int64_t n, int d, int k, float *acc, c3vq_stream_t stream);
 
 /*
+ * Same sums without per-row atomics: rows are counting-sorted by codeword, then summed segment by
+ * segment in registers (the table is touched only at segment boundaries).  Several times faster for
+ * wide rows, where the L2's fp32 reduction rate, not HBM, bounds c3vq_accumulate.
+ * ws: c3vq_accumulate_sorted_workspace_bytes(n, k) bytes.
+ */
+size_t c3vq_accumulate_sorted_workspace_bytes(int64_t n, int k);
+int c3vq_accumulate_sorted(const float *x, const float *w, const int64_t *rows, const int64_t *idx,
+                           int64_t n, int d, int k, float *acc,
+                           void *ws, size_t ws_bytes, c3vq_stream_t stream);
+
+/*
  * EMA epilogue on the k codewords:
  *   entry_importance = decay*entry_importance + (1-decay)*sum_w
  *   codebook         = decay*codebook + (1-decay) * sum_x / (sum_w + eps)
@@ -94,7 +105,9 @@ int c3vq_ema(float *codebook, float *entry_importance, const float *acc,
  * One VectorQuantize.update: assignment, weighted sums and EMA in one call, reading
  * x once.  out_dist / out_idx receive the per-row minimum distance and codeword
  * (either may be null).  ws: c3vq_update_workspace_bytes(n, d, k) bytes.
- * use_tensor_cores = 0 forces the SIMT exact assignment.
+ * use_tensor_cores: 0 = SIMT exact assignment + atomic sums; 1 = tensor-core assignment, then the sorted
+ * segmented sums (second pass over x, no per-row atomics); 2 = tensor-core assignment with the sums fused
+ * into the kernel (x read once, one bulk reduce-add per row: bounded by the L2's fp32 reduction rate).
  */
 size_t c3vq_update_workspace_bytes(int64_t n, int d, int k);
 int c3vq_update(const float *x, const float *w, const int64_t *rows, int64_t n, int d,

@@ -208,6 +208,53 @@ def test_accumulate_and_ema_vs_oracle(L, oracle, d):
         assert np.array_equal(ei_g.cpu().numpy().view(np.uint32), ei_o.view(np.uint32))
 
 
+@pytest.mark.parametrize("d", [3, 7, 45, 48, 64])
+@pytest.mark.parametrize("skew", [False, True])
+def test_accumulate_sorted_vs_oracle(L, oracle, d, skew):
+    """Sorted segmented sums (counting sort by codeword, no per-row atomics): same sums as the fp64 scatter,
+    incl. out-of-range codes ignored, empty codewords, a giant segment, the rows indirection and unit weights."""
+    n, k = 70001, 517
+    x, w, cb = _synth(n, d, k, seed=90 + d)
+    g = torch.Generator().manual_seed(d)
+    idx = torch.randint(0, k, (n,), generator=g)
+    if skew:
+        idx[torch.rand(n, generator=g) < 0.7] = 5             # one codeword owns most rows
+        idx[idx == 6] = 7                                     # and its neighbour is empty
+    sx64, sw64 = oracle.scatter_sum_f64(x.numpy(), w.numpy(), idx.numpy(), k)
+    bad = idx.clone()
+    extra_rows = torch.randint(0, n, (1000,), generator=g)
+    acc = L.accumulate(x.to(DEV), w.to(DEV), bad.to(DEV), k, sorted_path=True).cpu().numpy()
+    scale = np.abs(sx64).max(1, keepdims=True) + 1e-30
+    assert np.max(np.abs(acc[:, :d] - sx64) / scale) < 1e-5
+    assert np.allclose(acc[:, d], sw64, rtol=1e-5)
+    assert not acc[:, d + 1:].any()
+    # out-of-range codes are ignored (as in the atomic kernel); rows indirection; unit weights
+    idx2 = idx[extra_rows].clone()
+    idx2[::7] = k + 3
+    idx2[::11] = -1
+    keep = (idx2 >= 0) & (idx2 < k)
+    sx2, sw2 = oracle.scatter_sum_f64(x[extra_rows][keep].numpy(), np.ones(int(keep.sum()), np.float32),
+                                      idx2[keep].numpy(), k)
+    acc2 = L.accumulate(x.to(DEV), None, idx2.to(DEV), k, rows=extra_rows.to(DEV), sorted_path=True).cpu().numpy()
+    assert np.max(np.abs(acc2[:, :d] - sx2) / (np.abs(sx2).max(1, keepdims=True) + 1e-30)) < 1e-5
+    assert np.allclose(acc2[:, d], sw2, rtol=1e-6)
+
+
+@pytest.mark.parametrize("mode", [True, "fused", False])
+def test_assign_accumulate_modes_agree(L, oracle, mode):
+    """tensor-core assignment + sorted sums (default), fused bulk-reduce sums, SIMT + atomic sums."""
+    n, d, k = 30011, 45, 777
+    x, w, cb = _synth(n, d, k, seed=7)
+    dist_o, idx_o = oracle.assign(x.numpy(), cb.numpy())
+    sx64, sw64 = oracle.scatter_sum_f64(x.numpy(), w.numpy(), idx_o, k)
+    acc, dist, idx = L.assign_accumulate(x.to(DEV), w.to(DEV), cb.to(DEV), tensor_cores=mode, return_dist=True)
+    assert np.array_equal(idx.cpu().numpy(), idx_o)
+    assert np.array_equal(dist.cpu().numpy().view(np.uint32), dist_o.view(np.uint32))
+    acc = acc.cpu().numpy()
+    assert np.max(np.abs(acc[:, :d] - sx64) / (np.abs(sx64).max(1, keepdims=True) + 1e-30)) < 1e-5
+    assert np.allclose(acc[:, d], sw64, rtol=1e-5)
+
+
 def test_update_kats_empty_cluster_and_single_cluster(L):
     cb = torch.tensor([[1.0, 2.0], [100.0, 100.0]], device=DEV)
     ei = torch.tensor([0.5, 0.25], device=DEV)
@@ -337,6 +384,11 @@ def test_full_size_properties(L, d):
     # sums: total weight is conserved; decode of the assignment is idempotent under re-assignment
     acc = L.accumulate(x, w, idx_tc, k)
     assert abs(float(acc[:, d].double().sum()) - float(w.double().sum())) < 1e-4 * float(w.double().sum())
+    acc_s = L.accumulate(x, w, idx_tc, k, sorted_path=True)
+    assert abs(float(acc_s[:, d].double().sum()) - float(w.double().sum())) < 1e-5 * float(w.double().sum())
+    ref = torch.zeros(k, d, device=DEV, dtype=torch.float64).index_add_(0, idx_tc, x.double() * w.double()[:, None])
+    scale = ref.abs().max(1, keepdim=True).values + 1e-30
+    assert float(((acc_s[:, :d].double() - ref).abs() / scale).max()) < 1e-5
     q = L.gather(cb, idx_tc[:1_000_000])
     _, idx_q = L.assign(q, cb, exact=False)
     assert torch.equal(cb[idx_q], q)
