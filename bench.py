@@ -14,8 +14,8 @@ CUDA events around every launch of it inside the timed region), `cpu_baseline` (
 of the reference path on the box's host cores, rank 0, N=1), `e2e` (same job through the public API
 from pinned HOST buffers, H2D/D2H inside the timed region) and `gpu_launches`.
 
-`--impl reference` times the reference path's CPU port (oracle/, all host threads) on configs[0]
-(100 k x 45-D, K = 4096, 10 iterations).  oracle/ is used here only as that baseline.
+`--impl reference` times the reference path's CPU port (oracle/, all host threads) on a bounded sample
+(100 k rows, all 10 iterations per step) of the same workload.  oracle/ is used here only as that baseline.
 """
 from __future__ import annotations
 
@@ -119,13 +119,26 @@ def init_codebook(x: torch.Tensor, k: int, seed: int):
 
 
 # ------------------------------------------------------------------------------------------------
+def workload_config(n, d, world, assignment, sums):
+    return {"workload": f"configs[1]: SH codebook clustering, {n / 1e6:.1f}M Gaussians x {d}-D per GPU, K=4096, "
+                        "10 full-batch k-means iterations per step",
+            "rows_per_gpu": n, "dim": d, "codebook_size": K, "iterations_per_step": ITERS, "decay": DECAY,
+            "parallelism": f"rows sharded x{world}, codebook replicated, 1 all-reduce of K x (D+1) sums per iteration",
+            "l2": f"inputs ({n * (d + 1) * 4 / 1e9:.2f} GB per GPU) exceed the 126 MB L2; no explicit flush",
+            "assignment": assignment, "sums": sums}
+
+
+SAMPLE_ROWS = 100_000     # CPU legs: a bounded sample of the workload's rows (the metric is per row and iteration)
+
+
 def run_reference_arm(args, rank):
-    """CPU port of the reference path on configs[0]; rank 0 only."""
+    """The reference path's CPU implementation (oracle port: OpenMP C restatement of weighted_distance.cu +
+    vq.py's update) on the box's host cores, on a bounded sample of OUR arm's workload; rank 0 only."""
     if rank != 0:
         return
     from oracle import oracle
     oracle.build()
-    n, d = 100_000, 45
+    n, d = SAMPLE_ROWS, args.dim
     x, w = synth(n, d, 0)
     x, w = x.numpy(), w.numpy()
     wn = (w / w.max()).astype(np.float32)
@@ -138,7 +151,7 @@ def run_reference_arm(args, rank):
         for _ in range(ITERS):
             oracle.update(x, wn, cb, ei, DECAY, EPS)
 
-    # each step is a bounded sample (the whole configs[0] job, ~seconds); cap the run at a few minutes
+    # each step is a bounded sample (100k rows x 10 iterations, ~seconds); cap the run at a few minutes
     t_probe = time.time(); job(); t_probe = time.time() - t_probe
     warm = max(0, min(args.warmup, int(20 / max(t_probe, 1e-3))) - 1)
     steps = max(1, min(args.steps, int(120 / max(t_probe, 1e-3))))
@@ -149,15 +162,15 @@ def run_reference_arm(args, rank):
         job()
     dt = (time.time() - t0) / steps
     value = n * ITERS / dt
+    sample = (f"{n} of the workload's {args.rows} rows per GPU (x {d}-D, K=4096), all {ITERS} iterations per step; "
+              "oracle/c3vq_oracle.c (OpenMP restatement of weighted_distance.cu + vq.py update), "
+              f"{cores} host threads")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": steps, "warmup": warm + 1, "ms_per_step": dt * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "configs[0]: 100k Gaussians x 45-D SH, K=4096, 10 k-means iterations, CPU",
-                   "rows": n, "dim": d, "codebook_size": K, "iterations": ITERS},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
-                         "sample": "whole configs[0] job (100k x 45, K=4096, 10 iterations) per step; "
-                                   "oracle/c3vq_oracle.c (OpenMP+AVX2 restatement of weighted_distance.cu + vq.py update)"},
+        "config": workload_config(args.rows, d, max(1, args.gpus), "cpu-exact (reference arithmetic)", "cpu scatter"),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -165,10 +178,10 @@ def run_reference_arm(args, rank):
 
 
 # ------------------------------------------------------------------------------------------------
-def cpu_baseline_leg():
+def cpu_baseline_leg(d=45):
     from oracle import oracle
     oracle.build()
-    n, d = 100_000, 45
+    n = SAMPLE_ROWS
     x, w = synth(n, d, 0)
     x, w = x.numpy(), w.numpy()
     wn = (w / w.max()).astype(np.float32)
@@ -183,7 +196,8 @@ def cpu_baseline_leg():
         done += 1
     dt = time.time() - t0
     return {"value": n * done / dt, "unit": UNIT, "cores": oracle.num_threads(), "kind": "port",
-            "sample": f"configs[0] rows (100k x 45, K=4096), {done} update iterations, {dt:.1f} s of CPU work"}
+            "sample": f"{n} rows of the workload (x {d}-D, K=4096), {done} update iterations, {dt:.1f} s of CPU work; "
+                      "oracle/c3vq_oracle.c (OpenMP restatement of weighted_distance.cu + vq.py update)"}
 
 
 def main():
@@ -349,7 +363,7 @@ def main():
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cpu = cpu_baseline_leg()
+        cpu = cpu_baseline_leg(d)
 
     if rank == 0:
         line = {
@@ -357,14 +371,8 @@ def main():
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32 (tf32 tensor-core screening + exact fp32 re-rank)" if not args.simt else "f32",
             "data": "synthetic",
-            "config": {"workload": "configs[1]: SH codebook clustering, 5.8M Gaussians x 45-D per GPU, K=4096, "
-                                   "10 full-batch k-means iterations per step",
-                       "rows_per_gpu": n, "dim": d, "codebook_size": K, "iterations_per_step": ITERS,
-                       "decay": DECAY, "parallelism": f"rows sharded x{world}, codebook replicated, "
-                                                      "1 all-reduce of K x (D+1) sums per iteration",
-                       "l2": "inputs (1.04 GB per GPU) exceed the 126 MB L2; no explicit flush",
-                       "assignment": "simt-exact" if args.simt else "tcgen05-tf32+rerank",
-                       "sums": "atomic" if args.simt else args.sums},
+            "config": workload_config(n, d, world, "simt-exact" if args.simt else "tcgen05-tf32+rerank",
+                                      "atomic" if args.simt else args.sums),
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
             "clocks": clocks,
         }

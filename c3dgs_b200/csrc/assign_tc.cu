@@ -281,7 +281,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
         mbar_init(A_EMPTY, 1);
         for (int sl = 0; sl < 4; sl++) {
             mbar_init(ACC_FULL(sl), 1);
-            mbar_init(ACC_EMPTY(sl), 4);           // one arrival per drain warp of the tile/parity
+            mbar_init(ACC_EMPTY(sl), 8);           // one arrival per drain warp of the tile
         }
         for (int b = 0; b < 2; b++) {
             mbar_init(Q_FULL(b), TC_NDRAIN);
@@ -293,6 +293,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
     if (warp == TC_MISC_WARP0 + 2) {
         tmem_alloc(smem_u32(sTmem), 512);
         tmem_relinquish();
+        // all 512 columns belong to this CTA, so the allocation starts at lane 0, column 0; the MMA warp relies on it
+        if (*(volatile uint32_t *)sTmem != 0u) __trap();
     }
     if (tid < 80) sMu[tid] = tid < D ? p.mu[tid] : 0.f;
     tc_fence_before();
@@ -332,10 +334,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
         // The whole warp runs the loop convergently (so addresses and descriptors live in uniform registers and
         // the waits are warp-wide); one elected lane issues the tcgen05 instructions.
         {
+            // Everything the tcgen05 instructions consume is a compile-time constant or warp-uniform arithmetic
+            // on kernel parameters, so it stays in uniform registers: the TMEM base is 0 by construction (the CTA
+            // owns all 512 columns; checked after the allocation), and the B descriptor of (stage, ks) is the
+            // stage's low word plus ks * DLO_KS under a constant high word.
             constexpr uint32_t IDESC = idesc_tf32(TC_BM, BN);
-            const uint32_t tmem_b = *(volatile uint32_t *)sTmem;     // role-local copy (the kernel-wide one is spilled)
-            const uint32_t sb0 = smem_u32(sB);
-            uint32_t g = 0, pi = 0, stage = 0, phase = 0;
+            constexpr uint32_t DHI = ((TC_SBO >> 4) & 0x3FFFu) | (1u << 14);          // SBO, descriptor version 1
+            constexpr uint32_t DLO_KS = (2 * L::LBO_B) >> 4, DLO_STAGE = L::BSTAGE >> 4;
+            const uint32_t dlo0 = ((smem_u32(sB) & 0x3FFFFu) >> 4) | (((L::LBO_B >> 4) & 0x3FFFu) << 16);
+            uint32_t g = 0, pi = 0, stage = 0, phase = 0, dlo = dlo0;
             PROF_DECL;
             for (int64_t pair = blockIdx.x; pair < p.npairs; pair += gridDim.x, pi++) {
                 PROF(0);
@@ -347,21 +354,20 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                     mbar_wait(B_FULL(stage), phase);
                     PROF(2);   // prof[8+2]: MMA wait B_FULL
                     tc_fence_after();
-                    const uint32_t b_addr = sb0 + stage * L::BSTAGE;
+                    const uint32_t par = g & 1, eph = ((g >> 1) & 1) ^ 1;
 #pragma unroll
                     for (int t = 0; t < 2; t++) {
                         // row tile t owns slots 2t and 2t+1 and alternates between them step by step
-                        const uint32_t sl = 2 * t + (g & 1);
+                        const uint32_t sl = 2 * t + par;
                         PROF(0);
-                        mbar_wait(ACC_EMPTY(sl), ((g >> 1) & 1) ^ 1);
+                        mbar_wait(ACC_EMPTY(sl), eph);
                         PROF(3);   // prof[8+3]: MMA wait ACC_EMPTY
                         tc_fence_after();
                         if (elect_one()) {
 #pragma unroll
                             for (int ks = 0; ks < KSTEPS; ks++) {
-                                const uint64_t bd = smem_desc(b_addr + ks * 2 * L::LBO_B, L::LBO_B, TC_SBO);
-                                umma_tf32_ts(tmem_b + sl * BN, tmem_b + L::ACOL + t * DP + ks * 8, bd, IDESC,
-                                             ks > 0 ? 1u : 0u);
+                                const uint64_t bd = ((uint64_t)DHI << 32) | (uint64_t)(dlo + ks * DLO_KS);
+                                umma_tf32_ts(sl * BN, L::ACOL + t * DP + ks * 8, bd, IDESC, ks > 0 ? 1u : 0u);
                             }
                             umma_commit(ACC_FULL(sl));
                         }
@@ -370,9 +376,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                     }
                     if (elect_one()) umma_commit(B_EMPTY(stage));
                     __syncwarp();
+                    dlo += DLO_STAGE;
                     if (++stage == (uint32_t)S) {
                         stage = 0;
                         phase ^= 1;
+                        dlo = dlo0;
                     }
                 }
                 if (elect_one()) umma_commit(A_EMPTY);
@@ -632,18 +640,18 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
         }
     } else {
         // ===================== drain: TMEM scan, running minimum, chunk lists, work queue =====================
-        // Warp (tile t, lane quarter q, parity b) reads every column of slot 2t + b, i.e. the steps with
-        // (global step & 1) == b: two threads per row, each seeing every other BN-code block of the codebook.
+        // Warp (tile t, lane quarter q, column half h) reads its half of every accumulator slot of its tile: two
+        // threads per row, so a slot is back with the MMA warp after two short tcgen05.ld round trips.
         if (TC_REGS_DRAIN < 72) setmaxnreg_dec<TC_REGS_DRAIN < 72 ? TC_REGS_DRAIN : 64>();
         constexpr int NGH = BN / 8;                     // groups of 4 codes per half job (12 or 8)
         const int dw = warp - TC_DRAIN_WARP0;           // 0..15
         const int q = warp & 3;                         // TMEM lane quarter this warp may access
         const int t = (dw >> 2) & 1;                    // row tile
-        const int h = dw >> 3;                          // step parity served by this warp
-        const int lr = t * TC_BM + q * 32 + lane;       // local row 0..255 (shared with the other parity's thread)
+        const int h = dw >> 3;                          // column half of every slot served by this warp
+        const int lr = t * TC_BM + q * 32 + lane;       // local row 0..255 (shared with the other half's thread)
         const int dl = dw * 32 + lane;                  // drain thread 0..511 (list column)
-        const uint32_t tsrc = *(volatile uint32_t *)sTmem + ((uint32_t)(q * 32) << 16) + (2 * t + h) * BN;
-        const uint32_t acc_full = ACC_FULL(2 * t + h);  // ACC_EMPTY of the same slot is 32 bytes further
+        const uint32_t tsrc0 = ((uint32_t)(q * 32) << 16) + (2 * t) * BN + h * (BN / 2);   // TMEM base is 0 (checked)
+        const uint32_t acc_full0 = ACC_FULL(2 * t);     // ACC_EMPTY of the same slot is 32 bytes further
         constexpr uint32_t ACC_E_OFF = 32;
         uint32_t *listS = sListS + dl, *listP = sListP + dl;
         const uint32_t lS = smem_u32(listS);            // the payload plane is LIST_PLANE bytes further
@@ -716,13 +724,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                         p.dbg_scores[(pair * TC_PR + lr) * p.k + code0 + jj] = __uint_as_float(a[jj]);
             };
 
-            for (int s = (int)((g0 ^ (uint32_t)h) & 1u); s < nsteps; s += 2) {
-                const uint32_t use = (g0 + (uint32_t)s) >> 1;
+            for (int s = 0; s < nsteps; s++) {
+                const uint32_t gs = g0 + (uint32_t)s, par = gs & 1u, use = gs >> 1;   // slot 2t + par
+                const uint32_t acc_full = acc_full0 + 8u * par, tsrc = tsrc0 + par * BN;
                 PROF(4);   // prof[24+4]: drain (LDTM + min + lists)
                 mbar_wait_hint(acc_full, use & 1);
                 PROF(3);   // prof[24+3]: drain wait ACC_FULL
                 tc_fence_after();
-                const int code_s = s * BN;
+                const int code_s = s * BN + h * (BN / 2);
 #ifdef C3VQ_TC_EXP_NODRAIN   // experiment: hand the slot straight back (results are garbage)
                 tc_fence_before();
                 __syncwarp();
@@ -730,44 +739,29 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                 continue;
 #endif
                 uint32_t va[16], vb[16];
-                float gv[NGH], gw[NGH];
-                // all loads first (two 16-column chunks in flight), the slot goes back to the MMA warp as soon as
-                // the last one has landed; the threshold test / list append of both half jobs comes after that
+                float gv[NGH];
                 tmem_ld16_async(tsrc, va);
                 tmem_ld16_async(tsrc + 16, vb);
                 tmem_wait_ld16(va);
                 tmem_wait_ld16(vb);
                 if (DBG) { dump(va, code_s); dump(vb, code_s + 16); }
                 groups(va, gv);
-                tmem_ld16_async(tsrc + 32, va);
-                groups(vb, gv + 4);
-                tmem_ld16_async(tsrc + 48, vb);
-                tmem_wait_ld16(va);
-                tmem_wait_ld16(vb);
-                if (DBG) { dump(va, code_s + 32); dump(vb, code_s + 48); }
                 if (BN == 96) {
-                    groups(va, gv + 8);
-                    tmem_ld16_async(tsrc + 64, va);
-                    groups(vb, gw);
-                    tmem_ld16_async(tsrc + 80, vb);
-                    process(gv, (uint32_t)(2 * s));     // first half job judged while the last two chunks land
+                    tmem_ld16_async(tsrc + 32, va);
+                    groups(vb, gv + 4);
                     tmem_wait_ld16(va);
-                    tmem_wait_ld16(vb);
-                    tc_fence_before();                  // accumulator slot fully read: hand it back to the MMA warp
+                    tc_fence_before();                  // this half of the slot is read: hand it back to the MMA warp
                     __syncwarp();
                     if (lane == 0) mbar_arrive(acc_full + ACC_E_OFF);
-                    if (DBG) { dump(va, code_s + 64); dump(vb, code_s + 80); }
-                    groups(va, gw + 4);
-                    groups(vb, gw + 8);
-                } else {                                // BN == 64: two half jobs of 32 columns
+                    if (DBG) dump(va, code_s + 32);
+                    groups(va, gv + 8);
+                } else {                                // BN == 64: 32 columns per thread
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(acc_full + ACC_E_OFF);
-                    groups(va, gw);
-                    groups(vb, gw + 4);
-                    process(gv, (uint32_t)(2 * s));
+                    groups(vb, gv + 4);
                 }
-                process(gw, (uint32_t)(2 * s + 1));
+                process(gv, (uint32_t)(2 * s + h));
             }
             const int cnt = (int)(cnt_off / LIST_STRIDE);
             PROF(4);

@@ -47,6 +47,9 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
     }
 }
 
+#ifndef C3VQ_WAIT_HINT_NS
+#define C3VQ_WAIT_HINT_NS 20000u
+#endif
 // critical-path waiters: let the hardware park the thread (up to the hint, in ns) instead of spinning through
 // try_wait/branch pairs that compete for issue slots with the working warps
 __device__ __forceinline__ void mbar_wait_hint(uint32_t bar, uint32_t parity)
@@ -58,7 +61,7 @@ __device__ __forceinline__ void mbar_wait_hint(uint32_t bar, uint32_t parity)
             "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
             "selp.u32 %0, 1, 0, p;\n\t}"
             : "=r"(ok)
-            : "r"(bar), "r"(parity), "r"(20000u)
+            : "r"(bar), "r"(parity), "r"(C3VQ_WAIT_HINT_NS)
             : "memory");
     } while (!ok);
 }
