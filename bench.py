@@ -128,6 +128,9 @@ def workload_config(n, d, world, assignment, sums):
             "assignment": assignment, "sums": sums}
 
 
+# (rows, dim, simt) -> DRAM bytes of one launch of the dominant kernel, measured with ncu (see profiles/)
+NCU_DRAM_BYTES_PER_LAUNCH = {(5_800_000, 45, False): 1_094_076_872}
+
 SAMPLE_ROWS = 100_000     # CPU legs: a bounded sample of the workload's rows (the metric is per row and iteration)
 
 
@@ -191,7 +194,7 @@ def cpu_baseline_leg(d=45):
     oracle.update(x, wn, cb, ei, DECAY, EPS)            # warm-up iteration
     t0 = time.time()
     done = 0
-    while done < 3 * ITERS and (done < ITERS or time.time() - t0 < 10):
+    while done < 40 * ITERS and (done < ITERS or time.time() - t0 < 12):
         oracle.update(x, wn, cb, ei, DECAY, EPS)
         done += 1
     dt = time.time() - t0
@@ -312,8 +315,11 @@ def main():
     flops = 2.0 * K * d * n                               # assign flops = 2*K*D per Gaussian*iteration
     tf32_peak = pk["bf16_tflops_sustained"] / 2.0         # dense TF32 = half the bf16 rate; kernel timed inside a long step
     achieved = flops / (kern_ms * 1e-3) / 1e12
+    # dram__bytes_read.sum + dram__bytes_write.sum of ONE k_assign_tc launch from the committed `ncu --set full`
+    # capture (profiles/r1i_ncu_assign_tc_summary.txt); only valid for the configuration that capture ran
+    traffic = NCU_DRAM_BYTES_PER_LAUNCH.get((n, d, bool(args.simt)))
     roofline = {"bound": "tensor", "achieved": achieved, "peak": tf32_peak, "unit": "TFLOP/s",
-                "frac": achieved / tf32_peak, "traffic": None,
+                "frac": achieved / tf32_peak, "traffic": traffic,
                 "kernel": "k_assign_exact+k_accumulate (SIMT)" if args.simt else
                           ("k_assign_tc (assignment; sums by the sorted segmented-sum kernels)" if split
                            else "k_assign_tc (fused assign+sums)"),
