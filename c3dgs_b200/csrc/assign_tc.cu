@@ -724,11 +724,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                         p.dbg_scores[(pair * TC_PR + lr) * p.k + code0 + jj] = __uint_as_float(a[jj]);
             };
 
-            for (int s = 0; s < nsteps; s++) {
-                const uint32_t gs = g0 + (uint32_t)s, par = gs & 1u, use = gs >> 1;   // slot 2t + par
+            uint32_t par = g0 & 1u, wph = (g0 >> 1) & 1u;         // slot 2t + par of step g0 + s, its phase parity
+            for (int s = 0; s < nsteps; s++, wph ^= par, par ^= 1u) {
                 const uint32_t acc_full = acc_full0 + 8u * par, tsrc = tsrc0 + par * BN;
                 PROF(4);   // prof[24+4]: drain (LDTM + min + lists)
-                mbar_wait_hint(acc_full, use & 1);
+                mbar_wait_hint(acc_full, wph);
                 PROF(3);   // prof[24+3]: drain wait ACC_FULL
                 tc_fence_after();
                 const int code_s = s * BN + h * (BN / 2);
