@@ -29,9 +29,9 @@
 //               queue from the staged rows (4 lanes per group, shared-memory 64-bit atomicMin per row),
 //               write idx/dist, red.global.add.v4 the weighted rows; then prefetch.
 //   warp 24     bulk-copy (TMA engine, cp.async.bulk) producer: codebook image stages -> smem ring
-//   warp 25     MMA issuer: per stage 2 x KSTEPS tcgen05.mma (M=128, N=BN, K=8), commits to mbarriers
-//   warp 26     TMEM allocator (512 columns: four 128 x BN fp32 accumulator slots, two per row tile, then the
-//               A operand of both row tiles)
+//   warps 25,26 MMA issuers, one per row tile: per stage KSTEPS tcgen05.mma (M=128, N=BN, K=8), commits to mbarriers;
+//               warp 26 also allocates the TMEM (512 columns: four 128 x BN fp32 accumulator slots, two per row
+//               tile, then the A operand of both row tiles)
 // A pass is 256 rows x all K codes.  Each row tile owns two accumulator slots, so the MMA warp fills one while
 // the tile's 256 drain threads read the other: MMA, drain and re-rank all overlap.
 #include "common.cuh"
@@ -275,10 +275,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
     if (warp == TC_MISC_WARP0 && lane == 0) {
         for (int s = 0; s < TC_MAXSTAGES; s++) {
             mbar_init(B_FULL(s), 1);
-            mbar_init(B_EMPTY(s), 1);
+            mbar_init(B_EMPTY(s), 2);                  // one commit per MMA warp (row tile)
         }
         mbar_init(A_FULL, 8);                      // one arrival per producer warp
-        mbar_init(A_EMPTY, 1);
+        mbar_init(A_EMPTY, 2);
         for (int sl = 0; sl < 4; sl++) {
             mbar_init(ACC_FULL(sl), 1);
             mbar_init(ACC_EMPTY(sl), 8);           // one arrival per drain warp of the tile
@@ -329,19 +329,23 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             }
             PROF_FLUSH(0, true);
         }
-      } else if (warp == TC_MISC_WARP0 + 1) {
-        // ===================== MMA issuer =====================
-        // The whole warp runs the loop convergently (so addresses and descriptors live in uniform registers and
-        // the waits are warp-wide); one elected lane issues the tcgen05 instructions.
+      } else if (warp == TC_MISC_WARP0 + 1 || warp == TC_MISC_WARP0 + 2) {
+        // ===================== MMA issuers: one warp per row tile =====================
+        // Each warp runs its loop convergently (so addresses and descriptors live in uniform registers and the
+        // waits are warp-wide); one elected lane issues the tcgen05 instructions.  Two warps because the issue
+        // loop is a serial chain of ~50 instructions per job: one warp for both tiles cannot keep the tensor
+        // pipe's queue filled.
         {
             // Everything the tcgen05 instructions consume is a compile-time constant or warp-uniform arithmetic
             // on kernel parameters, so it stays in uniform registers: the TMEM base is 0 by construction (the CTA
             // owns all 512 columns; checked after the allocation), and the B descriptor of (stage, ks) is the
             // stage's low word plus ks * DLO_KS under a constant high word.
+            const int t = warp - (TC_MISC_WARP0 + 1);                                 // row tile of this warp
             constexpr uint32_t IDESC = idesc_tf32(TC_BM, BN);
             constexpr uint32_t DHI = ((TC_SBO >> 4) & 0x3FFFu) | (1u << 14);          // SBO, descriptor version 1
             constexpr uint32_t DLO_KS = (2 * L::LBO_B) >> 4, DLO_STAGE = L::BSTAGE >> 4;
             const uint32_t dlo0 = ((smem_u32(sB) & 0x3FFFFu) >> 4) | (((L::LBO_B >> 4) & 0x3FFFu) << 16);
+            const uint32_t a_col = L::ACOL + t * DP;
             uint32_t g = 0, pi = 0, stage = 0, phase = 0, dlo = dlo0;
             PROF_DECL;
             for (int64_t pair = blockIdx.x; pair < p.npairs; pair += gridDim.x, pi++) {
@@ -353,29 +357,22 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                     PROF(0);
                     mbar_wait(B_FULL(stage), phase);
                     PROF(2);   // prof[8+2]: MMA wait B_FULL
+                    // the tile owns slots 2t and 2t+1 and alternates between them step by step
+                    const uint32_t sl = 2 * t + (g & 1);
+                    mbar_wait(ACC_EMPTY(sl), ((g >> 1) & 1) ^ 1);
+                    PROF(3);   // prof[8+3]: MMA wait ACC_EMPTY
                     tc_fence_after();
-                    const uint32_t par = g & 1, eph = ((g >> 1) & 1) ^ 1;
+                    if (elect_one()) {
 #pragma unroll
-                    for (int t = 0; t < 2; t++) {
-                        // row tile t owns slots 2t and 2t+1 and alternates between them step by step
-                        const uint32_t sl = 2 * t + par;
-                        PROF(0);
-                        mbar_wait(ACC_EMPTY(sl), eph);
-                        PROF(3);   // prof[8+3]: MMA wait ACC_EMPTY
-                        tc_fence_after();
-                        if (elect_one()) {
-#pragma unroll
-                            for (int ks = 0; ks < KSTEPS; ks++) {
-                                const uint64_t bd = ((uint64_t)DHI << 32) | (uint64_t)(dlo + ks * DLO_KS);
-                                umma_tf32_ts(sl * BN, L::ACOL + t * DP + ks * 8, bd, IDESC, ks > 0 ? 1u : 0u);
-                            }
-                            umma_commit(ACC_FULL(sl));
+                        for (int ks = 0; ks < KSTEPS; ks++) {
+                            const uint64_t bd = ((uint64_t)DHI << 32) | (uint64_t)(dlo + ks * DLO_KS);
+                            umma_tf32_ts(sl * BN, a_col + ks * 8, bd, IDESC, ks > 0 ? 1u : 0u);
                         }
-                        __syncwarp();
-                        PROF(4);   // prof[8+4]: MMA issue of one job (KSTEPS instructions + commit)
+                        umma_commit(ACC_FULL(sl));
+                        umma_commit(B_EMPTY(stage));      // second arrival comes from the other tile's warp
                     }
-                    if (elect_one()) umma_commit(B_EMPTY(stage));
                     __syncwarp();
+                    PROF(4);   // prof[8+4]: MMA issue of one job (KSTEPS instructions + commits)
                     dlo += DLO_STAGE;
                     if (++stage == (uint32_t)S) {
                         stage = 0;
@@ -387,10 +384,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                 __syncwarp();
             }
             PROF(0);       // prof[8+0]: MMA issue + everything else
-            PROF_FLUSH(8, lane == 0);
+            PROF_FLUSH(8, lane == 0 && warp == TC_MISC_WARP0 + 1);
         }
       }
-      // TMEM allocator warp and the spare warp: nothing to do until teardown
+      // the spare warp: nothing to do until teardown
     } else if (warp >= TC_PROD_WARP0) {
         // ===================== feature producers + re-rankers (256 threads) =====================
         setmaxnreg_inc<TC_REGS_PROD>();
