@@ -17,7 +17,7 @@
 //      recorded group.
 //   3. RE-RANK all codes of the surviving groups with the reference arithmetic (in-order fma chain,
 //      first index wins ties).  Rows whose group list overflows, or whose magnitudes break the error
-//      model, go to an exact warp-per-row scan (k_assign_fallback).
+//      model, go to an exact scan (k_assign_fallback_scan / _finish).
 //
 // Kernel organisation (persistent, one CTA per SM, 896 threads, warp specialised, setmaxnreg per role):
 //   warps 0-15  drain: tcgen05.ld 16 columns at a time, running min + group list per row; two threads per
@@ -104,6 +104,7 @@ struct TcParams {
     float *acc;
     int acc_stride;
     unsigned int *fb_list;
+    unsigned long long *fb_best;   // per fallback row: running (distance bits, code) minimum
     float *dbg_scores, *dbg_norm2, *dbg_band;
     float gamma2;           // relative slack for the reference chain's own rounding
 };
@@ -513,6 +514,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                     st_fb++;
                     const unsigned int pos = atomicAdd(&p.hdr->fb_count, 1u);
                     p.fb_list[pos] = (unsigned int)gi;
+                    p.fb_best[pos] = ((unsigned long long)0x7f7fffffu) << 32;          // (FLT_MAX, code 0)
                 }
 #ifndef C3VQ_TC_EXP_NORED
                 if (p.acc) {
@@ -813,48 +815,76 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
 }
 
 // ------------------------------------------------------------------------------------------------
-// Exact scan for the rows the tensor-core kernel could not decide: one warp per row, lanes stride
-// over the codes, reference arithmetic, then a (distance, index) min-reduction with lowest-index ties.
+// Exact scan for the rows the tensor-core kernel could not decide (reference arithmetic, lowest index wins ties).
+// A work item is (fallback row, block of FB_CODES codewords) handled by one warp, so that even a single
+// undecided row (typical: a row whose nearest codewords are hundreds of collapsed dead entries) is spread over
+// k / FB_CODES warps instead of costing one warp a serial scan of the whole codebook.  The partial minima meet in
+// a 64-bit atomicMin on (distance bits, code): distances are sums of squares from +0, so the unsigned order of
+// the bits is the numeric order, NaN / inf sort above FLT_MAX and never win, ties go to the lower code.
+constexpr int FB_CODES = 256;
+constexpr unsigned long long FB_INIT = ((unsigned long long)0x7f7fffffu) << 32;      // (FLT_MAX, code 0)
+
 __global__ void __launch_bounds__(128)
-k_assign_fallback(const float *__restrict__ x, const float *__restrict__ w, const int64_t *__restrict__ rows, int d,
-                  const float *__restrict__ cb, int k, const TcHeader *hdr, const unsigned int *__restrict__ fb_list,
-                  float *__restrict__ out_dist, int64_t *__restrict__ out_idx, float *__restrict__ acc, int stride)
+k_assign_fallback_scan(const float *__restrict__ x, const int64_t *__restrict__ rows, int d,
+                       const float *__restrict__ cb, int k, const TcHeader *hdr,
+                       const unsigned int *__restrict__ fb_list, unsigned long long *__restrict__ fb_best)
 {
     __shared__ float xs[4][C3VQ_MAX_DIM];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const unsigned int count = hdr->fb_count;
+    const unsigned int nblk = (unsigned int)((k + FB_CODES - 1) / FB_CODES);
+    const unsigned long long items = (unsigned long long)count * nblk;
     const unsigned int nwarps = gridDim.x * 4;
-    for (unsigned int it = blockIdx.x * 4 + wib; it < count; it += nwarps) {
+    for (unsigned long long w = blockIdx.x * 4 + wib; w < items; w += nwarps) {
+        const unsigned int it = (unsigned int)(w / nblk), blk = (unsigned int)(w % nblk);
         const int64_t gi = fb_list[it];
         const int64_t src = rows ? rows[gi] : gi;
         __syncwarp();
         for (int c = lane; c < d; c += 32) xs[wib][c] = x[src * d + c];
         __syncwarp();
-        float best = FLT_MAX;
-        int bj = 0x7fffffff;
-        for (int j = lane; j < k; j += 32) {
+        unsigned long long key = ~0ull;
+        const int j1 = min(k, (int)(blk + 1) * FB_CODES);
+        for (int j = (int)blk * FB_CODES + lane; j < j1; j += 32) {
             const float *cr = cb + (size_t)j * d;
             float a = 0.f;
             for (int c = 0; c < d; c++) {
                 const float df = xs[wib][c] - cr[c];
                 a = fmaf(df, df, a);
             }
-            if (a < best) { best = a; bj = j; }
+            const unsigned long long kj = ((unsigned long long)__float_as_uint(a) << 32) | (unsigned int)j;
+            key = kj < key ? kj : key;
         }
         for (int o = 16; o > 0; o >>= 1) {
-            const float ob = __shfl_xor_sync(0xffffffffu, best, o);
-            const int oj = __shfl_xor_sync(0xffffffffu, bj, o);
-            if (ob < best || (ob == best && oj < bj)) { best = ob; bj = oj; }
+            const unsigned long long ok = __shfl_xor_sync(0xffffffffu, key, o);
+            key = ok < key ? ok : key;
         }
-        if (bj == 0x7fffffff) bj = 0;                    // nothing below FLT_MAX: defined fallback index
+        if (lane == 0 && key < FB_INIT) atomicMin(&fb_best[it], key);
+    }
+}
+
+// outputs of the fallback rows (and, in the fused mode, their weighted row into the centroid sums)
+__global__ void __launch_bounds__(128)
+k_assign_fallback_finish(const float *__restrict__ x, const float *__restrict__ w, const int64_t *__restrict__ rows,
+                         int d, const TcHeader *hdr, const unsigned int *__restrict__ fb_list,
+                         const unsigned long long *__restrict__ fb_best, float *__restrict__ out_dist,
+                         int64_t *__restrict__ out_idx, float *__restrict__ acc, int stride)
+{
+    const int lane = threadIdx.x & 31;
+    const unsigned int count = hdr->fb_count;
+    const unsigned int nwarps = gridDim.x * 4;
+    for (unsigned int it = blockIdx.x * 4 + (threadIdx.x >> 5); it < count; it += nwarps) {
+        const int64_t gi = fb_list[it];
+        const unsigned long long best = fb_best[it];
+        const int bj = (int)(best & 0xFFFFFFFFu);            // nothing below FLT_MAX: index 0, distance FLT_MAX
         if (lane == 0) {
             if (out_idx) out_idx[gi] = bj;
-            if (out_dist) out_dist[gi] = best;
+            if (out_dist) out_dist[gi] = __uint_as_float((unsigned int)(best >> 32));
         }
         if (acc) {
+            const int64_t src = rows ? rows[gi] : gi;
             const float wv = w ? w[src] : 1.f;
             float *ap = acc + (size_t)bj * stride;
-            for (int c = lane; c <= d; c += 32) atomicAdd(ap + c, c < d ? __fmul_rn(xs[wib][c], wv) : wv);
+            for (int c = lane; c <= d; c += 32) atomicAdd(ap + c, c < d ? __fmul_rn(x[src * d + c], wv) : wv);
         }
     }
 }
@@ -863,7 +893,7 @@ k_assign_fallback(const float *__restrict__ x, const float *__restrict__ w, cons
 static inline size_t al256(size_t v) { return (v + 255) & ~(size_t)255; }
 
 struct TcLayout {
-    size_t off_mu, off_bimg, off_cbp, off_fb, total;
+    size_t off_mu, off_bimg, off_cbp, off_fb, off_fbbest, total;
     int dp, nc, dpc, k_pad, bn;
 };
 
@@ -885,6 +915,8 @@ static TcLayout tc_layout(int64_t n, int d, int k)
     o += al256((size_t)(k > 0 ? k : 1) * l.dpc * sizeof(float));
     l.off_fb = o;
     o += al256((size_t)(n > 0 ? n : 1) * sizeof(unsigned int));
+    l.off_fbbest = o;
+    o += al256((size_t)(n > 0 ? n : 1) * sizeof(unsigned long long));
     l.total = o;
     return l;
 }
@@ -947,6 +979,7 @@ int launch_assign_tc(const float *x, const float *w, const int64_t *rows, int64_
     p.bimg = bimg; p.cbp = cbp; p.dpc = l.dpc; p.mu = mu; p.hdr = hdr;
     p.out_dist = out_dist; p.out_idx = out_idx; p.acc = acc; p.acc_stride = acc_stride(d);
     p.fb_list = fb;
+    p.fb_best = (unsigned long long *)(base + l.off_fbbest);
     p.dbg_scores = dbg_scores; p.dbg_norm2 = dbg_norm2; p.dbg_band = dbg_band;
     p.gamma2 = 2.1f * (float)(d + 3) * 5.9604644775390625e-8f;      // 2.1 (d+3) 2^-24
     const int sms = sm_count();
@@ -979,9 +1012,11 @@ int launch_assign_tc(const float *x, const float *w, const int64_t *rows, int64_
 #endif
     if (rc) return rc;
     if (dbg_scores == nullptr) {
-        k_assign_fallback<<<sms * 4, 128, 0, s>>>(x, w, rows, d, codebook, k, hdr, fb, out_dist, out_idx, acc,
-                                                  acc_stride(d));
-        C3VQ_LAUNCH_CHECK("k_assign_fallback");
+        k_assign_fallback_scan<<<sms * 4, 128, 0, s>>>(x, rows, d, codebook, k, hdr, fb, p.fb_best);
+        C3VQ_LAUNCH_CHECK("k_assign_fallback_scan");
+        k_assign_fallback_finish<<<sms, 128, 0, s>>>(x, w, rows, d, hdr, fb, p.fb_best, out_dist, out_idx, acc,
+                                                     acc_stride(d));
+        C3VQ_LAUNCH_CHECK("k_assign_fallback_finish");
     }
     return C3VQ_OK;
 }
