@@ -24,7 +24,7 @@ def install(patch_vq_module: bool = True) -> None:
     1. `weighted_distance` / `weighted_distance._C` in sys.modules -> this package's drop-in, so
        `from weighted_distance._C import weightedDistance` (compression/vq.py:12) binds to libc3vq.
     2. If the reference's `compression.vq` is (or later gets) imported and `patch_vq_module` is
-       true, its `VectorQuantize`, `vq_features` and `ema_inplace` are rebound to the fused
+       true, its `VectorQuantize`, `vq_features`, `ema_inplace` and `join_features` are rebound to the fused
        versions, so compress_color / compress_covariance (vq.py:139, :164) call them.
     """
     from . import weighted_distance as wd
@@ -46,3 +46,4 @@ def patch_reference_module(mod) -> None:
     mod.VectorQuantize = _vq.VectorQuantize
     mod.vq_features = _vq.vq_features
     mod.ema_inplace = _vq.ema_inplace
+    mod.join_features = _vq.join_features

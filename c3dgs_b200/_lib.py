@@ -64,6 +64,9 @@ SIGNATURES = {
                                         _c_vp, _c_vp, _c_sz, _c_vp]),
     "c3vq_gather": (_c_int, [_c_vp, _c_i64, _c_int, _c_vp, _c_i64, _c_vp, _c_vp]),
     "c3vq_scatter_add": (_c_int, [_c_vp, _c_vp, _c_i64, _c_int, _c_vp, _c_i64, _c_vp]),
+    "c3vq_join_workspace_bytes": (_c_sz, [_c_i64]),
+    "c3vq_join_count": (_c_int, [_c_vp, _c_i64, ctypes.POINTER(_c_i64), _c_vp, _c_sz, _c_vp]),
+    "c3vq_join_write": (_c_int, [_c_vp, _c_vp, _c_i64, _c_int, _c_vp, _c_i64, _c_vp, _c_vp, _c_vp, _c_vp, _c_vp]),
     "c3vq_gather_rows": (_c_int, [_c_vp, _c_vp, _c_vp, _c_i64, _c_int, _c_vp, _c_vp, _c_vp]),
     "c3vq_debug_scores": (_c_int, [_c_vp, _c_i64, _c_int, _c_vp, _c_int, _c_vp, _c_vp, _c_vp, _c_vp, _c_sz, _c_vp]),
     "c3vq_assign_stats": (_c_int, [_c_vp, ctypes.POINTER(_c_i64), _c_vp]),
@@ -305,6 +308,44 @@ def gather(table: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
     if rc:
         raise _err(rc)
     return out
+
+
+def join_features(all_features: torch.Tensor, keep_mask: torch.Tensor, codebook: torch.Tensor,
+                  codebook_indices: torch.Tensor):
+    """compression/vq.py:90-103 in two kernels: (cat(codebook, all_features[keep_mask]), remapped int64 indices).
+    c3vq_join_count + c3vq_join_write."""
+    _check(all_features, torch.float32, "all_features", 2)
+    _check(codebook, torch.float32, "codebook", 2)
+    _check(codebook_indices, torch.int64, "codebook_indices", 1)
+    if keep_mask.dtype != torch.bool or keep_mask.dim() != 1 or not keep_mask.is_cuda:
+        raise RuntimeError("keep_mask must be a 1-D CUDA bool tensor")
+    n, d = all_features.shape
+    if keep_mask.numel() != n:
+        raise RuntimeError("keep_mask must have one entry per row of all_features")
+    if codebook.numel() and codebook.size(1) != d:
+        raise RuntimeError("codebook and all_features must have the same number of channels")
+    all_features, keep_mask = all_features.contiguous(), keep_mask.contiguous()
+    codebook, codebook_indices = codebook.contiguous(), codebook_indices.contiguous()
+    k = codebook.size(0)
+    L = load()
+    with torch.cuda.device(all_features.device):
+        nbytes = L.c3vq_join_workspace_bytes(n)
+        ws = torch.empty(max(int(nbytes), 4), dtype=torch.uint8, device=all_features.device)
+        kept = _c_i64(0)
+        rc = L.c3vq_join_count(_ptr(keep_mask), n, ctypes.byref(kept), _ptr(ws), ws.numel(), _stream(all_features))
+        if rc:
+            raise _err(rc)
+        kept = int(kept.value)
+        if codebook_indices.numel() != n - kept:
+            raise RuntimeError(f"codebook_indices has {codebook_indices.numel()} entries for {n - kept} rows "
+                               "outside keep_mask")
+        out_f = torch.empty(k + kept, d, dtype=torch.float32, device=all_features.device)
+        out_i = torch.empty(n, dtype=torch.int64, device=all_features.device)
+        rc = L.c3vq_join_write(_ptr(all_features), _ptr(keep_mask), n, d, _ptr(codebook), k, _ptr(codebook_indices),
+                               _ptr(out_f), _ptr(out_i), _ptr(ws), _stream(all_features))
+    if rc:
+        raise _err(rc)
+    return out_f, out_i
 
 
 def scatter_add(grad_out: torch.Tensor, idx: torch.Tensor, table_rows: int) -> torch.Tensor:

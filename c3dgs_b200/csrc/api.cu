@@ -223,6 +223,35 @@ int c3vq_scatter_add(const float *grad_out, const int64_t *idx, int64_t n, int d
                              (cudaStream_t)stream);
 }
 
+size_t c3vq_join_workspace_bytes(int64_t n) { return n < 0 ? 0 : join_workspace_bytes(n); }
+
+int c3vq_join_count(const uint8_t *keep_mask, int64_t n, int64_t *out_kept, void *ws, size_t ws_bytes,
+                    c3vq_stream_t stream)
+{
+    C3VQ_CHECK_ARG(n >= 0, "n=%lld is negative", (long long)n);
+    C3VQ_CHECK_ARG(n == 0 || keep_mask != nullptr, "keep_mask is null");
+    C3VQ_CHECK_ARG(out_kept != nullptr, "out_kept is null");
+    cudaStream_t s = (cudaStream_t)stream;
+    int rc = launch_join_count(keep_mask, n, ws, ws_bytes, s);
+    if (rc) return rc;
+    const int64_t nb = (n + 1023) / 1024;
+    unsigned int kept = 0;
+    C3VQ_CUDA(cudaMemcpyAsync(&kept, (const unsigned int *)ws + nb, sizeof(kept), cudaMemcpyDeviceToHost, s));
+    C3VQ_CUDA(cudaStreamSynchronize(s));
+    *out_kept = (int64_t)kept;
+    return C3VQ_OK;
+}
+
+int c3vq_join_write(const float *all_features, const uint8_t *keep_mask, int64_t n, int d, const float *codebook,
+                    int64_t k, const int64_t *codebook_indices, float *out_features, int64_t *out_indices,
+                    const void *ws, c3vq_stream_t stream)
+{
+    C3VQ_CHECK_ARG(n >= 0 && d >= 0 && k >= 0, "negative size");
+    C3VQ_CHECK_ARG(n == 0 || (keep_mask && out_indices && ws), "null pointer");
+    return launch_join_write(all_features, keep_mask, n, d, codebook, k, codebook_indices, out_features, out_indices,
+                             ws, (cudaStream_t)stream);
+}
+
 int c3vq_gather_rows(const float *x, const float *w, const int64_t *rows, int64_t n, int d, float *out_x,
                      float *out_w, c3vq_stream_t stream)
 {

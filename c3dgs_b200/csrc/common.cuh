@@ -67,6 +67,12 @@ int launch_gather(const float *table, int64_t table_rows, int d, const int64_t *
 int launch_gather_rows(const float *x, const float *w, const int64_t *rows, int64_t n, int d, float *out_x,
                        float *out_w, cudaStream_t s);
 
+// join_features (gather.cu): count + scan of the keep mask (kept total at ((unsigned*)ws)[blocks]), then the write pass
+size_t join_workspace_bytes(int64_t n);
+int launch_join_count(const uint8_t *keep, int64_t n, void *ws, size_t ws_bytes, cudaStream_t s);
+int launch_join_write(const float *feats, const uint8_t *keep, int64_t n, int d, const float *codebook, int64_t k,
+                      const int64_t *cb_idx, float *out_feats, int64_t *out_idx, const void *ws, cudaStream_t s);
+
 // tensor-core assignment (assign_tc.cu)
 size_t tc_workspace_bytes(int64_t n, int d, int k);
 int launch_assign_tc(const float *x, const float *w, const int64_t *rows, int64_t n, int d, const float *codebook,

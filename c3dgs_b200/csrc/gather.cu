@@ -97,4 +97,134 @@ int launch_gather_rows(const float *x, const float *w, const int64_t *rows, int6
     return C3VQ_OK;
 }
 
+// ------------------------------------------------------------------------------------------------
+// join_features (compression/vq.py:90-103): the step right after the clustering.
+//   out_features = cat(codebook [k, d], all_features[keep_mask])            (boolean-mask compaction, stable)
+//   out_indices[i] = k + rank_keep(i)                        if keep_mask[i]
+//                  = codebook_indices[i - rank_keep(i)]      otherwise (the i-th non-kept row's codeword)
+// One pass over the mask for block counts, a scan of the counts, one pass that ranks every row inside its block
+// (warp ballots) and moves the kept rows with lanes over columns.  Integer / copy work: bit-exact.
+constexpr int JOIN_ROWS = 1024;     // rows per block (one per thread)
+
+__global__ void __launch_bounds__(JOIN_ROWS)
+k_join_count(const uint8_t *__restrict__ keep, int64_t n, unsigned int *__restrict__ block_counts)
+{
+    const int64_t i = (int64_t)blockIdx.x * JOIN_ROWS + threadIdx.x;
+    const int kp = (i < n && keep[i]) ? 1 : 0;
+    const int c = __syncthreads_count(kp);
+    if (threadIdx.x == 0) block_counts[blockIdx.x] = (unsigned int)c;
+}
+
+// exclusive scan of the block counts in place (one CTA); total kept rows -> counts[nb]
+__global__ void __launch_bounds__(1024)
+k_join_scan(unsigned int *__restrict__ counts, int nb)
+{
+    __shared__ unsigned int part[1024];
+    const int per = (nb + 1023) / 1024;
+    const int j0 = threadIdx.x * per;
+    unsigned int sum = 0;
+    for (int j = j0; j < min(nb, j0 + per); j++) sum += counts[j];
+    part[threadIdx.x] = sum;
+    __syncthreads();
+    for (int o = 1; o < 1024; o <<= 1) {
+        const unsigned int v = threadIdx.x >= o ? part[threadIdx.x - o] : 0u;
+        __syncthreads();
+        part[threadIdx.x] += v;
+        __syncthreads();
+    }
+    unsigned int run = part[threadIdx.x] - sum;
+    for (int j = j0; j < min(nb, j0 + per); j++) {
+        const unsigned int c = counts[j];
+        counts[j] = run;
+        run += c;
+    }
+    if (threadIdx.x == 1023) counts[nb] = part[1023];
+}
+
+__global__ void __launch_bounds__(JOIN_ROWS)
+k_join_write(const float *__restrict__ feats, const uint8_t *__restrict__ keep, int64_t n, int d, int64_t k,
+             const int64_t *__restrict__ cb_idx, const unsigned int *__restrict__ block_base,
+             float *__restrict__ out_feats, int64_t *__restrict__ out_idx)
+{
+    __shared__ unsigned int warp_cnt[32];
+    __shared__ unsigned int src_row[JOIN_ROWS];             // block-local list of kept rows (in order)
+    __shared__ unsigned int s_kept;
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int64_t i = (int64_t)blockIdx.x * JOIN_ROWS + threadIdx.x;
+    const bool kp = i < n && keep[i];
+    const unsigned int bal = __ballot_sync(0xffffffffu, kp);
+    if (lane == 0) warp_cnt[wib] = __popc(bal);
+    __syncthreads();
+    if (wib == 0) {                                         // exclusive scan of the 32 warp counts
+        unsigned int v = warp_cnt[lane], incl = v;
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned int u = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += u;
+        }
+        warp_cnt[lane] = incl - v;
+        if (lane == 31) s_kept = incl;
+    }
+    __syncthreads();
+    const unsigned int local = warp_cnt[wib] + __popc(bal & ((1u << lane) - 1u));   // kept rows before i in the block
+    const unsigned int base = block_base[blockIdx.x];       // kept rows before the block
+    if (i < n) {
+        if (kp) {
+            out_idx[i] = k + (int64_t)base + local;
+            src_row[local] = threadIdx.x;
+        } else {
+            out_idx[i] = cb_idx[i - ((int64_t)base + local)];
+        }
+    }
+    __syncthreads();
+    // move the kept rows: the block's rows land contiguously at out_feats[(k + base) * d ...]
+    const unsigned int kept = s_kept;
+    const int64_t total = (int64_t)kept * d;
+    float *dst = out_feats + (k + (int64_t)base) * d;
+    const float *srcb = feats + (int64_t)blockIdx.x * JOIN_ROWS * d;
+    for (int64_t e = threadIdx.x; e < total; e += JOIN_ROWS) {
+        const unsigned int r = (unsigned int)(e / d);
+        const int c = (int)(e - (int64_t)r * d);
+        dst[e] = srcb[(int64_t)src_row[r] * d + c];
+    }
+}
+
+size_t join_workspace_bytes(int64_t n)
+{
+    const int64_t nb = (n + JOIN_ROWS - 1) / JOIN_ROWS;
+    return (size_t)(nb + 1) * sizeof(unsigned int);
+}
+
+int launch_join_count(const uint8_t *keep, int64_t n, void *ws, size_t ws_bytes, cudaStream_t s)
+{
+    if (ws == nullptr || ws_bytes < join_workspace_bytes(n)) {
+        set_error("workspace too small: %zu < %zu", ws_bytes, join_workspace_bytes(n));
+        return C3VQ_EWORKSPACE;
+    }
+    unsigned int *counts = (unsigned int *)ws;
+    const int64_t nb = (n + JOIN_ROWS - 1) / JOIN_ROWS;
+    C3VQ_CHECK_ARG(nb < 0x7fffffffLL, "n=%lld too large", (long long)n);
+    if (nb == 0) {
+        C3VQ_CUDA(cudaMemsetAsync(counts, 0, sizeof(unsigned int), s));
+        return C3VQ_OK;
+    }
+    k_join_count<<<(unsigned)nb, JOIN_ROWS, 0, s>>>(keep, n, counts);
+    C3VQ_LAUNCH_CHECK("k_join_count");
+    k_join_scan<<<1, 1024, 0, s>>>(counts, (int)nb);
+    C3VQ_LAUNCH_CHECK("k_join_scan");
+    return C3VQ_OK;
+}
+
+int launch_join_write(const float *feats, const uint8_t *keep, int64_t n, int d, const float *codebook, int64_t k,
+                      const int64_t *cb_idx, float *out_feats, int64_t *out_idx, const void *ws, cudaStream_t s)
+{
+    if (k > 0 && d > 0)
+        C3VQ_CUDA(cudaMemcpyAsync(out_feats, codebook, (size_t)k * d * sizeof(float), cudaMemcpyDeviceToDevice, s));
+    const int64_t nb = (n + JOIN_ROWS - 1) / JOIN_ROWS;
+    if (nb == 0) return C3VQ_OK;
+    k_join_write<<<(unsigned)nb, JOIN_ROWS, 0, s>>>(feats, keep, n, d, k, cb_idx, (const unsigned int *)ws, out_feats,
+                                                     out_idx);
+    C3VQ_LAUNCH_CHECK("k_join_write");
+    return C3VQ_OK;
+}
+
 }  // namespace c3vq

@@ -138,12 +138,9 @@ def join_features(
         codebook: torch.Tensor,
         codebook_indices: torch.Tensor,
 ) -> Tuple[torch.Tensor, torch.Tensor]:
-    # vq.py:90-103 — boundary caller, unchanged semantics (plain torch for now)
-    keep_features = all_features[keep_mask]
-    compressed_features = torch.cat([codebook, keep_features], 0)
-
-    indices = torch.zeros(len(all_features), dtype=torch.long, device=all_features.device)
-    indices[~keep_mask] = codebook_indices
-    indices[keep_mask] = torch.arange(len(keep_features), device=indices.device) + len(codebook)
-
-    return compressed_features, indices
+    """Drop-in for compression/vq.py:90-103: stable compaction of the kept rows behind the
+    codebook and the index remap, in two kernels of libc3vq (c3vq_join_count / c3vq_join_write) instead of two
+    boolean-mask gathers, a cat, a zeros, two masked scatters and an arange."""
+    if codebook.dim() != 2:                      # the reference's empty covariance codebook is [0, C, 1] (vq.py:172)
+        codebook = codebook.reshape(codebook.shape[0], -1)
+    return _lib.join_features(all_features.detach(), keep_mask, codebook.detach(), codebook_indices)

@@ -135,6 +135,24 @@ int c3vq_gather(const float *table, int64_t table_rows, int d,
 int c3vq_scatter_add(const float *grad_out, const int64_t *idx, int64_t n, int d,
                      float *grad_table, int64_t table_rows, c3vq_stream_t stream);
 
+/*
+ * join_features (compression/vq.py:90-103), the step right after the clustering:
+ *   out_features [k + kept, d] = cat(codebook [k, d], all_features[keep_mask])     (stable compaction)
+ *   out_indices [n] (int64)    = k + rank among the kept rows                 where keep_mask[i] != 0
+ *                              = codebook_indices[rank among the other rows]  elsewhere
+ * Two calls because the output size depends on the data: c3vq_join_count scans the mask (one byte per row,
+ * torch.bool layout) into ws and returns the number of kept rows (host value; synchronises `stream`), the
+ * caller allocates out_features and calls c3vq_join_write with the same ws.  codebook_indices has n - kept
+ * entries.  ws: c3vq_join_workspace_bytes(n) bytes.  Integer / copy work: results are bit-exact.
+ */
+size_t c3vq_join_workspace_bytes(int64_t n);
+int c3vq_join_count(const uint8_t *keep_mask, int64_t n, int64_t *out_kept,
+                    void *ws, size_t ws_bytes, c3vq_stream_t stream);
+int c3vq_join_write(const float *all_features, const uint8_t *keep_mask, int64_t n, int d,
+                    const float *codebook, int64_t k, const int64_t *codebook_indices,
+                    float *out_features, int64_t *out_indices,
+                    const void *ws, c3vq_stream_t stream);
+
 /* Mini-batch row gather: out_x[i,:] = x[rows[i],:], out_w[i] = w[rows[i]] (w/out_w may be null). */
 int c3vq_gather_rows(const float *x, const float *w, const int64_t *rows, int64_t n, int d,
                      float *out_x, float *out_w, c3vq_stream_t stream);

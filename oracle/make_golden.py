@@ -118,12 +118,37 @@ def run_case(name, n, d, k, chunk, steps, scale_normalize, seed):
     return path
 
 
+def run_join_cases():
+    """join_features (compression/vq.py:90-103) of the reference, run unchanged on CPU tensors: inputs and outputs
+    of a few shapes incl. nothing kept, everything kept, an empty codebook and a ragged last block."""
+    mod = ref_loader.load()
+    out = {}
+    cases = [("a", 5000, 45, 64, 0.07), ("b", 2049, 6, 17, 0.5), ("none", 300, 7, 5, 0.0), ("all", 300, 7, 5, 1.0),
+             ("emptycb", 1500, 48, 0, 0.3), ("one", 1, 3, 2, 1.0)]
+    for name, n, d, k, frac in cases:
+        g = torch.Generator().manual_seed(n + d)
+        feats = torch.randn(n, d, generator=g)
+        keep = torch.rand(n, generator=g) < frac
+        cb = torch.randn(k, d, generator=g)
+        cb_idx = torch.randint(0, max(k, 1), (int((~keep).sum()),), generator=g)
+        comp, idx = mod.join_features(feats, keep, cb, cb_idx)
+        out.update({f"{name}_feats": feats.numpy(), f"{name}_keep": keep.numpy(), f"{name}_cb": cb.numpy(),
+                    f"{name}_cbidx": cb_idx.numpy(), f"{name}_out": comp.numpy(), f"{name}_idx": idx.numpy()})
+    out["names"] = np.array([c[0] for c in cases])
+    path = os.path.join(GOLDEN_DIR, "join_features.npz")
+    np.savez_compressed(path, **out)
+    return path
+
+
 def main():
     if not ref_loader.available():
         raise SystemExit("reference checkout not present; fixtures can only be generated in the build container")
-    for case in CASES:
-        p = run_case(*case)
-        print("wrote", p, os.path.getsize(p) // 1024, "KiB")
+    if "--join-only" not in sys.argv:
+        for case in CASES:
+            p = run_case(*case)
+            print("wrote", p, os.path.getsize(p) // 1024, "KiB")
+    p = run_join_cases()
+    print("wrote", p, os.path.getsize(p) // 1024, "KiB")
 
 
 if __name__ == "__main__":

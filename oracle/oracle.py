@@ -185,3 +185,17 @@ def vq_features(features, importance, codebook0, batches, decay=0.8, scale_norma
             trace_normalize(cb)
     _, final_idx = assign(features, cb)                       # vq.py:82
     return cb, ei, final_idx, trace
+
+
+def join_features(all_features, keep_mask, codebook, codebook_indices):
+    """compression/vq.py:90-103 restated in numpy (boolean-mask compaction is stable, like torch's):
+    returns (cat(codebook, all_features[keep_mask]), int64 indices)."""
+    all_features = np.asarray(all_features, np.float32)
+    keep_mask = np.asarray(keep_mask, bool)
+    codebook = np.asarray(codebook, np.float32).reshape(-1, all_features.shape[1])
+    keep_features = all_features[keep_mask]                                        # vq.py:96
+    compressed = np.concatenate([codebook, keep_features], 0)                      # vq.py:97
+    indices = np.zeros(len(all_features), np.int64)                                # vq.py:99
+    indices[~keep_mask] = np.asarray(codebook_indices, np.int64)                   # vq.py:100
+    indices[keep_mask] = np.arange(len(keep_features), dtype=np.int64) + len(codebook)   # vq.py:101
+    return compressed, indices

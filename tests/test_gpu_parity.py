@@ -362,6 +362,36 @@ def test_gather_rows_matches_indexing(L):
     assert torch.equal(ox.cpu(), x[rows]) and torch.equal(ow.cpu(), w[rows])
 
 
+# ---------------------------------------------------------------- join_features -------
+def test_join_features_bit_exact_vs_reference_golden(L, oracle):
+    g = np.load(golden_path("join_features").replace("vq_join_features", "join_features"))
+    import c3dgs_b200
+    for name in g["names"]:
+        comp, idx = c3dgs_b200.join_features(_t(g[f"{name}_feats"]), _t(g[f"{name}_keep"]), _t(g[f"{name}_cb"]),
+                                             _t(g[f"{name}_cbidx"]))
+        assert idx.dtype == torch.int64 and comp.dtype == torch.float32
+        assert np.array_equal(idx.cpu().numpy(), g[f"{name}_idx"]), name
+        assert tuple(comp.shape) == g[f"{name}_out"].shape, name
+        assert np.array_equal(comp.cpu().numpy().view(np.uint32), g[f"{name}_out"].view(np.uint32)), name
+
+
+def test_join_features_large_and_errors(L, oracle):
+    n, d, k = 1_000_003, 45, 4096
+    gen = torch.Generator(device=DEV).manual_seed(4)
+    feats = torch.randn(n, d, device=DEV, generator=gen)
+    keep = torch.rand(n, device=DEV, generator=gen) < 0.04
+    cb = torch.randn(k, d, device=DEV, generator=gen)
+    cb_idx = torch.randint(0, k, (int((~keep).sum()),), device=DEV, generator=gen)
+    comp, idx = L.join_features(feats, keep, cb, cb_idx)
+    comp_o, idx_o = oracle.join_features(feats.cpu().numpy(), keep.cpu().numpy(), cb.cpu().numpy(), cb_idx.cpu().numpy())
+    assert np.array_equal(idx.cpu().numpy(), idx_o) and np.array_equal(comp.cpu().numpy(), comp_o)
+    assert torch.equal(comp[idx], torch.where(keep[:, None], feats, cb[idx.clamp(max=k - 1)]))   # decode round trip
+    with pytest.raises(RuntimeError):
+        L.join_features(feats, keep, cb, cb_idx[:-1])
+    with pytest.raises(RuntimeError):
+        L.join_features(feats, keep.to(torch.uint8), cb, cb_idx)
+
+
 # ---------------------------------------------------------------- full size ------------------
 @pytest.mark.parametrize("d", [45, 7])
 def test_full_size_properties(L, d):

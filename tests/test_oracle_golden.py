@@ -151,3 +151,15 @@ def test_reference_module_agrees_with_oracle_on_fresh_inputs(oracle):
     assert np.array_equal(dist, dist_ref.numpy())
     assert np.array_equal(cb, vq.codebook.data.numpy())
     assert np.array_equal(ei, vq.entry_importance.data.numpy())
+
+
+def test_oracle_join_features_reproduces_reference(oracle):
+    """oracle.join_features against the reference's own join_features (compression/vq.py:90-103) run on CPU by
+    oracle/make_golden.py: kept rows compacted behind the codebook, int64 index remap."""
+    g = np.load(golden_path("join_features").replace("vq_join_features", "join_features"))
+    for name in g["names"]:
+        comp, idx = oracle.join_features(g[f"{name}_feats"], g[f"{name}_keep"], g[f"{name}_cb"], g[f"{name}_cbidx"])
+        assert idx.dtype == np.int64
+        assert np.array_equal(idx, g[f"{name}_idx"]), name
+        assert comp.shape == g[f"{name}_out"].shape and np.array_equal(comp.view(np.uint32),
+                                                                       g[f"{name}_out"].view(np.uint32)), name
