@@ -775,7 +775,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                 status = ROW_FALLBACK;
             // the two threads of a row exchange their running minima: both filter with the row's threshold
             sXchg[(qb * 2 + h) * TC_PR + lr] = m;             // double buffered: one barrier per pass is enough
-            named_bar_sync(2, TC_DT);
+            named_bar_sync(3 + (dw & 7), 64);                 // only the two warps that share these 32 rows meet
             m = fminf(m, sXchg[(qb * 2 + (h ^ 1)) * TC_PR + lr]);
             if (status == ROW_OK) {
                 thr = m + p.gamma2 * fabsf(m) + band;
