@@ -4,6 +4,7 @@ Public surface (mirrors the reference, compression/vq.py and submodules/weighted
     VectorQuantize, vq_features, ema_inplace, join_features      (c3dgs_b200.vq)
     weighted_distance._C.weightedDistance                        (c3dgs_b200.weighted_distance)
     indexed_decode                                               (c3dgs_b200.decode)
+    to_full_cov, extract_rot_scale                               (c3dgs_b200.splats)
     install()   register the drop-ins under the reference's module names
 """
 from __future__ import annotations
@@ -12,10 +13,11 @@ import sys
 
 from . import _lib  # noqa: F401
 from .decode import indexed_decode, decode_gaussians  # noqa: F401
+from .splats import extract_rot_scale, to_full_cov  # noqa: F401
 from .vq import VectorQuantize, ema_inplace, join_features, vq_features  # noqa: F401
 
 __all__ = ["VectorQuantize", "vq_features", "ema_inplace", "join_features", "indexed_decode",
-           "decode_gaussians", "install"]
+           "decode_gaussians", "to_full_cov", "extract_rot_scale", "install"]
 
 
 def install(patch_vq_module: bool = True) -> None:
@@ -24,8 +26,8 @@ def install(patch_vq_module: bool = True) -> None:
     1. `weighted_distance` / `weighted_distance._C` in sys.modules -> this package's drop-in, so
        `from weighted_distance._C import weightedDistance` (compression/vq.py:12) binds to libc3vq.
     2. If the reference's `compression.vq` is (or later gets) imported and `patch_vq_module` is
-       true, its `VectorQuantize`, `vq_features`, `ema_inplace` and `join_features` are rebound to the fused
-       versions, so compress_color / compress_covariance (vq.py:139, :164) call them.
+       true, its `VectorQuantize`, `vq_features`, `ema_inplace`, `join_features`, `to_full_cov` and
+       `extract_rot_scale` are rebound to the versions here, so compress_color / compress_covariance (vq.py:139, :164) call them.
     """
     from . import weighted_distance as wd
 
@@ -47,3 +49,7 @@ def patch_reference_module(mod) -> None:
     mod.vq_features = _vq.vq_features
     mod.ema_inplace = _vq.ema_inplace
     mod.join_features = _vq.join_features
+    if hasattr(mod, "extract_rot_scale"):                     # compression/vq.py:11 imports both by name
+        from . import splats as _splats
+        mod.extract_rot_scale = _splats.extract_rot_scale
+        mod.to_full_cov = _splats.to_full_cov

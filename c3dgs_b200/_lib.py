@@ -67,6 +67,7 @@ SIGNATURES = {
     "c3vq_join_workspace_bytes": (_c_sz, [_c_i64]),
     "c3vq_join_count": (_c_int, [_c_vp, _c_i64, ctypes.POINTER(_c_i64), _c_vp, _c_sz, _c_vp]),
     "c3vq_join_write": (_c_int, [_c_vp, _c_vp, _c_i64, _c_int, _c_vp, _c_i64, _c_vp, _c_vp, _c_vp, _c_vp, _c_vp]),
+    "c3vq_extract_rot_scale": (_c_int, [_c_vp, _c_i64, _c_int, _c_vp, _c_vp, _c_vp]),
     "c3vq_gather_rows": (_c_int, [_c_vp, _c_vp, _c_vp, _c_i64, _c_int, _c_vp, _c_vp, _c_vp]),
     "c3vq_debug_scores": (_c_int, [_c_vp, _c_i64, _c_int, _c_vp, _c_int, _c_vp, _c_vp, _c_vp, _c_vp, _c_sz, _c_vp]),
     "c3vq_assign_stats": (_c_int, [_c_vp, ctypes.POINTER(_c_i64), _c_vp]),
@@ -346,6 +347,27 @@ def join_features(all_features: torch.Tensor, keep_mask: torch.Tensor, codebook:
     if rc:
         raise _err(rc)
     return out_f, out_i
+
+
+def extract_rot_scale(cov: torch.Tensor):
+    """utils/splats.py:28-36 (with to_full_cov, :7-25, fused away when `cov` is [n,6]): cov [n,6] stored entries or
+    [n,3,3] -> (rot [n,4] unit quaternions, scaling [n,3] ascending).  c3vq_extract_rot_scale."""
+    _check(cov, torch.float32, "cov")
+    if cov.dim() == 2 and cov.size(1) == 6:
+        full = 0
+    elif cov.dim() == 3 and tuple(cov.shape[1:]) == (3, 3):
+        full = 1
+    else:
+        raise RuntimeError(f"cov must be [n,6] or [n,3,3], got {tuple(cov.shape)}")
+    cov = cov.contiguous()
+    n = cov.size(0)
+    with torch.cuda.device(cov.device):
+        rot = torch.empty(n, 4, dtype=torch.float32, device=cov.device)
+        scale = torch.empty(n, 3, dtype=torch.float32, device=cov.device)
+        rc = load().c3vq_extract_rot_scale(_ptr(cov), n, full, _ptr(rot), _ptr(scale), _stream(cov))
+    if rc:
+        raise _err(rc)
+    return rot, scale
 
 
 def scatter_add(grad_out: torch.Tensor, idx: torch.Tensor, table_rows: int) -> torch.Tensor:

@@ -252,6 +252,16 @@ int c3vq_join_write(const float *all_features, const uint8_t *keep_mask, int64_t
                              ws, (cudaStream_t)stream);
 }
 
+int c3vq_extract_rot_scale(const float *cov, int64_t n, int full, float *out_rot, float *out_scale,
+                           c3vq_stream_t stream)
+{
+    C3VQ_CHECK_ARG(n >= 0, "n=%lld is negative", (long long)n);
+    C3VQ_CHECK_ARG(n == 0 || (cov && out_rot && out_scale), "null pointer");
+    C3VQ_CHECK_ARG(((uintptr_t)cov & 7) == 0 && ((uintptr_t)out_rot & 15) == 0,
+                   "cov must be 8-byte and out_rot 16-byte aligned");
+    return launch_rot_scale(cov, n, full, out_rot, out_scale, (cudaStream_t)stream);
+}
+
 int c3vq_gather_rows(const float *x, const float *w, const int64_t *rows, int64_t n, int d, float *out_x,
                      float *out_w, c3vq_stream_t stream)
 {

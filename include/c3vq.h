@@ -153,6 +153,18 @@ int c3vq_join_write(const float *all_features, const uint8_t *keep_mask, int64_t
                     float *out_features, int64_t *out_indices,
                     const void *ws, c3vq_stream_t stream);
 
+/*
+ * extract_rot_scale(to_full_cov(cov)) (utils/splats.py:7-36; called on the joined covariance table at
+ * compression/vq.py:186): per row, add 1e-8 to the diagonal, eigendecompose the symmetric 3x3 (float32, upper
+ * triangle, eigenvalues ascending), out_scale = sqrt(eigenvalues) with NaN -> 1e-6, out_rot = unit quaternion
+ * (real part first) of eigenvectors * det.  cov rows are the 6 stored entries xx, xy, xz, yy, yz, zz when
+ * full == 0 (to_full_cov is fused away) or row-major 3x3 when full != 0.  Eigenvalues and R diag(s^2) R^T agree
+ * with the reference to float32 rounding (a few 1e-7 of the largest entry); the signs of individual
+ * eigenvectors are an implementation detail of LAPACK and are not reproduced.
+ */
+int c3vq_extract_rot_scale(const float *cov, int64_t n, int full, float *out_rot /* [n,4] */,
+                           float *out_scale /* [n,3] */, c3vq_stream_t stream);
+
 /* Mini-batch row gather: out_x[i,:] = x[rows[i],:], out_w[i] = w[rows[i]] (w/out_w may be null). */
 int c3vq_gather_rows(const float *x, const float *w, const int64_t *rows, int64_t n, int d,
                      float *out_x, float *out_w, c3vq_stream_t stream);

@@ -140,14 +140,57 @@ def run_join_cases():
     return path
 
 
+def synth_covariances(seed=0):
+    """Inputs for extract_rot_scale: trace-normalised covariances like get_normalized_covariance(strip_sym=True)
+    (scene/gaussian_model.py:274-278) plus the degenerate shapes the decomposition has to survive."""
+    g = torch.Generator().manual_seed(seed)
+    n = 4000
+    q = torch.nn.functional.normalize(torch.randn(n, 4, generator=g))
+    r, x, y, z = q.unbind(-1)
+    R = torch.stack([1 - 2 * (y * y + z * z), 2 * (x * y - r * z), 2 * (x * z + r * y),
+                     2 * (x * y + r * z), 1 - 2 * (x * x + z * z), 2 * (y * z - r * x),
+                     2 * (x * z - r * y), 2 * (y * z + r * x), 1 - 2 * (x * x + y * y)], -1).reshape(n, 3, 3)
+    s = torch.exp(torch.randn(n, 3, generator=g) * 1.5 - 3.0)
+    s[:500, 1] = s[:500, 0]                                  # a repeated eigenvalue
+    s[500:700] = s[500:700, :1]                              # isotropic
+    s[700:900, 0] = 0.0                                      # flat splats (rank 2)
+    s[900:1000, :2] = 0.0                                    # needles (rank 1)
+    s[1000:1100] *= 1e-4                                     # tiny
+    s[1100:1200] *= 1e3                                      # large
+    cov = R @ torch.diag_embed(s * s) @ R.transpose(-1, -2)
+    cov[1200:3000] /= cov[1200:3000].diagonal(dim1=-1, dim2=-2).sum(-1)[:, None, None]   # trace-normalised
+    cov6 = torch.stack([cov[:, 0, 0], cov[:, 0, 1], cov[:, 0, 2], cov[:, 1, 1], cov[:, 1, 2], cov[:, 2, 2]], -1)
+    special = torch.tensor([[0, 0, 0, 0, 0, 0], [1, 0, 0, 1, 0, 1], [3, 0, 0, 2, 0, 1], [1, 0, 0, 2, 0, 3],
+                            [1, 1, 1, 1, 1, 1], [-1, 0, 0, -2, 0, -3], [1, 2, 0, 1, 0, -5], [0, 1, 0, 0, 0, 0],
+                            [1e-12, 0, 0, 1e-12, 0, 1e-12], [2, -1, 0, 2, -1, 2]], dtype=torch.float32)
+    return torch.cat([special, cov6.float()], 0).contiguous()
+
+
+def run_rot_scale_case():
+    """extract_rot_scale(to_full_cov(.)) of the reference (utils/splats.py:7-36, called at compression/vq.py:186),
+    run unchanged on CPU tensors (float32 LAPACK)."""
+    mod = ref_loader.load()
+    cov6 = synth_covariances()
+    rot, scale = mod.extract_rot_scale(mod.to_full_cov(cov6))
+    path = os.path.join(GOLDEN_DIR, "rot_scale.npz")
+    np.savez_compressed(path, cov6=cov6.numpy(), rot=rot.numpy(), scale=scale.numpy())
+    return path
+
+
 def main():
     if not ref_loader.available():
         raise SystemExit("reference checkout not present; fixtures can only be generated in the build container")
+    if "--rot-scale-only" in sys.argv:
+        p = run_rot_scale_case()
+        print("wrote", p, os.path.getsize(p) // 1024, "KiB")
+        return
     if "--join-only" not in sys.argv:
         for case in CASES:
             p = run_case(*case)
             print("wrote", p, os.path.getsize(p) // 1024, "KiB")
     p = run_join_cases()
+    print("wrote", p, os.path.getsize(p) // 1024, "KiB")
+    p = run_rot_scale_case()
     print("wrote", p, os.path.getsize(p) // 1024, "KiB")
 
 

@@ -199,3 +199,69 @@ def join_features(all_features, keep_mask, codebook, codebook_indices):
     indices[~keep_mask] = np.asarray(codebook_indices, np.int64)                   # vq.py:100
     indices[keep_mask] = np.arange(len(keep_features), dtype=np.int64) + len(codebook)   # vq.py:101
     return compressed, indices
+
+
+# ---- §8(f) rank 2: covariance codebook -> (rotation quaternion, scaling), utils/splats.py ----------------------------
+def to_full_cov(cov6):
+    """utils/splats.py:7-25: the 6 stored entries (xx, xy, xz, yy, yz, zz) to a symmetric 3x3, float32."""
+    c = np.asarray(cov6, np.float32).reshape(-1, 6)
+    full = np.zeros((len(c), 3, 3), np.float32)
+    for (i, j), k in (((0, 0), 0), ((0, 1), 1), ((0, 2), 2), ((1, 1), 3), ((1, 2), 4), ((2, 2), 5)):
+        full[:, i, j] = c[:, k]
+        full[:, j, i] = c[:, k]
+    return full
+
+
+def _sqrt_positive_part(x):
+    """utils/splats.py:103-110."""
+    return np.sqrt(np.where(x > 0, x, 0.0))
+
+
+def matrix_to_quaternion(m):
+    """utils/splats.py:45-100 in float64: the four candidate quaternions (each scaled by one of r, i, j, k), pick the
+    one with the largest denominator (first maximum, like argmax)."""
+    m = np.asarray(m, np.float64)
+    m00, m01, m02, m10, m11, m12, m20, m21, m22 = [m[:, i, j] for i in range(3) for j in range(3)]
+    q_abs = _sqrt_positive_part(np.stack([1.0 + m00 + m11 + m22, 1.0 + m00 - m11 - m22,
+                                          1.0 - m00 + m11 - m22, 1.0 - m00 - m11 + m22], -1))     # :59-69
+    cand = np.stack([
+        np.stack([q_abs[:, 0] ** 2, m21 - m12, m02 - m20, m10 - m01], -1),
+        np.stack([m21 - m12, q_abs[:, 1] ** 2, m10 + m01, m02 + m20], -1),
+        np.stack([m02 - m20, m10 + m01, q_abs[:, 2] ** 2, m12 + m21], -1),
+        np.stack([m10 - m01, m20 + m02, m21 + m12, q_abs[:, 3] ** 2], -1)], -2)                   # :72-89
+    cand = cand / (2.0 * np.maximum(q_abs[:, :, None], 0.1))                                      # :93-94
+    return cand[np.arange(len(m)), np.argmax(q_abs, -1)]                                          # :99-101
+
+
+def quaternion_to_matrix(q):
+    """utils/splats.py:113-144 in float64 (real part first)."""
+    q = np.asarray(q, np.float64)
+    r, i, j, k = q[:, 0], q[:, 1], q[:, 2], q[:, 3]
+    two_s = 2.0 / (q * q).sum(-1)
+    o = np.stack([1 - two_s * (j * j + k * k), two_s * (i * j - k * r), two_s * (i * k + j * r),
+                  two_s * (i * j + k * r), 1 - two_s * (i * i + k * k), two_s * (j * k - i * r),
+                  two_s * (i * k - j * r), two_s * (j * k + i * r), 1 - two_s * (i * i + j * j)], -1)
+    return o.reshape(-1, 3, 3)
+
+
+def build_covariance(rotation, scaling):
+    """utils/splats.py:39-42: R diag(s^2) R^T, float64."""
+    R = quaternion_to_matrix(rotation)
+    s2 = np.asarray(scaling, np.float64) ** 2
+    return np.einsum("nij,nj,nkj->nik", R, s2, R)
+
+
+def extract_rot_scale(cov):
+    """utils/splats.py:28-36.  The 1e-8 is added to the diagonal in float32 as the reference does; the
+    eigendecomposition itself is LAPACK in float64 here (the reference's is float32 LAPACK / cuSOLVER), upper
+    triangle only, eigenvalues ascending.  Eigenvector signs are whatever LAPACK returns: the outputs are defined
+    up to the sign choices that leave R diag(s^2) R^T unchanged, and the tests compare through that product.
+    Returns (rot [n,4] f32 unit quaternions, real part first; scaling [n,3] f32 ascending)."""
+    a32 = np.asarray(cov, np.float32).reshape(-1, 3, 3) + (np.eye(3, dtype=np.float32) * np.float32(1e-8))
+    S, R = np.linalg.eigh(a32.astype(np.float64), UPLO="U")                                       # :30
+    with np.errstate(invalid="ignore"):
+        scaling = np.sqrt(S.astype(np.float32))
+    scaling = np.where(np.isnan(scaling), np.float32(1e-6), scaling).astype(np.float32)           # :31
+    q = matrix_to_quaternion(R * np.linalg.det(R)[:, None, None])                                 # :35
+    q = q / np.maximum(np.linalg.norm(q, axis=-1, keepdims=True), 1e-12)                          # F.normalize
+    return q.astype(np.float32), scaling
