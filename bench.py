@@ -384,6 +384,51 @@ def main():
                                             "rows_per_s": (mb_steps * mb_chunk + n) / dt,
                                             "note": "host wall clock incl. the reference's per-step CPU torch.randint"}}
 
+        # SURVEY §8f ranks 1-2, the steps right after the clustering: join_features (5 % of the rows kept) and
+        # extract_rot_scale on a joined covariance table of n/4 rows; HBM-bound, reported against the copy peak
+        from c3dgs_b200 import _lib as ops2
+        pk = peaks()
+
+        def timed(fn, reps=5):
+            fn()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(reps):
+                fn()
+            b.record()
+            torch.cuda.synchronize()
+            return a.elapsed_time(b) / reps
+
+        gen = torch.Generator(device=dev).manual_seed(5)
+        keep = torch.rand(n, device=dev, generator=gen) < 0.05
+        cbi = torch.randint(0, K, (int((~keep).sum()),), device=dev, generator=gen)
+        cbj = torch.randn(K, d, device=dev, generator=gen)
+        ms = timed(lambda: ops2.join_features(x, keep, cbj, cbi))
+        jbytes = n * (1 + 8) + int((~keep).sum()) * 8 + (K + int(keep.sum())) * d * 4 * 2
+        extras["join_features"] = {"rows": n, "kept_frac": 0.05, "ms": ms, "gbs": jbytes / ms * 1e-6,
+                                   "frac_of_hbm_peak": jbytes / ms * 1e-6 / pk["hbm_gbs"],
+                                   "note": "two kernels + one host sync for the kept count (output size is data dependent)"}
+        nr = n // 4
+        a6 = torch.randn(nr, 3, 3, device=dev, generator=gen)
+        a6 = a6 @ a6.transpose(-1, -2)
+        cov6 = torch.stack([a6[:, 0, 0], a6[:, 0, 1], a6[:, 0, 2], a6[:, 1, 1], a6[:, 1, 2], a6[:, 2, 2]], -1).contiguous()
+        ms = timed(lambda: ops2.extract_rot_scale(cov6))
+        rbytes = nr * (24 + 28)
+        ms_torch, n_torch = None, 0
+        for n_torch in (100_000, 32_768, 4_096):             # cuSOLVER's batched syev rejects large batches on some builds
+            sub = a6[:n_torch].contiguous()
+            try:
+                ms_torch = timed(lambda: torch.linalg.eigh(sub, UPLO="U"), reps=1)
+                break
+            except RuntimeError:
+                continue
+        extras["extract_rot_scale"] = {"rows": nr, "ms": ms, "gbs": rbytes / ms * 1e-6,
+                                       "frac_of_hbm_peak": rbytes / ms * 1e-6 / pk["hbm_gbs"],
+                                       "torch_eigh_ms": ms_torch, "torch_eigh_rows": n_torch,
+                                       "note": "torch.linalg.eigh (the reference's call, cuSOLVER batched) timed on "
+                                               "a slice for scale; it is not on the product path"}
+        del keep, cbi, cbj, a6, cov6, sub
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu = cpu_baseline_leg(d)

@@ -392,6 +392,62 @@ def test_join_features_large_and_errors(L, oracle):
         L.join_features(feats, keep.to(torch.uint8), cb, cb_idx)
 
 
+# ---------------------------------------------------------------- extract_rot_scale --
+def test_extract_rot_scale_vs_reference_golden(L, oracle):
+    """c3vq_extract_rot_scale on the fixture the reference's extract_rot_scale(to_full_cov(.)) produced
+    (utils/splats.py:7-36): squared scalings and R diag(s^2) R^T within float32 rounding of the float64 oracle
+    (tolerance 4e-6 of the row's largest entry; the reference itself sits at ~1e-6), unit quaternions, ascending
+    order, and eigenvectors equal to the reference's up to sign where the eigenvalues are separated."""
+    from test_oracle_golden import ROT_SCALE_TOL, rot_scale_errors
+    import c3dgs_b200
+    g = np.load(golden_path("rot_scale").replace("vq_rot_scale", "rot_scale"))
+    cov6 = g["cov6"]
+    rot, scale = c3dgs_b200.extract_rot_scale(_t(cov6))                              # [n,6] form
+    rot_f, scale_f = c3dgs_b200.extract_rot_scale(c3dgs_b200.to_full_cov(_t(cov6)))  # the reference's [n,3,3] form
+    assert torch.equal(rot, rot_f) and torch.equal(scale, scale_f)
+    assert np.array_equal(c3dgs_b200.to_full_cov(_t(cov6)).cpu().numpy(), oracle.to_full_cov(cov6))
+    rot, scale = rot.cpu().numpy(), scale.cpu().numpy()
+    assert rot.shape == g["rot"].shape and scale.shape == g["scale"].shape
+    e_s, e_c, e_q = rot_scale_errors(oracle, cov6, rot, scale)
+    assert e_s < ROT_SCALE_TOL and e_c < ROT_SCALE_TOL and e_q < 1e-6, (e_s, e_c, e_q)
+    assert np.all(np.diff(scale, axis=1) >= 0) and np.all(np.isfinite(rot)) and np.all(np.isfinite(scale))
+    assert np.array_equal(scale[5], np.full(3, 1e-6, np.float32))                    # negative definite: NaN -> 1e-6
+    lam = g["scale"].astype(np.float64) ** 2
+    sep = (np.diff(lam, axis=1).min(1) > 0.05 * lam[:, 2]) & (lam[:, 0] > 0)
+    dots = np.abs(np.einsum("nij,nij->nj", oracle.quaternion_to_matrix(g["rot"][sep]),
+                            oracle.quaternion_to_matrix(rot[sep])))
+    assert dots.min() > 1 - 1e-4
+
+
+def test_extract_rot_scale_large_and_errors(L, oracle):
+    """1.5 M rows (25 % of 6 M, the joined covariance table of SURVEY §8f): round trip through build_covariance
+    (utils/splats.py:39-42) in float64 on a sample, plus empty input and shape errors."""
+    n = 1_500_000
+    gen = torch.Generator(device=DEV).manual_seed(9)
+    q = torch.nn.functional.normalize(torch.randn(n, 4, device=DEV, generator=gen))
+    s = torch.exp(torch.randn(n, 3, device=DEV, generator=gen) - 2.0)
+    r, x, y, z = q.unbind(-1)
+    R = torch.stack([1 - 2 * (y * y + z * z), 2 * (x * y - r * z), 2 * (x * z + r * y),
+                     2 * (x * y + r * z), 1 - 2 * (x * x + z * z), 2 * (y * z - r * x),
+                     2 * (x * z - r * y), 2 * (y * z + r * x), 1 - 2 * (x * x + y * y)], -1).reshape(n, 3, 3)
+    cov = R @ torch.diag_embed(s * s) @ R.transpose(-1, -2)
+    cov = cov / cov.diagonal(dim1=-1, dim2=-2).sum(-1)[:, None, None]                # trace-normalised
+    cov6 = torch.stack([cov[:, 0, 0], cov[:, 0, 1], cov[:, 0, 2], cov[:, 1, 1], cov[:, 1, 2], cov[:, 2, 2]], -1)
+    rot, scale = L.extract_rot_scale(cov6.contiguous())
+    from test_oracle_golden import ROT_SCALE_TOL, rot_scale_errors
+    sel = torch.arange(0, n, 37, device=DEV)
+    e_s, e_c, e_q = rot_scale_errors(oracle, cov6[sel].cpu().numpy(), rot[sel].cpu().numpy(), scale[sel].cpu().numpy())
+    assert e_s < ROT_SCALE_TOL and e_c < ROT_SCALE_TOL and e_q < 1e-6, (e_s, e_c, e_q)
+    assert bool((scale[:, 1:] >= scale[:, :-1]).all()) and bool(torch.isfinite(rot).all())
+    assert torch.allclose((scale.double() ** 2).sum(1), torch.ones(n, device=DEV, dtype=torch.double) + 3e-8, atol=1e-5)
+    r0, s0 = L.extract_rot_scale(torch.empty(0, 6, device=DEV))
+    assert r0.shape == (0, 4) and s0.shape == (0, 3)
+    with pytest.raises(RuntimeError):
+        L.extract_rot_scale(torch.zeros(4, 5, device=DEV))
+    with pytest.raises(RuntimeError):
+        L.extract_rot_scale(torch.zeros(4, 6, device=DEV, dtype=torch.float64))
+
+
 # ---------------------------------------------------------------- full size ------------------
 @pytest.mark.parametrize("d", [45, 7])
 def test_full_size_properties(L, d):

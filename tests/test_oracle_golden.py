@@ -163,3 +163,43 @@ def test_oracle_join_features_reproduces_reference(oracle):
         assert np.array_equal(idx, g[f"{name}_idx"]), name
         assert comp.shape == g[f"{name}_out"].shape and np.array_equal(comp.view(np.uint32),
                                                                        g[f"{name}_out"].view(np.uint32)), name
+
+
+def rot_scale_errors(oracle, cov6, rot, scale):
+    """Sign-invariant comparison of an extract_rot_scale result with the float64 oracle: (max |s^2 - eigenvalue|,
+    max |R diag(s^2) R^T - (A + 1e-8 I)| over the positive semi-definite rows, max | |q| - 1 |), the first two
+    relative to each row's largest entry."""
+    a = oracle.to_full_cov(cov6).astype(np.float64) + np.eye(3) * 1e-8
+    nrm = np.abs(a).max(axis=(1, 2))
+    _, s_or = oracle.extract_rot_scale(oracle.to_full_cov(cov6))
+    e_s = (np.abs(scale.astype(np.float64) ** 2 - s_or.astype(np.float64) ** 2) / nrm[:, None]).max()
+    psd = np.linalg.eigvalsh(a)[:, 0] >= 0
+    rec = oracle.build_covariance(rot, scale)
+    e_c = (np.abs(rec - a).max(axis=(1, 2)) / nrm)[psd].max()
+    e_q = np.abs(np.linalg.norm(rot.astype(np.float64), axis=1) - 1).max()
+    return e_s, e_c, e_q
+
+
+ROT_SCALE_TOL = 4e-6    # float32 LAPACK (the reference) sits at 1.2e-6 / 0.9e-6 on the fixture
+
+
+def test_oracle_extract_rot_scale_matches_reference(oracle):
+    """oracle.extract_rot_scale (float64 LAPACK) against the reference's extract_rot_scale(to_full_cov(.))
+    (utils/splats.py:7-36, float32 LAPACK, run by oracle/make_golden.py): squared scalings and the rebuilt covariance
+    agree to float32 rounding; eigenvector signs are free, so quaternions are compared through R diag(s^2) R^T."""
+    g = np.load(golden_path("rot_scale").replace("vq_rot_scale", "rot_scale"))
+    cov6, rot, scale = g["cov6"], g["rot"], g["scale"]
+    e_s, e_c, e_q = rot_scale_errors(oracle, cov6, rot, scale)           # the reference against the oracle
+    assert e_s < ROT_SCALE_TOL and e_c < ROT_SCALE_TOL and e_q < 1e-6, (e_s, e_c, e_q)
+    q_or, s_or = oracle.extract_rot_scale(oracle.to_full_cov(cov6))
+    e_s, e_c, e_q = rot_scale_errors(oracle, cov6, q_or, s_or)           # the oracle against itself
+    assert e_s == 0 and e_c < 1e-6 and e_q < 1e-6
+    assert q_or.dtype == np.float32 and s_or.dtype == np.float32 and s_or.shape == scale.shape
+    assert np.all(np.diff(s_or[10:], axis=1) >= 0) and np.all(np.diff(scale[10:], axis=1) >= 0)   # eigh's ascending order
+    # well separated eigenvalues: eigenvectors agree up to sign, so the rotations differ by a half-turn group element
+    lam = s_or.astype(np.float64) ** 2
+    sep = (np.diff(lam, axis=1).min(1) > 0.05 * lam[:, 2]) & (lam[:, 0] > 0)
+    assert sep.sum() > 500
+    r_ref, r_or = oracle.quaternion_to_matrix(rot[sep]), oracle.quaternion_to_matrix(q_or[sep])
+    dots = np.abs(np.einsum("nij,nij->nj", r_ref, r_or))                 # |<column j of ref, column j of oracle>|
+    assert dots.min() > 1 - 1e-4
