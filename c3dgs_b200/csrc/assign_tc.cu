@@ -54,7 +54,13 @@ using namespace ptx;
 constexpr int TC_BM = 128;            // rows per UMMA tile
 constexpr int TC_PR = 2 * TC_BM;      // rows per CTA pass ("pair" of tiles)
 // codes per stage / per MMA: four accumulator slots plus the A operand of both row tiles share the 512 TMEM columns
+#ifdef C3VQ_TC_BN64   // experiment: 64 codes per MMA, three accumulator slots per row tile
+__host__ __device__ constexpr int tc_bn(int dp) { return 64; }
+__host__ __device__ constexpr int tc_spt(int dp) { return dp <= 48 ? 3 : 2; }
+#else
 __host__ __device__ constexpr int tc_bn(int dp) { return dp <= 64 ? 96 : 64; }
+__host__ __device__ constexpr int tc_spt(int dp) { return 2; }   // accumulator slots per row tile
+#endif
 __host__ __device__ constexpr int tc_lcap(int dp) { return dp <= 48 ? 6 : 4; }   // chunk-list capacity per drain thread
 constexpr int TC_QCAP = 1024;         // re-rank queue capacity per pass (groups of 4 codes)
 constexpr int TC_MAXSTAGES = 6;
@@ -205,7 +211,8 @@ struct TcSmem {
     static constexpr uint32_t W_BYTES = 2u * TC_PR * 4;                    // row weights, two passes in flight
     static constexpr uint32_t BAND_BYTES = 2u * TC_PR * 4;                 // per-row error band, two passes in flight
     // TMEM columns: NSLOT accumulator slots of BN (two per row tile), then the A operand of both row tiles
-    static constexpr int NSLOT = 4;
+    static constexpr int SPT = tc_spt(DP);
+    static constexpr int NSLOT = 2 * SPT;
     static constexpr uint32_t ACOL = NSLOT * BN;
     static_assert(ACOL + 2 * DP <= 512, "TMEM budget");
     static constexpr uint32_t LIST_BYTES = 2u * TC_DT * LCAP * 4;          // score words + payload words
@@ -265,9 +272,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
     auto B_EMPTY = [&](int s) { return bar0 + 8u * (TC_MAXSTAGES + s); };
     const uint32_t A_FULL = bar0 + 8u * (2 * TC_MAXSTAGES), A_EMPTY = A_FULL + 8u;
     auto ACC_FULL = [&](uint32_t sl) { return A_EMPTY + 8u * (1 + sl); };
-    auto ACC_EMPTY = [&](uint32_t sl) { return A_EMPTY + 8u * (5 + sl); };
-    auto Q_FULL = [&](int b) { return A_EMPTY + 8u * (9 + b); };
-    auto Q_EMPTY = [&](int b) { return A_EMPTY + 8u * (11 + b); };
+    auto ACC_EMPTY = [&](uint32_t sl) { return A_EMPTY + 8u * (1 + L::NSLOT + sl); };
+    auto Q_FULL = [&](int b) { return A_EMPTY + 8u * (1 + 2 * L::NSLOT + b); };
+    auto Q_EMPTY = [&](int b) { return A_EMPTY + 8u * (3 + 2 * L::NSLOT + b); };
 
     const int tid = threadIdx.x;
     const int warp = tid >> 5;
@@ -280,7 +287,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
         }
         mbar_init(A_FULL, 8);                      // one arrival per producer warp
         mbar_init(A_EMPTY, 2);
-        for (int sl = 0; sl < 4; sl++) {
+        for (int sl = 0; sl < L::NSLOT; sl++) {
             mbar_init(ACC_FULL(sl), 1);
             mbar_init(ACC_EMPTY(sl), 8);           // one arrival per drain warp of the tile
         }
@@ -347,20 +354,21 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             constexpr uint32_t DLO_KS = (2 * L::LBO_B) >> 4, DLO_STAGE = L::BSTAGE >> 4;
             const uint32_t dlo0 = ((smem_u32(sB) & 0x3FFFFu) >> 4) | (((L::LBO_B >> 4) & 0x3FFFu) << 16);
             const uint32_t a_col = L::ACOL + t * DP;
-            uint32_t g = 0, pi = 0, stage = 0, phase = 0, dlo = dlo0;
+            uint32_t pi = 0, stage = 0, phase = 0, dlo = dlo0;
+            uint32_t sk = 0, sph = 1;                 // slot of the tile used by this step, parity of its ACC_EMPTY wait
             PROF_DECL;
             for (int64_t pair = blockIdx.x; pair < p.npairs; pair += gridDim.x, pi++) {
                 PROF(0);
                 mbar_wait(A_FULL, pi & 1);
                 PROF(1);   // prof[8+1]: MMA wait A_FULL
                 tc_fence_after();
-                for (int s = 0; s < nsteps; s++, g++) {
+                for (int s = 0; s < nsteps; s++) {
                     PROF(0);
                     mbar_wait(B_FULL(stage), phase);
                     PROF(2);   // prof[8+2]: MMA wait B_FULL
-                    // the tile owns slots 2t and 2t+1 and alternates between them step by step
-                    const uint32_t sl = 2 * t + (g & 1);
-                    mbar_wait(ACC_EMPTY(sl), ((g >> 1) & 1) ^ 1);
+                    // the tile owns L::SPT consecutive slots and cycles through them step by step
+                    const uint32_t sl = L::SPT * t + sk;
+                    mbar_wait(ACC_EMPTY(sl), sph);
                     PROF(3);   // prof[8+3]: MMA wait ACC_EMPTY
                     tc_fence_after();
                     if (elect_one()) {
@@ -375,6 +383,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                     __syncwarp();
                     PROF(4);   // prof[8+4]: MMA issue of one job (KSTEPS instructions + commits)
                     dlo += DLO_STAGE;
+                    if (++sk == (uint32_t)L::SPT) {
+                        sk = 0;
+                        sph ^= 1u;
+                    }
                     if (++stage == (uint32_t)S) {
                         stage = 0;
                         phase ^= 1;
@@ -649,15 +661,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
         const int h = dw >> 3;                          // column half of every slot served by this warp
         const int lr = t * TC_BM + q * 32 + lane;       // local row 0..255 (shared with the other half's thread)
         const int dl = dw * 32 + lane;                  // drain thread 0..511 (list column)
-        const uint32_t tsrc0 = ((uint32_t)(q * 32) << 16) + (2 * t) * BN + h * (BN / 2);   // TMEM base is 0 (checked)
-        const uint32_t acc_full0 = ACC_FULL(2 * t);     // ACC_EMPTY of the same slot is 32 bytes further
-        constexpr uint32_t ACC_E_OFF = 32;
+        const uint32_t tsrc0 = ((uint32_t)(q * 32) << 16) + (L::SPT * t) * BN + h * (BN / 2);   // TMEM base is 0 (checked)
+        const uint32_t acc_full0 = ACC_FULL(L::SPT * t);     // ACC_EMPTY of the same slot is NSLOT barriers further
+        constexpr uint32_t ACC_E_OFF = 8u * L::NSLOT;
         uint32_t *listS = sListS + dl, *listP = sListP + dl;
         const uint32_t lS = smem_u32(listS);            // the payload plane is LIST_PLANE bytes further
         constexpr uint32_t LIST_STRIDE = TC_DT * 4, LIST_END = L::LCAP * LIST_STRIDE, LIST_PLANE = LIST_END;
-        uint32_t g0 = 0, pi = 0;                        // g0: global step counter at the start of the pass
+        uint32_t pi = 0;
+        uint32_t par = 0, wph = 0;                      // slot of the tile read by this step, its phase parity
         PROF_DECL;
-        for (int64_t pair = blockIdx.x; pair < p.npairs; pair += gridDim.x, pi++, g0 += nsteps) {
+        for (int64_t pair = blockIdx.x; pair < p.npairs; pair += gridDim.x, pi++) {
             PROF(0);
             mbar_wait(A_FULL, pi & 1);
             PROF(1);       // prof[24+1]: drain wait A_FULL
@@ -690,9 +703,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                     if (flag) {
                         m = fminf(m, cm);
                         thr = m + p.gamma2 * fabsf(m) + band;
-                        uint32_t gm = 0;
+                        // group mask without the ALU pipe's compare + select: the sign bit of thr - gv[i] (FADD) is
+                        // shifted in by one funnel shift per group; group i ends up at bit NGH-1-i, set = candidate
+                        uint32_t ng = 0;
 #pragma unroll
-                        for (int i = 0; i < NGH; i++) gm |= (gv[i] <= thr) ? (1u << i) : 0u;
+                        for (int i = 0; i < NGH; i++) ng = __funnelshift_l(__float_as_uint(thr - gv[i]), ng, 1);
+                        const uint32_t gm = ~ng & ((1u << NGH) - 1u);
                         if (cnt_off == LIST_END) {      // full: drop entries the tighter threshold excludes
                             uint32_t wpos = 0;
                             for (uint32_t e = 0; e < LIST_END; e += LIST_STRIDE) {
@@ -723,8 +739,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                         p.dbg_scores[(pair * TC_PR + lr) * p.k + code0 + jj] = __uint_as_float(a[jj]);
             };
 
-            uint32_t par = g0 & 1u, wph = (g0 >> 1) & 1u;         // slot 2t + par of step g0 + s, its phase parity
-            for (int s = 0; s < nsteps; s++, wph ^= par, par ^= 1u) {
+            for (int s = 0; s < nsteps; s++) {
                 const uint32_t acc_full = acc_full0 + 8u * par, tsrc = tsrc0 + par * BN;
                 PROF(4);   // prof[24+4]: drain (LDTM + min + lists)
                 mbar_wait_hint(acc_full, wph);
@@ -735,6 +750,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(acc_full + ACC_E_OFF);
+                if (++par == (uint32_t)L::SPT) {
+                    par = 0;
+                    wph ^= 1u;
+                }
                 continue;
 #endif
                 uint32_t va[16], vb[16];
@@ -761,6 +780,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                     groups(vb, gv + 4);
                 }
                 process(gv, (uint32_t)(2 * s + h));
+                if (++par == (uint32_t)L::SPT) {
+                    par = 0;
+                    wph ^= 1u;
+                }
             }
             const int cnt = (int)(cnt_off / LIST_STRIDE);
             PROF(4);
@@ -788,10 +811,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                     while (gm) {
                         const int bit = __ffs(gm) - 1;
                         gm &= gm - 1;
-                        if ((int)(grp0 + bit) * 4 < p.k) {
+                        if ((int)(grp0 + (NGH - 1 - bit)) * 4 < p.k) {
                             const uint32_t pos = atomicAdd(&sQCount[qb], 1u);
                             if (pos < (uint32_t)TC_QCAP)
-                                queue[pos] = ((uint32_t)lr << 16) | (grp0 + bit);
+                                queue[pos] = ((uint32_t)lr << 16) | (grp0 + (NGH - 1 - bit));
                             else
                                 status = ROW_FALLBACK;
                         }
