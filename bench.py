@@ -337,12 +337,11 @@ def main():
     xd, wd = torch.empty_like(x), torch.empty_like(wn)
 
     def e2e_job():
-        xd.copy_(xh, non_blocking=True)
-        wd.copy_(wh, non_blocking=True)
         vq.codebook.copy_(cb0)
         vq.entry_importance.zero_()
-        idx = None
-        for it in range(ITERS):
+        # iteration 1 straight from the pinned host rows: chunked upload, each chunk assigned as it lands
+        idx = vq.update_from_host(xh, wh, xd, wd)
+        for it in range(1, ITERS):
             vq._acc.zero_()
             _, idx = ops.assign_accumulate(xd, wd, vq.codebook, vq._acc)
             vq._all_reduce(vq._acc)

@@ -135,8 +135,9 @@ _workspace = Workspace()
 
 
 def assign(x: torch.Tensor, codebook: torch.Tensor, rows: torch.Tensor | None = None, exact: bool = False,
-           return_dist: bool = True):
-    """Nearest codeword per row -> (min_dist f32[n] | None, idx i64[n]).  c3vq_assign / c3vq_assign_exact."""
+           return_dist: bool = True, out_idx: torch.Tensor | None = None):
+    """Nearest codeword per row -> (min_dist f32[n] | None, idx i64[n]).  c3vq_assign / c3vq_assign_exact.
+    `out_idx`: optional contiguous int64 [n] destination (e.g. a slice of a larger index array)."""
     _check(x, torch.float32, "coefs")
     _check(codebook, torch.float32, "codebook")
     if x.dim() != 2 or codebook.dim() != 2:
@@ -155,7 +156,13 @@ def assign(x: torch.Tensor, codebook: torch.Tensor, rows: torch.Tensor | None = 
     L = load()
     with torch.cuda.device(x.device):
         dist = torch.empty(n, dtype=torch.float32, device=x.device) if return_dist else None
-        idx = torch.empty(n, dtype=torch.int64, device=x.device)
+        if out_idx is not None:
+            _check(out_idx, torch.int64, "out_idx", 1)
+            if out_idx.numel() != n or not out_idx.is_contiguous() or out_idx.device != x.device:
+                raise RuntimeError("out_idx must be a contiguous int64 tensor with one entry per row on x's device")
+            idx = out_idx
+        else:
+            idx = torch.empty(n, dtype=torch.int64, device=x.device)
         if exact:
             rc = L.c3vq_assign_exact(_ptr(x), _ptr(rows), n, d, _ptr(codebook), k, _ptr(dist), _ptr(idx),
                                      _stream(x))

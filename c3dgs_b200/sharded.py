@@ -46,8 +46,11 @@ class CudaOps:
     def ema(self, codebook, entry_importance, acc, decay, eps, scale_normalize):
         _lib.ema(codebook, entry_importance, acc, decay, eps, scale_normalize)
 
-    def assign(self, x, codebook):
-        return _lib.assign(x, codebook, exact=not self.tensor_cores, return_dist=False)[1]
+    def assign(self, x, codebook, out_idx=None):
+        return _lib.assign(x, codebook, exact=not self.tensor_cores, return_dist=False, out_idx=out_idx)[1]
+
+    def accumulate(self, x, w, idx, acc):
+        _lib.accumulate(x, w, idx, acc.size(0), acc=acc, sorted_path=bool(self.tensor_cores))
 
 
 class ShardedVectorQuantize:
@@ -99,6 +102,38 @@ class ShardedVectorQuantize:
         self._all_reduce(self._acc)                                   # the one exchange step per iteration
         self.ops.ema(self.codebook, self.entry_importance, self._acc, self.decay, self.eps, scale_normalize)
         return dist_, idx
+
+    def update_from_host(self, x_host: torch.Tensor, importance_host: torch.Tensor, x_dev: torch.Tensor,
+                         importance_dev: torch.Tensor, chunk_rows: int = 1 << 19, scale_normalize: bool = False):
+        """The first iteration when the rows still sit in (pinned) host memory: the upload runs in chunks on a copy
+        stream and every chunk is assigned as soon as it has landed, so the assignment hides under the PCIe
+        transfer; the sums, the all-reduce and the EMA follow once all rows are resident.  Same kernels and the
+        same result as `update(x_dev, importance_dev)` after a plain copy; later iterations use `update`.
+        `importance_host` is already normalised (vq.py:59).  Returns the assignments (int64 [n])."""
+        dev = x_dev.device
+        n = x_host.shape[0]
+        main = torch.cuda.current_stream(dev)
+        if getattr(self, "_copy_stream", None) is None:
+            self._copy_stream = torch.cuda.Stream(device=dev)
+        copy = self._copy_stream
+        copy.wait_stream(main)                                   # earlier work may still read x_dev
+        idx = torch.empty(n, dtype=torch.int64, device=dev)
+        self._acc.zero_()
+        for lo in range(0, n, chunk_rows):
+            hi = min(lo + chunk_rows, n)
+            with torch.cuda.stream(copy):
+                x_dev[lo:hi].copy_(x_host[lo:hi], non_blocking=True)
+                landed = copy.record_event()
+            main.wait_event(landed)
+            self.ops.assign(x_dev[lo:hi], self.codebook, out_idx=idx[lo:hi])
+        with torch.cuda.stream(copy):
+            importance_dev.copy_(importance_host, non_blocking=True)
+            landed = copy.record_event()
+        main.wait_event(landed)
+        self.ops.accumulate(x_dev, importance_dev, idx, self._acc)
+        self._all_reduce(self._acc)
+        self.ops.ema(self.codebook, self.entry_importance, self._acc, self.decay, self.eps, scale_normalize)
+        return idx
 
     def assign(self, x_local: torch.Tensor) -> torch.Tensor:
         return self.ops.assign(x_local, self.codebook)

@@ -392,6 +392,29 @@ def test_join_features_large_and_errors(L, oracle):
         L.join_features(feats, keep.to(torch.uint8), cb, cb_idx)
 
 
+def test_update_from_host_equals_update(L):
+    """The streamed first iteration (chunked upload on a copy stream, chunk-wise assignment) gives the same
+    assignments and the same codebook as a plain copy followed by update()."""
+    from c3dgs_b200.sharded import ShardedVectorQuantize
+    n, d, k = 300_001, 45, 512
+    g = torch.Generator().manual_seed(21)
+    xh = torch.randn(n, d, generator=g).pin_memory()
+    wh = (torch.rand(n, generator=g) ** 4).pin_memory()
+    cb0 = xh[torch.randint(0, n, (k,), generator=g)].to(DEV)
+    a = ShardedVectorQuantize(d, k, 0.8, device=DEV)
+    b = ShardedVectorQuantize(d, k, 0.8, device=DEV)
+    a.codebook.copy_(cb0)
+    b.codebook.copy_(cb0)
+    _, idx_a = a.update(xh.to(DEV), wh.to(DEV))
+    xd, wd = torch.empty(n, d, device=DEV), torch.empty(n, device=DEV)
+    idx_b = b.update_from_host(xh, wh, xd, wd, chunk_rows=70_000)
+    torch.cuda.synchronize()
+    assert torch.equal(idx_a, idx_b)
+    assert torch.equal(xd.cpu(), xh) and torch.equal(wd.cpu(), wh)
+    assert torch.allclose(a.codebook, b.codebook, rtol=1e-6, atol=1e-7)
+    assert torch.allclose(a.entry_importance, b.entry_importance, rtol=1e-6, atol=1e-7)
+
+
 # ---------------------------------------------------------------- extract_rot_scale (SURVEY §8f rank 2) --
 def test_extract_rot_scale_vs_reference_golden(L, oracle):
     """c3vq_extract_rot_scale on the fixture the reference's extract_rot_scale(to_full_cov(.)) produced
