@@ -426,7 +426,16 @@ def main():
                                        "torch_eigh_ms": ms_torch, "torch_eigh_rows": n_torch,
                                        "note": "torch.linalg.eigh (the reference's call, cuSOLVER batched) timed on "
                                                "a slice for scale; it is not on the product path"}
-        del keep, cbi, cbj, a6, cov6, sub
+        xyz = torch.randn(n, 3, device=dev, generator=gen)
+        ms = timed(lambda: ops2.morton_order(xyz))
+        mbytes = n * 12 * 2 + 8 * n * (8 + 8 + 12 + 12)       # min/max + keys, then 8 radix passes of (hist read, scatter read+write)
+        ms_torch = timed(lambda: torch.sort(torch.randint(0, 2 ** 62, (n,), device=dev, generator=gen)), reps=2)
+        extras["morton_order"] = {"rows": n, "ms": ms, "gbs": mbytes / ms * 1e-6,
+                                  "frac_of_hbm_peak": mbytes / ms * 1e-6 / pk["hbm_gbs"],
+                                  "torch_sort_int64_ms": ms_torch,
+                                  "note": "keys + stable 8x8-bit LSD radix sort of (u64 key, u32 row); torch.sort (cub) "
+                                          "of n random int64 incl. their generation, timed beside it for scale"}
+        del keep, cbi, cbj, a6, cov6, sub, xyz
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

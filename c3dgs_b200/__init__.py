@@ -4,7 +4,7 @@ Public surface (mirrors the reference, compression/vq.py and submodules/weighted
     VectorQuantize, vq_features, ema_inplace, join_features      (c3dgs_b200.vq)
     weighted_distance._C.weightedDistance                        (c3dgs_b200.weighted_distance)
     indexed_decode                                               (c3dgs_b200.decode)
-    to_full_cov, extract_rot_scale                               (c3dgs_b200.splats)
+    to_full_cov, extract_rot_scale, morton_order                 (c3dgs_b200.splats)
     install()   register the drop-ins under the reference's module names
 """
 from __future__ import annotations
@@ -13,11 +13,11 @@ import sys
 
 from . import _lib  # noqa: F401
 from .decode import indexed_decode, decode_gaussians  # noqa: F401
-from .splats import extract_rot_scale, to_full_cov  # noqa: F401
+from .splats import extract_rot_scale, morton_order, to_full_cov  # noqa: F401
 from .vq import VectorQuantize, ema_inplace, join_features, vq_features  # noqa: F401
 
 __all__ = ["VectorQuantize", "vq_features", "ema_inplace", "join_features", "indexed_decode",
-           "decode_gaussians", "to_full_cov", "extract_rot_scale", "install"]
+           "decode_gaussians", "to_full_cov", "extract_rot_scale", "morton_order", "install"]
 
 
 def install(patch_vq_module: bool = True) -> None:

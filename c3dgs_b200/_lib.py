@@ -68,6 +68,8 @@ SIGNATURES = {
     "c3vq_join_count": (_c_int, [_c_vp, _c_i64, ctypes.POINTER(_c_i64), _c_vp, _c_sz, _c_vp]),
     "c3vq_join_write": (_c_int, [_c_vp, _c_vp, _c_i64, _c_int, _c_vp, _c_i64, _c_vp, _c_vp, _c_vp, _c_vp, _c_vp]),
     "c3vq_extract_rot_scale": (_c_int, [_c_vp, _c_i64, _c_int, _c_vp, _c_vp, _c_vp]),
+    "c3vq_morton_workspace_bytes": (_c_sz, [_c_i64]),
+    "c3vq_morton_order": (_c_int, [_c_vp, _c_i64, _c_vp, _c_vp, _c_vp, _c_sz, _c_vp]),
     "c3vq_gather_rows": (_c_int, [_c_vp, _c_vp, _c_vp, _c_i64, _c_int, _c_vp, _c_vp, _c_vp]),
     "c3vq_debug_scores": (_c_int, [_c_vp, _c_i64, _c_int, _c_vp, _c_int, _c_vp, _c_vp, _c_vp, _c_vp, _c_sz, _c_vp]),
     "c3vq_assign_stats": (_c_int, [_c_vp, ctypes.POINTER(_c_i64), _c_vp]),
@@ -375,6 +377,26 @@ def extract_rot_scale(cov: torch.Tensor):
     if rc:
         raise _err(rc)
     return rot, scale
+
+
+def morton_order(xyz: torch.Tensor, return_keys: bool = False):
+    """scene/gaussian_model.py:997-1004: permutation that sorts the rows of xyz [n,3] by their 63-bit Morton key
+    (stable).  Returns int64 [n] (and the sorted int64 keys).  c3vq_morton_order."""
+    _check(xyz, torch.float32, "xyz", 2)
+    if xyz.size(1) != 3:
+        raise RuntimeError(f"xyz must be [n,3], got {tuple(xyz.shape)}")
+    xyz = xyz.contiguous()
+    n = xyz.size(0)
+    L = load()
+    with torch.cuda.device(xyz.device):
+        order = torch.empty(n, dtype=torch.int64, device=xyz.device)
+        keys = torch.empty(n, dtype=torch.int64, device=xyz.device) if return_keys else None
+        nbytes = L.c3vq_morton_workspace_bytes(n)
+        ws = torch.empty(max(int(nbytes), 4), dtype=torch.uint8, device=xyz.device)
+        rc = L.c3vq_morton_order(_ptr(xyz), n, _ptr(order), _ptr(keys), _ptr(ws), ws.numel(), _stream(xyz))
+    if rc:
+        raise _err(rc)
+    return (order, keys) if return_keys else order
 
 
 def scatter_add(grad_out: torch.Tensor, idx: torch.Tensor, table_rows: int) -> torch.Tensor:

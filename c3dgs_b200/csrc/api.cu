@@ -262,6 +262,16 @@ int c3vq_extract_rot_scale(const float *cov, int64_t n, int full, float *out_rot
     return launch_rot_scale(cov, n, full, out_rot, out_scale, (cudaStream_t)stream);
 }
 
+size_t c3vq_morton_workspace_bytes(int64_t n) { return n < 0 ? 0 : morton_workspace_bytes(n); }
+
+int c3vq_morton_order(const float *xyz, int64_t n, int64_t *out_order, uint64_t *out_keys, void *ws, size_t ws_bytes,
+                      c3vq_stream_t stream)
+{
+    C3VQ_CHECK_ARG(n >= 0 && n < ((int64_t)1 << 32), "n=%lld out of range (rows are tracked in 32 bits)", (long long)n);
+    C3VQ_CHECK_ARG(n == 0 || (xyz && out_order && ws), "null pointer");
+    return launch_morton_order(xyz, n, out_order, out_keys, ws, ws_bytes, (cudaStream_t)stream);
+}
+
 int c3vq_gather_rows(const float *x, const float *w, const int64_t *rows, int64_t n, int d, float *out_x,
                      float *out_w, c3vq_stream_t stream)
 {

@@ -70,6 +70,11 @@ int launch_gather_rows(const float *x, const float *w, const int64_t *rows, int6
 // extract_rot_scale (rot_scale.cu): cov rows (6 stored entries, or 3x3 when full != 0) -> quaternion [n,4], scaling [n,3]
 int launch_rot_scale(const float *cov, int64_t n, int full, float *rot, float *scale, cudaStream_t s);
 
+// Morton order (morton.cu): xyz [n,3] -> stable permutation sorted by the 63-bit Morton key (and the sorted keys)
+size_t morton_workspace_bytes(int64_t n);
+int launch_morton_order(const float *xyz, int64_t n, int64_t *out_order, uint64_t *out_keys, void *ws, size_t ws_bytes,
+                        cudaStream_t s);
+
 // join_features (gather.cu): count + scan of the keep mask (kept total at ((unsigned*)ws)[blocks]), then the write pass
 size_t join_workspace_bytes(int64_t n);
 int launch_join_count(const uint8_t *keep, int64_t n, void *ws, size_t ws_bytes, cudaStream_t s);

@@ -1,0 +1,310 @@
+// morton.cu — Morton (Z-order) permutation of the Gaussians, the reordering the reference applies before it writes
+// the compressed scene (GaussianModel._sort_morton, scene/gaussian_model.py:997-1004, with mortonEncode / splitBy3 at
+// :1415-1432; called from save_npz, :511).
+//
+//   pp_min = xyz.min(0); pp_diap = xyz.max(0) - pp_min
+//   q      = ((2^21 - 1) * (xyz - pp_min) / pp_diap).long()                    float32 arithmetic, truncation
+//   key    = splitBy3(q[a0]) | splitBy3(q[a1]) << 1 | splitBy3(q[a2]) << 2     a = argsort(pp_diap)
+//   order  = key.sort().indices
+//
+// Integer work after three IEEE float32 operations per coordinate, so keys are bit-exact.  The sort is a stable LSD
+// radix sort, 8 passes of 8 bits over (key u64, row u32) pairs: equal keys keep their row order (torch's sort makes no
+// promise for ties; its CUDA and CPU implementations both happen to be stable).
+//
+// Per pass: k_radix_hist (per-tile digit counts, digit-major table), k_radix_scan (one CTA per digit scans its row of
+// the table), k_radix_scatter (stable ranking: every warp owns a contiguous slice of the tile and walks it 32 keys at a
+// time with match.any, so ranks follow the input order without any atomics).  HBM-bound: 40 bytes per key and pass.
+#include "common.cuh"
+
+namespace c3vq {
+
+namespace {
+
+constexpr int RS_THREADS = 512;                       // 16 warps
+constexpr int RS_WARPS = RS_THREADS / 32;
+constexpr int RS_ROUNDS = 8;                          // 32-key rounds per warp
+constexpr int RS_TILE = RS_THREADS * RS_ROUNDS;       // 4096 keys per CTA
+
+// order-preserving float <-> unsigned maps for atomicMin / atomicMax
+__device__ __forceinline__ unsigned int f2ord(float f)
+{
+    const unsigned int u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float ord2f(unsigned int o)
+{
+    return __uint_as_float((o & 0x80000000u) ? (o & 0x7fffffffu) : ~o);
+}
+
+// mm[0..2] = ordered min per axis (init 0xffffffff), mm[3..5] = ordered max per axis (init 0)
+__global__ void __launch_bounds__(256) k_xyz_minmax(const float *__restrict__ xyz, int64_t n, unsigned int *__restrict__ mm)
+{
+    unsigned int lo[3] = {0xffffffffu, 0xffffffffu, 0xffffffffu}, hi[3] = {0u, 0u, 0u};
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+#pragma unroll
+        for (int a = 0; a < 3; a++) {
+            const unsigned int o = f2ord(xyz[i * 3 + a]);
+            lo[a] = min(lo[a], o);
+            hi[a] = max(hi[a], o);
+        }
+    }
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+        lo[a] = __reduce_min_sync(0xffffffffu, lo[a]);
+        hi[a] = __reduce_max_sync(0xffffffffu, hi[a]);
+    }
+    if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+        for (int a = 0; a < 3; a++) {
+            atomicMin(&mm[a], lo[a]);
+            atomicMax(&mm[3 + a], hi[a]);
+        }
+    }
+}
+
+// scene/gaussian_model.py:1415-1423
+__device__ __forceinline__ unsigned long long split_by_3(unsigned long long a)
+{
+    unsigned long long x = a & 0x1FFFFFull;
+    x = (x | x << 32) & 0x1F00000000FFFFull;
+    x = (x | x << 16) & 0x1F0000FF0000FFull;
+    x = (x | x << 8) & 0x100F00F00F00F00Full;
+    x = (x | x << 4) & 0x10C30C30C30C30C3ull;
+    x = (x | x << 2) & 0x1249249249249249ull;
+    return x;
+}
+
+__global__ void __launch_bounds__(256) k_morton_keys(const float *__restrict__ xyz, int64_t n,
+                                                     const unsigned int *__restrict__ mm,
+                                                     unsigned long long *__restrict__ keys)
+{
+    float mn[3], dp[3];
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+        mn[a] = ord2f(mm[a]);
+        dp[a] = __fsub_rn(ord2f(mm[3 + a]), mn[a]);                      // :999-1000
+    }
+    // stable ascending argsort of the three extents (:1003): rank of axis a = number of axes that sort before it
+    int rk[3];
+#pragma unroll
+    for (int a = 0; a < 3; a++) {
+        rk[a] = 0;
+#pragma unroll
+        for (int b = 0; b < 3; b++) rk[a] += (dp[b] < dp[a] || (dp[b] == dp[a] && b < a)) ? 1 : 0;
+    }
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        unsigned long long key = 0;
+#pragma unroll
+        for (int a = 0; a < 3; a++) {
+            // :1001, float32 multiply then divide, truncation toward zero; NaN (zero extent) becomes 0 bits
+            const float f = __fdiv_rn(__fmul_rn(2097151.f, __fsub_rn(xyz[i * 3 + a], mn[a])), dp[a]);
+            const long long q = (f == f) ? (long long)f : 0ll;
+            key |= split_by_3((unsigned long long)q) << rk[a];           // axis with the smallest extent -> bit 0
+        }
+        keys[i] = key;
+    }
+}
+
+// table[d * nb + tile] = number of keys of the tile whose digit is d
+__global__ void __launch_bounds__(RS_THREADS) k_radix_hist(const unsigned long long *__restrict__ keys, int64_t n, int shift,
+                                                           unsigned int *__restrict__ table, int nb)
+{
+    __shared__ unsigned int cnt[256];
+    if (threadIdx.x < 256) cnt[threadIdx.x] = 0;
+    __syncthreads();
+    const int64_t base = (int64_t)blockIdx.x * RS_TILE;
+#pragma unroll 4
+    for (int r = 0; r < RS_ROUNDS; r++) {
+        const int64_t i = base + (int64_t)r * RS_THREADS + threadIdx.x;
+        if (i < n) atomicAdd(&cnt[(unsigned int)(keys[i] >> shift) & 255u], 1u);
+    }
+    __syncthreads();
+    if (threadIdx.x < 256) table[(size_t)threadIdx.x * nb + blockIdx.x] = cnt[threadIdx.x];
+}
+
+// CTA d: exclusive scan of table[d * nb .. d * nb + nb) in place, total[d] = sum
+__global__ void __launch_bounds__(1024) k_radix_scan(unsigned int *__restrict__ table, int nb, unsigned int *__restrict__ total)
+{
+    __shared__ unsigned int part[1024];
+    unsigned int *row = table + (size_t)blockIdx.x * nb;
+    const int per = (nb + 1023) / 1024;
+    const int j0 = threadIdx.x * per, j1 = min(nb, j0 + per);
+    unsigned int sum = 0;
+    for (int j = j0; j < j1; j++) sum += row[j];
+    part[threadIdx.x] = sum;
+    __syncthreads();
+    for (int o = 1; o < 1024; o <<= 1) {
+        const unsigned int v = threadIdx.x >= o ? part[threadIdx.x - o] : 0u;
+        __syncthreads();
+        part[threadIdx.x] += v;
+        __syncthreads();
+    }
+    unsigned int run = part[threadIdx.x] - sum;
+    for (int j = j0; j < j1; j++) {
+        const unsigned int c = row[j];
+        row[j] = run;
+        run += c;
+    }
+    if (threadIdx.x == 1023) total[blockIdx.x] = part[1023];
+}
+
+// FIRST: the row payload is the position itself (pass 0); LAST: write int64 rows (and optionally the sorted keys)
+template <bool FIRST, bool LAST>
+__global__ void __launch_bounds__(RS_THREADS)
+k_radix_scatter(const unsigned long long *__restrict__ keys_in, const unsigned int *__restrict__ rows_in, int64_t n,
+                int shift, const unsigned int *__restrict__ table, int nb, const unsigned int *__restrict__ total,
+                unsigned long long *__restrict__ keys_out, unsigned int *__restrict__ rows_out,
+                int64_t *__restrict__ order_out)
+{
+    __shared__ unsigned int wcnt[RS_WARPS][256];       // per-warp digit counts, then per-warp running offsets
+    __shared__ unsigned int dbase[256];                // global position of the tile's first key of each digit
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const unsigned int lt = (1u << lane) - 1u;
+    for (int j = threadIdx.x; j < RS_WARPS * 256; j += RS_THREADS) (&wcnt[0][0])[j] = 0;
+    __syncthreads();
+    // warp w owns keys [base + w * 32 * RS_ROUNDS, + 32 * RS_ROUNDS) of the tile, 32 consecutive keys per round
+    const int64_t wbase = (int64_t)blockIdx.x * RS_TILE + (int64_t)warp * (32 * RS_ROUNDS);
+    unsigned long long key[RS_ROUNDS];
+#pragma unroll
+    for (int r = 0; r < RS_ROUNDS; r++) {
+        const int64_t i = wbase + r * 32 + lane;
+        key[r] = i < n ? keys_in[i] : ~0ull;
+        const unsigned int dgt = (unsigned int)(key[r] >> shift) & 255u;
+        const unsigned int act = __ballot_sync(0xffffffffu, i < n);
+        if (i < n) {
+            const unsigned int peers = __match_any_sync(act, dgt);
+            if ((peers & lt) == 0) wcnt[warp][dgt] += __popc(peers);     // lowest lane of each digit; rows are warp-private
+        }
+        __syncwarp();
+    }
+    __syncthreads();
+    // digit d: exclusive scan over the warps, plus where the tile's digit-d keys start globally
+    if (threadIdx.x < 256) {
+        const int dgt = threadIdx.x;
+        unsigned int run = 0;
+        for (int w = 0; w < RS_WARPS; w++) {
+            const unsigned int c = wcnt[w][dgt];
+            wcnt[w][dgt] = run;
+            run += c;
+        }
+        dbase[dgt] = table[(size_t)dgt * nb + blockIdx.x];
+    }
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        // exclusive prefix over digits of the global totals (every CTA recomputes it), 8 digits per lane
+        unsigned int t[8], s = 0;
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            t[j] = total[lane * 8 + j];
+            s += t[j];
+        }
+        unsigned int incl = s;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned int v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        unsigned int run = incl - s;
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            dbase[lane * 8 + j] += run;
+            run += t[j];
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < RS_ROUNDS; r++) {
+        const int64_t i = wbase + r * 32 + lane;
+        const unsigned int dgt = (unsigned int)(key[r] >> shift) & 255u;
+        const unsigned int act = __ballot_sync(0xffffffffu, i < n);
+        if (i < n) {
+            const unsigned int peers = __match_any_sync(act, dgt);
+            const unsigned int off = wcnt[warp][dgt];
+            const unsigned int pos = dbase[dgt] + off + __popc(peers & lt);
+            const unsigned int row = FIRST ? (unsigned int)i : rows_in[i];
+            if (LAST) {
+                order_out[pos] = (int64_t)row;
+                if (keys_out) keys_out[pos] = key[r];
+            } else {
+                keys_out[pos] = key[r];
+                rows_out[pos] = row;
+            }
+            __syncwarp(act);
+            if ((peers & lt) == 0) wcnt[warp][dgt] = off + __popc(peers);
+        }
+        __syncwarp();
+    }
+}
+
+struct MortonLayout {
+    size_t off_mm, off_total, off_table, off_keys0, off_keys1, off_rows0, off_rows1, bytes;
+    int nb;
+};
+
+MortonLayout morton_layout(int64_t n)
+{
+    MortonLayout l;
+    l.nb = (int)((n + RS_TILE - 1) / RS_TILE);
+    if (l.nb < 1) l.nb = 1;
+    auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    size_t o = 0;
+    l.off_mm = o, o += 256;
+    l.off_total = o, o += up(256 * 4);
+    l.off_table = o, o += up((size_t)256 * l.nb * 4);
+    l.off_keys0 = o, o += up((size_t)n * 8);
+    l.off_keys1 = o, o += up((size_t)n * 8);
+    l.off_rows0 = o, o += up((size_t)n * 4);
+    l.off_rows1 = o, o += up((size_t)n * 4);
+    l.bytes = o;
+    return l;
+}
+
+}  // namespace
+
+size_t morton_workspace_bytes(int64_t n) { return morton_layout(n).bytes; }
+
+int launch_morton_order(const float *xyz, int64_t n, int64_t *out_order, uint64_t *out_keys, void *ws, size_t ws_bytes,
+                        cudaStream_t s)
+{
+    if (n == 0) return C3VQ_OK;
+    const MortonLayout l = morton_layout(n);
+    if (ws_bytes < l.bytes) {
+        set_error("workspace too small: %zu < %zu", ws_bytes, l.bytes);
+        return C3VQ_EWORKSPACE;
+    }
+    uint8_t *w = (uint8_t *)ws;
+    unsigned int *mm = (unsigned int *)(w + l.off_mm), *total = (unsigned int *)(w + l.off_total);
+    unsigned int *table = (unsigned int *)(w + l.off_table);
+    unsigned long long *keys[2] = {(unsigned long long *)(w + l.off_keys0), (unsigned long long *)(w + l.off_keys1)};
+    unsigned int *rows[2] = {(unsigned int *)(w + l.off_rows0), (unsigned int *)(w + l.off_rows1)};
+
+    const unsigned int mm_init[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
+    C3VQ_CUDA(cudaMemcpyAsync(mm, mm_init, sizeof(mm_init), cudaMemcpyHostToDevice, s));
+    int64_t gb = (n + 255) / 256;
+    if (gb > (int64_t)sm_count() * 8) gb = (int64_t)sm_count() * 8;
+    k_xyz_minmax<<<(unsigned)gb, 256, 0, s>>>(xyz, n, mm);
+    C3VQ_LAUNCH_CHECK("k_xyz_minmax");
+    k_morton_keys<<<(unsigned)gb, 256, 0, s>>>(xyz, n, mm, keys[0]);
+    C3VQ_LAUNCH_CHECK("k_morton_keys");
+    constexpr int PASSES = 8;
+    for (int p = 0; p < PASSES; p++) {
+        const int in = p & 1, out = in ^ 1, shift = 8 * p;
+        k_radix_hist<<<l.nb, RS_THREADS, 0, s>>>(keys[in], n, shift, table, l.nb);
+        C3VQ_LAUNCH_CHECK("k_radix_hist");
+        k_radix_scan<<<256, 1024, 0, s>>>(table, l.nb, total);
+        C3VQ_LAUNCH_CHECK("k_radix_scan");
+        if (p == 0)
+            k_radix_scatter<true, false><<<l.nb, RS_THREADS, 0, s>>>(keys[in], nullptr, n, shift, table, l.nb, total,
+                                                                    keys[out], rows[out], nullptr);
+        else if (p == PASSES - 1)
+            k_radix_scatter<false, true><<<l.nb, RS_THREADS, 0, s>>>(keys[in], rows[in], n, shift, table, l.nb, total,
+                                                                    (unsigned long long *)out_keys, nullptr, out_order);
+        else
+            k_radix_scatter<false, false><<<l.nb, RS_THREADS, 0, s>>>(keys[in], rows[in], n, shift, table, l.nb, total,
+                                                                     keys[out], rows[out], nullptr);
+        C3VQ_LAUNCH_CHECK("k_radix_scatter");
+    }
+    return C3VQ_OK;
+}
+
+}  // namespace c3vq

@@ -26,3 +26,10 @@ def extract_rot_scale(cov: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
     """utils/splats.py:28-36.  Eigenvalues (ascending) and R diag(s^2) R^T match the reference to float32 rounding;
     eigenvector signs (hence the quaternion among its equivalent choices) are not LAPACK's."""
     return _lib.extract_rot_scale(cov)
+
+
+def morton_order(xyz: torch.Tensor) -> torch.Tensor:
+    """The permutation GaussianModel._sort_morton computes (scene/gaussian_model.py:997-1004):
+    `mortonEncode(xyz_q, pp_diap.argsort()).sort().indices` for xyz [n,3] float32, as one key kernel and a stable
+    radix sort (c3vq_morton_order).  The caller applies it to its per-Gaussian tensors (`t[order]`)."""
+    return _lib.morton_order(xyz)

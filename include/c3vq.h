@@ -165,6 +165,18 @@ int c3vq_join_write(const float *all_features, const uint8_t *keep_mask, int64_t
 int c3vq_extract_rot_scale(const float *cov, int64_t n, int full, float *out_rot /* [n,4] */,
                            float *out_scale /* [n,3] */, c3vq_stream_t stream);
 
+/*
+ * Morton (Z-order) permutation, GaussianModel._sort_morton (scene/gaussian_model.py:997-1004; mortonEncode and
+ * splitBy3 at :1415-1432), applied by the reference before the compressed scene is written (:511):
+ * q = ((2^21 - 1) * (xyz - min) / (max - min)).long() per axis in float32, key = bit-interleave with the axis of
+ * smallest extent in bit 0, out_order = argsort(key).  Keys are bit-exact; the sort is stable (equal keys keep
+ * their row order; so are the argsort of the three extents).  out_keys (optional) receives the sorted keys.
+ * ws: c3vq_morton_workspace_bytes(n) bytes.  n < 2^32.
+ */
+size_t c3vq_morton_workspace_bytes(int64_t n);
+int c3vq_morton_order(const float *xyz /* [n,3] */, int64_t n, int64_t *out_order /* [n] */,
+                      uint64_t *out_keys /* [n] or null */, void *ws, size_t ws_bytes, c3vq_stream_t stream);
+
 /* Mini-batch row gather: out_x[i,:] = x[rows[i],:], out_w[i] = w[rows[i]] (w/out_w may be null). */
 int c3vq_gather_rows(const float *x, const float *w, const int64_t *rows, int64_t n, int d,
                      float *out_x, float *out_w, c3vq_stream_t stream);

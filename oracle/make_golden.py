@@ -177,9 +177,54 @@ def run_rot_scale_case():
     return path
 
 
+def _reference_functions(path, names):
+    """Compile the named top-level functions of a reference file in isolation (the module itself imports the
+    rasterisers and simple_knn, which are not built here); nothing is copied into this repository."""
+    import ast
+    src = open(path).read()
+    tree = ast.parse(src)
+    ns = {"torch": torch}
+    for node in tree.body:
+        if isinstance(node, ast.FunctionDef) and node.name in names:
+            exec(compile(ast.Module([node], []), path, "exec"), ns)
+    return [ns[n] for n in names]
+
+
+def run_morton_cases():
+    """GaussianModel._sort_morton's permutation (scene/gaussian_model.py:997-1004) with the reference's own
+    mortonEncode / splitBy3 (:1415-1432) executed from the checkout, on CPU tensors."""
+    (morton_encode, _) = _reference_functions(os.path.join(ref_loader.REFERENCE_ROOT, "scene", "gaussian_model.py"),
+                                              ["mortonEncode", "splitBy3"])
+    out = {}
+    g = torch.Generator().manual_seed(77)
+    cases = {
+        "normal": torch.randn(20000, 3, generator=g) * torch.tensor([3.0, 1.0, 7.0]),
+        "ties": torch.randn(500, 3, generator=g)[torch.randint(0, 500, (6000,), generator=g)],
+        "flat": torch.cat([torch.rand(3000, 2, generator=g), torch.full((3000, 1), 0.25)], 1),
+        "five": torch.tensor([[0., 0, 0], [1, 1, 1], [0.5, 0.25, 0.75], [1, 0, 0], [0.5, 0.25, 0.75]]),
+        "one": torch.tensor([[1.5, -2.0, 3.0]]),
+    }
+    for name, xyz in cases.items():
+        xyz = xyz.float().contiguous()
+        pp_min = xyz.min(0).values                                                     # :999
+        pp_diap = xyz.max(0).values - pp_min                                           # :1000
+        xyz_q = ((2 ** 21 - 1) * (xyz - pp_min) / pp_diap).long()                      # :1001
+        keys = morton_encode(xyz_q, pp_diap.argsort())                                 # :1003
+        order = keys.sort().indices
+        out.update({f"{name}_xyz": xyz.numpy(), f"{name}_keys": keys.numpy(), f"{name}_order": order.numpy()})
+    out["names"] = np.array(list(cases))
+    path = os.path.join(GOLDEN_DIR, "morton.npz")
+    np.savez_compressed(path, **out)
+    return path
+
+
 def main():
     if not ref_loader.available():
         raise SystemExit("reference checkout not present; fixtures can only be generated in the build container")
+    if "--morton-only" in sys.argv:
+        p = run_morton_cases()
+        print("wrote", p, os.path.getsize(p) // 1024, "KiB")
+        return
     if "--rot-scale-only" in sys.argv:
         p = run_rot_scale_case()
         print("wrote", p, os.path.getsize(p) // 1024, "KiB")
@@ -191,6 +236,8 @@ def main():
     p = run_join_cases()
     print("wrote", p, os.path.getsize(p) // 1024, "KiB")
     p = run_rot_scale_case()
+    print("wrote", p, os.path.getsize(p) // 1024, "KiB")
+    p = run_morton_cases()
     print("wrote", p, os.path.getsize(p) // 1024, "KiB")
 
 

@@ -265,3 +265,33 @@ def extract_rot_scale(cov):
     q = matrix_to_quaternion(R * np.linalg.det(R)[:, None, None])                                 # :35
     q = q / np.maximum(np.linalg.norm(q, axis=-1, keepdims=True), 1e-12)                          # F.normalize
     return q.astype(np.float32), scaling
+
+
+# ---- §8(f) rank 3: Morton order of the Gaussians, scene/gaussian_model.py:997-1004, :1415-1432 -----------------------
+def split_by_3(a):
+    """scene/gaussian_model.py:1415-1423 on uint64 arrays."""
+    x = np.asarray(a).astype(np.uint64) & np.uint64(0x1FFFFF)
+    for sh, mask in ((32, 0x1F00000000FFFF), (16, 0x1F0000FF0000FF), (8, 0x100F00F00F00F00F),
+                     (4, 0x10C30C30C30C30C3), (2, 0x1249249249249249)):
+        x = (x | (x << np.uint64(sh))) & np.uint64(mask)
+    return x
+
+
+def morton_keys(xyz):
+    """scene/gaussian_model.py:998-1003 + mortonEncode (:1426-1432): float32 quantisation to 21 bits per axis,
+    interleave with the axis of smallest extent in bit 0 (stable argsort of the extents).  Returns int64 keys."""
+    xyz = np.asarray(xyz, np.float32)
+    pp_min = xyz.min(0)
+    pp_diap = xyz.max(0) - pp_min
+    with np.errstate(invalid="ignore", divide="ignore"):
+        f = (np.float32(2 ** 21 - 1) * (xyz - pp_min)) / pp_diap
+    q = np.where(np.isnan(f), np.float32(0), f).astype(np.int64)       # NaN.long() & 0x1FFFFF is 0 on CPU and GPU alike
+    ordering = np.argsort(pp_diap, kind="stable")
+    key = split_by_3(q[:, ordering[0]]) | (split_by_3(q[:, ordering[1]]) << np.uint64(1)) | \
+        (split_by_3(q[:, ordering[2]]) << np.uint64(2))
+    return key.astype(np.int64)
+
+
+def morton_order(xyz):
+    """`mortonEncode(...).sort().indices` (:1003) with ties in row order (stable)."""
+    return np.argsort(morton_keys(xyz), kind="stable").astype(np.int64)

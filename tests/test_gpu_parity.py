@@ -471,6 +471,41 @@ def test_extract_rot_scale_large_and_errors(L, oracle):
         L.extract_rot_scale(torch.zeros(4, 6, device=DEV, dtype=torch.float64))
 
 
+# ---------------------------------------------------------------- Morton order ------
+def test_morton_order_bit_exact_vs_reference_golden(L, oracle):
+    """c3vq_morton_order on the fixture made with the reference's own mortonEncode (scene/gaussian_model.py:997-1004,
+    :1415-1432): keys bit-exact, permutation identical to the stable argsort (= the reference's wherever its keys
+    are unique)."""
+    g = np.load(golden_path("morton").replace("vq_morton", "morton"))
+    for name in g["names"]:
+        xyz, keys, order = g[f"{name}_xyz"], g[f"{name}_keys"], g[f"{name}_order"]
+        o, ks = L.morton_order(_t(xyz), return_keys=True)
+        o, ks = o.cpu().numpy(), ks.cpu().numpy()
+        assert o.dtype == np.int64 and np.array_equal(ks, keys[order]), name            # the sorted key sequence
+        assert np.array_equal(o, np.argsort(keys, kind="stable")), name                  # stable permutation
+        if len(np.unique(keys)) == len(keys):
+            assert np.array_equal(o, order), name
+
+
+def test_morton_order_large_and_errors(L, oracle):
+    """6 M points (config 5's Gaussian count): against the numpy oracle on the full array (keys and permutation),
+    plus empty input and shape errors."""
+    n = 6_000_000
+    gen = torch.Generator(device=DEV).manual_seed(31)
+    xyz = torch.randn(n, 3, device=DEV, generator=gen) * torch.tensor([4.0, 9.0, 1.5], device=DEV)
+    xyz[1000:2000] = xyz[:1000]                                   # exact duplicates: ties must keep row order
+    o, ks = L.morton_order(xyz, return_keys=True)
+    k_or = oracle.morton_keys(xyz.cpu().numpy())
+    o_or = np.argsort(k_or, kind="stable")
+    assert np.array_equal(ks.cpu().numpy(), k_or[o_or])
+    assert np.array_equal(o.cpu().numpy(), o_or)
+    assert L.morton_order(torch.empty(0, 3, device=DEV)).shape == (0,)
+    with pytest.raises(RuntimeError):
+        L.morton_order(torch.zeros(4, 2, device=DEV))
+    with pytest.raises(RuntimeError):
+        L.morton_order(torch.zeros(4, 3, device=DEV, dtype=torch.float64))
+
+
 # ---------------------------------------------------------------- full size ------------------
 @pytest.mark.parametrize("d", [45, 7])
 def test_full_size_properties(L, d):

@@ -203,3 +203,19 @@ def test_oracle_extract_rot_scale_matches_reference(oracle):
     r_ref, r_or = oracle.quaternion_to_matrix(rot[sep]), oracle.quaternion_to_matrix(q_or[sep])
     dots = np.abs(np.einsum("nij,nij->nj", r_ref, r_or))                 # |<column j of ref, column j of oracle>|
     assert dots.min() > 1 - 1e-4
+
+
+def test_oracle_morton_order_reproduces_reference(oracle):
+    """oracle.morton_keys / morton_order against the reference's mortonEncode + sort (scene/gaussian_model.py:997-1004,
+    :1415-1432; run by oracle/make_golden.py): keys bit-exact; the order identical where keys are unique, and the same
+    sorted key sequence where the reference's unstable sort broke ties differently."""
+    g = np.load(golden_path("morton").replace("vq_morton", "morton"))
+    for name in g["names"]:
+        xyz, keys, order = g[f"{name}_xyz"], g[f"{name}_keys"], g[f"{name}_order"]
+        k = oracle.morton_keys(xyz)
+        o = oracle.morton_order(xyz)
+        assert k.dtype == np.int64 and np.array_equal(k, keys), name
+        assert np.array_equal(k[o], keys[order]), name
+        assert np.array_equal(np.sort(o), np.arange(len(xyz))), name
+        if len(np.unique(keys)) == len(keys):
+            assert np.array_equal(o, order), name
