@@ -129,7 +129,7 @@ def workload_config(n, d, world, assignment, sums):
 
 
 # (rows, dim, simt) -> DRAM bytes of one launch of the dominant kernel, measured with ncu (see profiles/)
-NCU_DRAM_BYTES_PER_LAUNCH = {(5_800_000, 45, False): 1_093_849_600}
+NCU_DRAM_BYTES_PER_LAUNCH = {(5_800_000, 45, False): 1_092_362_240}
 
 SAMPLE_ROWS = 100_000     # CPU legs: a bounded sample of the workload's rows (the metric is per row and iteration)
 
@@ -316,7 +316,7 @@ def main():
     tf32_peak = pk["bf16_tflops_sustained"] / 2.0         # dense TF32 = half the bf16 rate; kernel timed inside a long step
     achieved = flops / (kern_ms * 1e-3) / 1e12
     # dram__bytes_read.sum + dram__bytes_write.sum of ONE k_assign_tc launch from the committed `ncu --set full`
-    # capture (profiles/r1m_ncu_assign_tc_summary.txt); only valid for the configuration that capture ran
+    # capture (profiles/r1n_ncu_assign_tc_summary.txt); only valid for the configuration that capture ran
     traffic = NCU_DRAM_BYTES_PER_LAUNCH.get((n, d, bool(args.simt)))
     roofline = {"bound": "tensor", "achieved": achieved, "peak": tf32_peak, "unit": "TFLOP/s",
                 "frac": achieved / tf32_peak, "traffic": traffic,
