@@ -800,24 +800,57 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             sXchg[(qb * 2 + h) * TC_PR + lr] = m;             // double buffered: one barrier per pass is enough
             named_bar_sync(3 + (dw & 7), 64);                 // only the two warps that share these 32 rows meet
             m = fminf(m, sXchg[(qb * 2 + (h ^ 1)) * TC_PR + lr]);
-            if (status == ROW_OK) {
-                thr = m + p.gamma2 * fabsf(m) + band;
-                uint32_t *queue = sQueue + qb * TC_QCAP;
-                for (int e = 0; e < cnt; e++) {
-                    if (!(__uint_as_float(listS[e * TC_DT]) <= thr)) continue;
-                    const uint32_t ep = listP[e * TC_DT];
-                    uint32_t gm = ep & 0xFFFu;
-                    const uint32_t grp0 = (ep >> 12) * NGH;      // first group (code / 4) of the half job
+            // Surviving groups of the row's list, filtered with the final threshold.  Queue slots are allocated per
+            // WARP (prefix sum over the lanes, one shared-memory atomic), not per entry: a thousand same-address
+            // atomics per pass serialise in the shared-memory atomic unit.
+            thr = m + p.gamma2 * fabsf(m) + band;
+            uint32_t mk[L::LCAP], gb[L::LCAP], c = 0;
+#pragma unroll
+            for (int e = 0; e < L::LCAP; e++) {
+                mk[e] = 0;
+                gb[e] = 0;
+                if (status == ROW_OK && e < cnt) {
+                    const uint32_t es = ld_shared_u32(lS + e * LIST_STRIDE);
+                    if (__uint_as_float(es) <= thr) {
+                        const uint32_t ep = ld_shared_u32(lS + LIST_PLANE + e * LIST_STRIDE);
+                        uint32_t gm = ep & 0xFFFu;
+                        const uint32_t grp0 = (ep >> 12) * NGH;      // first group (code / 4) of the half job
+                        if ((int)(grp0 + NGH) * 4 > p.k) {           // the chunk that holds the end of the codebook
+                            uint32_t keep = 0;
+                            for (int bit = 0; bit < NGH; bit++)
+                                if ((int)(grp0 + (NGH - 1 - bit)) * 4 < p.k) keep |= 1u << bit;
+                            gm &= keep;
+                        }
+                        mk[e] = gm;
+                        gb[e] = grp0;
+                        c += __popc(gm);
+                    }
+                }
+            }
+            uint32_t incl = c;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += v;
+            }
+            const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+            if (total) {
+                uint32_t base = 0;
+                if (lane == 0) base = atomicAdd(&sQCount[qb], total);
+                base = __shfl_sync(0xffffffffu, base, 0);
+                uint32_t pos = base + incl - c;
+                const uint32_t qaddr = smem_u32(sQueue + qb * TC_QCAP);
+#pragma unroll
+                for (int e = 0; e < L::LCAP; e++) {
+                    uint32_t gm = mk[e];
                     while (gm) {
                         const int bit = __ffs(gm) - 1;
                         gm &= gm - 1;
-                        if ((int)(grp0 + (NGH - 1 - bit)) * 4 < p.k) {
-                            const uint32_t pos = atomicAdd(&sQCount[qb], 1u);
-                            if (pos < (uint32_t)TC_QCAP)
-                                queue[pos] = ((uint32_t)lr << 16) | (grp0 + (NGH - 1 - bit));
-                            else
-                                status = ROW_FALLBACK;
-                        }
+                        if (pos < (uint32_t)TC_QCAP)
+                            st_shared_u32(qaddr + pos * 4, ((uint32_t)lr << 16) | (gb[e] + (NGH - 1 - bit)));
+                        else
+                            status = ROW_FALLBACK;
+                        pos++;
                     }
                 }
             }
