@@ -120,7 +120,8 @@ def init_codebook(x: torch.Tensor, k: int, seed: int):
 
 # ------------------------------------------------------------------------------------------------
 def workload_config(n, d, world, assignment, sums):
-    return {"workload": f"configs[1]: SH codebook clustering, {n / 1e6:.1f}M Gaussians x {d}-D per GPU, K=4096, "
+    which = "configs[2]: shape codebook clustering" if d <= 8 else "configs[1]: SH codebook clustering"
+    return {"workload": f"{which}, {n / 1e6:.1f}M Gaussians x {d}-D per GPU, K=4096, "
                         "10 full-batch k-means iterations per step",
             "rows_per_gpu": n, "dim": d, "codebook_size": K, "iterations_per_step": ITERS, "decay": DECAY,
             "parallelism": f"rows sharded x{world}, codebook replicated, 1 all-reduce of K x (D+1) sums per iteration",
@@ -436,6 +437,77 @@ def main():
                                   "note": "keys + stable 8x8-bit LSD radix sort of (u64 key, u32 row); torch.sort (cub) "
                                           "of n random int64 incl. their generation, timed beside it for scale"}
         del keep, cbi, cbj, a6, cov6, sub, xyz
+        # SURVEY §8f ranks 1 and 3, the formats either side of the path: normalised covariance, mask compaction,
+        # int8 scene-file quantisation (algorithmic bytes / time against the measured copy peak)
+        s3 = torch.rand(n, 3, device=dev, generator=gen) + 0.05
+        r4 = torch.randn(n, 4, device=dev, generator=gen)
+        ms = timed(lambda: ops2.build_covariance(s3, r4, activate=True))
+        extras["build_covariance"] = {"rows": n, "ms": ms, "gbs": n * 52 / ms * 1e-6,
+                                      "frac_of_hbm_peak": n * 52 / ms * 1e-6 / pk["hbm_gbs"]}
+        keep2 = torch.rand(n, device=dev, generator=gen) < 0.6
+        ms = timed(lambda: ops2.compact([x], keep2))
+        cbytes = n + int(keep2.sum()) * d * 4 * 2
+        extras["mask_splats_compact"] = {"rows": n, "kept_frac": 0.6, "row_bytes": d * 4, "ms": ms,
+                                         "gbs": cbytes / ms * 1e-6, "frac_of_hbm_peak": cbytes / ms * 1e-6 / pk["hbm_gbs"],
+                                         "note": "mask scan + host sync for the kept count + row move"}
+        ms = timed(lambda: ops2.quantize_i8(x, 0.03125, 3))
+        ms_t = timed(lambda: torch.quantize_per_tensor(x, 0.03125, 3, torch.qint8).int_repr())
+        extras["quantize_i8"] = {"elements": x.numel(), "ms": ms, "gbs": x.numel() * 5 / ms * 1e-6,
+                                 "frac_of_hbm_peak": x.numel() * 5 / ms * 1e-6 / pk["hbm_gbs"],
+                                 "torch_quantize_per_tensor_ms": ms_t,
+                                 "note": "bit-exact with torch's CUDA quantiser (fp64 division there; fp32 fast path "
+                                         "with an exact fp64 slow path here), timed beside it"}
+        del s3, r4, keep2
+
+        # BASELINE configs[4]: the full compress pipeline on a synthetic 6M-Gaussian scene — prune, thresholds, both
+        # codebooks with the reference's default schedule shape (mini-batches), join, rotation/scaling extraction,
+        # decode of every attribute, Morton order + int8 scene tensors (file IO itself excluded: host numpy/zlib)
+        from c3dgs_b200 import CompressionSettings, SplatScene, compress_gaussians
+        npipe = 6_000_000
+        feats = torch.randn(npipe, 16, 3, device=dev, generator=gen)
+        scene = SplatScene(torch.randn(npipe, 3, device=dev, generator=gen), feats[:, :1].contiguous(),
+                           feats[:, 1:].contiguous(), torch.randn(npipe, 1, device=dev, generator=gen),
+                           torch.rand(npipe, 3, device=dev, generator=gen) + 0.05,
+                           torch.randn(npipe, 4, device=dev, generator=gen),
+                           torch.randn(npipe, 1, device=dev, generator=gen) - 3)
+        del feats
+        cimp = torch.rand(npipe, device=dev, generator=gen) ** 4
+        gimp = torch.rand(npipe, device=dev, generator=gen) ** 4
+        p_steps, p_batch = 100, 2 ** 18
+        cc = CompressionSettings(K, 0.0, 0.6, 0.9, p_steps, DECAY, p_batch)
+        gc_ = CompressionSettings(K, 0.0, 0.3, 0.9, p_steps, DECAY, p_batch)
+        torch.cuda.synchronize()
+        t0 = time.time()
+        compress_gaussians(scene, cimp, gimp, cc, gc_, color_compress_non_dir=True, prune_threshold=1e-8, silent=True)
+        torch.cuda.synchronize()
+        t1 = time.time()
+        from c3dgs_b200.decode import decode_gaussians
+        sdec, rdec, fdec = decode_gaussians(scene._scaling, scene._rotation,
+                                            torch.cat((scene._features_dc, scene._features_rest), 1),
+                                            scene._gaussian_indices, scene._feature_indices)
+        torch.cuda.synchronize()
+        t2 = time.time()
+        scene._sort_morton()
+        qbytes = 0
+        for name in ("features_dc", "features_rest", "opacity", "scaling", "scaling_factor", "rotation"):
+            t = scene._stored(name)
+            qbytes += ops2.quantize_i8(t, 0.01, 0).numel()
+        half = ops2.convert(scene._xyz, torch.float16)
+        i32 = ops2.convert(scene._feature_indices, torch.int32)
+        torch.cuda.synchronize()
+        t3 = time.time()
+        extras["compress_pipeline"] = {
+            "workload": "configs[4]: synthetic 6M-Gaussian scene, SH 48-D + shape 6-D codebooks (K=4096, "
+                        f"{p_steps} mini-batch steps of {p_batch} rows each + final full assignment), join, "
+                        "rot/scale, decode gather, Morton order, int8/fp16/int32 scene tensors",
+            "gaussians": npipe, "after_prune": int(scene._xyz.shape[0]),
+            "color_table_rows": int(scene._features_dc.shape[0]), "shape_table_rows": int(scene._rotation.shape[0]),
+            "compress_gaussians_ms": (t1 - t0) * 1e3, "decode_ms": (t2 - t1) * 1e3,
+            "morton_and_wire_ms": (t3 - t2) * 1e3, "total_ms": (t3 - t0) * 1e3,
+            "decoded_bytes": int(sdec.numel() + rdec.numel() + fdec.numel()) * 4, "int8_bytes": int(qbytes),
+            "note": "host wall clock, single run, includes workspace allocation and the host syncs the data-dependent "
+                    "output sizes need"}
+        del scene, cimp, gimp, sdec, rdec, fdec, half, i32
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

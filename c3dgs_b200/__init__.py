@@ -5,6 +5,8 @@ Public surface (mirrors the reference, compression/vq.py and submodules/weighted
     weighted_distance._C.weightedDistance                        (c3dgs_b200.weighted_distance)
     indexed_decode                                               (c3dgs_b200.decode)
     to_full_cov, extract_rot_scale, morton_order                 (c3dgs_b200.splats)
+    CompressionSettings, compress_color, compress_covariance, compress_gaussians   (c3dgs_b200.compress)
+    SplatScene (mask_splats, get_normalized_covariance, save_npz / load_npz, _sort_morton)   (c3dgs_b200.scene)
     install()   register the drop-ins under the reference's module names
 """
 from __future__ import annotations
@@ -15,9 +17,13 @@ from . import _lib  # noqa: F401
 from .decode import indexed_decode, decode_gaussians  # noqa: F401
 from .splats import extract_rot_scale, morton_order, to_full_cov  # noqa: F401
 from .vq import VectorQuantize, ema_inplace, join_features, vq_features  # noqa: F401
+from .compress import CompressionSettings, compress_color, compress_covariance, compress_gaussians  # noqa: F401
+from .scene import SplatScene, affine_qparams  # noqa: F401
 
 __all__ = ["VectorQuantize", "vq_features", "ema_inplace", "join_features", "indexed_decode",
-           "decode_gaussians", "to_full_cov", "extract_rot_scale", "morton_order", "install"]
+           "decode_gaussians", "to_full_cov", "extract_rot_scale", "morton_order", "install",
+           "CompressionSettings", "compress_color", "compress_covariance", "compress_gaussians", "SplatScene",
+           "affine_qparams"]
 
 
 def install(patch_vq_module: bool = True) -> None:

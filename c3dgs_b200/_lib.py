@@ -70,6 +70,11 @@ SIGNATURES = {
     "c3vq_extract_rot_scale": (_c_int, [_c_vp, _c_i64, _c_int, _c_vp, _c_vp, _c_vp]),
     "c3vq_morton_workspace_bytes": (_c_sz, [_c_i64]),
     "c3vq_morton_order": (_c_int, [_c_vp, _c_i64, _c_vp, _c_vp, _c_vp, _c_sz, _c_vp]),
+    "c3vq_quantize_i8": (_c_int, [_c_vp, _c_i64, _c_dbl, _c_i64, _c_vp, _c_vp]),
+    "c3vq_dequantize_i8": (_c_int, [_c_vp, _c_i64, ctypes.c_float, ctypes.c_int32, _c_vp, _c_vp]),
+    "c3vq_convert": (_c_int, [_c_int, _c_vp, _c_i64, _c_vp, _c_vp]),
+    "c3vq_build_covariance": (_c_int, [_c_vp, _c_vp, _c_i64, ctypes.c_float, _c_int, _c_vp, _c_vp]),
+    "c3vq_compact_rows": (_c_int, [_c_vp, _c_vp, _c_i64, _c_i64, _c_vp, _c_vp, _c_vp]),
     "c3vq_gather_rows": (_c_int, [_c_vp, _c_vp, _c_vp, _c_i64, _c_int, _c_vp, _c_vp, _c_vp]),
     "c3vq_debug_scores": (_c_int, [_c_vp, _c_i64, _c_int, _c_vp, _c_int, _c_vp, _c_vp, _c_vp, _c_vp, _c_sz, _c_vp]),
     "c3vq_assign_stats": (_c_int, [_c_vp, ctypes.POINTER(_c_i64), _c_vp]),
@@ -397,6 +402,119 @@ def morton_order(xyz: torch.Tensor, return_keys: bool = False):
     if rc:
         raise _err(rc)
     return (order, keys) if return_keys else order
+
+
+def _aligned(t: torch.Tensor) -> torch.Tensor:
+    """Contiguous and 16-byte aligned (a view into the middle of a storage may not be)."""
+    t = t.contiguous()
+    return t.clone() if t.data_ptr() % 16 else t
+
+
+def quantize_i8(x: torch.Tensor, scale, zero_point) -> torch.Tensor:
+    """torch.quantize_per_tensor(x, scale, zero_point, torch.qint8).int_repr() (scene/gaussian_model.py:528-620)
+    -> int8 tensor of x's shape.  scale / zero_point: python numbers or one-element tensors.  c3vq_quantize_i8."""
+    _check(x, torch.float32, "x")
+    x = _aligned(x)
+    scale = float(scale.item() if isinstance(scale, torch.Tensor) else scale)
+    zero_point = int(zero_point.item() if isinstance(zero_point, torch.Tensor) else zero_point)
+    with torch.cuda.device(x.device):
+        out = torch.empty(x.shape, dtype=torch.int8, device=x.device)
+        rc = load().c3vq_quantize_i8(_ptr(x), x.numel(), scale, zero_point, _ptr(out), _stream(x))
+    if rc:
+        raise _err(rc)
+    return out
+
+
+def dequantize_i8(q: torch.Tensor, scale, zero_point) -> torch.Tensor:
+    """(q.int() - zero_point) * scale (scene/gaussian_model.py:644-716) -> float32.  c3vq_dequantize_i8."""
+    _check(q, torch.int8, "q")
+    q = _aligned(q)
+    scale = float(scale.item() if isinstance(scale, torch.Tensor) else scale)
+    zero_point = int(zero_point.item() if isinstance(zero_point, torch.Tensor) else zero_point)
+    with torch.cuda.device(q.device):
+        out = torch.empty(q.shape, dtype=torch.float32, device=q.device)
+        rc = load().c3vq_dequantize_i8(_ptr(q), q.numel(), scale, zero_point, _ptr(out), _stream(q))
+    if rc:
+        raise _err(rc)
+    return out
+
+
+_CONVERSIONS = {  # (src dtype, dst dtype) -> C3VQ_* kind of include/c3vq.h
+    (torch.float32, torch.float16): 0, (torch.float16, torch.float32): 1,
+    (torch.int64, torch.int32): 2, (torch.int32, torch.int64): 3,
+}
+
+
+def convert(t: torch.Tensor, dtype: torch.dtype) -> torch.Tensor:
+    """The element-type conversions of the scene file format (float32 <-> float16 positions, int64 <-> int32
+    index arrays; scene/gaussian_model.py:522, :566-569, :639, :723-735).  c3vq_convert."""
+    kind = _CONVERSIONS.get((t.dtype, dtype))
+    if kind is None:
+        raise RuntimeError(f"no wire-format conversion from {t.dtype} to {dtype}")
+    _check(t, t.dtype, "t")
+    t = _aligned(t)
+    with torch.cuda.device(t.device):
+        out = torch.empty(t.shape, dtype=dtype, device=t.device)
+        rc = load().c3vq_convert(kind, _ptr(t), t.numel(), _ptr(out), _stream(t))
+    if rc:
+        raise _err(rc)
+    return out
+
+
+def build_covariance(scaling: torch.Tensor, rotation: torch.Tensor, scaling_modifier: float = 1.0,
+                     activate: bool = False) -> torch.Tensor:
+    """GaussianModel.get_normalized_covariance(strip_sym=True) (scene/gaussian_model.py:274-278): scaling [n,3],
+    rotation [n,4] -> cov [n,6].  activate=True takes the raw parameters (:66, :77).  c3vq_build_covariance."""
+    _check(scaling, torch.float32, "scaling", 2)
+    _check(rotation, torch.float32, "rotation", 2)
+    n = scaling.size(0)
+    if scaling.size(1) != 3 or tuple(rotation.shape) != (n, 4):
+        raise RuntimeError(f"scaling must be [n,3] and rotation [n,4], got {tuple(scaling.shape)} and "
+                           f"{tuple(rotation.shape)}")
+    scaling, rotation = scaling.contiguous(), rotation.contiguous()
+    with torch.cuda.device(scaling.device):
+        cov = torch.empty(n, 6, dtype=torch.float32, device=scaling.device)
+        rc = load().c3vq_build_covariance(_ptr(scaling), _ptr(rotation), n, float(scaling_modifier),
+                                          1 if activate else 0, _ptr(cov), _stream(scaling))
+    if rc:
+        raise _err(rc)
+    return cov
+
+
+def compact(tensors, keep_mask: torch.Tensor):
+    """[t[keep_mask] for t in tensors] (GaussianModel.mask_splats, scene/gaussian_model.py:1027-1046): one scan of
+    the mask (c3vq_join_count) shared by all tensors, one row-move kernel per tensor (c3vq_compact_rows).  Tensors
+    are float32 / int32 / int64 with the mask's length as first dimension; None entries pass through."""
+    if keep_mask.dtype != torch.bool or keep_mask.dim() != 1 or not keep_mask.is_cuda:
+        raise RuntimeError("keep_mask must be a 1-D CUDA bool tensor")
+    keep_mask = keep_mask.contiguous()
+    n = keep_mask.numel()
+    L = load()
+    dev = keep_mask.device
+    with torch.cuda.device(dev):
+        ws = torch.empty(max(int(L.c3vq_join_workspace_bytes(n)), 4), dtype=torch.uint8, device=dev)
+        kept = _c_i64(0)
+        rc = L.c3vq_join_count(_ptr(keep_mask), n, ctypes.byref(kept), _ptr(ws), ws.numel(), _stream(keep_mask))
+        if rc:
+            raise _err(rc)
+        kept = int(kept.value)
+        outs = []
+        for t in tensors:
+            if t is None:
+                outs.append(None)
+                continue
+            if not t.is_cuda or t.dtype not in (torch.float32, torch.int32, torch.int64):
+                raise RuntimeError("compact() takes float32 / int32 / int64 CUDA tensors")
+            if t.dim() < 1 or t.size(0) != n:
+                raise RuntimeError(f"tensor of shape {tuple(t.shape)} does not match the mask ({n} rows)")
+            t = t.detach().contiguous()
+            out = torch.empty((kept,) + tuple(t.shape[1:]), dtype=t.dtype, device=dev)
+            row_bytes = (t.numel() // n) * t.element_size() if n else 0
+            rc = L.c3vq_compact_rows(_ptr(t), _ptr(keep_mask), n, row_bytes, _ptr(out), _ptr(ws), _stream(keep_mask))
+            if rc:
+                raise _err(rc)
+            outs.append(out)
+    return outs
 
 
 def scatter_add(grad_out: torch.Tensor, idx: torch.Tensor, table_rows: int) -> torch.Tensor:

@@ -15,7 +15,8 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libc3vq.so")
-SOURCES = ["api.cu", "assign_exact.cu", "assign_tc.cu", "update.cu", "gather.cu", "rot_scale.cu", "morton.cu"]
+SOURCES = ["api.cu", "assign_exact.cu", "assign_tc.cu", "update.cu", "gather.cu", "rot_scale.cu", "morton.cu",
+           "wire.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-std=c++17", "-lineinfo",
@@ -40,21 +41,47 @@ def stale() -> bool:
     return any(os.path.getmtime(p) > t for p in deps)
 
 
+def _run(cmd):
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError("nvcc failed:\n" + " ".join(cmd) + "\n" + res.stdout + res.stderr)
+    return res
+
+
+def _compile_objects(sources, objdir, extra, verbose=False):
+    """One object per source, rebuilt only when the source, a header or the flags are newer; sources compile
+    in parallel (assign_tc.cu alone takes minutes, the rest seconds)."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    os.makedirs(objdir, exist_ok=True)
+    # the image exports CC/CXX wrappers that lack some spec files; let nvcc pick the distro g++
+    ccbin = ["-ccbin", "/usr/bin/g++"] if os.path.exists("/usr/bin/g++") else []
+    headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))] + \
+              [os.path.join(HERE, "..", "include", "c3vq.h"), os.path.abspath(__file__)]
+    hdr_t = max(os.path.getmtime(h) for h in headers)
+    flags = [f for f in NVCC_FLAGS if f != "-shared"] + extra + (["-Xptxas", "-v"] if verbose else [])
+    jobs, objs = [], []
+    for src in sources:
+        obj = os.path.join(objdir, src.replace(".cu", ".o"))
+        objs.append(obj)
+        srcp = os.path.join(CSRC, src)
+        if not os.path.exists(obj) or os.path.getmtime(obj) < max(hdr_t, os.path.getmtime(srcp)):
+            jobs.append([nvcc()] + ccbin + flags + ["-c", srcp, "-o", obj])
+    with ThreadPoolExecutor(max_workers=max(1, min(len(jobs), os.cpu_count() or 1))) as ex:
+        for res in ex.map(_run, jobs):
+            if verbose:
+                sys.stderr.write(res.stderr)
+    return objs, ccbin
+
+
 def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not stale():
         return LIB
-    cmd = [nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + \
-          [os.path.join(CSRC, s) for s in SOURCES] + ["-o", LIB]
-    env = dict(os.environ)
-    # the image exports CC/CXX wrappers that lack some spec files; let nvcc pick the distro g++
-    ccbin = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else None
-    if ccbin:
-        cmd[1:1] = ["-ccbin", ccbin]
-    res = subprocess.run(cmd, env=env, capture_output=True, text=True)
-    if verbose:
-        sys.stderr.write(res.stderr)
-    if res.returncode != 0:
-        raise RuntimeError("nvcc failed:\n" + " ".join(cmd) + "\n" + res.stdout + res.stderr)
+    objdir = os.path.join(HERE, "_obj")
+    if force and os.path.isdir(objdir):
+        shutil.rmtree(objdir)
+    objs, ccbin = _compile_objects(SOURCES, objdir, [], verbose)
+    _run([nvcc()] + ccbin + NVCC_FLAGS + objs + ["-o", LIB])
     return LIB
 
 
@@ -65,9 +92,9 @@ if __name__ == "__main__":
 def build_dev(defines, out_name="libc3vq_dev.so") -> str:
     """Developer build with extra -D flags (e.g. C3VQ_TC_SINGLE, C3VQ_TC_PROF); load it with C3VQ_LIB=<path>."""
     out = os.path.join(HERE, out_name)
-    cmd = [nvcc(), "-ccbin", "/usr/bin/g++"] + NVCC_FLAGS + ["-D" + d for d in defines] + \
-          [os.path.join(CSRC, s) for s in SOURCES] + ["-o", out]
-    res = subprocess.run(cmd, capture_output=True, text=True)
-    if res.returncode != 0:
-        raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
+    objdir = os.path.join(HERE, "_obj_" + out_name.replace(".so", ""))
+    if os.path.isdir(objdir):
+        shutil.rmtree(objdir)
+    objs, ccbin = _compile_objects(SOURCES, objdir, ["-D" + d for d in defines])
+    _run([nvcc()] + ccbin + NVCC_FLAGS + objs + ["-o", out])
     return out

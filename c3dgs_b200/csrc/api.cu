@@ -272,6 +272,50 @@ int c3vq_morton_order(const float *xyz, int64_t n, int64_t *out_order, uint64_t 
     return launch_morton_order(xyz, n, out_order, out_keys, ws, ws_bytes, (cudaStream_t)stream);
 }
 
+int c3vq_quantize_i8(const float *x, int64_t n, double scale, int64_t zero_point, int8_t *out, c3vq_stream_t stream)
+{
+    C3VQ_CHECK_ARG(n >= 0, "n=%lld is negative", (long long)n);
+    C3VQ_CHECK_ARG(n == 0 || (x && out), "null pointer");
+    C3VQ_CHECK_ARG(scale > 0.0 && scale == scale, "scale must be positive");
+    C3VQ_CHECK_ARG(((uintptr_t)x & 15) == 0 && ((uintptr_t)out & 3) == 0, "x must be 16-byte and out 4-byte aligned");
+    return launch_quantize_i8(x, n, scale, zero_point, out, (cudaStream_t)stream);
+}
+
+int c3vq_dequantize_i8(const int8_t *q, int64_t n, float scale, int32_t zero_point, float *out, c3vq_stream_t stream)
+{
+    C3VQ_CHECK_ARG(n >= 0, "n=%lld is negative", (long long)n);
+    C3VQ_CHECK_ARG(n == 0 || (q && out), "null pointer");
+    C3VQ_CHECK_ARG(((uintptr_t)q & 3) == 0 && ((uintptr_t)out & 15) == 0, "q must be 4-byte and out 16-byte aligned");
+    return launch_dequantize_i8(q, n, scale, zero_point, out, (cudaStream_t)stream);
+}
+
+int c3vq_convert(int kind, const void *src, int64_t n, void *dst, c3vq_stream_t stream)
+{
+    C3VQ_CHECK_ARG(n >= 0, "n=%lld is negative", (long long)n);
+    C3VQ_CHECK_ARG(n == 0 || (src && dst), "null pointer");
+    C3VQ_CHECK_ARG(((uintptr_t)src & 15) == 0 && ((uintptr_t)dst & 15) == 0, "src and dst must be 16-byte aligned");
+    return launch_convert(kind, src, n, dst, (cudaStream_t)stream);
+}
+
+int c3vq_build_covariance(const float *scaling, const float *rotation, int64_t n, float scaling_modifier,
+                          int activate, float *out_cov, c3vq_stream_t stream)
+{
+    C3VQ_CHECK_ARG(n >= 0, "n=%lld is negative", (long long)n);
+    C3VQ_CHECK_ARG(n == 0 || (scaling && rotation && out_cov), "null pointer");
+    return launch_build_cov(scaling, rotation, n, scaling_modifier, activate, out_cov, (cudaStream_t)stream);
+}
+
+int c3vq_compact_rows(const void *src, const uint8_t *keep_mask, int64_t n, int64_t row_bytes, void *out,
+                      const void *ws, c3vq_stream_t stream)
+{
+    C3VQ_CHECK_ARG(n >= 0 && row_bytes >= 0, "negative size");
+    C3VQ_CHECK_ARG((row_bytes & 3) == 0 && row_bytes < ((int64_t)1 << 31), "row_bytes=%lld must be a multiple of 4",
+                   (long long)row_bytes);
+    C3VQ_CHECK_ARG(n == 0 || row_bytes == 0 || (src && keep_mask && out && ws), "null pointer");
+    C3VQ_CHECK_ARG(((uintptr_t)src & 3) == 0 && ((uintptr_t)out & 3) == 0, "src and out must be 4-byte aligned");
+    return launch_compact_rows(src, keep_mask, n, (int)(row_bytes / 4), out, ws, (cudaStream_t)stream);
+}
+
 int c3vq_gather_rows(const float *x, const float *w, const int64_t *rows, int64_t n, int d, float *out_x,
                      float *out_w, c3vq_stream_t stream)
 {

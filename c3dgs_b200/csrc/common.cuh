@@ -81,6 +81,15 @@ int launch_join_count(const uint8_t *keep, int64_t n, void *ws, size_t ws_bytes,
 int launch_join_write(const float *feats, const uint8_t *keep, int64_t n, int d, const float *codebook, int64_t k,
                       const int64_t *cb_idx, float *out_feats, int64_t *out_idx, const void *ws, cudaStream_t s);
 
+// wire formats and pipeline glue (wire.cu)
+int launch_quantize_i8(const float *x, int64_t n, double scale, int64_t zero_point, int8_t *out, cudaStream_t s);
+int launch_dequantize_i8(const int8_t *q, int64_t n, float scale, int zero_point, float *out, cudaStream_t s);
+int launch_convert(int kind, const void *src, int64_t n, void *dst, cudaStream_t s);
+int launch_build_cov(const float *scaling, const float *rotation, int64_t n, float modifier, int activate, float *cov,
+                     cudaStream_t s);
+int launch_compact_rows(const void *src, const uint8_t *keep, int64_t n, int words, void *out, const void *ws,
+                        cudaStream_t s);
+
 // tensor-core assignment (assign_tc.cu)
 size_t tc_workspace_bytes(int64_t n, int d, int k);
 int launch_assign_tc(const float *x, const float *w, const int64_t *rows, int64_t n, int d, const float *codebook,

@@ -177,6 +177,47 @@ size_t c3vq_morton_workspace_bytes(int64_t n);
 int c3vq_morton_order(const float *xyz /* [n,3] */, int64_t n, int64_t *out_order /* [n] */,
                       uint64_t *out_keys /* [n] or null */, void *ws, size_t ws_bytes, c3vq_stream_t stream);
 
+/*
+ * Per-tensor int8 affine quantisation of the compressed scene file, GaussianModel.save_npz
+ * (scene/gaussian_model.py:528-620: torch.quantize_per_tensor(x, scale, zero_point, torch.qint8).int_repr()):
+ *   out[i] = clamp((int64)(nearbyint((double)x[i] / scale) + zero_point), -128, 127)     (round half to even)
+ * which is the arithmetic of torch's CUDA quantiser; results are bit-exact with it.  x 16-byte aligned.
+ */
+int c3vq_quantize_i8(const float *x, int64_t n, double scale, int64_t zero_point, int8_t *out, c3vq_stream_t stream);
+
+/* Its inverse, GaussianModel.load_npz (scene/gaussian_model.py:644-716): out[i] = (float)(q[i] - zero_point) * scale. */
+int c3vq_dequantize_i8(const int8_t *q, int64_t n, float scale, int32_t zero_point, float *out, c3vq_stream_t stream);
+
+/*
+ * Element-type conversions of the same file format: positions are stored as float16 (gaussian_model.py:522,
+ * read back :639), index arrays as int32 (:566-569, read back :723-735).
+ */
+#define C3VQ_F32_TO_F16 0   /* round to nearest even (Tensor.half()) */
+#define C3VQ_F16_TO_F32 1
+#define C3VQ_I64_TO_I32 2   /* keeps the low 32 bits (Tensor.int()) */
+#define C3VQ_I32_TO_I64 3
+int c3vq_convert(int kind, const void *src, int64_t n, void *dst, c3vq_stream_t stream);
+
+/*
+ * The normalised covariance the shape codebook is learnt on, GaussianModel.get_normalized_covariance(strip_sym=True)
+ * (scene/gaussian_model.py:274-278 -> :55-63; utils/general_utils.py:68-119): q <- rotation / |rotation|,
+ * L = R(q) diag(scaling_modifier * scaling), out_cov [n,6] = upper triangle (xx, xy, xz, yy, yz, zz) of L L^T.
+ * activate != 0 applies the model's activations first (scaling <- normalize(relu(scaling)), rotation <-
+ * normalize(rotation); gaussian_model.py:66, :77), i.e. the call takes the raw parameters.  float32; agrees with
+ * the reference's batched matmul to rounding (sum order of three products).
+ */
+int c3vq_build_covariance(const float *scaling /* [n,3] */, const float *rotation /* [n,4] */, int64_t n,
+                          float scaling_modifier, int activate, float *out_cov /* [n,6] */, c3vq_stream_t stream);
+
+/*
+ * Boolean-mask row compaction, t[mask] for every per-Gaussian tensor in GaussianModel.mask_splats
+ * (scene/gaussian_model.py:1027-1046; the pruning step of compress_gaussians, compression/vq.py:206-210):
+ * out[rank(i), :] = src[i, :] where keep_mask[i] != 0, rows of row_bytes bytes (a multiple of 4).  ws is the
+ * workspace c3vq_join_count filled for the same mask (one count serves all tensors of the model).
+ */
+int c3vq_compact_rows(const void *src, const uint8_t *keep_mask, int64_t n, int64_t row_bytes, void *out,
+                      const void *ws, c3vq_stream_t stream);
+
 /* Mini-batch row gather: out_x[i,:] = x[rows[i],:], out_w[i] = w[rows[i]] (w/out_w may be null). */
 int c3vq_gather_rows(const float *x, const float *w, const int64_t *rows, int64_t n, int d,
                      float *out_x, float *out_w, c3vq_stream_t stream);

@@ -218,9 +218,49 @@ def run_morton_cases():
     return path
 
 
+def run_wire_cases():
+    """The scene-file arithmetic and the covariance construction, produced by torch / the reference's own functions
+    on CPU tensors: torch.quantize_per_tensor(...).int_repr() and (q.int() - zp) * scale as save_npz / load_npz
+    write them (scene/gaussian_model.py:528-620, :644-716), Tensor.half(), and
+    strip_symmetric(L @ L^T) with L = build_scaling_rotation(s, q) from utils/general_utils.py (imported unchanged)
+    as GaussianModel.get_normalized_covariance evaluates it (:55-63, :274-278)."""
+    sys.path.insert(0, ref_loader.REFERENCE_ROOT)
+    import utils.general_utils as gu   # the reference's module
+    g = torch.Generator().manual_seed(11)
+    out = {}
+    x = torch.randn(20011, generator=g) * 0.8
+    x[:64] = (torch.arange(-32, 32).float() + 0.5) * 0.0123          # rounding boundaries
+    x[64:70] = torch.tensor([1e9, -1e9, 3.3e38, -3.3e38, 0.0, -0.0])
+    for i, (scale, zp) in enumerate([(0.0123, -7), (0.0041, 12), (1.7, 0)]):
+        scale = float(np.float32(scale))
+        q = torch.quantize_per_tensor(x, scale, zp, torch.qint8).int_repr()
+        out[f"q{i}_scale"] = np.float32(scale)
+        out[f"q{i}_zp"] = np.int32(zp)
+        out[f"q{i}_q"] = q.numpy()
+        out[f"q{i}_deq"] = ((q.int() - torch.tensor([zp], dtype=torch.int32)) * torch.tensor([scale])).numpy()
+    out["q_x"] = x.numpy()
+    out["half_x"] = (torch.randn(4099, generator=g) * 37.0).numpy()
+    out["half_y"] = torch.from_numpy(out["half_x"]).half().numpy()
+    n = 3001
+    s_raw = torch.randn(n, 3, generator=g)
+    r_raw = torch.randn(n, 4, generator=g) * 2.0
+    s_act = torch.nn.functional.normalize(torch.nn.functional.relu(s_raw))
+    r_act = torch.nn.functional.normalize(r_raw)
+    for mod in (1.0, 0.7):
+        L = gu.build_scaling_rotation(mod * s_act, r_act)
+        out[f"cov_m{mod}"] = gu.strip_symmetric(L @ L.transpose(1, 2)).numpy()
+    out["cov_s_raw"], out["cov_r_raw"] = s_raw.numpy(), r_raw.numpy()
+    out["cov_s_act"], out["cov_r_act"] = s_act.numpy(), r_act.numpy()
+    np.savez_compressed(os.path.join(GOLDEN_DIR, "wire.npz"), **out)
+    print("wire.npz written")
+
+
 def main():
     if not ref_loader.available():
         raise SystemExit("reference checkout not present; fixtures can only be generated in the build container")
+    if "--wire-only" in sys.argv:
+        run_wire_cases()
+        return
     if "--morton-only" in sys.argv:
         p = run_morton_cases()
         print("wrote", p, os.path.getsize(p) // 1024, "KiB")
@@ -239,6 +279,7 @@ def main():
     print("wrote", p, os.path.getsize(p) // 1024, "KiB")
     p = run_morton_cases()
     print("wrote", p, os.path.getsize(p) // 1024, "KiB")
+    run_wire_cases()
 
 
 if __name__ == "__main__":

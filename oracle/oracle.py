@@ -295,3 +295,63 @@ def morton_keys(xyz):
 def morton_order(xyz):
     """`mortonEncode(...).sort().indices` (:1003) with ties in row order (stable)."""
     return np.argsort(morton_keys(xyz), kind="stable").astype(np.int64)
+
+
+# ---- §8(f) ranks 1 and 3: the scene-file wire format and the glue around the path ------------------------------------
+def quantize_i8(x, scale, zero_point):
+    """torch.quantize_per_tensor(x, scale, zero_point, torch.qint8).int_repr() as save_npz calls it on the model's
+    device (scene/gaussian_model.py:528-620).  torch's CUDA quantiser evaluates
+    clamp(int64(nearbyint(double(x) / scale) + zero_point), -128, 127) with round-half-to-even; its CPU quantiser
+    multiplies by float32(1/scale) instead, so the two differ on a few elements per million that sit on a rounding
+    boundary (tests/test_oracle_golden.py bounds exactly that).  NaN quantises like 0 (the integer conversion)."""
+    xd = np.asarray(x, np.float32).astype(np.float64)
+    with np.errstate(invalid="ignore", over="ignore"):
+        t = np.rint(xd / float(scale)) + float(int(zero_point))
+    t = np.where(np.isnan(t), 0.0, t)
+    return np.clip(t, -128, 127).astype(np.int8)
+
+
+def dequantize_i8(q, scale, zero_point):
+    """load_npz (scene/gaussian_model.py:644-716): (q.int() - zero_point) * scale, int32 difference times a float32."""
+    d = np.asarray(q, np.int8).astype(np.int32) - np.int32(zero_point)
+    return d.astype(np.float32) * np.float32(scale)
+
+
+def build_rotation(r):
+    """utils/general_utils.py:84-107: quaternion (real part first, normalised here) -> 3x3, float32."""
+    r = np.asarray(r, np.float32)
+    norm = np.sqrt(r[:, 0] * r[:, 0] + r[:, 1] * r[:, 1] + r[:, 2] * r[:, 2] + r[:, 3] * r[:, 3])
+    q = r / norm[:, None]
+    w, x, y, z = q[:, 0], q[:, 1], q[:, 2], q[:, 3]
+    one, two = np.float32(1), np.float32(2)
+    R = np.zeros((len(q), 3, 3), np.float32)
+    R[:, 0, 0] = one - two * (y * y + z * z)
+    R[:, 0, 1] = two * (x * y - w * z)
+    R[:, 0, 2] = two * (x * z + w * y)
+    R[:, 1, 0] = two * (x * y + w * z)
+    R[:, 1, 1] = one - two * (x * x + z * z)
+    R[:, 1, 2] = two * (y * z - w * x)
+    R[:, 2, 0] = two * (x * z - w * y)
+    R[:, 2, 1] = two * (y * z + w * x)
+    R[:, 2, 2] = one - two * (x * x + y * y)
+    return R
+
+
+def normalized_covariance(scaling, rotation, scaling_modifier=1.0, activate=False):
+    """GaussianModel.get_normalized_covariance(strip_sym=True) (scene/gaussian_model.py:274-278, :55-63;
+    utils/general_utils.py:68-119): L = R diag(modifier * s), upper triangle of L L^T as [n,6], float32.
+    activate: scaling <- normalize(relu(scaling)), rotation <- normalize(rotation) first (:66, :77)."""
+    s = np.asarray(scaling, np.float32)
+    r = np.asarray(rotation, np.float32)
+    if activate:
+        s = np.maximum(s, np.float32(0))
+        s = s / np.maximum(np.sqrt((s * s).sum(1, dtype=np.float32)), np.float32(1e-12))[:, None]
+        r = r / np.maximum(np.sqrt((r * r).sum(1, dtype=np.float32)), np.float32(1e-12))[:, None]
+    L = build_rotation(r) * (np.float32(scaling_modifier) * s)[:, None, :]
+    cov = np.einsum("nij,nkj->nik", L, L).astype(np.float32)
+    return np.stack([cov[:, 0, 0], cov[:, 0, 1], cov[:, 0, 2], cov[:, 1, 1], cov[:, 1, 2], cov[:, 2, 2]], 1)
+
+
+def mask_rows(t, mask):
+    """t[mask] of GaussianModel.mask_splats (scene/gaussian_model.py:1027-1046): stable boolean-mask compaction."""
+    return np.asarray(t)[np.asarray(mask, bool)]

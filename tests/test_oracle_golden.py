@@ -4,7 +4,9 @@ compression/vq.py (oracle/make_golden.py), plus known-answer tests for the assig
 import numpy as np
 import pytest
 
-from conftest import GOLDEN_CASES, golden_path
+import os
+
+from conftest import GOLDEN_CASES, ROOT, golden_path
 
 
 @pytest.mark.parametrize("name", GOLDEN_CASES)
@@ -219,3 +221,45 @@ def test_oracle_morton_order_reproduces_reference(oracle):
         assert np.array_equal(np.sort(o), np.arange(len(xyz))), name
         if len(np.unique(keys)) == len(keys):
             assert np.array_equal(o, order), name
+
+
+# ---------------------------------------------------------------- scene-file wire format, covariance ---------------
+def _wire():
+    return np.load(os.path.join(ROOT, "tests", "golden", "wire.npz"))
+
+
+def test_oracle_quantize_matches_torch_except_on_rounding_boundaries(oracle):
+    """wire.npz holds torch's CPU quantiser; the oracle restates torch's CUDA one (double division).  They may differ
+    only where x/scale sits on a rounding boundary (by one step) or overflows int32 (the CPU vector conversion wraps)."""
+    g = _wire()
+    x = g["q_x"]
+    for i in range(3):
+        scale, zp = float(g[f"q{i}_scale"]), int(g[f"q{i}_zp"])
+        q = oracle.quantize_i8(x, scale, zp)
+        t = x.astype(np.float64) / scale
+        on_boundary = np.abs(np.abs(t - np.rint(t)) - 0.5) < 1e-5
+        overflow = np.abs(t) >= 2.0 ** 31
+        diff = q.astype(np.int32) - g[f"q{i}_q"].astype(np.int32)
+        assert np.all(diff[~on_boundary & ~overflow] == 0)
+        assert np.abs(diff[on_boundary & ~overflow]).max(initial=0) <= 1
+        assert (diff != 0).sum() < 40
+        assert np.array_equal(q[overflow], np.where(t[overflow] > 0, 127, -128).astype(np.int8))
+
+
+def test_oracle_dequantize_bit_exact_vs_torch(oracle):
+    g = _wire()
+    for i in range(3):
+        deq = oracle.dequantize_i8(g[f"q{i}_q"], g[f"q{i}_scale"], g[f"q{i}_zp"])
+        assert np.array_equal(deq, g[f"q{i}_deq"])
+    assert np.array_equal(g["half_x"].astype(np.float16), g["half_y"])
+
+
+def test_oracle_normalized_covariance_vs_reference_golden(oracle):
+    g = _wire()
+    for mod in (1.0, 0.7):
+        ref = g[f"cov_m{mod}"]
+        for args in ((g["cov_s_act"], g["cov_r_act"], mod, False), (g["cov_s_raw"], g["cov_r_raw"], mod, True)):
+            cov = oracle.normalized_covariance(*args)
+            assert np.abs(cov - ref).max() <= 1e-6            # entries are <= 1; float32 sum-order differences
+    keep = g["cov_s_raw"][:, 0] > 0
+    assert np.array_equal(oracle.mask_rows(g["cov_r_raw"], keep), g["cov_r_raw"][keep])
