@@ -510,6 +510,9 @@ def compact(tensors, keep_mask: torch.Tensor):
             t = t.detach().contiguous()
             out = torch.empty((kept,) + tuple(t.shape[1:]), dtype=t.dtype, device=dev)
             row_bytes = (t.numel() // n) * t.element_size() if n else 0
+            if kept == 0 or row_bytes == 0:
+                outs.append(out)
+                continue
             rc = L.c3vq_compact_rows(_ptr(t), _ptr(keep_mask), n, row_bytes, _ptr(out), _ptr(ws), _stream(keep_mask))
             if rc:
                 raise _err(rc)

@@ -84,9 +84,13 @@ struct TcHeader {
     unsigned long long fb_rows;     // stats: rows sent to the exact fallback
     unsigned int fb_count;          // fallback list length
     unsigned int force_fallback;    // set by prep when a finite code breaks the magnitude limit
-    int cmax_bits;                  // max |c'_j| over finite codes, float bits (non-negative)
-    int live;                       // number of finite codes
-    float mu_sum[72];               // column sums over finite codes
+    int cmax_bits;                  // max |c'_j| over the regular codes, float bits (non-negative)
+    int live;                       // number of regular codes
+    float mu_sum[72];               // column sums over the regular codes
+    int thr_exp;                    // regular code <=> finite and exponent of |c_j|^2 <= thr_exp (k_tc_prep_mean)
+    int xs_max_bits;                // float bits of max |x_i|^2 over a sample of the rows (k_tc_prep_hist)
+    int excl_gap_bits;              // 0x7f800000 - float bits of min |c'_j| over the finite outlier codes (0: none)
+    unsigned int exp_hist[256];     // exponent histogram of |c_j|^2 over the finite codes (k_tc_prep_hist)
     unsigned long long prof[32];    // developer build (C3VQ_TC_PROF): cycle counters per role/phase
 };
 
@@ -116,15 +120,82 @@ struct TcParams {
 };
 
 // ------------------------------------------------------------------------------------------------
-// prep 1: column sums over finite codes (for the centre mu)
+// Outlier codewords.  The error band of a row grows with Cmax = max |c'_j|, so a single far-away codeword would put
+// every code of every row inside the band.  They are a fact of the reference's own pipeline: the shape codebook is
+// divided by its trace after every step (vq.py:76-77), and a codeword nobody uses keeps its random initial value, whose
+// trace can be anything, 0 included.  A code is "regular" when its squared norm lies at most one binade above the
+// larger of (the 75th percentile over the codebook, the largest |x_i|^2 among a sample of the rows) and at most 8
+// binades above that percentile; live codewords are weighted means of rows and so always regular, a freshly drawn
+// uniform-box codebook has its norms within one binade of its own 75th percentile.  The other codes are kept out of
+// the screening (score 2^126, like a non-finite code) and out of mu / Cmax.  That is exact, not
+// a heuristic, for every row that passes the test the producer warps make after the re-rank: with Cx = min |c'_j|
+// over the outliers, every outlier is at least Cx - |x'| away from the row, and the row keeps the winner among the
+// regular codes only if 0.98 (Cx - 1.001 |x'|)^2 exceeds that winner's exact distance — a margin no fp32 rounding of
+// the reference chain, of the centring or of the norms can bridge.  Rows that fail it (the ones that really live out
+// there) take the exact scan.  The percentile only decides how many rows that is.
+constexpr int TC_OUTLIER_BINADES = 8;
+
+// prep 0: exponent histogram of |c_j|^2 over the finite codes (warp per code)
+__global__ void __launch_bounds__(256) k_tc_prep_hist(const float *__restrict__ cb, int k, int d,
+                                                      const float *__restrict__ x, const int64_t *__restrict__ rows,
+                                                      int64_t n, TcHeader *hdr)
+{
+    __shared__ unsigned int sh[256];
+    sh[threadIdx.x] = 0;
+    __syncthreads();
+    {   // data scale: the largest |x_i|^2 among gridDim.x * 256 rows spread evenly over the input
+        const int64_t S = (int64_t)gridDim.x * 256, si = (int64_t)blockIdx.x * 256 + threadIdx.x;
+        int bits = 0;
+        if (si < n) {
+            const int64_t i = S < n ? (int64_t)(((unsigned long long)si * (unsigned long long)n) / (unsigned long long)S) : si;
+            const float *row = x + (size_t)(rows ? rows[i] : i) * d;
+            float r = 0.f;
+            for (int c = 0; c < d; c++) r = fmaf(row[c], row[c], r);
+            if (isfinite(r)) bits = __float_as_int(r);
+        }
+        bits = __reduce_max_sync(0xffffffffu, bits);
+        if ((threadIdx.x & 31) == 0 && bits) atomicMax(&hdr->xs_max_bits, bits);
+    }
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int j0 = blockIdx.x * 128;
+    for (int j = j0 + wib; j < min(k, j0 + 128); j += 8) {
+        const float *row = cb + (size_t)j * d;
+        const float v0 = lane < d ? row[lane] : 0.f;
+        const float v1 = lane + 32 < d ? row[lane + 32] : 0.f;
+        float r = fmaf(v0, v0, v1 * v1);
+        for (int o = 16; o; o >>= 1) r += __shfl_xor_sync(0xffffffffu, r, o);
+        if (lane == 0 && isfinite(r)) atomicAdd(&sh[(__float_as_uint(r) >> 23) & 0xff], 1u);
+    }
+    __syncthreads();
+    if (sh[threadIdx.x]) atomicAdd(&hdr->exp_hist[threadIdx.x], sh[threadIdx.x]);
+}
+
+// prep 1: column sums over the regular codes (for the centre mu)
 __global__ void __launch_bounds__(256) k_tc_prep_mean(const float *__restrict__ cb, int k, int d, TcHeader *hdr)
 {
     // warp per code (lanes over columns, coalesced row reads), 128 codes per block
     __shared__ float ssum[72];
     __shared__ int slive;
+    __shared__ int sthr;
     if (threadIdx.x < 72) ssum[threadIdx.x] = 0.f;
-    if (threadIdx.x == 0) slive = 0;
+    if (threadIdx.x == 0) {
+        slive = 0;
+        unsigned int total = 0, run = 0;
+        for (int e = 0; e < 256; e++) total += hdr->exp_hist[e];
+        int e75 = 255;
+        for (int e = 0; e < 256; e++) {
+            run += hdr->exp_hist[e];
+            if (4ull * run >= 3ull * total) { e75 = e; break; }
+        }
+        const int ex = (hdr->xs_max_bits >> 23) & 0xff;
+        sthr = min(min(max(ex, e75) + 1, e75 + TC_OUTLIER_BINADES), 254);
+#ifdef C3VQ_TC_NO_OUTLIERS
+        sthr = 254;                  // developer build: every finite code is regular (the behaviour before r1q)
+#endif
+        if (blockIdx.x == 0) hdr->thr_exp = sthr;
+    }
     __syncthreads();
+    const int thr = sthr;
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     float s0 = 0.f, s1 = 0.f;
     int live = 0;
@@ -133,7 +204,10 @@ __global__ void __launch_bounds__(256) k_tc_prep_mean(const float *__restrict__ 
         const float *row = cb + (size_t)j * d;
         const float v0 = lane < d ? row[lane] : 0.f;
         const float v1 = lane + 32 < d ? row[lane + 32] : 0.f;
-        const bool fin = __all_sync(0xffffffffu, isfinite(v0) && isfinite(v1));
+        float r = fmaf(v0, v0, v1 * v1);
+        for (int o = 16; o; o >>= 1) r += __shfl_xor_sync(0xffffffffu, r, o);
+        const bool fin = __all_sync(0xffffffffu, isfinite(v0) && isfinite(v1)) && isfinite(r) &&
+                         (int)((__float_as_uint(r) >> 23) & 0xff) <= thr;
         if (fin) { s0 += v0; s1 += v1; live++; }
     }
     if (lane < d) atomicAdd(&ssum[lane], s0);
@@ -156,6 +230,7 @@ __global__ void k_tc_prep_image(const float *__restrict__ cb, int k, int k_pad, 
     float *img = bimg + (size_t)(j / bn) * (bn * dp) + (size_t)(j % bn) * 4;   // + chunk*BN*4 + (kk&3)
     bool fin = j < k;
     double n2 = 0.0;
+    float raw2 = 0.f;
     if (j < k) {
         const float *row = cb + (size_t)j * d;
         for (int c = 0; c < d; c++) {
@@ -165,11 +240,17 @@ __global__ void k_tc_prep_image(const float *__restrict__ cb, int k, int k_pad, 
             if (j == 0) mu_out[c] = m;
             const float cc = v - m;
             n2 += (double)cc * (double)cc;
+            raw2 = fmaf(v, v, raw2);
             cbp[(size_t)j * dpc + c] = v;
         }
         for (int c = d; c < dpc; c++) cbp[(size_t)j * dpc + c] = 0.f;
     }
     const float nf = (float)n2;
+    if (fin && !(isfinite(raw2) && (int)((__float_as_uint(raw2) >> 23) & 0xff) <= hdr->thr_exp)) {
+        // finite outlier: out of the screening; the producers check every row against the nearest of them
+        atomicMax(&hdr->excl_gap_bits, 0x7f800000 - __float_as_int(fminf(sqrtf(nf), __int_as_float(0x7f800000))));
+        fin = false;
+    }
     if (fin && !(nf < TC_HUGE2)) {      // finite code outside the error model: everything goes exact
         atomicOr(&hdr->force_fallback, 1u);
     }
@@ -445,6 +526,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
         // staging stores, lane <-> row (= TMEM lane, this warp's quarter pw & 3 of tile pw >> 2) for the A operand
         const uint32_t a_tmem = *(volatile uint32_t *)sTmem + ((uint32_t)((pw & 3) * 32) << 16) + L::ACOL + (pw >> 2) * DP;
         const float cmax = __int_as_float(p.hdr->cmax_bits);
+        const float cexcl = __int_as_float(0x7f800000 - p.hdr->excl_gap_bits);   // nearest outlier code (inf: none)
+        const bool has_outliers = p.hdr->excl_gap_bits != 0;
+        // constants of the band formula below (C1, C2): 2 C2 Cmax^2 and 1 / (2 C1 Cmax)
+        const float outl_c2 = 2.f * (3.814697265625e-6f + 4.76837158203125e-7f) * cmax * cmax * 0.999f;
+        const float outl_inv = 1.001f / (2.f * (1.002f * 0.001953125f + 7.62939453125e-6f) * cmax);
         const bool force_fb = p.hdr->force_fallback != 0;
         const bool need_dist = p.out_dist != nullptr;
         unsigned long long st_rows = 0, st_cands = 0, st_fb = 0;
@@ -513,10 +599,20 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             {
                 const int lr = pw * 32 + lane;
                 const uint8_t st0 = sFlag[(qb * 2 + 0) * TC_PR + lr], st1 = sFlag[(qb * 2 + 1) * TC_PR + lr];
-                const uint8_t status = st0 > st1 ? st0 : st1;
+                uint8_t status = st0 > st1 ? st0 : st1;
                 const int64_t gi = pair * TC_PR + lr;
                 const unsigned long long best = sBest[lr];
                 const int bj = (int)(best & 0xFFFFFFFFu);
+                if (has_outliers && status == ROW_OK) {
+                    // the nearest outlier code is at least cexcl - |x'| away; the row keeps its regular winner only
+                    // if that bound clears the winner's exact distance with room for every rounding involved
+                    // |x'| from the row's band (sBand, written when the row was staged): band >= 1.01 * 2 * (C1 |x'| Cmax +
+                    // C2 Cmax^2), so the quotient below is an upper bound of |x'|, tight to a fraction of a percent
+                    const float sx = (sBand[qb * TC_PR + lr] * (1.f / 1.01f) - outl_c2) * outl_inv;
+                    const float gap = cexcl - 1.001f * sx;
+                    const float lim = gap > 0.f ? 0.98f * gap * gap : 0.f;
+                    if (!(__uint_as_float((unsigned int)(best >> 32)) < lim)) status = ROW_FALLBACK;
+                }
                 if (status == ROW_OK) {
                     st_rows++;
                     if (p.out_idx) p.out_idx[gi] = bj;
@@ -1022,6 +1118,8 @@ int launch_assign_tc(const float *x, const float *w, const int64_t *rows, int64_
     unsigned int *fb = (unsigned int *)(base + l.off_fb);
 
     C3VQ_CUDA(cudaMemsetAsync(hdr, 0, sizeof(TcHeader), s));
+    k_tc_prep_hist<<<(k + 127) / 128, 256, 0, s>>>(codebook, k, d, x, rows, n, hdr);
+    C3VQ_LAUNCH_CHECK("k_tc_prep_hist");
     k_tc_prep_mean<<<(k + 127) / 128, 256, 0, s>>>(codebook, k, d, hdr);
     C3VQ_LAUNCH_CHECK("k_tc_prep_mean");
     k_tc_prep_image<<<(l.k_pad + 127) / 128, 128, 0, s>>>(codebook, k, l.k_pad, d, l.dp, l.nc, l.dpc, l.bn, hdr, mu,

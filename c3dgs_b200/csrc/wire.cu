@@ -176,18 +176,33 @@ k_build_cov(const float *__restrict__ scaling, const float *__restrict__ rotatio
         if (activate) {
             // scaling_activation = normalize(relu(s)), rotation_activation = normalize(q)   (gaussian_model.py:66, :77)
             s0 = fmaxf(s0, 0.0f), s1 = fmaxf(s1, 0.0f), s2 = fmaxf(s2, 0.0f);
-            const float sn = fmaxf(sqrtf(s0 * s0 + s1 * s1 + s2 * s2), 1e-12f);
+            const float sn = fmaxf(sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(s0, s0), __fmul_rn(s1, s1)), __fmul_rn(s2, s2))), 1e-12f);
             s0 = s0 / sn, s1 = s1 / sn, s2 = s2 / sn;
-            const float qn = fmaxf(sqrtf(qr * qr + qx * qx + qy * qy + qz * qz), 1e-12f);
+            const float qn = fmaxf(sqrtf(__fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(qr, qr), __fmul_rn(qx, qx)), __fmul_rn(qy, qy)),
+                                                   __fmul_rn(qz, qz))), 1e-12f);
             qr = qr / qn, qx = qx / qn, qy = qy / qn, qz = qz / qn;
         }
         s0 *= modifier, s1 *= modifier, s2 *= modifier;
         // build_rotation (general_utils.py:84-107) divides by the norm once more
-        const float nrm = sqrtf(qr * qr + qx * qx + qy * qy + qz * qz);
+        const float nrm = sqrtf(__fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(qr, qr), __fmul_rn(qx, qx)), __fmul_rn(qy, qy)),
+                                          __fmul_rn(qz, qz)));
         qr = qr / nrm, qx = qx / nrm, qy = qy / nrm, qz = qz / nrm;
-        const float r00 = 1.f - 2.f * (qy * qy + qz * qz), r01 = 2.f * (qx * qy - qr * qz), r02 = 2.f * (qx * qz + qr * qy);
-        const float r10 = 2.f * (qx * qy + qr * qz), r11 = 1.f - 2.f * (qx * qx + qz * qz), r12 = 2.f * (qy * qz - qr * qx);
-        const float r20 = 2.f * (qx * qz - qr * qy), r21 = 2.f * (qy * qz + qr * qx), r22 = 1.f - 2.f * (qx * qx + qy * qy);
+        // every product / sum rounded on its own, as the reference's elementwise torch ops do (no fma contraction)
+#define MUL(a, b) __fmul_rn(a, b)
+#define ADD(a, b) __fadd_rn(a, b)
+#define SUB(a, b) __fsub_rn(a, b)
+        const float r00 = SUB(1.f, MUL(2.f, ADD(MUL(qy, qy), MUL(qz, qz))));
+        const float r01 = MUL(2.f, SUB(MUL(qx, qy), MUL(qr, qz)));
+        const float r02 = MUL(2.f, ADD(MUL(qx, qz), MUL(qr, qy)));
+        const float r10 = MUL(2.f, ADD(MUL(qx, qy), MUL(qr, qz)));
+        const float r11 = SUB(1.f, MUL(2.f, ADD(MUL(qx, qx), MUL(qz, qz))));
+        const float r12 = MUL(2.f, SUB(MUL(qy, qz), MUL(qr, qx)));
+        const float r20 = MUL(2.f, SUB(MUL(qx, qz), MUL(qr, qy)));
+        const float r21 = MUL(2.f, ADD(MUL(qy, qz), MUL(qr, qx)));
+        const float r22 = SUB(1.f, MUL(2.f, ADD(MUL(qx, qx), MUL(qy, qy))));
+#undef MUL
+#undef ADD
+#undef SUB
         // L = R diag(s); cov = L L^T, upper triangle (strip_symmetric)
         const float l00 = r00 * s0, l01 = r01 * s1, l02 = r02 * s2;
         const float l10 = r10 * s0, l11 = r11 * s1, l12 = r12 * s2;

@@ -8,7 +8,6 @@ CPU or torch fallback for it.
 """
 from __future__ import annotations
 
-import gc
 import time
 from typing import Optional, Tuple
 
@@ -120,8 +119,9 @@ def vq_features(
         events[slot] = ev
         # vq.py:70-77: gather + update (+ trace normalise), one fused call
         vq_model.update_indexed(features, importance_n, batch, scale_normalize=scale_normalize)
-    gc.collect()
-    torch.cuda.empty_cache()
+    # vq.py:79-80 runs gc.collect() + torch.cuda.empty_cache() here to make room for the three [N, D] temporaries
+    # of its update; this path has none (the kernels read rows in place), and returning the allocator's blocks to the
+    # driver costs more than the final assignment, so the cache is left alone.
 
     start = time.time()
     vq_indices = vq_model.assign(features)                                           # vq.py:82

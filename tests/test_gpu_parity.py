@@ -536,3 +536,53 @@ def test_full_size_properties(L, d):
     q = L.gather(cb, idx_tc[:1_000_000])
     _, idx_q = L.assign(q, cb, exact=False)
     assert torch.equal(cb[idx_q], q)
+
+
+# ---------------------------------------------------------------- outlier codewords ----------------
+@pytest.mark.parametrize("d", [6, 45, 48])
+def test_assign_outlier_codewords_stay_exact_and_off_the_fallback(L, oracle, d):
+    """The trace normalisation of the shape codebook (vq.py:76-77) turns unused codewords into far outliers (their
+    random initial trace can be ~0).  They must not widen every row's error band: results stay bit-exact, and only the
+    rows that are themselves far out may take the exact scan."""
+    n, k = 20_000, 512
+    x, _, cb = _synth(n, d, k, seed=77 + d)
+    g = torch.Generator().manual_seed(d)
+    cb[5] *= 3.0e3
+    cb[100] *= 1.0e6
+    cb[101] = cb[101] * 1.0e19
+    cb[300] = -cb[300] * 4.0e4
+    cb[301, 0] = 3.0e38
+    cb[400] = float("nan")
+    far = torch.randint(0, n, (40,), generator=g)
+    x[far[:20]] = cb[5] + 0.5 * torch.randn(20, d, generator=g)           # rows whose nearest code IS an outlier
+    x[far[20:]] = cb[300] * (1 + 1e-3 * torch.randn(20, 1, generator=g))
+    dist_o, idx_o = oracle.assign(x.numpy(), cb.numpy())
+    assert (idx_o[far.numpy()[:20]] == 5).all()
+    dist, idx = L.assign(x.to(DEV), cb.to(DEV), exact=False)
+    rows, cands, fb = L.assign_stats(DEV)
+    assert np.array_equal(idx.cpu().numpy(), idx_o)
+    assert np.array_equal(dist.cpu().numpy().view(np.uint32), dist_o.view(np.uint32))
+    assert rows == n and fb <= 200, f"{fb} of {n} rows took the exact scan"
+
+
+def test_trace_normalised_shape_codebook_keeps_the_tensor_core_path(L, oracle):
+    """vq_features(..., scale_normalize=True) on covariance rows: after the first step the codebook holds dead codewords
+    divided by an arbitrary trace; the mini-batch steps must keep screening on the tensor cores."""
+    n, k, b = 200_000, 4096, 65_536
+    g = torch.Generator().manual_seed(9)
+    s = torch.nn.functional.normalize(torch.rand(n, 3, generator=g) + 0.05)
+    r = torch.randn(n, 4, generator=g)
+    cov = L.build_covariance(s.to(DEV), r.to(DEV))
+    w = (torch.rand(n, generator=g) ** 4).to(DEV)
+    from c3dgs_b200.vq import VectorQuantize
+    m = VectorQuantize(6, k, 0.8).to(DEV)
+    amin, amax = cov.aminmax()
+    m.codebook.data = (torch.rand(k, 6, generator=g).to(DEV) * (amax - amin) + amin)
+    for step in range(4):
+        batch = torch.randint(0, n, (b,), generator=g).to(DEV)
+        cb_before = m.codebook.data.clone()
+        dist = m.update_indexed(cov, w, batch, scale_normalize=True, return_dist=True)
+        rows, cands, fb = L.assign_stats(DEV)
+        assert rows == b and fb <= b // 20, f"step {step}: {fb} of {b} rows took the exact scan"
+        dist_o, _ = oracle.assign(cov[batch].cpu().numpy(), cb_before.cpu().numpy())
+        assert np.array_equal(dist.cpu().numpy().view(np.uint32), dist_o.view(np.uint32))
