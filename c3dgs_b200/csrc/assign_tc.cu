@@ -124,7 +124,7 @@ struct TcParams {
 // every code of every row inside the band.  They are a fact of the reference's own pipeline: the shape codebook is
 // divided by its trace after every step (vq.py:76-77), and a codeword nobody uses keeps its random initial value, whose
 // trace can be anything, 0 included.  A code is "regular" when its squared norm lies at most one binade above the
-// larger of (the 75th percentile over the codebook, the largest |x_i|^2 among a sample of the rows) and at most 8
+// larger of (the 75th percentile over the codebook, the largest |x_i|^2 among 2 k rows (K / 2) spread over the input) and at most 8
 // binades above that percentile; live codewords are weighted means of rows and so always regular, a freshly drawn
 // uniform-box codebook has its norms within one binade of its own 75th percentile.  The other codes are kept out of
 // the screening (score 2^126, like a non-finite code) and out of mu / Cmax.  That is exact, not
@@ -134,6 +134,7 @@ struct TcParams {
 // the reference chain, of the centring or of the norms can bridge.  Rows that fail it (the ones that really live out
 // there) take the exact scan.  The percentile only decides how many rows that is.
 constexpr int TC_OUTLIER_BINADES = 8;
+constexpr int TC_PREP_CODES = 32;       // codes per block of the two reduction kernels (4 per warp: short latency chains)
 
 // prep 0: exponent histogram of |c_j|^2 over the finite codes (warp per code)
 __global__ void __launch_bounds__(256) k_tc_prep_hist(const float *__restrict__ cb, int k, int d,
@@ -143,22 +144,28 @@ __global__ void __launch_bounds__(256) k_tc_prep_hist(const float *__restrict__ 
     __shared__ unsigned int sh[256];
     sh[threadIdx.x] = 0;
     __syncthreads();
-    {   // data scale: the largest |x_i|^2 among gridDim.x * 256 rows spread evenly over the input
-        const int64_t S = (int64_t)gridDim.x * 256, si = (int64_t)blockIdx.x * 256 + threadIdx.x;
-        int bits = 0;
-        if (si < n) {
-            const int64_t i = S < n ? (int64_t)(((unsigned long long)si * (unsigned long long)n) / (unsigned long long)S) : si;
-            const float *row = x + (size_t)(rows ? rows[i] : i) * d;
-            float r = 0.f;
-            for (int c = 0; c < d; c++) r = fmaf(row[c], row[c], r);
-            if (isfinite(r)) bits = __float_as_int(r);
-        }
-        bits = __reduce_max_sync(0xffffffffu, bits);
-        if ((threadIdx.x & 31) == 0 && bits) atomicMax(&hdr->xs_max_bits, bits);
-    }
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-    const int j0 = blockIdx.x * 128;
-    for (int j = j0 + wib; j < min(k, j0 + 128); j += 8) {
+    {   // data scale: the largest |x_i|^2 among gridDim.x * 16 rows spread evenly over the input (warp per row)
+        const int64_t S = (int64_t)gridDim.x * 16;
+        int bits = 0;
+#pragma unroll
+        for (int t = 0; t < 2; t++) {
+            const int64_t si = (int64_t)blockIdx.x * 16 + wib * 2 + t;
+            if (si < n) {
+                const int64_t i = S < n ? (int64_t)(((unsigned long long)si * (unsigned long long)n) / (unsigned long long)S) : si;
+                const float *row = x + (size_t)(rows ? rows[i] : i) * d;
+                const float v0 = lane < d ? row[lane] : 0.f;
+                const float v1 = lane + 32 < d ? row[lane + 32] : 0.f;
+                float r = fmaf(v0, v0, v1 * v1);
+                for (int o = 16; o; o >>= 1) r += __shfl_xor_sync(0xffffffffu, r, o);
+                if (isfinite(r)) bits = max(bits, __float_as_int(r));
+            }
+        }
+        if (lane == 0 && bits) atomicMax(&hdr->xs_max_bits, bits);
+    }
+    const int j0 = blockIdx.x * TC_PREP_CODES;
+#pragma unroll
+    for (int j = j0 + wib; j < min(k, j0 + TC_PREP_CODES); j += 8) {
         const float *row = cb + (size_t)j * d;
         const float v0 = lane < d ? row[lane] : 0.f;
         const float v1 = lane + 32 < d ? row[lane + 32] : 0.f;
@@ -173,18 +180,21 @@ __global__ void __launch_bounds__(256) k_tc_prep_hist(const float *__restrict__ 
 // prep 1: column sums over the regular codes (for the centre mu)
 __global__ void __launch_bounds__(256) k_tc_prep_mean(const float *__restrict__ cb, int k, int d, TcHeader *hdr)
 {
-    // warp per code (lanes over columns, coalesced row reads), 128 codes per block
+    // warp per code (lanes over columns, coalesced row reads), TC_PREP_CODES codes per block
     __shared__ float ssum[72];
     __shared__ int slive;
     __shared__ int sthr;
+    __shared__ unsigned int shist[256];
     if (threadIdx.x < 72) ssum[threadIdx.x] = 0.f;
+    shist[threadIdx.x] = hdr->exp_hist[threadIdx.x];
+    __syncthreads();
     if (threadIdx.x == 0) {
         slive = 0;
         unsigned int total = 0, run = 0;
-        for (int e = 0; e < 256; e++) total += hdr->exp_hist[e];
+        for (int e = 0; e < 256; e++) total += shist[e];
         int e75 = 255;
         for (int e = 0; e < 256; e++) {
-            run += hdr->exp_hist[e];
+            run += shist[e];
             if (4ull * run >= 3ull * total) { e75 = e; break; }
         }
         const int ex = (hdr->xs_max_bits >> 23) & 0xff;
@@ -199,8 +209,9 @@ __global__ void __launch_bounds__(256) k_tc_prep_mean(const float *__restrict__ 
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     float s0 = 0.f, s1 = 0.f;
     int live = 0;
-    const int j0 = blockIdx.x * 128;
-    for (int j = j0 + wib; j < min(k, j0 + 128); j += 8) {
+    const int j0 = blockIdx.x * TC_PREP_CODES;
+#pragma unroll
+    for (int j = j0 + wib; j < min(k, j0 + TC_PREP_CODES); j += 8) {
         const float *row = cb + (size_t)j * d;
         const float v0 = lane < d ? row[lane] : 0.f;
         const float v1 = lane + 32 < d ? row[lane + 32] : 0.f;
@@ -233,7 +244,8 @@ __global__ void k_tc_prep_image(const float *__restrict__ cb, int k, int k_pad, 
     float raw2 = 0.f;
     if (j < k) {
         const float *row = cb + (size_t)j * d;
-        for (int c = 0; c < d; c++) {
+#pragma unroll 8
+        for (int c = 0; c < d; c++) {                        // unrolled: the row loads of a group issue together
             const float v = row[c];
             fin = fin && isfinite(v);
             const float m = hdr->mu_sum[c] * inv;
@@ -1118,9 +1130,9 @@ int launch_assign_tc(const float *x, const float *w, const int64_t *rows, int64_
     unsigned int *fb = (unsigned int *)(base + l.off_fb);
 
     C3VQ_CUDA(cudaMemsetAsync(hdr, 0, sizeof(TcHeader), s));
-    k_tc_prep_hist<<<(k + 127) / 128, 256, 0, s>>>(codebook, k, d, x, rows, n, hdr);
+    k_tc_prep_hist<<<(k + TC_PREP_CODES - 1) / TC_PREP_CODES, 256, 0, s>>>(codebook, k, d, x, rows, n, hdr);
     C3VQ_LAUNCH_CHECK("k_tc_prep_hist");
-    k_tc_prep_mean<<<(k + 127) / 128, 256, 0, s>>>(codebook, k, d, hdr);
+    k_tc_prep_mean<<<(k + TC_PREP_CODES - 1) / TC_PREP_CODES, 256, 0, s>>>(codebook, k, d, hdr);
     C3VQ_LAUNCH_CHECK("k_tc_prep_mean");
     k_tc_prep_image<<<(l.k_pad + 127) / 128, 128, 0, s>>>(codebook, k, l.k_pad, d, l.dp, l.nc, l.dpc, l.bn, hdr, mu,
                                                         bimg, cbp);

@@ -181,10 +181,18 @@ k_join_write(const float *__restrict__ feats, const uint8_t *__restrict__ keep, 
     const int64_t total = (int64_t)kept * d;
     float *dst = out_feats + (k + (int64_t)base) * d;
     const float *srcb = feats + (int64_t)blockIdx.x * JOIN_ROWS * d;
-    for (int64_t e = threadIdx.x; e < total; e += JOIN_ROWS) {
-        const unsigned int r = (unsigned int)(e / d);
-        const int c = (int)(e - (int64_t)r * d);
-        dst[e] = srcb[(int64_t)src_row[r] * d + c];
+    if (d <= (1 << 20)) {                                   // 32-bit index arithmetic (one division per word moved)
+        const unsigned int total32 = (unsigned int)total, d32 = (unsigned int)d;
+        for (unsigned int e = threadIdx.x; e < total32; e += JOIN_ROWS) {
+            const unsigned int r = e / d32;
+            dst[e] = srcb[src_row[r] * d32 + (e - r * d32)];
+        }
+    } else {
+        for (int64_t e = threadIdx.x; e < total; e += JOIN_ROWS) {
+            const unsigned int r = (unsigned int)(e / d);
+            const int c = (int)(e - (int64_t)r * d);
+            dst[e] = srcb[(int64_t)src_row[r] * d + c];
+        }
     }
 }
 

@@ -28,10 +28,10 @@ inline unsigned wire_grid(int64_t work_items)
 
 // ---- int8 affine quantisation --------------------------------------------------------------------------------
 // torch's CUDA kernel computes, per element, in double:  q = (int64)(nearbyint((double)x / scale) + zero_point),
-// clamped to [-128, 127].  The float quotient t = x / (float)scale is within 2^-24 |t| of the double one when the
-// scale is a float32 value (it is: FakeQuantize keeps it in a float32 tensor), so rintf(t) is the same integer
-// unless t lies within that distance of a rounding boundary; only those elements (a few per 100 k), non-finite
-// ones and non-float32 scales take the double expression itself.
+// clamped to [-128, 127].  The float product t = x * fl(1 / (float)scale) is within 2^-23 |t| of the double quotient
+// when the scale is a float32 value (it is: FakeQuantize keeps it in a float32 tensor), so rintf(t) is the same
+// integer unless t lies within that distance of a rounding boundary; only those elements (a few per 100 k),
+// non-finite ones and non-float32 scales take the double expression itself.
 __device__ __forceinline__ int quantize_slow(float x, double scale, long long zp)
 {
     long long q = (long long)(nearbyint((double)x / scale) + (double)zp);
@@ -40,13 +40,13 @@ __device__ __forceinline__ int quantize_slow(float x, double scale, long long zp
     return (int)q;
 }
 
-__device__ __forceinline__ int quantize_one(float x, float scale_f, double scale, int zp, bool fast_ok)
+__device__ __forceinline__ int quantize_one(float x, float inv_scale_f, double scale, int zp, bool fast_ok)
 {
-    const float t = __fdiv_rn(x, scale_f);
+    const float t = __fmul_rn(x, inv_scale_f);
     const float r = rintf(t);
     const float f = fabsf(t - r);                            // exact for |t| < 2^23
     const float at = fabsf(t);
-    // at < 1024 also rejects NaN/Inf; the margin is twice the quotient's rounding error
+    // at < 1024 also rejects NaN/Inf; the margin (2^-22 |t|) is twice the product's distance from the quotient
     const bool safe = fast_ok && at < 1024.0f && (0.5f - f) > at * 2.3841858e-7f;
     if (!safe) return quantize_slow(x, scale, (long long)zp);
     int q = (int)r + zp;
@@ -55,24 +55,24 @@ __device__ __forceinline__ int quantize_one(float x, float scale_f, double scale
 }
 
 __global__ void __launch_bounds__(WIRE_THREADS)
-k_quantize_i8(const float *__restrict__ x, int64_t n, float scale_f, double scale, int zp, int fast_ok,
+k_quantize_i8(const float *__restrict__ x, int64_t n, float inv_scale_f, double scale, int zp, int fast_ok,
               int8_t *__restrict__ out)
 {
     const int64_t n4 = n >> 2;
     const int64_t stride = (int64_t)gridDim.x * WIRE_THREADS;
     for (int64_t i = (int64_t)blockIdx.x * WIRE_THREADS + threadIdx.x; i < n4; i += stride) {
         const float4 v = __ldg(reinterpret_cast<const float4 *>(x) + i);
-        const int q0 = quantize_one(v.x, scale_f, scale, zp, fast_ok);
-        const int q1 = quantize_one(v.y, scale_f, scale, zp, fast_ok);
-        const int q2 = quantize_one(v.z, scale_f, scale, zp, fast_ok);
-        const int q3 = quantize_one(v.w, scale_f, scale, zp, fast_ok);
+        const int q0 = quantize_one(v.x, inv_scale_f, scale, zp, fast_ok);
+        const int q1 = quantize_one(v.y, inv_scale_f, scale, zp, fast_ok);
+        const int q2 = quantize_one(v.z, inv_scale_f, scale, zp, fast_ok);
+        const int q3 = quantize_one(v.w, inv_scale_f, scale, zp, fast_ok);
         const unsigned packed = (unsigned)(q0 & 0xff) | ((unsigned)(q1 & 0xff) << 8) | ((unsigned)(q2 & 0xff) << 16) |
                                 ((unsigned)(q3 & 0xff) << 24);
         reinterpret_cast<unsigned *>(out)[i] = packed;
     }
     // tail (n not a multiple of 4)
     const int64_t t = (n4 << 2) + (int64_t)blockIdx.x * WIRE_THREADS + threadIdx.x;
-    if (t < n) out[t] = (int8_t)quantize_one(x[t], scale_f, scale, zp, fast_ok);
+    if (t < n) out[t] = (int8_t)quantize_one(x[t], inv_scale_f, scale, zp, fast_ok);
 }
 
 __global__ void __launch_bounds__(WIRE_THREADS)
@@ -252,10 +252,18 @@ k_compact_rows(const uint32_t *__restrict__ src, const uint8_t *__restrict__ kee
     const int64_t total = (int64_t)s_kept * words;
     uint32_t *dst = out + (int64_t)block_base[blockIdx.x] * words;
     const uint32_t *srcb = src + (int64_t)blockIdx.x * COMPACT_ROWS * words;
-    for (int64_t e = threadIdx.x; e < total; e += COMPACT_ROWS) {
-        const unsigned int r = (unsigned int)(e / words);
-        const int c = (int)(e - (int64_t)r * words);
-        dst[e] = srcb[(int64_t)src_row[r] * words + c];
+    if (words <= (1 << 20)) {                               // 32-bit index arithmetic (one division per word moved)
+        const unsigned int total32 = (unsigned int)total, w32 = (unsigned int)words;
+        for (unsigned int e = threadIdx.x; e < total32; e += COMPACT_ROWS) {
+            const unsigned int r = e / w32;
+            dst[e] = srcb[src_row[r] * w32 + (e - r * w32)];
+        }
+    } else {
+        for (int64_t e = threadIdx.x; e < total; e += COMPACT_ROWS) {
+            const unsigned int r = (unsigned int)(e / words);
+            const int c = (int)(e - (int64_t)r * words);
+            dst[e] = srcb[(int64_t)src_row[r] * words + c];
+        }
     }
 }
 
@@ -265,6 +273,7 @@ int launch_quantize_i8(const float *x, int64_t n, double scale, int64_t zero_poi
 {
     if (n == 0) return C3VQ_OK;
     const float scale_f = (float)scale;
+    const float inv_scale_f = 1.0f / scale_f;
     // the fast path needs the scale to be a float32 value, the zero point a small integer and 16-byte alignment
     const int fast_ok = ((double)scale_f == scale) && zero_point >= -1024 && zero_point <= 1024;
     const int zp = (int)(zero_point < -100000 ? -100000 : (zero_point > 100000 ? 100000 : zero_point));
@@ -272,7 +281,7 @@ int launch_quantize_i8(const float *x, int64_t n, double scale, int64_t zero_poi
         set_error("zero_point=%lld out of range for int8 quantisation", (long long)zero_point);
         return C3VQ_EINVAL;
     }
-    k_quantize_i8<<<wire_grid(n / 4 + 3), WIRE_THREADS, 0, s>>>(x, n, scale_f, scale, zp, fast_ok, out);
+    k_quantize_i8<<<wire_grid(n / 4 + 3), WIRE_THREADS, 0, s>>>(x, n, inv_scale_f, scale, zp, fast_ok, out);
     C3VQ_LAUNCH_CHECK("k_quantize_i8");
     return C3VQ_OK;
 }

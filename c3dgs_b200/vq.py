@@ -8,6 +8,8 @@ CPU or torch fallback for it.
 """
 from __future__ import annotations
 
+import queue
+import threading
 import time
 from typing import Optional, Tuple
 
@@ -90,7 +92,7 @@ def vq_features(
 
     Same random stream as the reference: uniform_init draws from the device generator,
     every step draws `torch.randint(low=0, high=N, size=[vq_chunk])` from the CPU generator
-    (with replacement).  The per-step `.mean().item()` of the reference only feeds a list
+    (with replacement; the draws are made in step order on one helper thread, ahead of the launches).  The per-step `.mean().item()` of the reference only feeds a list
     that is never read (vq.py:64,71-72), so no host sync is made here.
     """
     if not features.is_cuda:
@@ -106,19 +108,53 @@ def vq_features(
     if not silent:
         from tqdm import tqdm
         diap = tqdm(diap)
-    pinned = [torch.empty(vq_chunk, dtype=torch.int64).pin_memory() for _ in range(2)]
-    events = [None, None]
-    for step in diap:
-        slot = step & 1
-        if events[slot] is not None:
-            events[slot].synchronize()          # the H2D copy that last used this pinned buffer is done
-        torch.randint(low=0, high=features.shape[0], size=[vq_chunk], out=pinned[slot])   # vq.py:69
-        batch = pinned[slot].to(features.device, non_blocking=True)
-        ev = torch.cuda.Event()
-        ev.record(torch.cuda.current_stream(features.device))
-        events[slot] = ev
-        # vq.py:70-77: gather + update (+ trace normalise), one fused call
-        vq_model.update_indexed(features, importance_n, batch, scale_normalize=scale_normalize)
+    # vq.py:69 draws every batch with the CPU generator (0.8 ms per 2^18 indices, more than the GPU needs for the
+    # step), so the draws run ahead on a helper thread — one thread, in step order, hence the same random stream —
+    # into a small ring of pinned buffers while this thread uploads and launches.
+    ring = 4
+    pinned = [torch.empty(vq_chunk, dtype=torch.int64).pin_memory() for _ in range(ring)]
+    uploaded = [None] * ring                    # event: the H2D copy that last read pinned[slot] has finished
+    drawn: "queue.Queue" = queue.Queue(maxsize=ring - 1)
+    free: "queue.Queue" = queue.Queue()
+    for slot in range(ring):
+        free.put(slot)
+    n_rows = features.shape[0]
+
+    def draw_batches():
+        try:
+            for _ in range(steps):
+                slot = free.get()
+                if slot is None:
+                    return
+                if uploaded[slot] is not None:
+                    uploaded[slot].synchronize()
+                torch.randint(low=0, high=n_rows, size=[vq_chunk], out=pinned[slot])       # vq.py:69
+                drawn.put(slot)
+        except BaseException as exc:            # surface the failure in the consumer instead of hanging it
+            drawn.put(exc)
+
+    drawer = threading.Thread(target=draw_batches, name="c3vq-batch-draw", daemon=True)
+    drawer.start()
+    try:
+        for step in diap:
+            slot = drawn.get()
+            if isinstance(slot, BaseException):
+                raise slot
+            batch = pinned[slot].to(features.device, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(features.device))
+            uploaded[slot] = ev
+            free.put(slot)
+            # vq.py:70-77: gather + update (+ trace normalise), one fused call
+            vq_model.update_indexed(features, importance_n, batch, scale_normalize=scale_normalize)
+    finally:
+        free.put(None)                          # normal end: the drawer has left already; after an error: stop it
+        while drawer.is_alive():
+            try:
+                drawn.get_nowait()              # it may be blocked handing over a batch nobody will take
+            except queue.Empty:
+                pass
+            drawer.join(timeout=0.01)
     # vq.py:79-80 runs gc.collect() + torch.cuda.empty_cache() here to make room for the three [N, D] temporaries
     # of its update; this path has none (the kernels read rows in place), and returning the allocator's blocks to the
     # driver costs more than the final assignment, so the cache is left alone.

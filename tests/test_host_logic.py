@@ -47,3 +47,71 @@ def test_settings_record_and_cpu_inputs_raise():
         scene.get_normalized_covariance()
     with pytest.raises(RuntimeError, match="CUDA"):
         scene.save_npz("/tmp/never_written.npz")
+
+
+class _RecordingModel:
+    """Stand-in for VectorQuantize that records the batches vq_features hands to the kernels."""
+    fail_at = None
+
+    def __init__(self, *a, **k):
+        self.batches = []
+        self.codebook = torch.nn.Parameter(torch.zeros(4, 3))
+
+    def to(self, **k):
+        return self
+
+    def uniform_init(self, x):
+        pass
+
+    def update_indexed(self, features, importance, batch, scale_normalize=False):
+        if self.fail_at is not None and len(self.batches) == self.fail_at:
+            raise ValueError("boom")
+        self.batches.append(batch)
+
+    def assign(self, features):
+        return torch.zeros(features.shape[0], dtype=torch.int64)
+
+
+def _host_only():
+    """vq_features with every CUDA call stubbed: what is left is the batch-draw thread and its ring of buffers."""
+    import contextlib
+    import unittest.mock as um
+    stack = contextlib.ExitStack()
+    stack.enter_context(um.patch.object(torch.Tensor, "is_cuda", new=property(lambda self: True)))
+    stack.enter_context(um.patch.object(torch.Tensor, "pin_memory", lambda self: self))
+    stack.enter_context(um.patch.object(torch.Tensor, "to", lambda self, *a, **k: self.clone()))
+    for name in ("torch.cuda.Event", "torch.cuda.current_stream", "torch.cuda.synchronize"):
+        stack.enter_context(um.patch(name))
+    return stack
+
+
+def test_vq_features_batch_draws_keep_the_reference_random_stream(monkeypatch):
+    """The draws of vq.py:69 run ahead on a helper thread; the batches must still be the sequence a plain loop of
+    torch.randint calls produces from the same CPU seed."""
+    from c3dgs_b200 import vq
+    made = []
+    monkeypatch.setattr(vq, "VectorQuantize", lambda *a, **k: made.append(_RecordingModel()) or made[-1])
+    x, w = torch.randn(1000, 3), torch.rand(1000)
+    for steps in (0, 1, 3, 250):
+        made.clear()
+        torch.manual_seed(5)
+        with _host_only():
+            vq.vq_features(x, w, 4, vq_chunk=64, steps=steps, silent=True)
+        torch.manual_seed(5)
+        want = [torch.randint(low=0, high=1000, size=[64]) for _ in range(steps)]
+        assert len(made[0].batches) == steps
+        assert all(torch.equal(a, b) for a, b in zip(made[0].batches, want))
+
+
+@pytest.mark.timeout(60)
+def test_vq_features_error_in_a_step_does_not_hang_the_draw_thread(monkeypatch):
+    import threading
+    from c3dgs_b200 import vq
+
+    class Failing(_RecordingModel):
+        fail_at = 3
+
+    monkeypatch.setattr(vq, "VectorQuantize", lambda *a, **k: Failing())
+    with _host_only(), pytest.raises(ValueError, match="boom"):
+        vq.vq_features(torch.randn(100, 3), torch.rand(100), 4, vq_chunk=16, steps=200, silent=True)
+    assert not [t for t in threading.enumerate() if t.name == "c3vq-batch-draw"]
