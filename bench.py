@@ -507,6 +507,28 @@ def main():
             "decoded_bytes": int(sdec.numel() + rdec.numel() + fdec.numel()) * 4, "int8_bytes": int(qbytes),
             "note": "host wall clock, single run, includes workspace allocation and the host syncs the data-dependent "
                     "output sizes need"}
+        # the indexed rasteriser's per-Gaussian preprocess on the compressed scene just built
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        from preprocess_scene import camera
+        cam = camera(width=1297, height=840, fovx=0.9)
+        camt = {k_: torch.from_numpy(v_).to(dev) for k_, v_ in cam.items() if hasattr(v_, "dtype")}
+        table = torch.cat((scene._features_dc, scene._features_rest), 1).contiguous()
+        npre = scene._xyz.shape[0]
+        pre = {}
+
+        def run_pre():
+            pre.update(ops2.preprocess_indexed(scene._xyz, scene._scaling, torch.exp(scene._scaling_factor), scene._rotation,
+                                               torch.sigmoid(scene._opacity), table, scene._feature_indices,
+                                               scene._gaussian_indices, camt["viewmatrix"], camt["projmatrix"],
+                                               camt["cam_pos"], cam["width"], cam["height"], cam["tan_fovx"],
+                                               cam["tan_fovy"]))
+        ms = timed(run_pre)
+        nvis = int((pre["radii"] > 0).sum())
+        pbytes = npre * 36 + nvis * (52 + 192 + 51)
+        extras["preprocess_indexed"] = {"gaussians": npre, "visible": nvis, "ms": ms, "gbs": pbytes / ms * 1e-6,
+                                        "frac_of_hbm_peak": pbytes / ms * 1e-6 / pk["hbm_gbs"],
+                                        "note": "incl. the activations (exp, sigmoid: torch) and zero-filling the outputs"}
+        del table, pre
         del scene, cimp, gimp, sdec, rdec, fdec, half, i32
 
     cpu = None

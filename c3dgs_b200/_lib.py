@@ -75,6 +75,10 @@ SIGNATURES = {
     "c3vq_convert": (_c_int, [_c_int, _c_vp, _c_i64, _c_vp, _c_vp]),
     "c3vq_build_covariance": (_c_int, [_c_vp, _c_vp, _c_i64, ctypes.c_float, _c_int, _c_vp, _c_vp]),
     "c3vq_compact_rows": (_c_int, [_c_vp, _c_vp, _c_i64, _c_i64, _c_vp, _c_vp, _c_vp]),
+    "c3vq_preprocess_indexed": (_c_int, [_c_i64, _c_int, _c_int, _c_vp, _c_vp, _c_vp, ctypes.c_float, _c_vp, _c_vp, _c_vp,
+                                         _c_vp, _c_vp, _c_vp, _c_int, _c_int, ctypes.c_float, ctypes.c_float,
+                                         ctypes.c_float, ctypes.c_float, _c_int, _c_vp, _c_vp, _c_int, _c_vp, _c_vp,
+                                         _c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_vp]),
     "c3vq_gather_rows": (_c_int, [_c_vp, _c_vp, _c_vp, _c_i64, _c_int, _c_vp, _c_vp, _c_vp]),
     "c3vq_debug_scores": (_c_int, [_c_vp, _c_i64, _c_int, _c_vp, _c_int, _c_vp, _c_vp, _c_vp, _c_vp, _c_sz, _c_vp]),
     "c3vq_assign_stats": (_c_int, [_c_vp, ctypes.POINTER(_c_i64), _c_vp]),
@@ -518,6 +522,58 @@ def compact(tensors, keep_mask: torch.Tensor):
                 raise _err(rc)
             outs.append(out)
     return outs
+
+
+def preprocess_indexed(means3d, scales, scale_factors, rotations, opacities, shs, sh_indices, g_indices, viewmatrix,
+                       projmatrix, cam_pos, width: int, height: int, tan_fovx: float, tan_fovy: float,
+                       sh_degree: int = 3, scale_modifier: float = 1.0, prefiltered: bool = False,
+                       clamp_color: bool = True):
+    """FORWARD::preprocess_indexed of the reference's indexed rasteriser (cuda_rasterizer/forward_indexed.cu:166-272):
+    returns a dict with radii [P] int32, xy [P,2], depths [P], cov3d [P,6], rgb [P,3], conic_opacity [P,4],
+    tiles_touched [P] int32 (bit pattern of the reference's uint32) and clamped [P,3] bool.  The kernel writes every
+    row: culled Gaussians read as zeros (the reference leaves them untouched).  viewmatrix / projmatrix: 4x4 CUDA tensors whose flat storage is the
+    column-major matrix, exactly what the reference's Python side passes.  c3vq_preprocess_indexed."""
+    p = means3d.size(0)
+    for t, name, shape in ((means3d, "means3d", (p, 3)), (scale_factors, "scale_factors", None),
+                           (opacities, "opacities", None), (scales, "scales", (scales.size(0), 3)),
+                           (rotations, "rotations", (rotations.size(0), 4)), (viewmatrix, "viewmatrix", None),
+                           (projmatrix, "projmatrix", None), (cam_pos, "cam_pos", None), (shs, "shs", None)):
+        _check(t, torch.float32, name)
+        if shape is not None and tuple(t.shape) != shape:
+            raise RuntimeError(f"{name} must be {shape}, got {tuple(t.shape)}")
+    _check(sh_indices, torch.int64, "sh_indices", 1)
+    _check(g_indices, torch.int64, "g_indices", 1)
+    if scale_factors.numel() != p or opacities.numel() != p or sh_indices.numel() != p or g_indices.numel() != p:
+        raise RuntimeError("scale_factors, opacities, sh_indices and g_indices need one entry per Gaussian")
+    if viewmatrix.numel() != 16 or projmatrix.numel() != 16 or cam_pos.numel() != 3:
+        raise RuntimeError("viewmatrix / projmatrix must hold 16 values and cam_pos 3")
+    if shs.dim() != 3 or shs.size(2) != 3:
+        raise RuntimeError(f"shs must be [F, coefficients, 3], got {tuple(shs.shape)}")
+    means3d, scales, scale_factors, rotations = (means3d.contiguous(), scales.contiguous(), scale_factors.contiguous(),
+                                                 _aligned(rotations))
+    opacities, shs, sh_indices, g_indices = opacities.contiguous(), shs.contiguous(), sh_indices.contiguous(), g_indices.contiguous()
+    viewmatrix, projmatrix, cam_pos = viewmatrix.contiguous(), projmatrix.contiguous(), cam_pos.contiguous()
+    dev = means3d.device
+    import numpy as np
+    # rasterizer_impl.cu:219-220: focal lengths from the field of view, in float32
+    focal_y = float(np.float32(height) / (np.float32(2.0) * np.float32(tan_fovy)))
+    focal_x = float(np.float32(width) / (np.float32(2.0) * np.float32(tan_fovx)))
+    with torch.cuda.device(dev):
+        out = {"radii": torch.empty(p, dtype=torch.int32, device=dev), "xy": torch.empty(p, 2, device=dev),
+               "depths": torch.empty(p, device=dev), "cov3d": torch.empty(p, 6, device=dev),
+               "rgb": torch.empty(p, 3, device=dev), "conic_opacity": torch.empty(p, 4, device=dev),
+               "tiles_touched": torch.empty(p, dtype=torch.int32, device=dev),
+               "clamped": torch.empty(p, 3, dtype=torch.bool, device=dev)}
+        rc = load().c3vq_preprocess_indexed(
+            p, int(sh_degree), shs.size(1), _ptr(means3d), _ptr(scales), _ptr(scale_factors), float(scale_modifier),
+            _ptr(rotations), _ptr(opacities), _ptr(shs), _ptr(viewmatrix), _ptr(projmatrix), _ptr(cam_pos),
+            int(width), int(height), focal_x, focal_y, float(tan_fovx), float(tan_fovy), 1 if prefiltered else 0,
+            _ptr(sh_indices), _ptr(g_indices), 1 if clamp_color else 0, _ptr(out["radii"]), _ptr(out["xy"]),
+            _ptr(out["depths"]), _ptr(out["cov3d"]), _ptr(out["rgb"]), _ptr(out["conic_opacity"]),
+            _ptr(out["tiles_touched"]), _ptr(out["clamped"]), _stream(means3d))
+    if rc:
+        raise _err(rc)
+    return out
 
 
 def scatter_add(grad_out: torch.Tensor, idx: torch.Tensor, table_rows: int) -> torch.Tensor:

@@ -316,6 +316,36 @@ int c3vq_compact_rows(const void *src, const uint8_t *keep_mask, int64_t n, int6
     return launch_compact_rows(src, keep_mask, n, (int)(row_bytes / 4), out, ws, (cudaStream_t)stream);
 }
 
+int c3vq_preprocess_indexed(int64_t p, int sh_degree, int sh_coeffs, const float *means3d, const float *scales,
+                            const float *scale_factors, float scale_modifier, const float *rotations,
+                            const float *opacities, const float *shs, const float *viewmatrix, const float *projmatrix,
+                            const float *cam_pos, int width, int height, float focal_x, float focal_y, float tan_fovx,
+                            float tan_fovy, int prefiltered, const int64_t *sh_indices, const int64_t *g_indices,
+                            int clamp_color, int32_t *out_radii, float *out_xy, float *out_depths, float *out_cov3d,
+                            float *out_rgb, float *out_conic_opacity, uint32_t *out_tiles_touched, uint8_t *out_clamped,
+                            c3vq_stream_t stream)
+{
+    C3VQ_CHECK_ARG(p >= 0, "p=%lld is negative", (long long)p);
+    C3VQ_CHECK_ARG(sh_degree >= 0 && sh_degree <= 3 && sh_coeffs >= (sh_degree + 1) * (sh_degree + 1),
+                   "sh_degree=%d needs %d coefficients per row, got %d", sh_degree, (sh_degree + 1) * (sh_degree + 1),
+                   sh_coeffs);
+    C3VQ_CHECK_ARG(width > 0 && height > 0, "bad image size %d x %d", width, height);
+    C3VQ_CHECK_ARG(p == 0 || (means3d && scales && scale_factors && rotations && opacities && shs && viewmatrix &&
+                              projmatrix && cam_pos && sh_indices && g_indices),
+                   "null input pointer");
+    C3VQ_CHECK_ARG(p == 0 || (out_radii && out_xy && out_depths && out_cov3d && out_rgb && out_conic_opacity &&
+                              out_tiles_touched && out_clamped),
+                   "null output pointer");
+    C3VQ_CHECK_ARG(((uintptr_t)rotations & 15) == 0 && ((uintptr_t)out_conic_opacity & 15) == 0 &&
+                       ((uintptr_t)out_xy & 7) == 0,
+                   "rotations / out_conic_opacity must be 16-byte and out_xy 8-byte aligned");
+    return launch_preprocess_indexed(p, sh_degree, sh_coeffs, means3d, scales, scale_factors, scale_modifier, rotations,
+                                     opacities, shs, viewmatrix, projmatrix, cam_pos, width, height, focal_x, focal_y,
+                                     tan_fovx, tan_fovy, prefiltered, sh_indices, g_indices, clamp_color, out_radii,
+                                     out_xy, out_depths, out_cov3d, out_rgb, out_conic_opacity, out_tiles_touched,
+                                     out_clamped, (cudaStream_t)stream);
+}
+
 int c3vq_gather_rows(const float *x, const float *w, const int64_t *rows, int64_t n, int d, float *out_x,
                      float *out_w, c3vq_stream_t stream)
 {

@@ -90,6 +90,14 @@ int launch_build_cov(const float *scaling, const float *rotation, int64_t n, flo
 int launch_compact_rows(const void *src, const uint8_t *keep, int64_t n, int words, void *out, const void *ws,
                         cudaStream_t s);
 
+// indexed rasteriser preprocess (preprocess.cu)
+int launch_preprocess_indexed(int64_t P, int deg, int M, const float *means, const float *scales, const float *factors,
+                              float scale_modifier, const float *rots, const float *opac, const float *shs,
+                              const float *view, const float *proj, const float *campos, int W, int H, float focal_x,
+                              float focal_y, float tan_fovx, float tan_fovy, int prefiltered, const int64_t *sh_idx,
+                              const int64_t *g_idx, int clamp_color, int *radii, float *xy, float *depths, float *cov3d,
+                              float *rgb, float *conic, unsigned int *tiles, uint8_t *clamped, cudaStream_t s);
+
 // tensor-core assignment (assign_tc.cu)
 size_t tc_workspace_bytes(int64_t n, int d, int k);
 int launch_assign_tc(const float *x, const float *w, const int64_t *rows, int64_t n, int d, const float *codebook,

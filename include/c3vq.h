@@ -218,6 +218,31 @@ int c3vq_build_covariance(const float *scaling /* [n,3] */, const float *rotatio
 int c3vq_compact_rows(const void *src, const uint8_t *keep_mask, int64_t n, int64_t row_bytes, void *out,
                       const void *ws, c3vq_stream_t stream);
 
+/*
+ * Per-Gaussian preprocess of the indexed rasteriser — the consumer that decodes the codebooks inside the kernel
+ * (submodules/diff-gaussian-rasterization/cuda_rasterizer/forward_indexed.cu:166-272, FORWARD::preprocess_indexed
+ * declared at forward.h:53-81; helpers forward_indexed.cu:20-159 and auxiliary.h:42-152).  Same arguments, in the
+ * reference's order, minus the two "precomputed" inputs the indexed path passes as null:
+ *   scales [G,3] / rotations [G,4] are the shape table read through g_indices [P]; shs [F, sh_coeffs, 3] is the colour
+ *   table read through sh_indices [P]; scale_factors, opacities, means3d are per Gaussian; viewmatrix / projmatrix
+ *   (column-major 4x4) and cam_pos are device arrays like in the reference.
+ * Outputs as in the reference: radii (0 = culled), screen position, view depth, world covariance (6), rgb, conic +
+ * opacity, number of 16 x 16 tiles covered, per-channel clamp flags.  Every row of every output is written: a Gaussian
+ * culled at the near plane (depth <= 0.01) gets zeros everywhere, one with a singular 2D covariance or no covered tile
+ * gets its cov3d and zeros elsewhere (the reference leaves those rows untouched).
+ * float32 throughout; agrees with the reference kernel to rounding (sum order inside the 3x3 products), see
+ * tests/test_gpu_preprocess.py for the stated tolerances.
+ */
+int c3vq_preprocess_indexed(int64_t p, int sh_degree, int sh_coeffs, const float *means3d, const float *scales,
+                            const float *scale_factors, float scale_modifier, const float *rotations,
+                            const float *opacities, const float *shs, const float *viewmatrix, const float *projmatrix,
+                            const float *cam_pos, int width, int height, float focal_x, float focal_y, float tan_fovx,
+                            float tan_fovy, int prefiltered, const int64_t *sh_indices, const int64_t *g_indices,
+                            int clamp_color, int32_t *out_radii, float *out_xy /* [P,2] */, float *out_depths,
+                            float *out_cov3d /* [P,6] */, float *out_rgb /* [P,3] */,
+                            float *out_conic_opacity /* [P,4] */, uint32_t *out_tiles_touched,
+                            uint8_t *out_clamped /* [P,3] */, c3vq_stream_t stream);
+
 /* Mini-batch row gather: out_x[i,:] = x[rows[i],:], out_w[i] = w[rows[i]] (w/out_w may be null). */
 int c3vq_gather_rows(const float *x, const float *w, const int64_t *rows, int64_t n, int d,
                      float *out_x, float *out_w, c3vq_stream_t stream);

@@ -355,3 +355,129 @@ def normalized_covariance(scaling, rotation, scaling_modifier=1.0, activate=Fals
 def mask_rows(t, mask):
     """t[mask] of GaussianModel.mask_splats (scene/gaussian_model.py:1027-1046): stable boolean-mask compaction."""
     return np.asarray(t)[np.asarray(mask, bool)]
+
+
+# ---- §8(f) rank 4: per-Gaussian preprocess of the indexed rasteriser ---------------------------------------------------
+_SH_C0 = np.float32(0.28209479177387814)
+_SH_C1 = np.float32(0.4886025119029199)
+_SH_C2 = np.array([1.0925484305920792, -1.0925484305920792, 0.31539156525252005, -1.0925484305920792,
+                   0.5462742152960396], np.float32)
+_SH_C3 = np.array([-0.5900435899266435, 2.890611442640554, -0.4570457994644658, 0.3731763325901154,
+                   -0.4570457994644658, 1.445305721320277, -0.5900435899266435], np.float32)
+
+
+def preprocess_indexed(means3d, scales, scale_factors, rotations, opacities, shs, sh_indices, g_indices, viewmatrix,
+                       projmatrix, cam_pos, width, height, tan_fovx, tan_fovy, sh_degree=3, scale_modifier=1.0,
+                       clamp_color=True):
+    """preprocess_indexedCUDA restated in numpy float32 (submodules/diff-gaussian-rasterization/cuda_rasterizer/
+    forward_indexed.cu:166-272; computeColorFromSH_indexed :20-77, computeCov2D_indexed :79-121, computeCov3D_indexed
+    :123-159; in_frustum / ndc2Pix / getRect / transformPoint auxiliary.h:42-152; focal lengths rasterizer_impl.cu:
+    219-220).  viewmatrix / projmatrix: 16 floats, column-major.  Returns the kernel's outputs (zeros where the
+    kernel returns early)."""
+    f = np.float32
+    P = len(means3d)
+    m = np.asarray(means3d, f)
+    v = np.asarray(viewmatrix, f).reshape(16)
+    pj = np.asarray(projmatrix, f).reshape(16)
+    cam = np.asarray(cam_pos, f).reshape(3)
+    focal_y = f(height) / (f(2.0) * f(tan_fovy))
+    focal_x = f(width) / (f(2.0) * f(tan_fovx))
+    px, py, pz = m[:, 0], m[:, 1], m[:, 2]
+    out = {"radii": np.zeros(P, np.int32), "xy": np.zeros((P, 2), f), "depths": np.zeros(P, f),
+           "cov3d": np.zeros((P, 6), f), "rgb": np.zeros((P, 3), f), "conic_opacity": np.zeros((P, 4), f),
+           "tiles_touched": np.zeros(P, np.uint32), "clamped": np.zeros((P, 3), bool)}
+    with np.errstate(all="ignore"):
+        vx = v[0] * px + v[4] * py + v[8] * pz + v[12]
+        vy = v[1] * px + v[5] * py + v[9] * pz + v[13]
+        vz = v[2] * px + v[6] * py + v[10] * pz + v[14]
+        alive = ~(vz <= f(0.01))                                                    # auxiliary.h:139-152
+        hx = pj[0] * px + pj[4] * py + pj[8] * pz + pj[12]
+        hy = pj[1] * px + pj[5] * py + pj[9] * pz + pj[13]
+        hw = pj[3] * px + pj[7] * py + pj[11] * pz + pj[15]
+        p_w = f(1.0) / (hw + f(0.0000001))
+        projx, projy = hx * p_w, hy * p_w
+        # computeCov3D_indexed: quaternion used as stored, scale = factor * modifier * scaling row
+        g = np.asarray(g_indices, np.int64)
+        mod = np.asarray(scale_factors, f).reshape(P) * f(scale_modifier)
+        sc = np.asarray(scales, f)[g] * mod[:, None]
+        q = np.asarray(rotations, f)[g]
+        r, x, y, z = q[:, 0], q[:, 1], q[:, 2], q[:, 3]
+        one, two = f(1), f(2)
+        R = np.empty((P, 3, 3), f)
+        R[:, 0, 0] = one - two * (y * y + z * z); R[:, 0, 1] = two * (x * y - r * z); R[:, 0, 2] = two * (x * z + r * y)
+        R[:, 1, 0] = two * (x * y + r * z); R[:, 1, 1] = one - two * (x * x + z * z); R[:, 1, 2] = two * (y * z - r * x)
+        R[:, 2, 0] = two * (x * z - r * y); R[:, 2, 1] = two * (y * z + r * x); R[:, 2, 2] = one - two * (x * x + y * y)
+        Mm = sc[:, :, None] * np.transpose(R, (0, 2, 1))                             # M[k][j] = s_k R[j][k]
+        Sig = np.zeros((P, 3, 3), f)
+        for k in range(3):
+            Sig = Sig + Mm[:, k, :, None] * Mm[:, k, None, :]
+        cov3 = np.stack([Sig[:, 0, 0], Sig[:, 0, 1], Sig[:, 0, 2], Sig[:, 1, 1], Sig[:, 1, 2], Sig[:, 2, 2]], 1)
+        # computeCov2D_indexed
+        limx, limy = f(1.3) * f(tan_fovx), f(1.3) * f(tan_fovy)
+        tz = vz
+        tx = np.minimum(limx, np.maximum(-limx, vx / tz)) * tz
+        ty = np.minimum(limy, np.maximum(-limy, vy / tz)) * tz
+        j00, j02 = focal_x / tz, -(focal_x * tx) / (tz * tz)
+        j11, j12 = focal_y / tz, -(focal_y * ty) / (tz * tz)
+        a0 = np.stack([v[0] * j00 + v[2] * j02, v[4] * j00 + v[6] * j02, v[8] * j00 + v[10] * j02], 1)
+        a1 = np.stack([v[1] * j11 + v[2] * j12, v[5] * j11 + v[6] * j12, v[9] * j11 + v[10] * j12], 1)
+        b0 = np.einsum("nij,nj->ni", Sig, a0).astype(f)
+        b1 = np.einsum("nij,nj->ni", Sig, a1).astype(f)
+        covx = (a0 * b0).sum(1, dtype=f) + f(0.3)
+        covy = (a0 * b1).sum(1, dtype=f)
+        covz = (a1 * b1).sum(1, dtype=f) + f(0.3)
+        det = covx * covz - covy * covy
+        alive2 = alive & ~(det == 0)
+        det_inv = one / det
+        mid = f(0.5) * (covx + covz)
+        disc = np.sqrt(np.maximum(f(0.1), mid * mid - det))
+        radius = np.ceil(f(3.0) * np.sqrt(np.maximum(mid + disc, mid - disc)))
+        pix_x = (((projx.astype(np.float64) + 1.0) * width - 1.0) * 0.5).astype(f)   # ndc2Pix, in double
+        pix_y = (((projy.astype(np.float64) + 1.0) * height - 1.0) * 0.5).astype(f)
+        rad = np.nan_to_num(radius, nan=0.0, posinf=2.0 ** 31 - 1, neginf=0.0).astype(np.int64)
+        gx, gy = (width + 15) // 16, (height + 15) // 16
+        radf = rad.astype(f)
+
+        def tile(val):                                                             # (int) truncation, clamp at 0
+            t = np.nan_to_num(val / f(16), nan=0.0, posinf=2.0 ** 31 - 1, neginf=-2.0 ** 31)
+            return np.maximum(0, np.trunc(t).astype(np.int64))
+
+        rminx, rminy = np.minimum(gx, tile(pix_x - radf)), np.minimum(gy, tile(pix_y - radf))
+        rmaxx, rmaxy = np.minimum(gx, tile(pix_x + radf + f(15))), np.minimum(gy, tile(pix_y + radf + f(15)))
+        tiles = (rmaxx - rminx) * (rmaxy - rminy)
+        vis = alive2 & (tiles != 0)
+        # computeColorFromSH_indexed
+        d = m - cam[None, :]
+        d = d / np.sqrt((d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1] + d[:, 2] * d[:, 2]))[:, None]
+        dx, dy, dz = d[:, 0], d[:, 1], d[:, 2]
+        sh = np.asarray(shs, f)[np.asarray(sh_indices, np.int64)]                    # [P, M, 3]
+        res = _SH_C0 * sh[:, 0]
+        if sh_degree > 0:
+            res = res - (_SH_C1 * dy)[:, None] * sh[:, 1] + (_SH_C1 * dz)[:, None] * sh[:, 2] - (_SH_C1 * dx)[:, None] * sh[:, 3]
+            if sh_degree > 1:
+                xx, yy, zz, xy, yz, xz = dx * dx, dy * dy, dz * dz, dx * dy, dy * dz, dx * dz
+                res = (res + (_SH_C2[0] * xy)[:, None] * sh[:, 4] + (_SH_C2[1] * yz)[:, None] * sh[:, 5]
+                       + (_SH_C2[2] * (two * zz - xx - yy))[:, None] * sh[:, 6] + (_SH_C2[3] * xz)[:, None] * sh[:, 7]
+                       + (_SH_C2[4] * (xx - yy))[:, None] * sh[:, 8])
+                if sh_degree > 2:
+                    res = (res + (_SH_C3[0] * dy * (f(3) * xx - yy))[:, None] * sh[:, 9]
+                           + (_SH_C3[1] * xy * dz)[:, None] * sh[:, 10]
+                           + (_SH_C3[2] * dy * (f(4) * zz - xx - yy))[:, None] * sh[:, 11]
+                           + (_SH_C3[3] * dz * (two * zz - f(3) * xx - f(3) * yy))[:, None] * sh[:, 12]
+                           + (_SH_C3[4] * dx * (f(4) * zz - xx - yy))[:, None] * sh[:, 13]
+                           + (_SH_C3[5] * dz * (xx - yy))[:, None] * sh[:, 14]
+                           + (_SH_C3[6] * dx * (xx - f(3) * yy))[:, None] * sh[:, 15])
+        res = (res + f(0.5)).astype(f)
+        clamped = (res < 0) if clamp_color else np.zeros_like(res, bool)
+        if clamp_color:
+            res = np.maximum(res, f(0))
+    out["cov3d"][alive] = cov3[alive]
+    out["radii"][vis] = rad[vis].astype(np.int32)
+    out["tiles_touched"][vis] = tiles[vis].astype(np.uint32)
+    out["xy"][vis] = np.stack([pix_x, pix_y], 1)[vis]
+    out["depths"][vis] = vz[vis]
+    out["rgb"][vis] = res[vis]
+    out["clamped"][vis] = clamped[vis]
+    out["conic_opacity"][vis] = np.stack([covz * det_inv, -covy * det_inv, covx * det_inv,
+                                          np.asarray(opacities, f).reshape(P)], 1)[vis]
+    return out

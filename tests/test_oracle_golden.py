@@ -263,3 +263,36 @@ def test_oracle_normalized_covariance_vs_reference_golden(oracle):
             assert np.abs(cov - ref).max() <= 1e-6            # entries are <= 1; float32 sum-order differences
     keep = g["cov_s_raw"][:, 0] > 0
     assert np.array_equal(oracle.mask_rows(g["cov_r_raw"], keep), g["cov_r_raw"][keep])
+
+
+# ---------------------------------------------------------------- indexed preprocess: known answers -----------------
+def test_oracle_preprocess_known_answers(oracle):
+    """Hand-computable cases of preprocess_indexedCUDA (forward_indexed.cu:166-272): a Gaussian on the optical axis
+    lands on the image centre with the EWA radius of an isotropic splat, one behind the camera is culled, a DC-only
+    colour row gives SH_C0 * c + 0.5 (clamped at 0)."""
+    w, h, tanx = 640, 480, 0.5
+    tany = tanx * h / w
+    view = np.eye(4, dtype=np.float32).reshape(16)              # camera at the origin looking down +z
+    proj = np.zeros((4, 4), np.float32)
+    proj[0, 0], proj[1, 1], proj[2, 2], proj[3, 2] = 1 / tanx, 1 / tany, 1.0, 1.0
+    projm = proj.T.reshape(16).copy()                           # flat storage is column-major
+    means = np.array([[0, 0, 5.0], [0, 0, -5.0], [1.0, 0.5, 4.0]], np.float32)
+    s = 0.2
+    scales = np.array([[1.0, 1.0, 1.0]], np.float32)
+    rots = np.array([[1.0, 0, 0, 0]], np.float32)
+    shs = np.zeros((2, 16, 3), np.float32)
+    shs[0, 0] = [1.0, -3.0, 0.25]
+    out = oracle.preprocess_indexed(means, scales, np.full(3, s, np.float32), rots, np.array([0.9, 0.8, 0.7], np.float32),
+                                    shs, np.array([0, 0, 1]), np.array([0, 0, 0]), view, projm, np.zeros(3, np.float32),
+                                    w, h, tanx, tany, sh_degree=3)
+    fx = w / (2 * tanx)
+    assert out["radii"][1] == 0 and out["tiles_touched"][1] == 0 and not out["cov3d"][1].any()
+    assert np.allclose(out["xy"][0], [(w - 1) / 2, (h - 1) / 2])
+    assert np.allclose(out["cov3d"][0], [s * s, 0, 0, s * s, 0, s * s], rtol=1e-6)
+    lam = (fx * s / 5.0) ** 2 + 0.3
+    assert out["radii"][0] == int(np.ceil(3 * np.sqrt(lam)))
+    assert np.allclose(out["conic_opacity"][0], [1 / lam, 0, 1 / lam, 0.9], rtol=1e-5)
+    assert np.allclose(out["rgb"][0], [0.28209479 * 1.0 + 0.5, 0.0, 0.28209479 * 0.25 + 0.5], atol=1e-6)
+    assert out["clamped"][0].tolist() == [False, True, False]
+    assert np.allclose(out["rgb"][2], 0.5) and out["depths"][2] == 4.0
+    assert np.allclose(out["xy"][2], [((1.0 / 4 / tanx + 1) * w - 1) / 2, ((0.5 / 4 / tany + 1) * h - 1) / 2], atol=1e-3)

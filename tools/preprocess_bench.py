@@ -1,0 +1,87 @@
+"""Indexed preprocess on a 6M-Gaussian indexed scene: product kernel vs the reference's own kernel
+(oracle/_ref/libpreprocess_ref.so, compiled unmodified) on the same inputs, CUDA-event timed.
+Algorithmic bytes per Gaussian: 36 in (position, factor, opacity, two int64 indices) + 28 + 192 gathered table bytes
++ 75 out for a visible one."""
+import ctypes
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+from c3dgs_b200 import _lib  # noqa: E402
+from preprocess_scene import camera  # noqa: E402
+
+dev = torch.device("cuda:0")
+p, g, f = 6_000_000, 1_500_000, 720_000
+gen = torch.Generator(device=dev).manual_seed(0)
+cam = camera(width=1297, height=840, fovx=0.9)
+c = {k: torch.from_numpy(v).to(dev) for k, v in cam.items() if isinstance(v, np.ndarray)}
+means = torch.randn(p, 3, device=dev, generator=gen) * torch.tensor([2.5, 1.5, 3.0], device=dev)
+scales = torch.nn.functional.normalize(torch.rand(g, 3, device=dev, generator=gen) + 0.05)
+rots = torch.nn.functional.normalize(torch.randn(g, 4, device=dev, generator=gen))
+factors = torch.exp(torch.randn(p, device=dev, generator=gen) * 0.7 - 4.5)
+opac = torch.rand(p, device=dev, generator=gen)
+shs = torch.randn(f, 16, 3, device=dev, generator=gen) * 0.3
+shi = torch.randint(0, f, (p,), device=dev, generator=gen)
+gi = torch.randint(0, g, (p,), device=dev, generator=gen)
+
+
+def timed(fn, reps=10):
+    fn()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(reps):
+        fn()
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) / reps
+
+
+out = {}
+
+
+def ours():
+    out.update(_lib.preprocess_indexed(means, scales, factors, rots, opac, shs, shi, gi, c["viewmatrix"], c["projmatrix"],
+                                       c["cam_pos"], cam["width"], cam["height"], cam["tan_fovx"], cam["tan_fovy"]))
+
+
+ms = timed(ours)
+import time as _t
+torch.cuda.synchronize()
+t0 = _t.time()
+for _ in range(10):
+    tmp = _lib.preprocess_indexed(means, scales, factors, rots, opac, shs, shi, gi, c["viewmatrix"], c["projmatrix"],
+                                  c["cam_pos"], cam["width"], cam["height"], cam["tan_fovx"], cam["tan_fovy"])
+t1 = _t.time()
+torch.cuda.synchronize()
+t2 = _t.time()
+print(f"host per call {(t1 - t0) * 100:.3f} ms, wall per call {(t2 - t0) * 100:.3f} ms (outputs dropped each call)")
+vis = int((out["radii"] > 0).sum())
+nbytes = p * 36 + (p - int((out["cov3d"].abs().sum(1) == 0).sum())) * 52 + vis * (192 + 51)
+print(f"product: {ms:.3f} ms for {p} Gaussians ({vis} visible), through the Python wrapper; "
+      f"{nbytes / ms * 1e-6:.0f} GB/s algorithmic")
+so = os.path.join(ROOT, "oracle", "_ref", "libpreprocess_ref.so")
+if os.path.exists(so):
+    lib = ctypes.CDLL(so)
+    vp, fl, it = ctypes.c_void_p, ctypes.c_float, ctypes.c_int
+    lib.ref_preprocess_indexed.argtypes = [it, it, it, vp, vp, vp, fl, vp, vp, vp, vp, vp, vp, vp, it, it, fl, fl, fl, fl,
+                                           vp, vp, vp, vp, vp, vp, vp, vp, vp, it]
+    o = {k: torch.zeros_like(v) for k, v in out.items()}
+    fy = float(np.float32(cam["height"]) / (np.float32(2.0) * np.float32(cam["tan_fovy"])))
+    fx = float(np.float32(cam["width"]) / (np.float32(2.0) * np.float32(cam["tan_fovx"])))
+
+    def ref():
+        lib.ref_preprocess_indexed(p, 3, 16, means.data_ptr(), scales.data_ptr(), factors.data_ptr(), 1.0, rots.data_ptr(),
+                                   opac.data_ptr(), shs.data_ptr(), o["clamped"].data_ptr(), c["viewmatrix"].data_ptr(),
+                                   c["projmatrix"].data_ptr(), c["cam_pos"].data_ptr(), cam["width"], cam["height"], fx, fy,
+                                   cam["tan_fovx"], cam["tan_fovy"], o["radii"].data_ptr(), o["xy"].data_ptr(),
+                                   o["depths"].data_ptr(), o["cov3d"].data_ptr(), o["rgb"].data_ptr(),
+                                   o["conic_opacity"].data_ptr(), o["tiles_touched"].data_ptr(), shi.data_ptr(),
+                                   gi.data_ptr(), 1)
+
+    torch.cuda.synchronize()
+    print(f"reference kernel (forward_indexed.cu, unmodified, legacy stream, host-synchronised per call): {timed(ref):.3f} ms")
