@@ -555,7 +555,7 @@ def preprocess_indexed(means3d, scales, scale_factors, rotations, opacities, shs
     viewmatrix, projmatrix, cam_pos = viewmatrix.contiguous(), projmatrix.contiguous(), cam_pos.contiguous()
     dev = means3d.device
     import numpy as np
-    # rasterizer_impl.cu:219-220: focal lengths from the field of view, in float32
+    # rasterizer_impl.cu:468-469: focal lengths from the field of view, in float32
     focal_y = float(np.float32(height) / (np.float32(2.0) * np.float32(tan_fovy)))
     focal_x = float(np.float32(width) / (np.float32(2.0) * np.float32(tan_fovx)))
     with torch.cuda.device(dev):

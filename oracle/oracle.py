@@ -372,7 +372,7 @@ def preprocess_indexed(means3d, scales, scale_factors, rotations, opacities, shs
     """preprocess_indexedCUDA restated in numpy float32 (submodules/diff-gaussian-rasterization/cuda_rasterizer/
     forward_indexed.cu:166-272; computeColorFromSH_indexed :20-77, computeCov2D_indexed :79-121, computeCov3D_indexed
     :123-159; in_frustum / ndc2Pix / getRect / transformPoint auxiliary.h:42-152; focal lengths rasterizer_impl.cu:
-    219-220).  viewmatrix / projmatrix: 16 floats, column-major.  Returns the kernel's outputs (zeros where the
+    468-469).  viewmatrix / projmatrix: 16 floats, column-major.  Returns the kernel's outputs (zeros where the
     kernel returns early)."""
     f = np.float32
     P = len(means3d)

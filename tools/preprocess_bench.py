@@ -41,29 +41,17 @@ def timed(fn, reps=10):
     return a.elapsed_time(b) / reps
 
 
-out = {}
-
-
 def ours():
-    out.update(_lib.preprocess_indexed(means, scales, factors, rots, opac, shs, shi, gi, c["viewmatrix"], c["projmatrix"],
-                                       c["cam_pos"], cam["width"], cam["height"], cam["tan_fovx"], cam["tan_fovy"]))
+    return _lib.preprocess_indexed(means, scales, factors, rots, opac, shs, shi, gi, c["viewmatrix"], c["projmatrix"],
+                                   c["cam_pos"], cam["width"], cam["height"], cam["tan_fovx"], cam["tan_fovy"])
 
 
+out = ours()
 ms = timed(ours)
-import time as _t
-torch.cuda.synchronize()
-t0 = _t.time()
-for _ in range(10):
-    tmp = _lib.preprocess_indexed(means, scales, factors, rots, opac, shs, shi, gi, c["viewmatrix"], c["projmatrix"],
-                                  c["cam_pos"], cam["width"], cam["height"], cam["tan_fovx"], cam["tan_fovy"])
-t1 = _t.time()
-torch.cuda.synchronize()
-t2 = _t.time()
-print(f"host per call {(t1 - t0) * 100:.3f} ms, wall per call {(t2 - t0) * 100:.3f} ms (outputs dropped each call)")
 vis = int((out["radii"] > 0).sum())
-nbytes = p * 36 + (p - int((out["cov3d"].abs().sum(1) == 0).sum())) * 52 + vis * (192 + 51)
-print(f"product: {ms:.3f} ms for {p} Gaussians ({vis} visible), through the Python wrapper; "
-      f"{nbytes / ms * 1e-6:.0f} GB/s algorithmic")
+nbytes = p * 36 + int((out["cov3d"].abs().sum(1) != 0).sum()) * 52 + vis * (192 + 51)
+print(f"product: {ms:.3f} ms per call for {p} Gaussians ({vis} visible), through the Python wrapper (allocates the "
+      f"eight outputs every call); {nbytes / ms * 1e-6:.0f} GB/s algorithmic; kernel-only times: ncu")
 so = os.path.join(ROOT, "oracle", "_ref", "libpreprocess_ref.so")
 if os.path.exists(so):
     lib = ctypes.CDLL(so)
