@@ -527,11 +527,12 @@ def compact(tensors, keep_mask: torch.Tensor):
 def preprocess_indexed(means3d, scales, scale_factors, rotations, opacities, shs, sh_indices, g_indices, viewmatrix,
                        projmatrix, cam_pos, width: int, height: int, tan_fovx: float, tan_fovy: float,
                        sh_degree: int = 3, scale_modifier: float = 1.0, prefiltered: bool = False,
-                       clamp_color: bool = True):
+                       clamp_color: bool = True, out=None):
     """FORWARD::preprocess_indexed of the reference's indexed rasteriser (cuda_rasterizer/forward_indexed.cu:166-272):
     returns a dict with radii [P] int32, xy [P,2], depths [P], cov3d [P,6], rgb [P,3], conic_opacity [P,4],
     tiles_touched [P] int32 (bit pattern of the reference's uint32) and clamped [P,3] bool.  The kernel writes every
-    row: culled Gaussians read as zeros (the reference leaves them untouched).  viewmatrix / projmatrix: 4x4 CUDA tensors whose flat storage is the
+    row: culled Gaussians read as zeros (the reference leaves them untouched).  `out`: the dict of an earlier call
+    with the same number of Gaussians, to write into its buffers again.  viewmatrix / projmatrix: 4x4 CUDA tensors whose flat storage is the
     column-major matrix, exactly what the reference's Python side passes.  c3vq_preprocess_indexed."""
     p = means3d.size(0)
     for t, name, shape in ((means3d, "means3d", (p, 3)), (scale_factors, "scale_factors", None),
@@ -559,11 +560,20 @@ def preprocess_indexed(means3d, scales, scale_factors, rotations, opacities, shs
     focal_y = float(np.float32(height) / (np.float32(2.0) * np.float32(tan_fovy)))
     focal_x = float(np.float32(width) / (np.float32(2.0) * np.float32(tan_fovx)))
     with torch.cuda.device(dev):
-        out = {"radii": torch.empty(p, dtype=torch.int32, device=dev), "xy": torch.empty(p, 2, device=dev),
-               "depths": torch.empty(p, device=dev), "cov3d": torch.empty(p, 6, device=dev),
-               "rgb": torch.empty(p, 3, device=dev), "conic_opacity": torch.empty(p, 4, device=dev),
-               "tiles_touched": torch.empty(p, dtype=torch.int32, device=dev),
-               "clamped": torch.empty(p, 3, dtype=torch.bool, device=dev)}
+        if out is None or out["radii"].numel() != p or out["radii"].device != dev:
+            # one allocation carved into the eight outputs (like the reference's geometry-state chunk), segments
+            # aligned to 256 bytes
+            spec = (("conic_opacity", (p, 4), torch.float32), ("cov3d", (p, 6), torch.float32),
+                    ("rgb", (p, 3), torch.float32), ("xy", (p, 2), torch.float32), ("depths", (p,), torch.float32),
+                    ("radii", (p,), torch.int32), ("tiles_touched", (p,), torch.int32), ("clamped", (p, 3), torch.bool))
+            sizes = [((int(torch.Size(shape).numel()) * torch.empty(0, dtype=dt).element_size() + 255) // 256) * 256
+                     for _, shape, dt in spec]
+            chunk = torch.empty(sum(sizes), dtype=torch.uint8, device=dev)
+            out, off = {}, 0
+            for (name, shape, dt), size in zip(spec, sizes):
+                nbytes = int(torch.Size(shape).numel()) * torch.empty(0, dtype=dt).element_size()
+                out[name] = chunk[off:off + nbytes].view(dt).reshape(shape)
+                off += size
         rc = load().c3vq_preprocess_indexed(
             p, int(sh_degree), shs.size(1), _ptr(means3d), _ptr(scales), _ptr(scale_factors), float(scale_modifier),
             _ptr(rotations), _ptr(opacities), _ptr(shs), _ptr(viewmatrix), _ptr(projmatrix), _ptr(cam_pos),

@@ -47,7 +47,7 @@ __device__ __forceinline__ V3 sh_row(const float *__restrict__ shs, int64_t row,
     return {__ldg(p), __ldg(p + 1), __ldg(p + 2)};
 }
 
-__global__ void __launch_bounds__(PRE_THREADS) k_preprocess_indexed(const PreParams q)
+__global__ void __launch_bounds__(PRE_THREADS, 4) k_preprocess_indexed(const PreParams q)
 {
     __shared__ float sv[16], sp[16], scam[3];
     if (threadIdx.x < 16) {
