@@ -266,7 +266,10 @@ __global__ void k_tc_prep_image(const float *__restrict__ cb, int k, int k_pad, 
     if (fin && !(nf < TC_HUGE2)) {      // finite code outside the error model: everything goes exact
         atomicOr(&hdr->force_fallback, 1u);
     }
-    if (fin) atomicMax(&hdr->cmax_bits, __float_as_int(sqrtf(nf)));
+    {   // Cmax: one atomic per warp instead of one per code (k_pad is a multiple of 32: whole warps are here)
+        const int cb_bits = __reduce_max_sync(0xffffffffu, fin ? __float_as_int(sqrtf(nf)) : 0);
+        if ((threadIdx.x & 31) == 0 && cb_bits) atomicMax(&hdr->cmax_bits, cb_bits);
+    }
     for (int c = 0; c < dp; c++) {
         float v = 0.f;
         if (fin && nf < TC_HUGE2) {
