@@ -586,3 +586,30 @@ def test_trace_normalised_shape_codebook_keeps_the_tensor_core_path(L, oracle):
         assert rows == b and fb <= b // 20, f"step {step}: {fb} of {b} rows took the exact scan"
         dist_o, _ = oracle.assign(cov[batch].cpu().numpy(), cb_before.cpu().numpy())
         assert np.array_equal(dist.cpu().numpy().view(np.uint32), dist_o.view(np.uint32))
+
+
+def test_full_size_shape_codebook_trace_normalised(L):
+    """BASELINE configs[2] at full size on the fork's real shape width: 5.8 M normalised covariances x 6-D, K = 4096,
+    full-batch updates with the trace normalisation (vq.py:76-77).  Every iteration's tensor-core result must equal the
+    SIMT exact kernel's on the same codebook bit for bit, and the outlier codewords the normalisation creates must not
+    push more than 2 % of the rows to the exact scan."""
+    n, k = 5_800_000, 4096
+    g = torch.Generator(device=DEV).manual_seed(3)
+    s = torch.nn.functional.normalize(torch.rand(n, 3, device=DEV, generator=g) + 0.05)
+    r = torch.randn(n, 4, device=DEV, generator=g)
+    cov = L.build_covariance(s, r)
+    w = torch.rand(n, device=DEV, generator=g) ** 4
+    amin, amax = cov.aminmax()
+    cb = (torch.rand(k, 6, device=DEV, generator=g) * (amax - amin) + amin).contiguous()
+    ei = torch.zeros(k, device=DEV)
+    for it in range(4):
+        d_exact, i_exact = L.assign(cov, cb, exact=True)
+        d_tc, i_tc = L.update(cov, w, cb, ei, 0.8, 1e-5, scale_normalize=True, tensor_cores=True, return_dist=True,
+                              return_idx=True)
+        rows, cands, fb = L.assign_stats(DEV)
+        assert torch.equal(d_tc, d_exact), f"iteration {it}: min distances differ"
+        assert torch.equal(i_tc, i_exact), f"iteration {it}: assignments differ"
+        assert rows == n and fb <= n // 50, f"iteration {it}: {fb} of {n} rows took the exact scan"
+        tr = cb[:, 0] + cb[:, 3] + cb[:, 5]
+        fin = torch.isfinite(tr)
+        assert (tr[fin] - 1).abs().max() < 1e-3
