@@ -437,6 +437,20 @@ def main():
                                   "note": "keys + stable 8x8-bit LSD radix sort of (u64 key, u32 row); torch.sort (cub) "
                                           "of n random int64 incl. their generation, timed beside it for scale"}
         del keep, cbi, cbj, a6, cov6, sub, xyz
+        # the indexed-codebook decode, codebook[idx] -> [n, d] (8 B index in + 4 d B out per row)
+        idx_dec = torch.randint(0, K, (n,), device=dev, generator=gen)
+        ms = timed(lambda: ops2.gather(cbj, idx_dec))
+        gbytes = n * (8 + 4 * d)
+        extras["decode_gather"] = {"rows": n, "dim": d, "ms": ms, "gbs": gbytes / ms * 1e-6,
+                                   "frac_of_hbm_peak": gbytes / ms * 1e-6 / pk["hbm_gbs"]}
+        tab48 = torch.randn(K + n // 20, 16, 3, device=dev, generator=gen)
+        idx48 = torch.randint(0, tab48.shape[0], (n,), device=dev, generator=gen)
+        ms = timed(lambda: ops2.gather(tab48, idx48))
+        gbytes = n * (8 + 4 * 48)
+        extras["decode_gather_sh48"] = {"rows": n, "dim": 48, "table_rows": int(tab48.shape[0]), "ms": ms,
+                                        "gbs": gbytes / ms * 1e-6, "frac_of_hbm_peak": gbytes / ms * 1e-6 / pk["hbm_gbs"]}
+        del idx_dec, tab48, idx48
+
         # SURVEY §8f ranks 1 and 3, the formats either side of the path: normalised covariance, mask compaction,
         # int8 scene-file quantisation (algorithmic bytes / time against the measured copy peak)
         s3 = torch.rand(n, 3, device=dev, generator=gen) + 0.05

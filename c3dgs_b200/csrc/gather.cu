@@ -5,7 +5,7 @@
 // `features[batch]` (compression/vq.py:70).  HBM bound: algorithmic bytes per output
 // row = 8 (idx, i64) + 4*d (row written); the table is L2 resident for codebooks.
 // Rows whose byte length is a multiple of 16 move as float4 with fully coalesced
-// stores; other widths move one float per thread, still with coalesced stores.
+// stores; other widths are written as float4 too, a warp per span of 32 output rows (k_gather_span).
 #include "common.cuh"
 
 namespace c3vq {
@@ -43,6 +43,50 @@ k_gather32(const T *__restrict__ table, int64_t table_rows, int dv, const int64_
     }
 }
 
+// Rows that are not a multiple of 16 bytes (45 floats = 180 B is the SH width): a warp takes 32 consecutive output rows,
+// i.e. one contiguous, 16-byte aligned span of 32*d floats, reads its 32 indices with one coalesced load, parks them in
+// shared memory and writes the span as float4 — one integer division and one 16-byte store per four elements instead
+// of a division, an index load and a 4-byte store per element.
+__global__ void __launch_bounds__(256)
+k_gather_span(const float *__restrict__ table, int64_t table_rows, int d, const int64_t *__restrict__ idx, int64_t n,
+              float *__restrict__ out)
+{
+    __shared__ long long sj[8][32];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int64_t nwarps = (int64_t)gridDim.x * 8;
+    for (int64_t r0 = ((int64_t)blockIdx.x * 8 + wib) * 32; r0 < n; r0 += nwarps * 32) {
+        const int rows_here = (int)min((int64_t)32, n - r0);
+        long long j = -1;
+        if (lane < rows_here) {
+            j = idx[r0 + lane];
+            if ((uint64_t)j >= (uint64_t)table_rows) j = -1;          // out of range: zeros, as before
+        }
+        __syncwarp();
+        sj[wib][lane] = j;
+        __syncwarp();
+        float *dst = out + r0 * d;                                    // 32 * d * 4 bytes per span: 16-byte aligned
+        const unsigned int total = (unsigned int)rows_here * (unsigned int)d;
+        for (unsigned int e = lane * 4; e < total; e += 128) {
+            unsigned int r = e / (unsigned int)d, c = e - r * (unsigned int)d;
+            float v[4];
+#pragma unroll
+            for (int t = 0; t < 4; t++) {
+                v[t] = 0.f;
+                if (e + t < total) {
+                    const long long jj = sj[wib][r];
+                    if (jj >= 0) v[t] = __ldg(table + jj * d + c);
+                    if (++c == (unsigned int)d) c = 0, r++;
+                }
+            }
+            if (e + 3 < total) {
+                *reinterpret_cast<float4 *>(dst + e) = make_float4(v[0], v[1], v[2], v[3]);
+            } else {
+                for (int t = 0; t < 4 && e + t < total; t++) dst[e + t] = v[t];
+            }
+        }
+    }
+}
+
 template <typename T>
 static int launch_gather_t(const T *table, int64_t table_rows, int dv, const int64_t *idx, int64_t n, T *out,
                            cudaStream_t s)
@@ -68,6 +112,14 @@ int launch_gather(const float *table, int64_t table_rows, int d, const int64_t *
     if (v4)
         return launch_gather_t<float4>(reinterpret_cast<const float4 *>(table), table_rows, d / 4, idx, n,
                                        reinterpret_cast<float4 *>(out), s);
+    if ((reinterpret_cast<uintptr_t>(out) & 15) == 0 && d < (1 << 24)) {
+        int64_t blocks = (n + 255) / 256;                         // 8 warps x 32 rows per block and round
+        const int64_t cap = (int64_t)sm_count() * 16;
+        if (blocks > cap) blocks = cap;
+        k_gather_span<<<(unsigned)blocks, 256, 0, s>>>(table, table_rows, d, idx, n, out);
+        C3VQ_LAUNCH_CHECK("k_gather_span");
+        return C3VQ_OK;
+    }
     return launch_gather_t<float>(table, table_rows, d, idx, n, out, s);
 }
 
