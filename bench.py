@@ -439,7 +439,8 @@ def main():
         del keep, cbi, cbj, a6, cov6, sub, xyz
         # the indexed-codebook decode, codebook[idx] -> [n, d] (8 B index in + 4 d B out per row)
         idx_dec = torch.randint(0, K, (n,), device=dev, generator=gen)
-        ms = timed(lambda: ops2.gather(cbj, idx_dec))
+        cb_dec = torch.randn(K, d, device=dev, generator=gen)
+        ms = timed(lambda: ops2.gather(cb_dec, idx_dec))
         gbytes = n * (8 + 4 * d)
         extras["decode_gather"] = {"rows": n, "dim": d, "ms": ms, "gbs": gbytes / ms * 1e-6,
                                    "frac_of_hbm_peak": gbytes / ms * 1e-6 / pk["hbm_gbs"]}
@@ -449,7 +450,7 @@ def main():
         gbytes = n * (8 + 4 * 48)
         extras["decode_gather_sh48"] = {"rows": n, "dim": 48, "table_rows": int(tab48.shape[0]), "ms": ms,
                                         "gbs": gbytes / ms * 1e-6, "frac_of_hbm_peak": gbytes / ms * 1e-6 / pk["hbm_gbs"]}
-        del idx_dec, tab48, idx48
+        del idx_dec, cb_dec, tab48, idx48
 
         # SURVEY §8f ranks 1 and 3, the formats either side of the path: normalised covariance, mask compaction,
         # int8 scene-file quantisation (algorithmic bytes / time against the measured copy peak)
