@@ -51,7 +51,7 @@ __global__ void __launch_bounds__(256)
 k_gather_span(const float *__restrict__ table, int64_t table_rows, int d, const int64_t *__restrict__ idx, int64_t n,
               float *__restrict__ out)
 {
-    __shared__ long long sj[8][32];
+    __shared__ const float *sj[8][32];                               // source row of each output row (null: zeros)
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t nwarps = (int64_t)gridDim.x * 8;
     for (int64_t r0 = ((int64_t)blockIdx.x * 8 + wib) * 32; r0 < n; r0 += nwarps * 32) {
@@ -62,7 +62,7 @@ k_gather_span(const float *__restrict__ table, int64_t table_rows, int d, const 
             if ((uint64_t)j >= (uint64_t)table_rows) j = -1;          // out of range: zeros, as before
         }
         __syncwarp();
-        sj[wib][lane] = j;
+        sj[wib][lane] = j >= 0 ? table + j * d : nullptr;
         __syncwarp();
         float *dst = out + r0 * d;                                    // 32 * d * 4 bytes per span: 16-byte aligned
         const unsigned int total = (unsigned int)rows_here * (unsigned int)d;
@@ -73,8 +73,8 @@ k_gather_span(const float *__restrict__ table, int64_t table_rows, int d, const 
             for (int t = 0; t < 4; t++) {
                 v[t] = 0.f;
                 if (e + t < total) {
-                    const long long jj = sj[wib][r];
-                    if (jj >= 0) v[t] = __ldg(table + jj * d + c);
+                    const float *src = sj[wib][r];
+                    if (src != nullptr) v[t] = __ldg(src + c);
                     if (++c == (unsigned int)d) c = 0, r++;
                 }
             }

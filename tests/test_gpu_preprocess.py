@@ -131,6 +131,18 @@ def test_preprocess_edge_cases_and_errors(L, oracle):
             assert np.array_equal(got["radii"] > 0, _compare_small["radii"] > 0)
     t = {k: torch.from_numpy(v).to(DEV) for k, v in sc.items()}
     c = {k: torch.from_numpy(v).to(DEV) for k, v in cam.items() if isinstance(v, np.ndarray)}
+    # buffer reuse: a second call into the first call's outputs (dirtied in between) gives the same result in place
+    s3 = scene(5000, g=50, f=40, seed=8)
+    t3 = {k: torch.from_numpy(v).to(DEV) for k, v in s3.items()}
+    args3 = (t3["means3d"], t3["scales"], t3["scale_factors"], t3["rotations"], t3["opacities"], t3["shs"],
+             t3["sh_indices"], t3["g_indices"], c["viewmatrix"], c["projmatrix"], c["cam_pos"], 64, 48,
+             cam["tan_fovx"], cam["tan_fovy"])
+    first = L.preprocess_indexed(*args3)
+    keep = {k: v.clone() for k, v in first.items()}
+    for v in first.values():
+        v.fill_(1)
+    again = L.preprocess_indexed(*args3, out=first)
+    assert all(again[k].data_ptr() == first[k].data_ptr() and torch.equal(again[k], keep[k]) for k in keep)
     with pytest.raises(RuntimeError):                          # degree 3 needs 16 coefficients per row
         L.preprocess_indexed(t["means3d"], t["scales"], t["scale_factors"], t["rotations"], t["opacities"],
                              t["shs"][:, :9].contiguous(), t["sh_indices"], t["g_indices"], c["viewmatrix"],
