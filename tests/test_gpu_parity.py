@@ -613,3 +613,34 @@ def test_full_size_shape_codebook_trace_normalised(L):
         tr = cb[:, 0] + cb[:, 3] + cb[:, 5]
         fin = torch.isfinite(tr)
         assert (tr[fin] - 1).abs().max() < 1e-3
+
+
+def test_outlier_rows_keep_their_sums_in_every_mode(L, oracle):
+    """Rows that the outlier check sends to the exact scan after the re-rank must still contribute their weighted row
+    to the centroid sums, in the sorted, the fused and the SIMT mode alike (codebooks within 1e-5 of the oracle)."""
+    n, k, d = 30_000, 512, 6
+    g = torch.Generator().manual_seed(21)
+    s = torch.nn.functional.normalize(torch.rand(n, 3, generator=g) + 0.05)
+    r = torch.randn(n, 4, generator=g)
+    cov = L.build_covariance(s.to(DEV), r.to(DEV)).cpu()
+    w = torch.rand(n, generator=g) ** 4
+    amin, amax = cov.aminmax()
+    cb0 = torch.rand(k, d, generator=g) * (amax - amin) + amin
+    cb0[7] *= 2.0e3                                              # planted outliers, one of them with members
+    cb0[9] = cov[5] * 300.0
+    cov[100:140] = cb0[9] + 0.01 * torch.randn(40, d, generator=g)
+    cb_o, ei_o = cb0.numpy().copy(), np.zeros(k, np.float32)
+    dist_o, idx_o = oracle.assign(cov.numpy(), cb_o)
+    assert (idx_o[100:140] == 9).all()
+    oracle.update(cov.numpy(), w.numpy(), cb_o, ei_o, 0.8)
+    for mode in (True, "fused", False):
+        cb, ei = cb0.clone().to(DEV), torch.zeros(k, device=DEV)
+        dist, idx = L.update(cov.to(DEV), w.to(DEV), cb, ei, 0.8, 1e-5, tensor_cores=mode, return_dist=True,
+                             return_idx=True)
+        assert np.array_equal(idx.cpu().numpy(), idx_o), mode
+        assert np.array_equal(dist.cpu().numpy().view(np.uint32), dist_o.view(np.uint32)), mode
+        if mode:
+            rows, _, fb = L.assign_stats(DEV)
+            assert 40 <= fb <= 2000, f"{mode}: {fb} rows in the exact scan"
+        _cb_close(cb.cpu().numpy(), cb_o)
+        assert np.allclose(ei.cpu().numpy(), ei_o, rtol=1e-5, atol=1e-7)
