@@ -330,11 +330,13 @@ def main():
 
     # e2e: the same job from pinned HOST buffers through the public API, copies inside the timed region
     e2e = None
-    xh = torch.empty(x.shape, dtype=torch.float32).pin_memory()
-    wh = torch.empty(w.shape, dtype=torch.float32).pin_memory()
+    from c3dgs_b200.sharded import gpu_local_host_memory
+    with gpu_local_host_memory(local_rank):          # pinned staging buffers on this GPU's NUMA node
+        xh = torch.empty(x.shape, dtype=torch.float32).pin_memory()
+        wh = torch.empty(w.shape, dtype=torch.float32).pin_memory()
+        cbh = torch.empty(K, d, dtype=torch.float32).pin_memory()
+        idxh = torch.empty(n, dtype=torch.int64).pin_memory()
     xh.copy_(x); wh.copy_(wn)
-    cbh = torch.empty(K, d, dtype=torch.float32).pin_memory()
-    idxh = torch.empty(n, dtype=torch.int64).pin_memory()
     xd, wd = torch.empty_like(x), torch.empty_like(wn)
 
     def e2e_job():

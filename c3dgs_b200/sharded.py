@@ -14,12 +14,44 @@ on CPU tensors (the default ops raise for them).
 """
 from __future__ import annotations
 
+import contextlib
+import os
 from typing import Optional, Tuple
 
 import torch
 import torch.distributed as dist
 
 from . import _lib
+
+
+@contextlib.contextmanager
+def gpu_local_host_memory(device_index: int):
+    """Run the enclosed host allocations on the CPUs next to GPU `device_index` (NVML's ideal CPU set), so that pinned
+    staging buffers land on that GPU's NUMA node: with one process per GPU and eight uploads at once, buffers on the
+    far socket share one inter-socket link.  The previous affinity is restored on exit (the pages stay where they
+    were allocated).  Does nothing when NVML or the topology is unavailable."""
+    old = None
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        props = torch.cuda.get_device_properties(device_index)
+        bus_id = f"{props.pci_domain_id:08x}:{props.pci_bus_id:02x}:{props.pci_device_id:02x}.0"
+        handle = pynvml.nvmlDeviceGetHandleByPciBusId(bus_id.encode())
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(handle, words)
+        cpus = {64 * i + b for i, word in enumerate(mask) for b in range(64) if (int(word) >> b) & 1}
+        allowed = os.sched_getaffinity(0)
+        target = cpus & allowed
+        if target and target != allowed:
+            old = allowed
+            os.sched_setaffinity(0, target)
+    except Exception:                            # no NVML / no topology in this container: leave the affinity alone
+        old = None
+    try:
+        yield
+    finally:
+        if old is not None:
+            os.sched_setaffinity(0, old)
 
 
 def shard_bounds(n: int, rank: int, world: int) -> Tuple[int, int]:
