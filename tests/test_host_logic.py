@@ -115,3 +115,14 @@ def test_vq_features_error_in_a_step_does_not_hang_the_draw_thread(monkeypatch):
     with _host_only(), pytest.raises(ValueError, match="boom"):
         vq.vq_features(torch.randn(100, 3), torch.rand(100), 4, vq_chunk=16, steps=200, silent=True)
     assert not [t for t in threading.enumerate() if t.name == "c3vq-batch-draw"]
+
+
+def test_gpu_local_host_memory_restores_the_affinity():
+    """The NUMA helper must leave the process affinity as it found it (and be a no-op without NVML / a GPU)."""
+    import os
+    from c3dgs_b200.sharded import gpu_local_host_memory
+    before = os.sched_getaffinity(0)
+    with gpu_local_host_memory(0):
+        inside = os.sched_getaffinity(0)
+        assert inside and inside <= before
+    assert os.sched_getaffinity(0) == before
