@@ -148,6 +148,8 @@ def run_reference_arm(args, rank):
     wn = (w / w.max()).astype(np.float32)
     rng = np.random.default_rng(0)
     cb0 = (rng.random((K, d), dtype=np.float32) * (x.max() - x.min()) + x.min()).astype(np.float32)
+    # torchrun exports OMP_NUM_THREADS=1 to every rank; this leg is the only CPU work of the job and takes every core
+    oracle.set_threads(len(os.sched_getaffinity(0)))
     cores = oracle.num_threads()
 
     def job():
@@ -192,6 +194,7 @@ def cpu_baseline_leg(d=45):
     rng = np.random.default_rng(0)
     cb = (rng.random((K, d), dtype=np.float32) * (x.max() - x.min()) + x.min()).astype(np.float32)
     ei = np.zeros(K, np.float32)
+    oracle.set_threads(len(os.sched_getaffinity(0)))    # all host cores, whatever OMP_NUM_THREADS says
     oracle.update(x, wn, cb, ei, DECAY, EPS)            # warm-up iteration
     t0 = time.time()
     done = 0
