@@ -33,13 +33,29 @@ __global__ void __launch_bounds__(256)
 k_gather32(const T *__restrict__ table, int64_t table_rows, int dv, const int64_t *__restrict__ idx, int total,
            T *__restrict__ out)
 {
-    for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < total; e += gridDim.x * blockDim.x) {
-        const int i = e / dv;
-        const int c = e - i * dv;
-        const int64_t j = idx[i];
-        T v = T();
-        if ((uint64_t)j < (uint64_t)table_rows) v = table[j * dv + c];
-        out[e] = v;
+    // four independent elements per thread and round: the table rows of a large table (kept rows behind a codebook)
+    // come from the L2 or DRAM, and one load in flight per thread leaves the gather latency bound
+    const int stride = gridDim.x * blockDim.x;
+    for (int e0 = blockIdx.x * blockDim.x + threadIdx.x; e0 < total; e0 += 4 * stride) {
+        const T *src[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int e = e0 + u * stride;
+            src[u] = nullptr;
+            if (e < total && e >= 0) {
+                const int i = e / dv;
+                const int64_t j = idx[i];
+                if ((uint64_t)j < (uint64_t)table_rows) src[u] = table + j * dv + (e - i * dv);
+            }
+        }
+        T v[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) v[u] = src[u] ? __ldg(src[u]) : T();
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int e = e0 + u * stride;
+            if (e < total && e >= 0) out[e] = v[u];
+        }
     }
 }
 
@@ -95,7 +111,7 @@ static int launch_gather_t(const T *table, int64_t table_rows, int dv, const int
     int64_t blocks = (total + 255) / 256;
     const int64_t cap = (int64_t)sm_count() * 64;
     if (blocks > cap) blocks = cap;
-    if (total < 0x7fffffffLL)
+    if (total < 0x70000000LL)                 // leaves room for the 4 x stride look-ahead of the 32-bit index
         k_gather32<T><<<(unsigned)blocks, 256, 0, s>>>(table, table_rows, dv, idx, (int)total, out);
     else
         k_gather<T><<<(unsigned)blocks, 256, 0, s>>>(table, table_rows, dv, idx, n, out);
