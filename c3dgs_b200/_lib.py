@@ -79,6 +79,10 @@ SIGNATURES = {
                                          _c_vp, _c_vp, _c_vp, _c_int, _c_int, ctypes.c_float, ctypes.c_float,
                                          ctypes.c_float, ctypes.c_float, _c_int, _c_vp, _c_vp, _c_int, _c_vp, _c_vp,
                                          _c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_vp]),
+    "c3vq_preprocess_indexed_backward": (_c_int, [_c_i64, _c_int, _c_int, _c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_vp,
+                                                  ctypes.c_float, _c_vp, _c_vp, _c_vp, ctypes.c_float, ctypes.c_float,
+                                                  ctypes.c_float, ctypes.c_float, _c_vp, _c_vp, _c_vp, _c_vp, _c_vp,
+                                                  _c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_vp, _c_vp]),
     "c3vq_gather_rows": (_c_int, [_c_vp, _c_vp, _c_vp, _c_i64, _c_int, _c_vp, _c_vp, _c_vp]),
     "c3vq_debug_scores": (_c_int, [_c_vp, _c_i64, _c_int, _c_vp, _c_int, _c_vp, _c_vp, _c_vp, _c_vp, _c_sz, _c_vp]),
     "c3vq_assign_stats": (_c_int, [_c_vp, ctypes.POINTER(_c_i64), _c_vp]),
@@ -581,6 +585,66 @@ def preprocess_indexed(means3d, scales, scale_factors, rotations, opacities, shs
             _ptr(sh_indices), _ptr(g_indices), 1 if clamp_color else 0, _ptr(out["radii"]), _ptr(out["xy"]),
             _ptr(out["depths"]), _ptr(out["cov3d"]), _ptr(out["rgb"]), _ptr(out["conic_opacity"]),
             _ptr(out["tiles_touched"]), _ptr(out["clamped"]), _stream(means3d))
+    if rc:
+        raise _err(rc)
+    return out
+
+
+def preprocess_indexed_backward(means3d, radii, shs, clamped, scales, scale_factors, rotations, cov3d, viewmatrix,
+                                projmatrix, cam_pos, width: int, height: int, tan_fovx: float, tan_fovy: float,
+                                dl_dmean2d, dl_dconic, dl_dcolor, sh_indices, g_indices, sh_degree: int = 3,
+                                scale_modifier: float = 1.0):
+    """BACKWARD::preprocess_indexed of the reference's indexed rasteriser (cuda_rasterizer/backward_indexed.cu:
+    469-550): gradients of the per-Gaussian preprocess.  `radii`, `clamped`, `cov3d` are the forward's outputs
+    (preprocess_indexed); dl_dmean2d [P,3], dl_dconic [P,2,2] (or [P,4]) and dl_dcolor [P,3] come from the render
+    backward.  Returns a dict: means3d [P,3], cov3d [P,6], scale_factors [P,1] per Gaussian, and the TABLE gradients
+    shs [F,M,3], scales [G,3], rotations [G,4] summed over the Gaussians that reference each row (allocated as zeros
+    here, like rasterize_points_indexed.cu:166-175).  c3vq_preprocess_indexed_backward."""
+    p = means3d.size(0)
+    for t, name in ((means3d, "means3d"), (shs, "shs"), (scales, "scales"), (scale_factors, "scale_factors"),
+                    (rotations, "rotations"), (cov3d, "cov3d"), (viewmatrix, "viewmatrix"), (projmatrix, "projmatrix"),
+                    (cam_pos, "cam_pos"), (dl_dmean2d, "dl_dmean2d"), (dl_dconic, "dl_dconic"), (dl_dcolor, "dl_dcolor")):
+        _check(t, torch.float32, name)
+    _check(radii, torch.int32, "radii", 1)
+    _check(sh_indices, torch.int64, "sh_indices", 1)
+    _check(g_indices, torch.int64, "g_indices", 1)
+    if clamped.dtype not in (torch.bool, torch.uint8) or not clamped.is_cuda:
+        raise RuntimeError("clamped must be a CUDA bool tensor")
+    if shs.dim() != 3 or shs.size(2) != 3:
+        raise RuntimeError(f"shs must be [F, coefficients, 3], got {tuple(shs.shape)}")
+    if tuple(scales.shape[1:]) != (3,) or tuple(rotations.shape) != (scales.size(0), 4):
+        raise RuntimeError("scales must be [G,3] and rotations [G,4]")
+    for t, name, numel in ((radii, "radii", p), (clamped, "clamped", 3 * p), (scale_factors, "scale_factors", p),
+                           (cov3d, "cov3d", 6 * p), (dl_dmean2d, "dl_dmean2d", 3 * p), (dl_dconic, "dl_dconic", 4 * p),
+                           (dl_dcolor, "dl_dcolor", 3 * p), (sh_indices, "sh_indices", p), (g_indices, "g_indices", p),
+                           (means3d, "means3d", 3 * p)):
+        if t.numel() != numel:
+            raise RuntimeError(f"{name} has {t.numel()} elements for {p} Gaussians, expected {numel}")
+    if viewmatrix.numel() != 16 or projmatrix.numel() != 16 or cam_pos.numel() != 3:
+        raise RuntimeError("viewmatrix / projmatrix must hold 16 values and cam_pos 3")
+    means3d, radii, shs, clamped = means3d.contiguous(), radii.contiguous(), shs.contiguous(), clamped.contiguous()
+    scales, scale_factors, rotations, cov3d = scales.contiguous(), scale_factors.contiguous(), _aligned(rotations), cov3d.contiguous()
+    viewmatrix, projmatrix, cam_pos = viewmatrix.contiguous(), projmatrix.contiguous(), cam_pos.contiguous()
+    dl_dmean2d, dl_dconic, dl_dcolor = dl_dmean2d.contiguous(), _aligned(dl_dconic), dl_dcolor.contiguous()
+    sh_indices, g_indices = sh_indices.contiguous(), g_indices.contiguous()
+    dev = means3d.device
+    import numpy as np
+    focal_y = float(np.float32(height) / (np.float32(2.0) * np.float32(tan_fovy)))       # rasterizer_impl.cu:468-469
+    focal_x = float(np.float32(width) / (np.float32(2.0) * np.float32(tan_fovx)))
+    with torch.cuda.device(dev):
+        out = {"means3d": torch.empty(p, 3, dtype=torch.float32, device=dev),
+               "cov3d": torch.empty(p, 6, dtype=torch.float32, device=dev),
+               "scale_factors": torch.empty(p, 1, dtype=torch.float32, device=dev),
+               "shs": torch.zeros(shs.shape, dtype=torch.float32, device=dev),
+               "scales": torch.zeros(scales.shape, dtype=torch.float32, device=dev),
+               "rotations": torch.zeros(rotations.shape, dtype=torch.float32, device=dev)}
+        rc = load().c3vq_preprocess_indexed_backward(
+            p, int(sh_degree), shs.size(1), _ptr(means3d), _ptr(radii), _ptr(shs), _ptr(clamped), _ptr(scales),
+            _ptr(scale_factors), _ptr(rotations), float(scale_modifier), _ptr(cov3d), _ptr(viewmatrix),
+            _ptr(projmatrix), focal_x, focal_y, float(tan_fovx), float(tan_fovy), _ptr(cam_pos), _ptr(dl_dmean2d),
+            _ptr(dl_dconic), _ptr(dl_dcolor), _ptr(out["means3d"]), _ptr(out["cov3d"]), _ptr(out["shs"]),
+            _ptr(out["scales"]), _ptr(out["scale_factors"]), _ptr(out["rotations"]), _ptr(sh_indices),
+            _ptr(g_indices), _stream(means3d))
     if rc:
         raise _err(rc)
     return out

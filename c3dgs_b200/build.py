@@ -16,7 +16,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libc3vq.so")
 SOURCES = ["api.cu", "assign_exact.cu", "assign_tc.cu", "update.cu", "gather.cu", "rot_scale.cu", "morton.cu",
-           "wire.cu", "preprocess.cu"]
+           "wire.cu", "preprocess.cu", "preprocess_bwd.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-std=c++17", "-lineinfo",

@@ -346,6 +346,38 @@ int c3vq_preprocess_indexed(int64_t p, int sh_degree, int sh_coeffs, const float
                                      out_clamped, (cudaStream_t)stream);
 }
 
+int c3vq_preprocess_indexed_backward(int64_t p, int sh_degree, int sh_coeffs, const float *means3d,
+                                     const int32_t *radii, const float *shs, const uint8_t *clamped,
+                                     const float *scales, const float *scale_factors, const float *rotations,
+                                     float scale_modifier, const float *cov3ds, const float *viewmatrix,
+                                     const float *projmatrix, float focal_x, float focal_y, float tan_fovx,
+                                     float tan_fovy, const float *cam_pos, const float *dl_dmean2d,
+                                     const float *dl_dconic, const float *dl_dcolor, float *dl_dmeans,
+                                     float *dl_dcov3d, float *dl_dsh, float *dl_dscale, float *dl_dscale_factor,
+                                     float *dl_drot, const int64_t *sh_indices, const int64_t *g_indices,
+                                     c3vq_stream_t stream)
+{
+    C3VQ_CHECK_ARG(p >= 0, "p=%lld is negative", (long long)p);
+    C3VQ_CHECK_ARG(sh_degree >= 0 && sh_degree <= 3 && sh_coeffs >= (sh_degree + 1) * (sh_degree + 1),
+                   "sh_degree=%d needs %d coefficients per row, got %d", sh_degree, (sh_degree + 1) * (sh_degree + 1),
+                   sh_coeffs);
+    C3VQ_CHECK_ARG(p == 0 || (means3d && radii && cov3ds && viewmatrix && projmatrix && cam_pos && dl_dmean2d &&
+                              dl_dconic && scale_factors),
+                   "null input pointer");
+    C3VQ_CHECK_ARG(p == 0 || shs == nullptr || (clamped && dl_dcolor && dl_dsh && sh_indices),
+                   "shs given without clamped / dl_dcolor / dl_dsh / sh_indices");
+    C3VQ_CHECK_ARG(p == 0 || scales == nullptr || (rotations && dl_dscale && dl_drot && g_indices),
+                   "scales given without rotations / dl_dscale / dl_drot / g_indices");
+    C3VQ_CHECK_ARG(p == 0 || (dl_dmeans && dl_dcov3d && dl_dscale_factor), "null output pointer");
+    C3VQ_CHECK_ARG(((uintptr_t)rotations & 15) == 0 && ((uintptr_t)dl_drot & 15) == 0 && ((uintptr_t)dl_dconic & 15) == 0,
+                   "rotations / dl_drot / dl_dconic must be 16-byte aligned");
+    return launch_preprocess_indexed_bwd(p, sh_degree, sh_coeffs, means3d, radii, shs, clamped, scales, scale_factors,
+                                         rotations, scale_modifier, cov3ds, viewmatrix, projmatrix, focal_x, focal_y,
+                                         tan_fovx, tan_fovy, cam_pos, dl_dmean2d, dl_dconic, dl_dcolor, dl_dmeans,
+                                         dl_dcov3d, dl_dsh, dl_dscale, dl_dscale_factor, dl_drot, sh_indices, g_indices,
+                                         (cudaStream_t)stream);
+}
+
 int c3vq_gather_rows(const float *x, const float *w, const int64_t *rows, int64_t n, int d, float *out_x,
                      float *out_w, c3vq_stream_t stream)
 {

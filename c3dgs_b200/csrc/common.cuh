@@ -98,6 +98,15 @@ int launch_preprocess_indexed(int64_t P, int deg, int M, const float *means, con
                               const int64_t *g_idx, int clamp_color, int *radii, float *xy, float *depths, float *cov3d,
                               float *rgb, float *conic, unsigned int *tiles, uint8_t *clamped, cudaStream_t s);
 
+// backward of the indexed preprocess (preprocess_bwd.cu); dL_dsh / dL_dscale / dL_drot are accumulated into
+int launch_preprocess_indexed_bwd(int64_t P, int deg, int M, const float *means, const int *radii, const float *shs,
+                                  const uint8_t *clamped, const float *scales, const float *factors, const float *rots,
+                                  float scale_modifier, const float *cov3d, const float *view, const float *proj,
+                                  float focal_x, float focal_y, float tan_fovx, float tan_fovy, const float *campos,
+                                  const float *dL_dmean2d, const float *dL_dconic, const float *dL_dcolor,
+                                  float *dL_dmeans, float *dL_dcov3d, float *dL_dsh, float *dL_dscale, float *dL_dfactor,
+                                  float *dL_drot, const int64_t *sh_idx, const int64_t *g_idx, cudaStream_t s);
+
 // tensor-core assignment (assign_tc.cu)
 size_t tc_workspace_bytes(int64_t n, int d, int k);
 int launch_assign_tc(const float *x, const float *w, const int64_t *rows, int64_t n, int d, const float *codebook,

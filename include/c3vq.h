@@ -243,6 +243,33 @@ int c3vq_preprocess_indexed(int64_t p, int sh_degree, int sh_coeffs, const float
                             float *out_conic_opacity /* [P,4] */, uint32_t *out_tiles_touched,
                             uint8_t *out_clamped /* [P,3] */, c3vq_stream_t stream);
 
+/*
+ * Backward of the same preprocess — where finetuning writes gradients into the two codebooks
+ * (cuda_rasterizer/backward_indexed.cu:469-550 BACKWARD::preprocess_indexed, declared at backward.h:63-92: the kernels
+ * computeCov2D_indexedCUDA :346-465 and preprocess_indexedCUDA :288-341 with computeColorFromSH_indexed :20-205 and
+ * computeCov3D_indexed :210-283).  Arguments in the reference's order:
+ *   inputs  radii / clamped / cov3ds are the forward pass' outputs; dl_dmean2d [P,3] (x, y used), dl_dconic [P,2,2]
+ *           (entries 0, 1, 3 used) and dl_dcolor [P,3] come from the render backward.
+ *   outputs dl_dmeans [P,3], dl_dcov3d [P,6], dl_dscale_factor [P] are written for every Gaussian (zeros where
+ *           radii <= 0; the reference leaves those rows at the zeros its wrapper allocated);
+ *           dl_dsh [F, sh_coeffs, 3], dl_dscale [G,3], dl_drot [G,4] are the TABLE gradients: every visible Gaussian
+ *           ADDS into the rows sh_indices / g_indices name, so the caller zeroes them first
+ *           (rasterize_points_indexed.cu:172-175 does the same with torch::zeros).
+ * One kernel instead of the reference's two; colour rows of 16 coefficients and rotation rows are added with 16-byte
+ * vector reductions.  float32; the sums over Gaussians are order dependent here as in the reference (atomics), so the
+ * table gradients agree to rounding, not bit for bit (tests/test_gpu_preprocess.py states the tolerances).
+ */
+int c3vq_preprocess_indexed_backward(int64_t p, int sh_degree, int sh_coeffs, const float *means3d,
+                                     const int32_t *radii, const float *shs, const uint8_t *clamped /* [P,3] */,
+                                     const float *scales, const float *scale_factors, const float *rotations,
+                                     float scale_modifier, const float *cov3ds /* [P,6] */, const float *viewmatrix,
+                                     const float *projmatrix, float focal_x, float focal_y, float tan_fovx,
+                                     float tan_fovy, const float *cam_pos, const float *dl_dmean2d,
+                                     const float *dl_dconic, const float *dl_dcolor, float *dl_dmeans,
+                                     float *dl_dcov3d, float *dl_dsh, float *dl_dscale, float *dl_dscale_factor,
+                                     float *dl_drot, const int64_t *sh_indices, const int64_t *g_indices,
+                                     c3vq_stream_t stream);
+
 /* Mini-batch row gather: out_x[i,:] = x[rows[i],:], out_w[i] = w[rows[i]] (w/out_w may be null). */
 int c3vq_gather_rows(const float *x, const float *w, const int64_t *rows, int64_t n, int d,
                      float *out_x, float *out_w, c3vq_stream_t stream);

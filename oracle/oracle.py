@@ -368,13 +368,14 @@ _SH_C3 = np.array([-0.5900435899266435, 2.890611442640554, -0.4570457994644658, 
 
 def preprocess_indexed(means3d, scales, scale_factors, rotations, opacities, shs, sh_indices, g_indices, viewmatrix,
                        projmatrix, cam_pos, width, height, tan_fovx, tan_fovy, sh_degree=3, scale_modifier=1.0,
-                       clamp_color=True):
+                       clamp_color=True, dtype=np.float32):
     """preprocess_indexedCUDA restated in numpy float32 (submodules/diff-gaussian-rasterization/cuda_rasterizer/
     forward_indexed.cu:166-272; computeColorFromSH_indexed :20-77, computeCov2D_indexed :79-121, computeCov3D_indexed
     :123-159; in_frustum / ndc2Pix / getRect / transformPoint auxiliary.h:42-152; focal lengths rasterizer_impl.cu:
     468-469).  viewmatrix / projmatrix: 16 floats, column-major.  Returns the kernel's outputs (zeros where the
-    kernel returns early)."""
-    f = np.float32
+    kernel returns early).  dtype=np.float64 evaluates the same expressions in double (used to check the backward
+    restatement below by finite differences)."""
+    f = dtype
     P = len(means3d)
     m = np.asarray(means3d, f)
     v = np.asarray(viewmatrix, f).reshape(16)
@@ -480,4 +481,182 @@ def preprocess_indexed(means3d, scales, scale_factors, rotations, opacities, shs
     out["clamped"][vis] = clamped[vis]
     out["conic_opacity"][vis] = np.stack([covz * det_inv, -covy * det_inv, covx * det_inv,
                                           np.asarray(opacities, f).reshape(P)], 1)[vis]
+    return out
+
+
+def preprocess_indexed_backward(means3d, radii, shs, clamped, scales, scale_factors, rotations, cov3d, viewmatrix,
+                                projmatrix, cam_pos, width, height, tan_fovx, tan_fovy, dl_dmean2d, dl_dconic,
+                                dl_dcolor, sh_indices, g_indices, sh_degree=3, scale_modifier=1.0, dtype=np.float32):
+    """BACKWARD::preprocess_indexed restated in numpy (submodules/diff-gaussian-rasterization/cuda_rasterizer/
+    backward_indexed.cu:469-550): computeCov2D_indexedCUDA :346-465, preprocess_indexedCUDA :288-341,
+    computeColorFromSH_indexed :20-205, computeCov3D_indexed :210-283; dnormvdv / transformVec4x3Transpose
+    auxiliary.h:83-110).  glm matrices are column-major: T[c][r] below is the reference's T[c][r].
+    Returns dict(means3d [P,3], cov3d [P,6], scale_factors [P], shs [F,M,3], scales [G,3], rotations [G,4]);
+    the table gradients are summed in float64 and rounded once (the reference's atomics are order dependent)."""
+    f = dtype
+    P = len(means3d)
+    m = np.asarray(means3d, f)
+    v = np.asarray(viewmatrix, f).reshape(16)
+    pj = np.asarray(projmatrix, f).reshape(16)
+    cam = np.asarray(cam_pos, f).reshape(3)
+    h_y = f(height) / (f(2.0) * f(tan_fovy))
+    h_x = f(width) / (f(2.0) * f(tan_fovx))
+    vis = np.asarray(radii).reshape(P) > 0
+    shs = np.asarray(shs, f)
+    F_, M = shs.shape[0], shs.shape[1]
+    G = len(scales)
+    two, one, half = f(2), f(1), f(0.5)
+    mx, my, mz = m[:, 0], m[:, 1], m[:, 2]
+    out = {"means3d": np.zeros((P, 3), f), "cov3d": np.zeros((P, 6), f), "scale_factors": np.zeros(P, f)}
+    with np.errstate(all="ignore"):
+        # ---- computeCov2D_indexedCUDA ----
+        c3 = np.asarray(cov3d, f).reshape(P, 6)
+        c0, c1, c2, c3_, c4, c5 = (c3[:, i] for i in range(6))
+        dcon = np.asarray(dl_dconic, f).reshape(P, 4)
+        dcx, dcy, dcz = dcon[:, 0], dcon[:, 1], dcon[:, 3]
+        tx = v[0] * mx + v[4] * my + v[8] * mz + v[12]
+        ty = v[1] * mx + v[5] * my + v[9] * mz + v[13]
+        tz = v[2] * mx + v[6] * my + v[10] * mz + v[14]
+        limx, limy = f(1.3) * f(tan_fovx), f(1.3) * f(tan_fovy)
+        txtz, tytz = tx / tz, ty / tz
+        tx = np.minimum(limx, np.maximum(-limx, txtz)) * tz
+        ty = np.minimum(limy, np.maximum(-limy, tytz)) * tz
+        xg = np.where((txtz < -limx) | (txtz > limx), f(0), f(1))
+        yg = np.where((tytz < -limy) | (tytz > limy), f(0), f(1))
+        j00, j02 = h_x / tz, -(h_x * tx) / (tz * tz)
+        j11, j12 = h_y / tz, -(h_y * ty) / (tz * tz)
+        T00, T01, T02 = v[0] * j00 + v[2] * j02, v[4] * j00 + v[6] * j02, v[8] * j00 + v[10] * j02
+        T10, T11, T12 = v[1] * j11 + v[2] * j12, v[5] * j11 + v[6] * j12, v[9] * j11 + v[10] * j12
+        u0, u1, u2 = T00 * c0 + T01 * c1 + T02 * c2, T00 * c1 + T01 * c3_ + T02 * c4, T00 * c2 + T01 * c4 + T02 * c5
+        w0, w1, w2 = T10 * c0 + T11 * c1 + T12 * c2, T10 * c1 + T11 * c3_ + T12 * c4, T10 * c2 + T11 * c4 + T12 * c5
+        a = T00 * u0 + T01 * u1 + T02 * u2 + f(0.3)
+        b = T00 * w0 + T01 * w1 + T02 * w2
+        c = T10 * w0 + T11 * w1 + T12 * w2 + f(0.3)
+        denom = a * c - b * b
+        d2 = one / ((denom * denom) + f(0.0000001))
+        ok = d2 != 0
+        dL_da = np.where(ok, d2 * (-c * c * dcx + two * b * c * dcy + (denom - a * c) * dcz), f(0))
+        dL_dc = np.where(ok, d2 * (-a * a * dcz + two * a * b * dcy + (denom - a * c) * dcx), f(0))
+        dL_db = np.where(ok, d2 * two * (b * c * dcx - (denom + two * b * b) * dcy + a * b * dcz), f(0))
+        dc3 = np.stack([
+            T00 * T00 * dL_da + T00 * T10 * dL_db + T10 * T10 * dL_dc,
+            two * T00 * T01 * dL_da + (T00 * T11 + T01 * T10) * dL_db + two * T10 * T11 * dL_dc,
+            two * T00 * T02 * dL_da + (T00 * T12 + T02 * T10) * dL_db + two * T10 * T12 * dL_dc,
+            T01 * T01 * dL_da + T01 * T11 * dL_db + T11 * T11 * dL_dc,
+            two * T02 * T01 * dL_da + (T01 * T12 + T02 * T11) * dL_db + two * T11 * T12 * dL_dc,
+            T02 * T02 * dL_da + T02 * T12 * dL_db + T12 * T12 * dL_dc], 1)
+        dc3 = np.where(ok[:, None], dc3, f(0)).astype(f)
+        dT00, dT01, dT02 = two * u0 * dL_da + w0 * dL_db, two * u1 * dL_da + w1 * dL_db, two * u2 * dL_da + w2 * dL_db
+        dT10, dT11, dT12 = two * w0 * dL_dc + u0 * dL_db, two * w1 * dL_dc + u1 * dL_db, two * w2 * dL_dc + u2 * dL_db
+        dJ00 = v[0] * dT00 + v[4] * dT01 + v[8] * dT02
+        dJ02 = v[2] * dT00 + v[6] * dT01 + v[10] * dT02
+        dJ11 = v[1] * dT10 + v[5] * dT11 + v[9] * dT12
+        dJ12 = v[2] * dT10 + v[6] * dT11 + v[10] * dT12
+        itz = one / tz
+        itz2 = itz * itz
+        itz3 = itz2 * itz
+        dtx = xg * -h_x * itz2 * dJ02
+        dty = yg * -h_y * itz2 * dJ12
+        dtz = -h_x * itz2 * dJ00 - h_y * itz2 * dJ11 + (two * h_x * tx) * itz3 * dJ02 + (two * h_y * ty) * itz3 * dJ12
+        dm = np.stack([v[0] * dtx + v[1] * dty + v[2] * dtz, v[4] * dtx + v[5] * dty + v[6] * dtz,
+                       v[8] * dtx + v[9] * dty + v[10] * dtz], 1)
+        # ---- preprocess_indexedCUDA: screen position ----
+        hw = pj[3] * mx + pj[7] * my + pj[11] * mz + pj[15]
+        m_w = one / (hw + f(0.0000001))
+        mul1 = (pj[0] * mx + pj[4] * my + pj[8] * mz + pj[12]) * m_w * m_w
+        mul2 = (pj[1] * mx + pj[5] * my + pj[9] * mz + pj[13]) * m_w * m_w
+        g2 = np.asarray(dl_dmean2d, f).reshape(P, 3)
+        g2x, g2y = g2[:, 0], g2[:, 1]
+        dm = dm + np.stack([(pj[0] * m_w - pj[3] * mul1) * g2x + (pj[1] * m_w - pj[3] * mul2) * g2y,
+                            (pj[4] * m_w - pj[7] * mul1) * g2x + (pj[5] * m_w - pj[7] * mul2) * g2y,
+                            (pj[8] * m_w - pj[11] * mul1) * g2x + (pj[9] * m_w - pj[11] * mul2) * g2y], 1)
+        # ---- computeColorFromSH_indexed ----
+        si = np.asarray(sh_indices, np.int64)
+        o = m - cam[None, :]
+        ln = np.sqrt(o[:, 0] * o[:, 0] + o[:, 1] * o[:, 1] + o[:, 2] * o[:, 2])
+        x, y, z = o[:, 0] / ln, o[:, 1] / ln, o[:, 2] / ln
+        sh = shs[si]
+        gRGB = np.asarray(dl_dcolor, f).reshape(P, 3) * np.where(np.asarray(clamped).reshape(P, 3), f(0), f(1))
+        bw = np.zeros((P, M), f)
+        bw[:, 0] = _SH_C0
+        dRx, dRy, dRz = np.zeros((P, 3), f), np.zeros((P, 3), f), np.zeros((P, 3), f)
+        C1, C2, C3 = f(_SH_C1), _SH_C2.astype(f), _SH_C3.astype(f)
+        col = lambda t: t[:, None]                                                   # noqa: E731
+        if sh_degree > 0:
+            bw[:, 1], bw[:, 2], bw[:, 3] = -C1 * y, C1 * z, -C1 * x
+            dRx, dRy, dRz = -C1 * sh[:, 3], -C1 * sh[:, 1], C1 * sh[:, 2]
+            if sh_degree > 1:
+                xx, yy, zz, xy, yz, xz = x * x, y * y, z * z, x * y, y * z, x * z
+                bw[:, 4], bw[:, 5], bw[:, 6] = C2[0] * xy, C2[1] * yz, C2[2] * (two * zz - xx - yy)
+                bw[:, 7], bw[:, 8] = C2[3] * xz, C2[4] * (xx - yy)
+                dRx = dRx + col(C2[0] * y) * sh[:, 4] + col(C2[2] * two * -x) * sh[:, 6] + col(C2[3] * z) * sh[:, 7] + col(C2[4] * two * x) * sh[:, 8]
+                dRy = dRy + col(C2[0] * x) * sh[:, 4] + col(C2[1] * z) * sh[:, 5] + col(C2[2] * two * -y) * sh[:, 6] + col(C2[4] * two * -y) * sh[:, 8]
+                dRz = dRz + col(C2[1] * y) * sh[:, 5] + col(C2[2] * two * two * z) * sh[:, 6] + col(C2[3] * x) * sh[:, 7]
+                if sh_degree > 2:
+                    t3, t4 = f(3), f(4)
+                    bw[:, 9] = C3[0] * y * (t3 * xx - yy)
+                    bw[:, 10] = C3[1] * xy * z
+                    bw[:, 11] = C3[2] * y * (t4 * zz - xx - yy)
+                    bw[:, 12] = C3[3] * z * (two * zz - t3 * xx - t3 * yy)
+                    bw[:, 13] = C3[4] * x * (t4 * zz - xx - yy)
+                    bw[:, 14] = C3[5] * z * (xx - yy)
+                    bw[:, 15] = C3[6] * x * (xx - t3 * yy)
+                    dRx = dRx + (col(C3[0] * t3 * two * xy) * sh[:, 9] + col(C3[1] * yz) * sh[:, 10] + col(C3[2] * -two * xy) * sh[:, 11]
+                                 + col(C3[3] * -t3 * two * xz) * sh[:, 12] + col(C3[4] * (-t3 * xx + t4 * zz - yy)) * sh[:, 13]
+                                 + col(C3[5] * two * xz) * sh[:, 14] + col(C3[6] * t3 * (xx - yy)) * sh[:, 15])
+                    dRy = dRy + (col(C3[0] * t3 * (xx - yy)) * sh[:, 9] + col(C3[1] * xz) * sh[:, 10]
+                                 + col(C3[2] * (-t3 * yy + t4 * zz - xx)) * sh[:, 11] + col(C3[3] * -t3 * two * yz) * sh[:, 12]
+                                 + col(C3[4] * -two * xy) * sh[:, 13] + col(C3[5] * -two * yz) * sh[:, 14]
+                                 + col(C3[6] * -t3 * two * xy) * sh[:, 15])
+                    dRz = dRz + (col(C3[1] * xy) * sh[:, 10] + col(C3[2] * t4 * two * yz) * sh[:, 11]
+                                 + col(C3[3] * t3 * (two * zz - xx - yy)) * sh[:, 12] + col(C3[4] * t4 * two * xz) * sh[:, 13]
+                                 + col(C3[5] * (xx - yy)) * sh[:, 14])
+        contrib_sh = bw[:, :, None] * gRGB[:, None, :]                                # [P, M, 3]
+        if sh_degree > 0:
+            ddir = np.stack([(dRx * gRGB).sum(1), (dRy * gRGB).sum(1), (dRz * gRGB).sum(1)], 1).astype(f)
+        else:
+            ddir = np.zeros((P, 3), f)
+        ox, oy, oz = o[:, 0], o[:, 1], o[:, 2]
+        sum2 = ox * ox + oy * oy + oz * oz
+        inv32 = one / np.sqrt(sum2 * sum2 * sum2)
+        dm = dm + np.stack([((sum2 - ox * ox) * ddir[:, 0] - oy * ox * ddir[:, 1] - oz * ox * ddir[:, 2]) * inv32,
+                            (-ox * oy * ddir[:, 0] + (sum2 - oy * oy) * ddir[:, 1] - oz * oy * ddir[:, 2]) * inv32,
+                            (-ox * oz * ddir[:, 0] - oy * oz * ddir[:, 1] + (sum2 - oz * oz) * ddir[:, 2]) * inv32], 1)
+        # ---- computeCov3D_indexed ----
+        gi = np.asarray(g_indices, np.int64)
+        fac = np.asarray(scale_factors, f).reshape(P)
+        scl = np.asarray(scales, f)[gi]
+        q = np.asarray(rotations, f)[gi]
+        r, qx, qy, qz = q[:, 0], q[:, 1], q[:, 2], q[:, 3]
+        s = (fac * f(scale_modifier))[:, None] * scl
+        Rs = np.empty((P, 3, 3), f)                                                  # standard rotation matrix
+        Rs[:, 0, 0] = one - two * (qy * qy + qz * qz); Rs[:, 0, 1] = two * (qx * qy - r * qz); Rs[:, 0, 2] = two * (qx * qz + r * qy)
+        Rs[:, 1, 0] = two * (qx * qy + r * qz); Rs[:, 1, 1] = one - two * (qx * qx + qz * qz); Rs[:, 1, 2] = two * (qy * qz - r * qx)
+        Rs[:, 2, 0] = two * (qx * qz - r * qy); Rs[:, 2, 1] = two * (qy * qz + r * qx); Rs[:, 2, 2] = one - two * (qx * qx + qy * qy)
+        dS = np.empty((P, 3, 3), f)
+        dS[:, 0, 0], dS[:, 1, 1], dS[:, 2, 2] = dc3[:, 0], dc3[:, 3], dc3[:, 5]
+        dS[:, 0, 1] = dS[:, 1, 0] = half * dc3[:, 1]
+        dS[:, 0, 2] = dS[:, 2, 0] = half * dc3[:, 2]
+        dS[:, 1, 2] = dS[:, 2, 1] = half * dc3[:, 4]
+        Mm = two * (s[:, :, None] * np.transpose(Rs, (0, 2, 1)))                      # 2 M[i][k] = 2 s_i Rs[k][i]
+        N = np.einsum("nik,nkc->nic", Mm, dS).astype(f)                               # dL_dM[i][c]
+        ds = np.einsum("nci,nic->ni", Rs, N).astype(f)                                # sum_c Rs[c][i] N[i][c]
+        contrib_scale = ds * fac[:, None]
+        dfac = (ds * scl).sum(1).astype(f)
+        N = N * s[:, :, None]
+        dq = np.stack([
+            two * qz * (N[:, 0, 1] - N[:, 1, 0]) + two * qy * (N[:, 2, 0] - N[:, 0, 2]) + two * qx * (N[:, 1, 2] - N[:, 2, 1]),
+            two * qy * (N[:, 1, 0] + N[:, 0, 1]) + two * qz * (N[:, 2, 0] + N[:, 0, 2]) + two * r * (N[:, 1, 2] - N[:, 2, 1]) - f(4) * qx * (N[:, 2, 2] + N[:, 1, 1]),
+            two * qx * (N[:, 1, 0] + N[:, 0, 1]) + two * r * (N[:, 2, 0] - N[:, 0, 2]) + two * qz * (N[:, 1, 2] + N[:, 2, 1]) - f(4) * qy * (N[:, 2, 2] + N[:, 0, 0]),
+            two * r * (N[:, 0, 1] - N[:, 1, 0]) + two * qx * (N[:, 2, 0] + N[:, 0, 2]) + two * qy * (N[:, 1, 2] + N[:, 2, 1]) - f(4) * qz * (N[:, 1, 1] + N[:, 0, 0])], 1)
+    out["means3d"][vis] = dm[vis]
+    out["cov3d"][vis] = dc3[vis]
+    out["scale_factors"][vis] = dfac[vis]
+    acc_sh = np.zeros((F_, M, 3), np.float64)
+    np.add.at(acc_sh, si[vis], contrib_sh[vis].astype(np.float64))
+    acc_s = np.zeros((G, 3), np.float64)
+    np.add.at(acc_s, gi[vis], contrib_scale[vis].astype(np.float64))
+    acc_q = np.zeros((G, 4), np.float64)
+    np.add.at(acc_q, gi[vis], dq[vis].astype(np.float64))
+    out["shs"], out["scales"], out["rotations"] = acc_sh.astype(f), acc_s.astype(f), acc_q.astype(f)
     return out

@@ -150,3 +150,153 @@ def test_preprocess_edge_cases_and_errors(L, oracle):
     with pytest.raises(RuntimeError, match="CUDA"):
         L.preprocess_indexed(t["means3d"].cpu(), t["scales"], t["scale_factors"], t["rotations"], t["opacities"], t["shs"],
                              t["sh_indices"], t["g_indices"], c["viewmatrix"], c["projmatrix"], c["cam_pos"], 64, 48, 0.5, 0.4)
+
+
+# ------------------------------------------------------------------------------------------------
+# Backward (second half): c3vq_preprocess_indexed_backward against the numpy oracle and against
+# the reference's own backward_indexed.cu compiled unmodified (oracle/_ref/libpreprocess_bwd_ref.so).
+#
+# Tolerances.  float32 throughout; the three implementations differ in fma contraction and in the order of sums,
+# and the table gradients are sums over Gaussians in atomic order (reference and product alike).  Errors are measured
+# per row, relative to the row's largest entry.  The float32 and float64 evaluations of the oracle itself differ by
+# 2e-7 (median), 1e-4 (99.9th percentile) and 1e-2 (worst row: the size-factor gradient is a sum of three cancelling
+# terms), so the test asks for median <= 2e-6, 99.9th percentile <= 5e-4, worst row <= 5e-2.
+BWD_SO = os.path.join(ROOT, "oracle", "_ref", "libpreprocess_bwd_ref.so")
+BWD_KEYS = ("means3d", "cov3d", "scale_factors", "shs", "scales", "rotations")
+
+
+def _grads(p, seed):
+    rng = np.random.default_rng(seed)
+    return {"dl_dmean2d": rng.standard_normal((p, 3)).astype(np.float32),
+            "dl_dconic": rng.standard_normal((p, 2, 2)).astype(np.float32),
+            "dl_dcolor": rng.standard_normal((p, 3)).astype(np.float32)}
+
+
+def _run_bwd(L, sc, cam, fwd, gr, deg=3, mod=1.0):
+    t = {k: torch.from_numpy(np.ascontiguousarray(v)).to(DEV) for k, v in {**sc, **gr}.items()}
+    c = {k: torch.from_numpy(v).to(DEV) for k, v in cam.items() if isinstance(v, np.ndarray)}
+    out = L.preprocess_indexed_backward(
+        t["means3d"], torch.from_numpy(fwd["radii"]).to(DEV), t["shs"], torch.from_numpy(fwd["clamped"]).to(DEV),
+        t["scales"], t["scale_factors"], t["rotations"], torch.from_numpy(fwd["cov3d"]).to(DEV), c["viewmatrix"],
+        c["projmatrix"], c["cam_pos"], cam["width"], cam["height"], cam["tan_fovx"], cam["tan_fovy"], t["dl_dmean2d"],
+        t["dl_dconic"], t["dl_dcolor"], t["sh_indices"], t["g_indices"], sh_degree=deg, scale_modifier=mod)
+    return {k: v.cpu().numpy().reshape(v.shape[0], -1) for k, v in out.items()}
+
+
+def _run_bwd_reference(sc, cam, fwd, gr, deg=3, mod=1.0):
+    lib = ctypes.CDLL(BWD_SO)
+    p = len(sc["means3d"])
+    t = {k: torch.from_numpy(np.ascontiguousarray(v)).to(DEV) for k, v in {**sc, **gr}.items()}
+    c = {k: torch.from_numpy(v).to(DEV) for k, v in cam.items() if isinstance(v, np.ndarray)}
+    radii, clamped, cov3d = (torch.from_numpy(fwd[k]).to(DEV) for k in ("radii", "clamped", "cov3d"))
+    out = {"means3d": torch.zeros(p, 3, device=DEV), "cov3d": torch.zeros(p, 6, device=DEV),
+           "scale_factors": torch.zeros(p, 1, device=DEV), "shs": torch.zeros_like(t["shs"]),
+           "scales": torch.zeros_like(t["scales"]), "rotations": torch.zeros_like(t["rotations"])}
+    vp, fl, it = ctypes.c_void_p, ctypes.c_float, ctypes.c_int
+    lib.ref_preprocess_indexed_backward.argtypes = [it, it, it, vp, vp, vp, vp, vp, vp, vp, fl, vp, vp, vp, fl, fl, fl,
+                                                    fl, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]
+    f32 = np.float32
+    focal_y = float(f32(cam["height"]) / (f32(2.0) * f32(cam["tan_fovy"])))
+    focal_x = float(f32(cam["width"]) / (f32(2.0) * f32(cam["tan_fovx"])))
+    torch.cuda.synchronize()
+    rc = lib.ref_preprocess_indexed_backward(
+        p, deg, sc["shs"].shape[1], t["means3d"].data_ptr(), radii.data_ptr(), t["shs"].data_ptr(), clamped.data_ptr(),
+        t["scales"].data_ptr(), t["scale_factors"].data_ptr(), t["rotations"].data_ptr(), mod, cov3d.data_ptr(),
+        c["viewmatrix"].data_ptr(), c["projmatrix"].data_ptr(), focal_x, focal_y, cam["tan_fovx"], cam["tan_fovy"],
+        c["cam_pos"].data_ptr(), t["dl_dmean2d"].data_ptr(), t["dl_dconic"].data_ptr(), out["means3d"].data_ptr(),
+        t["dl_dcolor"].data_ptr(), out["cov3d"].data_ptr(), out["shs"].data_ptr(), out["scales"].data_ptr(),
+        out["scale_factors"].data_ptr(), out["rotations"].data_ptr(), t["sh_indices"].data_ptr(),
+        t["g_indices"].data_ptr())
+    assert rc == 0
+    return {k: v.cpu().numpy().reshape(v.shape[0], -1) for k, v in out.items()}
+
+
+def _oracle_bwd(oracle, sc, cam, fwd, gr, deg=3, mod=1.0, dtype=np.float32):
+    out = oracle.preprocess_indexed_backward(
+        sc["means3d"], fwd["radii"], sc["shs"], fwd["clamped"], sc["scales"], sc["scale_factors"], sc["rotations"],
+        fwd["cov3d"], cam["viewmatrix"], cam["projmatrix"], cam["cam_pos"], cam["width"], cam["height"],
+        cam["tan_fovx"], cam["tan_fovy"], gr["dl_dmean2d"], gr["dl_dconic"], gr["dl_dcolor"], sc["sh_indices"],
+        sc["g_indices"], sh_degree=deg, scale_modifier=mod, dtype=dtype)
+    return {k: np.asarray(v).reshape(len(v), -1) for k, v in out.items()}
+
+
+def _compare_bwd(a, b, what):
+    for k in BWD_KEYS:
+        x, y = a[k].astype(np.float64), b[k].astype(np.float64)
+        assert x.shape == y.shape, f"{what}: {k} shape {x.shape} vs {y.shape}"
+        assert np.array_equal(np.abs(x).sum(1) > 0, np.abs(y).sum(1) > 0) or \
+            ((np.abs(x).sum(1) > 0) != (np.abs(y).sum(1) > 0)).mean() <= 1e-4, f"{what}: {k} support differs"
+        live = np.abs(y).max(1) > 0
+        assert live.sum() > 0, f"{what}: {k} is all zero"
+        e = (np.abs(x - y)[live] / np.abs(y)[live].max(1, keepdims=True)).max(1)
+        assert np.isfinite(x).all(), f"{what}: {k} holds non-finite values"
+        assert np.median(e) <= 2e-6 and np.quantile(e, 0.999) <= 5e-4 and e.max() <= 5e-2, \
+            f"{what}: {k} row-relative error median {np.median(e):.2e}, p99.9 {np.quantile(e, 0.999):.2e}, max {e.max():.2e}"
+
+
+@pytest.mark.parametrize("deg,mod", [(3, 1.0), (0, 1.0), (2, 0.6), (1, 1.7)])
+def test_preprocess_backward_vs_oracle(L, oracle, deg, mod):
+    sc, cam = scene(60_000, seed=20 + deg), camera()
+    fwd = _run(L, sc, cam, deg, mod, True)
+    gr = _grads(60_000, deg)
+    got = _run_bwd(L, sc, cam, fwd, gr, deg, mod)
+    want = _oracle_bwd(oracle, sc, cam, fwd, gr, deg, mod)
+    culled = fwd["radii"] <= 0
+    assert culled.any() and (~culled).any()
+    for k in ("means3d", "cov3d", "scale_factors"):                 # culled Gaussians: exact zeros
+        assert not got[k][culled].any()
+    if deg < 3:                                                     # coefficients beyond the active degree: untouched
+        assert not got["shs"].reshape(len(sc["shs"]), 16, 3)[:, (deg + 1) ** 2:].any()
+    _compare_bwd(got, want, "oracle")
+
+
+@pytest.mark.skipif(not os.path.exists(BWD_SO), reason="oracle/_ref/libpreprocess_bwd_ref.so not built (make -C oracle ref_preprocess_bwd)")
+@pytest.mark.parametrize("deg,mod", [(3, 1.0), (2, 0.6)])
+def test_reference_backward_kernels_pin_oracle_and_product(L, oracle, deg, mod):
+    """The reference's own computeCov2D_indexedCUDA + preprocess_indexedCUDA (backward_indexed.cu, unmodified) on the
+    B200 next to the product kernel and the numpy restatement, on a 300 k-Gaussian scene with 20 k shape rows and
+    50 k colour rows (so table rows collect several Gaussians each)."""
+    sc, cam = scene(300_000, g=20_000, f=50_000, seed=30 + deg), camera(width=1297, height=840, fovx=0.9)
+    fwd = _run(L, sc, cam, deg, mod, True)
+    gr = _grads(300_000, 7 + deg)
+    ref = _run_bwd_reference(sc, cam, fwd, gr, deg, mod)
+    got = _run_bwd(L, sc, cam, fwd, gr, deg, mod)
+    want = _oracle_bwd(oracle, sc, cam, fwd, gr, deg, mod)
+    _compare_bwd(got, ref, "product vs reference kernels")
+    _compare_bwd(want, ref, "oracle vs reference kernels")
+
+
+def test_preprocess_backward_edge_cases_and_errors(L, oracle):
+    cam = camera(width=64, height=48)
+    c = {k: torch.from_numpy(v).to(DEV) for k, v in cam.items() if isinstance(v, np.ndarray)}
+    for p in (0, 1, 255, 257):
+        s2 = scene(max(p, 1), g=3, f=2, seed=40 + p)
+        if p == 0:
+            s2 = {k: (v[:0] if k in ("means3d", "scale_factors", "opacities", "sh_indices", "g_indices") else v) for k, v in s2.items()}
+        fwd = _run(L, s2, cam)
+        got = _run_bwd(L, s2, cam, fwd, _grads(p, p))
+        assert got["means3d"].shape == (p, 3) and got["shs"].shape == (2, 48) and got["rotations"].shape == (3, 4)
+        if p:
+            _compare_bwd_small = _oracle_bwd(oracle, s2, cam, fwd, _grads(p, p))
+            for k in BWD_KEYS:
+                assert np.allclose(got[k], _compare_bwd_small[k], rtol=2e-3, atol=1e-5 * (np.abs(_compare_bwd_small[k]).max() + 1e-30))
+    # a colour table with 9 coefficients per row (degree 2 scenes): the scalar-atomic path
+    s9 = scene(5000, g=50, f=40, seed=9, coeffs=9)
+    fwd = _run(L, s9, cam, deg=2)
+    gr = _grads(5000, 9)
+    got = _run_bwd(L, s9, cam, fwd, gr, deg=2)
+    want = _oracle_bwd(oracle, s9, cam, fwd, gr, deg=2)
+    _compare_bwd(got, want, "9-coefficient table")
+    t = {k: torch.from_numpy(v).to(DEV) for k, v in s9.items()}
+    g = {k: torch.from_numpy(v).to(DEV) for k, v in gr.items()}
+    f = {k: torch.from_numpy(fwd[k]).to(DEV) for k in ("radii", "clamped", "cov3d")}
+    with pytest.raises(RuntimeError):                          # degree 3 needs 16 coefficients per row
+        L.preprocess_indexed_backward(t["means3d"], f["radii"], t["shs"], f["clamped"], t["scales"], t["scale_factors"],
+                                      t["rotations"], f["cov3d"], c["viewmatrix"], c["projmatrix"], c["cam_pos"], 64, 48,
+                                      0.5, 0.4, g["dl_dmean2d"], g["dl_dconic"], g["dl_dcolor"], t["sh_indices"],
+                                      t["g_indices"], sh_degree=3)
+    with pytest.raises(RuntimeError, match="elements"):        # gradient array of the wrong length
+        L.preprocess_indexed_backward(t["means3d"], f["radii"], t["shs"], f["clamped"], t["scales"], t["scale_factors"],
+                                      t["rotations"], f["cov3d"], c["viewmatrix"], c["projmatrix"], c["cam_pos"], 64, 48,
+                                      0.5, 0.4, g["dl_dmean2d"][:10], g["dl_dconic"], g["dl_dcolor"], t["sh_indices"],
+                                      t["g_indices"], sh_degree=2)

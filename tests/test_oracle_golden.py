@@ -296,3 +296,60 @@ def test_oracle_preprocess_known_answers(oracle):
     assert out["clamped"][0].tolist() == [False, True, False]
     assert np.allclose(out["rgb"][2], 0.5) and out["depths"][2] == 4.0
     assert np.allclose(out["xy"][2], [((1.0 / 4 / tanx + 1) * w - 1) / 2, ((0.5 / 4 / tany + 1) * h - 1) / 2], atol=1e-3)
+
+
+def test_oracle_preprocess_backward_matches_finite_differences(oracle):
+    """The backward restatement (backward_indexed.cu:20-465) against central differences of the forward restatement,
+    both evaluated in float64: L = <g, conic> + <g, pixel position> + <g, rgb> over the visible Gaussians.  The
+    render backward hands over the screen-position gradient in NDC units (pixel gradient x W/2, H/2) and HALF the
+    gradient of the conic's off-diagonal entry (it appears twice in the quadratic form; backward_indexed.cu:415-417
+    multiply it back by 2)."""
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from preprocess_scene import camera, scene
+    P = 300
+    sc, cam = scene(P, g=30, f=40, seed=1), camera(width=320, height=200)
+    for deg in (3, 1):
+        def fw(s):
+            return oracle.preprocess_indexed(**s, **cam, sh_degree=deg, clamp_color=True, dtype=np.float64)
+        base = fw(sc)
+        vis = base["radii"] > 0
+        assert 0.2 < vis.mean() < 0.9
+        rng = np.random.default_rng(5)
+        gcon, gxy, grgb = rng.standard_normal((P, 3)), rng.standard_normal((P, 2)) * 1e-2, rng.standard_normal((P, 3))
+
+        def loss(s):
+            o = fw(s)
+            assert np.array_equal(o["radii"] > 0, vis)
+            return ((gcon[vis] * o["conic_opacity"][vis, :3]).sum() + (gxy[vis] * o["xy"][vis]).sum()
+                    + (grgb[vis] * o["rgb"][vis]).sum())
+
+        dcon = np.zeros((P, 4))
+        dcon[:, 0], dcon[:, 1], dcon[:, 3] = gcon[:, 0], 0.5 * gcon[:, 1], gcon[:, 2]
+        d2d = np.zeros((P, 3))
+        d2d[:, 0], d2d[:, 1] = gxy[:, 0] * cam["width"] / 2, gxy[:, 1] * cam["height"] / 2
+        bw = oracle.preprocess_indexed_backward(
+            sc["means3d"], base["radii"], sc["shs"], base["clamped"], sc["scales"], sc["scale_factors"], sc["rotations"],
+            base["cov3d"], cam["viewmatrix"], cam["projmatrix"], cam["cam_pos"], cam["width"], cam["height"],
+            cam["tan_fovx"], cam["tan_fovy"], d2d, dcon, grgb, sc["sh_indices"], sc["g_indices"], sh_degree=deg,
+            dtype=np.float64)
+        assert not bw["means3d"][~vis].any() and not bw["cov3d"][~vis].any()
+        visidx = np.flatnonzero(vis)
+        for key, eps in (("means3d", 1e-6), ("scale_factors", 1e-8), ("shs", 1e-5), ("scales", 1e-6), ("rotations", 1e-6)):
+            for _ in range(6):
+                i = visidx[rng.integers(len(visidx))]
+                if key == "means3d":
+                    ix = (i, rng.integers(3))
+                elif key == "scale_factors":
+                    ix = (i,)
+                elif key == "shs":
+                    ix = (sc["sh_indices"][i], rng.integers((deg + 1) ** 2), rng.integers(3))
+                else:
+                    ix = (sc["g_indices"][i], rng.integers(3 if key == "scales" else 4))
+                s2 = {k: (v.astype(np.float64) if v.dtype == np.float32 else v) for k, v in sc.items()}
+                s2[key][ix] += eps
+                lp = loss(s2)
+                s2[key][ix] -= 2 * eps
+                lm = loss(s2)
+                num, ana = (lp - lm) / (2 * eps), bw[key][ix]
+                assert abs(num - ana) <= 5e-5 * (abs(num) + abs(ana)) + 1e-9, (deg, key, ix, num, ana)
