@@ -131,18 +131,42 @@ def _check(t: torch.Tensor, dtype, name: str, ndim=None):
         raise RuntimeError(f"{name} must have {ndim} dimensions, got {t.dim()}")
 
 
+def _check_rows(rows: torch.Tensor, n_rows: int, trusted: bool = False) -> torch.Tensor:
+    """Mini-batch indirection: int64 row numbers into x.  The kernels read x[rows[i]] unchecked, so the range is
+    verified here (the reference's features[batch] raises a device-side assert for the same input) unless the
+    caller vouches for it (`rows_checked=True`: indices drawn by torch.randint(0, n), as vq_features does — the
+    check costs a reduction and a host sync per call)."""
+    _check(rows, torch.int64, "rows", 1)
+    rows = rows.contiguous()
+    if rows.numel() and not trusted:
+        lo, hi = torch.aminmax(rows)
+        if int(lo) < 0 or int(hi) >= n_rows:
+            raise IndexError(f"rows must lie in [0, {n_rows}), got [{int(lo)}, {int(hi)}]")
+    return rows
+
+
 class Workspace:
-    """Grow-only device scratch owned by the Python side (the C side never allocates)."""
+    """Grow-only device scratch owned by the Python side (the C side never allocates), one buffer per
+    (device, stream).  The scratch holds state a running kernel depends on (stats header, TF32 codebook image,
+    fallback list, sorted-sum tables), so two streams of one device must not share it; a buffer is allocated while
+    its stream is current, which is also what makes dropping it on a grow safe (the caching allocator hands a freed
+    block to later work of the same stream only).  Callers on one stream are serialised by the stream itself;
+    Python threads are serialised by the lock around the lookup."""
 
     def __init__(self):
         self._buf = {}
+        self._lock = threading.Lock()
 
     def get(self, device: torch.device, nbytes: int) -> torch.Tensor:
-        key = (device.type, device.index)
-        buf = self._buf.get(key)
-        if buf is None or buf.numel() < nbytes:
-            buf = torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=device)
-            self._buf[key] = buf
+        index = device.index if device.index is not None else torch.cuda.current_device()
+        dev = torch.device("cuda", index)
+        key = (index, torch.cuda.current_stream(dev).cuda_stream)
+        with self._lock:
+            buf = self._buf.get(key)
+            if buf is None or buf.numel() < nbytes:
+                with torch.cuda.device(dev):
+                    buf = torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=dev)
+                self._buf[key] = buf
         return buf
 
 
@@ -193,7 +217,7 @@ def assign(x: torch.Tensor, codebook: torch.Tensor, rows: torch.Tensor | None = 
 
 def update(x: torch.Tensor, w: torch.Tensor, codebook: torch.Tensor, entry_importance: torch.Tensor,
            decay: float, eps: float, rows: torch.Tensor | None = None, scale_normalize: bool = False,
-           tensor_cores: bool = True, return_dist: bool = True, return_idx: bool = False):
+           tensor_cores: bool = True, return_dist: bool = True, return_idx: bool = False, rows_checked: bool = False):
     """One VectorQuantize.update (vq.py:28-35) in place on codebook / entry_importance.  c3vq_update."""
     _check(x, torch.float32, "x", 2)
     _check(w, torch.float32, "importance", 1)
@@ -205,15 +229,17 @@ def update(x: torch.Tensor, w: torch.Tensor, codebook: torch.Tensor, entry_impor
         raise RuntimeError("coefs and codebook must have same number of channels")
     x = x.contiguous()
     w = w.contiguous()
+    if w.numel() != x.size(0):
+        # with `rows` the kernels read w[rows[i]]: importance is indexed like x, not like the batch
+        raise RuntimeError("importance must have one entry per row of x")
     if rows is not None:
-        _check(rows, torch.int64, "rows", 1)
-        rows = rows.contiguous()
+        rows = _check_rows(rows, x.size(0), rows_checked)
         n = rows.numel()
     else:
         n = x.size(0)
-        if w.numel() != n:
-            raise RuntimeError("importance must have one entry per row of x")
     d, k = x.size(1), codebook.size(0)
+    if scale_normalize and d < 6:
+        raise RuntimeError("scale_normalize needs the 6 stored covariance entries (columns 0, 3, 5 are the trace)")
     L = load()
     with torch.cuda.device(x.device):
         dist = torch.empty(n, dtype=torch.float32, device=x.device) if return_dist else None
@@ -229,7 +255,7 @@ def update(x: torch.Tensor, w: torch.Tensor, codebook: torch.Tensor, entry_impor
 
 
 def assign_accumulate(x, w, codebook, acc: torch.Tensor | None = None, rows=None, tensor_cores: bool = True,
-                      return_dist: bool = False, return_idx: bool = True):
+                      return_dist: bool = False, return_idx: bool = True, rows_checked: bool = False):
     """Assignment + weighted sums added into acc, no EMA (multi-GPU building block).  c3vq_assign_accumulate."""
     _check(x, torch.float32, "x", 2)
     _check(w, torch.float32, "importance", 1)
@@ -237,9 +263,10 @@ def assign_accumulate(x, w, codebook, acc: torch.Tensor | None = None, rows=None
     if codebook.size(1) != x.size(1):
         raise RuntimeError("coefs and codebook must have same number of channels")
     x, w, codebook = x.contiguous(), w.contiguous(), codebook.contiguous()
+    if w.numel() != x.size(0):
+        raise RuntimeError("importance must have one entry per row of x")
     if rows is not None:
-        _check(rows, torch.int64, "rows", 1)
-        rows = rows.contiguous()
+        rows = _check_rows(rows, x.size(0), rows_checked)
     n = rows.numel() if rows is not None else x.size(0)
     d, k = x.size(1), codebook.size(0)
     L = load()

@@ -114,6 +114,7 @@ int c3vq_ema(float *codebook, float *entry_importance, const float *acc, int k, 
     C3VQ_CHECK_ARG(d >= 1 && d <= C3VQ_MAX_DIM, "d=%d outside [1, %d]", d, C3VQ_MAX_DIM);
     C3VQ_CHECK_ARG(k >= 0, "k=%d is negative", k);
     C3VQ_CHECK_ARG(k == 0 || (codebook && entry_importance && acc), "null pointer");
+    C3VQ_CHECK_ARG(!scale_normalize || d >= 6, "scale_normalize divides by columns 0 + 3 + 5 (vq.py:76-77): d=%d < 6", d);
     return launch_ema(codebook, entry_importance, acc, k, d, decay, eps, scale_normalize, (cudaStream_t)stream);
 }
 
@@ -184,11 +185,14 @@ int c3vq_update(const float *x, const float *w, const int64_t *rows, int64_t n, 
     if (rc) return rc;
     C3VQ_CHECK_ARG(k == 0 || entry_importance != nullptr, "entry_importance is null");
     C3VQ_CHECK_ARG(n == 0 || w != nullptr, "w is null");
+    C3VQ_CHECK_ARG(!scale_normalize || d >= 6, "scale_normalize divides by columns 0 + 3 + 5 (vq.py:76-77): d=%d < 6", d);
     if (ws_bytes < c3vq_update_workspace_bytes(n, d, k) || (ws == nullptr && ws_bytes > 0)) {
         set_error("workspace too small: %zu < %zu", ws_bytes, c3vq_update_workspace_bytes(n, d, k));
         return C3VQ_EWORKSPACE;
     }
     if (k == 0) return C3VQ_OK;
+    // n == 0 is not a no-op: the reference's update on an empty batch scatters nothing and then applies both EMAs
+    // (vq.py:31-34), i.e. every codeword and entry_importance decay by `decay`; the same happens here.
     cudaStream_t s = (cudaStream_t)stream;
     char *p = (char *)ws;
     const size_t tc_bytes = tc_workspace_bytes(n, d, k);

@@ -70,9 +70,9 @@ class CudaOps:
     def new_acc(self, k: int, d: int, device) -> torch.Tensor:
         return torch.zeros(k, _lib.acc_stride(d), dtype=torch.float32, device=device)
 
-    def assign_accumulate(self, x, w, codebook, acc, rows=None, return_dist=False):
+    def assign_accumulate(self, x, w, codebook, acc, rows=None, return_dist=False, rows_checked=False):
         _, dist_, idx = _lib.assign_accumulate(x, w, codebook, acc=acc, rows=rows, tensor_cores=self.tensor_cores,
-                                               return_dist=return_dist, return_idx=True)
+                                               return_dist=return_dist, return_idx=True, rows_checked=rows_checked)
         return dist_, idx
 
     def ema(self, codebook, entry_importance, acc, decay, eps, scale_normalize):

@@ -46,14 +46,15 @@ class VectorQuantize(nn.Module):
             return min_dists
 
     def update_indexed(self, features: torch.Tensor, importance: torch.Tensor, batch: torch.Tensor,
-                       scale_normalize: bool = False, return_dist: bool = False):
+                       scale_normalize: bool = False, return_dist: bool = False, batch_checked: bool = False):
         """`update(features[batch], importance[batch])` (+ optional vq.py:73-77 trace normalise) without
-        materialising the gathered rows: the kernels read rows through `batch`."""
+        materialising the gathered rows: the kernels read rows through `batch`.  `batch_checked`: the caller
+        guarantees 0 <= batch < len(features) (skips the range check and its host sync)."""
         with torch.no_grad():
             min_dists, _ = _lib.update(features.detach(), importance.detach(), self.codebook.data,
                                        self.entry_importance.data, self.decay, self.eps, rows=batch,
                                        scale_normalize=scale_normalize, tensor_cores=self.tensor_cores,
-                                       return_dist=return_dist)
+                                       return_dist=return_dist, rows_checked=batch_checked)
             return min_dists
 
     def forward(self, x: torch.Tensor, return_dists: bool = False
@@ -146,7 +147,8 @@ def vq_features(
             uploaded[slot] = ev
             free.put(slot)
             # vq.py:70-77: gather + update (+ trace normalise), one fused call
-            vq_model.update_indexed(features, importance_n, batch, scale_normalize=scale_normalize)
+            vq_model.update_indexed(features, importance_n, batch, scale_normalize=scale_normalize,
+                                    batch_checked=True)              # drawn by randint(0, n_rows) above
     finally:
         free.put(None)                          # normal end: the drawer has left already; after an error: stop it
         while drawer.is_alive():

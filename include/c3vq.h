@@ -97,6 +97,8 @@ int c3vq_accumulate_sorted(const float *x, const float *w, const int64_t *rows, 
  * then, if scale_normalize, codebook[j,:] /= codebook[j,0]+codebook[j,3]+codebook[j,5].
  * decay and eps are the Python doubles of the reference; they are narrowed to fp32
  * exactly as torch narrows them ((float)decay, (float)(1.0-decay), (float)eps).
+ * scale_normalize needs d >= 6 (columns 0, 3, 5 are the trace of the stored covariance; the reference raises an
+ * index error for narrower rows): C3VQ_EINVAL otherwise.
  */
 int c3vq_ema(float *codebook, float *entry_importance, const float *acc,
              int k, int d, double decay, double eps, int scale_normalize, c3vq_stream_t stream);
@@ -108,6 +110,10 @@ int c3vq_ema(float *codebook, float *entry_importance, const float *acc,
  * use_tensor_cores: 0 = SIMT exact assignment + atomic sums; 1 = tensor-core assignment, then the sorted
  * segmented sums (second pass over x, no per-row atomics); 2 = tensor-core assignment with the sums fused
  * into the kernel (x read once, one bulk reduce-add per row: bounded by the L2's fp32 reduction rate).
+ * n == 0 is not a no-op: like the reference's update on an empty batch (vq.py:31-34: nothing scattered, both EMAs
+ * applied) every codeword and entry_importance decay by `decay`.  `rows`, when given, must lie in [0, rows of x):
+ * the kernels do not check them (the Python host does unless the caller vouches for them).
+ * One workspace serves one stream at a time: calls that may run concurrently need their own.
  */
 size_t c3vq_update_workspace_bytes(int64_t n, int d, int k);
 int c3vq_update(const float *x, const float *w, const int64_t *rows, int64_t n, int d,
