@@ -8,11 +8,17 @@ One "step" = one 10-iteration clustering job (10 x VectorQuantize.update over AL
 K = 4096, decay 0.8) on synthetic inputs shaped like BASELINE.json configs[1]: 5.8 M Gaussians x 45-D
 SH features with heavy-tailed sensitivities.  With N GPUs every rank holds its own 5.8 M rows (weak
 scaling), the codebook is replicated and each iteration all-reduces the K x (D+1) partial sums (NCCL).
+`--scaling strong --total-rows 24000000` splits a fixed number of rows over the ranks instead (configs[3]);
+the default run reports that configuration under `extras.strong_24M` at every N.
 
-The JSON line carries, besides the base contract: `roofline` (dominant kernel, measured live with
-CUDA events around every launch of it inside the timed region), `cpu_baseline` (the CPU oracle port
-of the reference path on the box's host cores, rank 0, N=1), `e2e` (same job through the public API
-from pinned HOST buffers, H2D/D2H inside the timed region) and `gpu_launches`.
+The JSON line carries, besides the base contract: `roofline` (assignment kernels, tensor roofline),
+`roofline_update` (centroid sums + EMA, HBM roofline), `roofline_gather` (decode gather, HBM roofline) — all
+from CUDA events inside this run —, `cpu_baseline` (the CPU oracle port of the reference path on the box's host
+cores, rank 0, N=1), `e2e` (same job through the public API from pinned HOST buffers, H2D/D2H inside the timed
+region), `gpu_launches`, `assign_stats` (candidates per row / rows in the exact scan), at N > 1 `parity`
+(replica agreement + agreement with a one-rank run of the same rows) and `h2d_probe`, and `extras` with the other
+BASELINE configs (shape 7-D, trace-normalised 6-D, 48-D, iid rows, the reference's own CUDA kernel on the same
+inputs, the compress pipeline).
 
 `--impl reference` times the reference path's CPU port (oracle/, all host threads) on a bounded sample
 (100 k rows, all 10 iterations per step) of the same workload.  oracle/ is used here only as that baseline.
@@ -38,6 +44,7 @@ UNIT = "Gaussian*iter/s"
 K = 4096
 ITERS = 10
 DECAY, EPS = 0.8, 1e-5
+TF32_SPEC_TFLOPS = 1125.0          # dense TF32 of the B200 data sheet (half the 2.25 PFLOP/s bf16 figure)
 
 
 def peaks():
@@ -47,6 +54,42 @@ def peaks():
         return {"hbm_gbs": j["hbm_gbs"], "bf16_tflops": j["bf16_tflops"],
                 "bf16_tflops_sustained": j.get("bf16_tflops_sustained", j["bf16_tflops"]), "source": "measured"}
     return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
+
+
+def measure_tf32_peak(device, seconds: float = 2.0, n: int = 8192):
+    """Dense TF32 matmul rate of this GPU, measured the way MEASURED_PEAKS.json measures bf16: torch.matmul of fp32
+    n^3 with allow_tf32 (cuBLAS), best of 10 (burst) and back to back for `seconds` (sustained)."""
+    old = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = True
+    try:
+        a = torch.randn(n, n, device=device)
+        b = torch.randn(n, n, device=device)
+        c = torch.empty(n, n, device=device)
+        for _ in range(3):
+            torch.matmul(a, b, out=c)
+        torch.cuda.synchronize(device)
+        flops = 2.0 * n ** 3
+        best = 1e9
+        for _ in range(10):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            torch.matmul(a, b, out=c)
+            e1.record()
+            torch.cuda.synchronize(device)
+            best = min(best, e0.elapsed_time(e1))
+        reps = max(10, int(seconds * 1e3 / best))
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            torch.matmul(a, b, out=c)
+        e1.record()
+        torch.cuda.synchronize(device)
+        sustained_ms = e0.elapsed_time(e1) / reps
+        return {"tf32_tflops": flops / best * 1e-9, "tf32_tflops_sustained": flops / sustained_ms * 1e-9,
+                "how": f"torch.matmul fp32 {n}^3 with allow_tf32 (cuBLAS): best of 10 (burst) and {reps} back to back "
+                       f"({sustained_ms * reps * 1e-3:.1f} s, sustained), CUDA events, this run"}
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = old
 
 
 class ClockSampler:
@@ -92,22 +135,23 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
-def synth(n: int, d: int, seed: int, device=None, pin=False):
-    """Seeded synthetic scene: clustered SH-like features with band decay, w = rand**4.
-    Generated on the device generator for speed (CPU generation of 5.8M x 45 takes seconds per rank)."""
-    if device is None:
-        g = torch.Generator().manual_seed(seed)
-        centres = torch.randn(8192, d, generator=g)
-        x = centres[torch.randint(0, 8192, (n,), generator=g)] + 0.05 * torch.randn(n, d, generator=g)
-        w = torch.rand(n, generator=g) ** 4
+def synth(n: int, d: int, seed: int, device=None, kind: str = "clustered"):
+    """Seeded synthetic rows.  `clustered`: 8192 centres ~N(0,1) with the per-band decay of SH
+    coefficients, points = centre + 0.05 N(0,1); `iid`: N(0,1).  w = rand**4 (heavy-tailed sensitivities).
+    The same expressions on either generator: the CUDA generator on the GPU arm (CPU generation of 5.8 M x 45 takes
+    seconds per rank, and BASELINE.md §3's "identical bits on every box" needs a 1 GB upload per run for no benefit
+    to a throughput number), the CPU generator for the CPU legs; the two streams differ, the distribution does not."""
+    g = torch.Generator(device=device if device is not None else "cpu").manual_seed(seed)
+    kw = {"device": device, "generator": g} if device is not None else {"generator": g}
+    if kind == "iid":
+        x = torch.randn(n, d, **kw)
     else:
-        g = torch.Generator(device=device).manual_seed(seed)
-        centres = torch.randn(8192, d, device=device, generator=g)
+        centres = torch.randn(8192, d, **kw)
         band = torch.arange(d, device=device) // 3
         centres = centres / (1.0 + band.float().sqrt())
-        x = centres[torch.randint(0, 8192, (n,), device=device, generator=g)]
-        x = x + 0.05 * torch.randn(n, d, device=device, generator=g)
-        w = torch.rand(n, device=device, generator=g) ** 4
+        x = centres[torch.randint(0, 8192, (n,), **kw)]
+        x = x + 0.05 * torch.randn(n, d, **kw)
+    w = torch.rand(n, **kw) ** 4
     return x.contiguous(), w.contiguous()
 
 
@@ -119,20 +163,28 @@ def init_codebook(x: torch.Tensor, k: int, seed: int):
 
 
 # ------------------------------------------------------------------------------------------------
-def workload_config(n, d, world, assignment, sums):
+def workload_config(n, d, world, scaling="weak"):
+    """The workload only (identical for both arms); how each arm computes it is in `implementation`."""
     which = "configs[2]: shape codebook clustering" if d <= 8 else "configs[1]: SH codebook clustering"
+    if scaling == "strong":
+        which = "configs[3]: sharded SH clustering, fixed total rows"
     return {"workload": f"{which}, {n / 1e6:.1f}M Gaussians x {d}-D per GPU, K=4096, "
                         "10 full-batch k-means iterations per step",
             "rows_per_gpu": n, "dim": d, "codebook_size": K, "iterations_per_step": ITERS, "decay": DECAY,
+            "distribution": "clustered (8192 centres, SH band decay, sigma 0.05), w = rand**4, uniform-box initial codebook",
             "parallelism": f"rows sharded x{world}, codebook replicated, 1 all-reduce of K x (D+1) sums per iteration",
-            "l2": f"inputs ({n * (d + 1) * 4 / 1e9:.2f} GB per GPU) exceed the 126 MB L2; no explicit flush",
-            "assignment": assignment, "sums": sums}
+            "l2": f"inputs ({n * (d + 1) * 4 / 1e9:.2f} GB per GPU) exceed the 126 MB L2; no explicit flush"}
 
-
-# (rows, dim, simt) -> DRAM bytes of one launch of the dominant kernel, measured with ncu (see profiles/)
-NCU_DRAM_BYTES_PER_LAUNCH = {(5_800_000, 45, False): 1_092_362_240}
 
 SAMPLE_ROWS = 100_000     # CPU legs: a bounded sample of the workload's rows (the metric is per row and iteration)
+
+
+def cpu_sample(d):
+    """The CPU legs' inputs: SAMPLE_ROWS rows of the workload's distribution, normalised weights, uniform-box codebook
+    (same expressions and seeds as the GPU arm; the CPU generator's stream)."""
+    x, w = synth(SAMPLE_ROWS, d, 1234)
+    cb0 = init_codebook(x, K, 99)
+    return x.numpy(), (w / w.max()).numpy().astype(np.float32), cb0.numpy()
 
 
 def run_reference_arm(args, rank):
@@ -143,11 +195,7 @@ def run_reference_arm(args, rank):
     from oracle import oracle
     oracle.build()
     n, d = SAMPLE_ROWS, args.dim
-    x, w = synth(n, d, 0)
-    x, w = x.numpy(), w.numpy()
-    wn = (w / w.max()).astype(np.float32)
-    rng = np.random.default_rng(0)
-    cb0 = (rng.random((K, d), dtype=np.float32) * (x.max() - x.min()) + x.min()).astype(np.float32)
+    x, wn, cb0 = cpu_sample(d)
     # torchrun exports OMP_NUM_THREADS=1 to every rank; this leg is the only CPU work of the job and takes every core
     oracle.set_threads(len(os.sched_getaffinity(0)))
     cores = oracle.num_threads()
@@ -170,12 +218,14 @@ def run_reference_arm(args, rank):
     value = n * ITERS / dt
     sample = (f"{n} of the workload's {args.rows} rows per GPU (x {d}-D, K=4096), all {ITERS} iterations per step; "
               "oracle/c3vq_oracle.c (OpenMP restatement of weighted_distance.cu + vq.py update), "
-              f"{cores} host threads")
+              f"{cores} host threads; ONE CPU box whatever --gpus says (the metric is per row and iteration)")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": steps, "warmup": warm + 1, "ms_per_step": dt * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args.rows, d, max(1, args.gpus), "cpu-exact (reference arithmetic)", "cpu scatter"),
+        "config": workload_config(args.rows, d, max(1, args.gpus)),
+        "implementation": {"assignment": "cpu-exact (reference arithmetic)", "sums": "cpu scatter",
+                           "sampled_rows": n},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -188,11 +238,7 @@ def cpu_baseline_leg(d=45):
     from oracle import oracle
     oracle.build()
     n = SAMPLE_ROWS
-    x, w = synth(n, d, 0)
-    x, w = x.numpy(), w.numpy()
-    wn = (w / w.max()).astype(np.float32)
-    rng = np.random.default_rng(0)
-    cb = (rng.random((K, d), dtype=np.float32) * (x.max() - x.min()) + x.min()).astype(np.float32)
+    x, wn, cb = cpu_sample(d)
     ei = np.zeros(K, np.float32)
     oracle.set_threads(len(os.sched_getaffinity(0)))    # all host cores, whatever OMP_NUM_THREADS says
     oracle.update(x, wn, cb, ei, DECAY, EPS)            # warm-up iteration
@@ -207,6 +253,136 @@ def cpu_baseline_leg(d=45):
                       "oracle/c3vq_oracle.c (OpenMP restatement of weighted_distance.cu + vq.py update)"}
 
 
+class Clustering:
+    """10 full-batch iterations over this rank's rows through the same kernels c3vq_update launches, as separate
+    calls so that the assignment (prep + k_assign_tc + fallback scan) and the update (sums + EMA) can be bracketed
+    by CUDA events on their own; the all-reduce of the sums sits between the two halves of the update."""
+
+    def __init__(self, x, wn, cb0, dev, simt=False, sums="sorted", scale_normalize=False):
+        from c3dgs_b200 import _lib
+        from c3dgs_b200.sharded import CudaOps, ShardedVectorQuantize
+        self.L, self.x, self.wn, self.cb0 = _lib, x, wn, cb0
+        self.n, self.d = x.shape
+        self.scale_normalize = scale_normalize
+        self.ops = CudaOps()
+        self.ops.tensor_cores = False if simt else ("fused" if sums == "fused" else True)
+        self.split = (not simt) and sums == "sorted"
+        self.vq = ShardedVectorQuantize(self.d, K, DECAY, device=dev, ops=self.ops)
+        self.events = []           # per iteration (e0, e1, e2, e3, e4)
+
+    def step(self, record: bool):
+        vq, L = self.vq, self.L
+        vq.codebook.copy_(self.cb0)
+        vq.entry_importance.zero_()
+        for _ in range(ITERS):
+            vq._acc.zero_()
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)] if record else None
+            if record:
+                ev[0].record()
+            if self.split:
+                idx = L.assign(self.x, vq.codebook, return_dist=False)[1]
+                if record:
+                    ev[1].record()
+                L.accumulate(self.x, self.wn, idx, K, acc=vq._acc, sorted_path=True)
+            else:
+                self.ops.assign_accumulate(self.x, self.wn, vq.codebook, vq._acc)
+                if record:
+                    ev[1].record()
+            if record:
+                ev[2].record()
+            vq._all_reduce(vq._acc)
+            if record:
+                ev[3].record()
+            self.ops.ema(vq.codebook, vq.entry_importance, vq._acc, DECAY, EPS, self.scale_normalize)
+            if record:
+                ev[4].record()
+                self.events.append(ev)
+
+    def kernel_ms(self):
+        """(assignment ms, update ms) per iteration, averaged over the recorded iterations."""
+        a = float(np.mean([e[0].elapsed_time(e[1]) for e in self.events]))
+        u = float(np.mean([e[1].elapsed_time(e[2]) + e[3].elapsed_time(e[4]) for e in self.events]))
+        return a, u
+
+
+def timed(fn, reps=5):
+    fn()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(reps):
+        fn()
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) / reps
+
+
+def assignment_roofline(n, d, kern_ms, share, pk, tf32, simt, split):
+    """Tensor roofline for the wide rows, the score-drain (TMEM read) roofline for D <= 8 (that width
+    is compare-rate bound, the MMA is a single k-step)."""
+    flops = 2.0 * K * d * n                               # SURVEY §8d: assign flops = 2*K*D per Gaussian*iteration
+    kernel = ("k_assign_exact (SIMT)" if simt else
+              ("k_tc_prep_* + k_assign_tc + k_assign_fallback_* (assignment; sums by the sorted segmented-sum kernels)"
+               if split else "k_assign_tc (fused assign+sums)"))
+    if d > 8:
+        achieved = flops / (kern_ms * 1e-3) / 1e12
+        peak = tf32["tf32_tflops_sustained"]
+        return {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+                "traffic": None,
+                "traffic_source": "not measured in this run; ncu dram__bytes of one k_assign_tc<48,45> launch at 5.8M x 45: "
+                                  "profiles/r1q_ncu_assign_tc_summary.txt (1.094 GB = the algorithmic bytes)",
+                "kernel": kernel, "kernel_ms": kern_ms, "kernel_share_of_step": share,
+                "peak_source": "measured in this run: cuBLAS TF32 matmul 8192^3, sustained (kernel timed inside a long step)",
+                "frac_vs_tf32_burst": achieved / tf32["tf32_tflops"],
+                "frac_vs_half_bf16_sustained": achieved / (pk["bf16_tflops_sustained"] / 2.0),
+                "frac_vs_spec_1125": achieved / TF32_SPEC_TFLOPS,
+                "tf32_peak_measured": tf32, "algorithmic_flops_per_launch": flops}
+    # every one of the n*K scores is read from TMEM once: 4 B each at 64 B/clk per SM sub-partition (4 per SM)
+    sm_clk = 1.965e9
+    peak = 148 * 4 * 64 * sm_clk / 4 / 1e12               # 1e12 scores/s
+    achieved = n * K / (kern_ms * 1e-3) / 1e12
+    return {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "Tscore/s", "frac": achieved / peak,
+            "traffic": None, "kernel": kernel, "kernel_ms": kern_ms, "kernel_share_of_step": share,
+            "peak_source": "score-drain roofline for D <= 8 (SURVEY §8d: compare-rate bound): n*K fp32 scores read from "
+                           "TMEM at 64 B/clk per SM sub-partition x 592 sub-partitions x 1.965 GHz max clock",
+            "tensor_tflops": flops / (kern_ms * 1e-3) / 1e12,
+            "hbm_floor_ms": n * (4 * d + 12) / pk["hbm_gbs"] * 1e-6, "algorithmic_scores_per_launch": float(n) * K}
+
+
+def update_roofline(n, d, upd_ms, share, pk):
+    nbytes = float(n) * (4 * d + 4 + 8)                   # SURVEY §8d: update bytes = 4*D + 4 (w) + 8 (idx) per row
+    achieved = nbytes / (upd_ms * 1e-3) / 1e9
+    return {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": achieved / pk["hbm_gbs"],
+            "traffic": None, "kernel": "k_wseg_rank + k_wseg_scan + k_wseg_place + k_wseg_sum + k_ema (centroid sums + EMA)",
+            "kernel_ms": upd_ms, "kernel_share_of_step": share, "algorithmic_bytes_per_launch": nbytes,
+            "peak_source": f"{pk['source']}: MEASURED_PEAKS.json hbm_gbs (copy bandwidth)"}
+
+
+def run_config(name, x, w, dev, steps=3, scale_normalize=False, cb0=None, pk=None, tf32=None):
+    """One of the other BASELINE configurations on this GPU: ms per 10-iteration step, kernel times, screening stats."""
+    from c3dgs_b200 import _lib
+    n, d = x.shape
+    wn = (w / w.max()).contiguous()
+    cb0 = init_codebook(x, K, 99) if cb0 is None else cb0
+    job = Clustering(x, wn, cb0, dev, scale_normalize=scale_normalize)
+    for _ in range(2):
+        job.step(False)
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(steps):
+        job.step(True)
+    b.record()
+    torch.cuda.synchronize()
+    ms = a.elapsed_time(b) / steps
+    rows, cands, fb = _lib.assign_stats(dev)              # last iteration's assignment
+    am, um = job.kernel_ms()
+    out = {"workload": name, "rows": n, "dim": d, "ms_per_step": ms, "value": n * ITERS / (ms * 1e-3),
+           "assign_ms": am, "update_ms": um, "candidates_per_row": cands / max(rows, 1), "fallback_rows": fb,
+           "roofline": assignment_roofline(n, d, am, am * ITERS / ms, pk, tf32, False, True),
+           "roofline_update": update_roofline(n, d, um, um * ITERS / ms, pk)}
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -215,10 +391,13 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--rows", type=int, default=5_800_000, help="rows per GPU (default: configs[1])")
     ap.add_argument("--dim", type=int, default=45)
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
+    ap.add_argument("--total-rows", type=int, default=24_000_000, help="--scaling strong: rows split over the ranks")
     ap.add_argument("--simt", action="store_true", help="use the SIMT exact assignment instead of tensor cores")
     ap.add_argument("--sums", default="sorted", choices=["sorted", "fused"],
                     help="centroid sums: sorted segmented sum after the assignment (default) or fused bulk reduce-adds")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -233,7 +412,6 @@ def main():
         raise SystemExit("bench.py needs a CUDA device: the product has no CPU path (use --impl reference for the CPU port)")
     import torch.distributed as dist
     from c3dgs_b200 import _lib
-    from c3dgs_b200.sharded import ShardedVectorQuantize, CudaOps
 
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
@@ -242,8 +420,21 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
     assert world == args.gpus or world == 1, f"--gpus {args.gpus} but WORLD_SIZE={world}"
     _lib.load()
+    pk = peaks()
 
-    n, d = args.rows, args.dim
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    d = args.dim
+    n = args.rows if args.scaling == "weak" else args.total_rows // world
     warm = max(3, args.warmup)
     x, w = synth(n, d, 1234 + rank, device=dev)
     wmax = w.max().clone()
@@ -251,88 +442,89 @@ def main():
         dist.all_reduce(wmax, op=dist.ReduceOp.MAX)
     wn = (w / wmax).contiguous()
     cb0 = init_codebook(x, K, 99)                       # same seed on every rank -> identical replicas
-    ops = CudaOps()
-    ops.tensor_cores = False if args.simt else ("fused" if args.sums == "fused" else True)
-    vq = ShardedVectorQuantize(d, K, DECAY, device=dev, ops=ops)
+    if world > 1:
+        dist.broadcast(cb0, src=0)                      # the box bounds differ per shard: rank 0's codebook everywhere
+    job = Clustering(x, wn, cb0, dev, simt=args.simt, sums=args.sums)
+    vq, ops = job.vq, job.ops
 
-    ev_pairs = []
-    split = (not args.simt) and args.sums == "sorted"
-
-    def job(record: bool):
-        """10 iterations of update over all local rows; the dominant kernel is bracketed by events."""
-        vq.codebook.copy_(cb0)
-        vq.entry_importance.zero_()
-        for _ in range(ITERS):
-            vq._acc.zero_()
-            if record:
-                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                e0.record()
-            if split:
-                # the same kernels c3vq_assign_accumulate launches, as two calls so that the assignment
-                # (prep + k_assign_tc + fallback scan) can be bracketed on its own
-                idx = _lib.assign(x, vq.codebook, return_dist=False)[1]
-                if record:
-                    e1.record()
-                _lib.accumulate(x, wn, idx, K, acc=vq._acc, sorted_path=True)
-            else:
-                ops.assign_accumulate(x, wn, vq.codebook, vq._acc)
-                if record:
-                    e1.record()
-            if record:
-                ev_pairs.append((e0, e1))
-            vq._all_reduce(vq._acc)
-            ops.ema(vq.codebook, vq.entry_importance, vq._acc, DECAY, EPS, False)
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
+    # the TF32 tensor peak the assignment is quoted against, measured on this GPU before the timed region
+    tf32 = measure_tf32_peak(dev)
 
     for _ in range(warm):
-        job(False)
+        job.step(False)
     barrier()
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
         time.sleep(0.3)
     launches0 = _lib.launch_count()
-    start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    marks = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
     barrier()
     t_wall0 = time.time()
-    start.record()
-    for _ in range(args.steps):
-        job(True)
-    stop.record()
+    marks[0].record()
+    for s in range(args.steps):
+        job.step(True)
+        marks[s + 1].record()
     barrier()
     t_wall1 = time.time()
     launches = _lib.launch_count() - launches0
-    ms_total = torch.tensor([start.elapsed_time(stop)], device=dev, dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(ms_total, op=dist.ReduceOp.MAX)
-    ms_per_step = float(ms_total.item()) / args.steps
+    ms_per_step = max_over_ranks(marks[0].elapsed_time(marks[-1])) / args.steps
+    per_step = [marks[i].elapsed_time(marks[i + 1]) for i in range(args.steps)]
     clocks = sampler.stop(t_wall0, t_wall1) if rank == 0 else None
     value = world * n * ITERS / (ms_per_step * 1e-3)
+    stats_rows, stats_cands, stats_fb = (_lib.assign_stats(dev) if not args.simt else (n, 0, 0))
+    replica_hash = int(vq.codebook.view(torch.int32).to(torch.int64).sum().item()) & 0xFFFFFFFFFFFF
 
-    # dominant kernel: fused assignment(+sums) launch, average duration over the timed region
-    kern_ms = float(np.mean([a.elapsed_time(b) for a, b in ev_pairs]))
-    pk = peaks()
-    flops = 2.0 * K * d * n                               # SURVEY §8d: assign flops = 2*K*D per Gaussian*iteration
-    tf32_peak = pk["bf16_tflops_sustained"] / 2.0         # dense TF32 = half the bf16 rate; kernel timed inside a long step
-    achieved = flops / (kern_ms * 1e-3) / 1e12
-    # dram__bytes_read.sum + dram__bytes_write.sum of ONE k_assign_tc launch from the committed `ncu --set full`
-    # capture (profiles/r1n_ncu_assign_tc_summary.txt); only valid for the configuration that capture ran
-    traffic = NCU_DRAM_BYTES_PER_LAUNCH.get((n, d, bool(args.simt)))
-    roofline = {"bound": "tensor", "achieved": achieved, "peak": tf32_peak, "unit": "TFLOP/s",
-                "frac": achieved / tf32_peak, "traffic": traffic,
-                "kernel": "k_assign_exact+k_accumulate (SIMT)" if args.simt else
-                          ("k_assign_tc (assignment; sums by the sorted segmented-sum kernels)" if split
-                           else "k_assign_tc (fused assign+sums)"),
-                "kernel_ms": kern_ms, "kernel_share_of_step": kern_ms * ITERS / ms_per_step,
-                "peak_source": f"{pk['source']}: bf16_tflops_sustained/2 (TF32 dense = half bf16)",
-                "algorithmic_flops_per_launch": flops}
+    assign_ms, update_ms = job.kernel_ms()
+    roofline = assignment_roofline(n, d, assign_ms, assign_ms * ITERS / ms_per_step, pk, tf32, args.simt, job.split)
+    roofline_update = update_roofline(n, d, update_ms, update_ms * ITERS / ms_per_step, pk) if job.split else None
 
-    # e2e: the same job from pinned HOST buffers through the public API, copies inside the timed region
-    e2e = None
+    # decode gather: codebook[idx] -> [n, d], 8 B index in + 4 d B out per row
+    gen = torch.Generator(device=dev).manual_seed(5 + rank)
+    idx_dec = torch.randint(0, K, (n,), device=dev, generator=gen)
+    ms_g = timed(lambda: _lib.gather(vq.codebook, idx_dec))
+    gbytes = float(n) * (8 + 4 * d)
+    roofline_gather = {"bound": "hbm", "achieved": gbytes / ms_g * 1e-6, "peak": pk["hbm_gbs"], "unit": "GB/s",
+                       "frac": gbytes / ms_g * 1e-6 / pk["hbm_gbs"], "traffic": None, "kernel": "k_gather_span / k_gather32",
+                       "kernel_ms": ms_g, "algorithmic_bytes_per_launch": gbytes,
+                       "peak_source": f"{pk['source']}: MEASURED_PEAKS.json hbm_gbs (copy bandwidth)"}
+    del idx_dec
+
+    # ---- N > 1: replica agreement, and agreement with a one-rank run of the same rows at a reduced size ----
+    parity = None
+    if world > 1:
+        hashes = [None] * world
+        dist.all_gather_object(hashes, replica_hash)
+        sub = 262_144                                     # rows per rank in the reduced problem
+        xs, ws = x[:sub].contiguous(), wn[:sub].contiguous()
+        pj = Clustering(xs, ws, cb0, dev)
+        pj.step(False)                                    # sharded: all ranks, NCCL all-reduce per iteration
+        cb_sharded = pj.vq.codebook.clone()
+        gx = [torch.empty_like(xs) for _ in range(world)] if rank == 0 else None
+        gw = [torch.empty_like(ws) for _ in range(world)] if rank == 0 else None
+        dist.gather(xs, gx, dst=0)
+        dist.gather(ws, gw, dst=0)
+        if rank == 0:
+            xa, wa = torch.cat(gx), torch.cat(gw)
+            one = Clustering(xa, wa, cb0, dev)
+            one.vq._world = lambda: 1                     # no collectives: the same rows on one GPU
+            one.step(False)
+            scale = one.vq.codebook.abs().max(1, keepdim=True).values + 1e-30
+            fin = torch.isfinite(one.vq.codebook).all(1)
+            err = float(((one.vq.codebook - cb_sharded).abs() / scale)[fin].max())
+            agree = float((_lib.assign(xa, one.vq.codebook)[1] == _lib.assign(xa, cb_sharded)[1]).float().mean())
+            parity = {"replicas_identical": len(set(hashes)) == 1, "codebook_hashes": hashes,
+                      "one_rank_rows": int(xa.shape[0]), "codebook_max_rel_err_vs_one_rank": err,
+                      "assignments_equal_frac_vs_one_rank": agree, "tolerance": 1e-5,
+                      "ok": bool(len(set(hashes)) == 1 and err < 1e-5),
+                      "note": "headline run: 48-bit checksum of the final codebook bits of every rank; reduced problem: "
+                              f"{sub} rows of every rank, 10 iterations sharded over {world} ranks (NCCL) vs the same "
+                              "rows on rank 0 alone (codebooks within 1e-5 relative, row-normalised)"}
+            del xa, wa, one
+        del pj, xs, ws
+        barrier()
+
+    # ---- e2e: the same job from pinned HOST buffers through the public API, copies inside the timed region ----
     from c3dgs_b200.sharded import gpu_local_host_memory
     with gpu_local_host_memory(local_rank):          # pinned staging buffers on this GPU's NUMA node
         xh = torch.empty(x.shape, dtype=torch.float32).pin_memory()
@@ -364,192 +556,102 @@ def main():
         e2e_job()
     t2.record()
     barrier()
-    ms_e2e = torch.tensor([s2.elapsed_time(t2)], device=dev, dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(ms_e2e, op=dist.ReduceOp.MAX)
-    ms_e2e = float(ms_e2e.item()) / e2e_steps
+    ms_e2e = max_over_ranks(s2.elapsed_time(t2)) / e2e_steps
     e2e = {"value": world * n * ITERS / (ms_e2e * 1e-3), "unit": UNIT,
            "h2d_bytes_per_step": int(xh.numel() * 4 + wh.numel() * 4),
            "d2h_bytes_per_step": int(cbh.numel() * 4 + idxh.numel() * 8), "ms_per_step": ms_e2e}
 
-    # the reference's real default, mini-batch mode, through the drop-in vq_features
-    # (CPU randint batches with replacement, 100 x 2^18 rows, then the final full assignment); reported, not the metric
-    extras = None
-    if world == 1 and not args.simt:
-        from c3dgs_b200.vq import vq_features
-        mb_steps, mb_chunk = 100, 2 ** 18
-        vq_features(x, w, K, vq_chunk=mb_chunk, steps=3, decay=DECAY, silent=True)      # warm-up
-        torch.cuda.synchronize()
-        t0 = time.time()
-        vq_features(x, w, K, vq_chunk=mb_chunk, steps=mb_steps, decay=DECAY, silent=True)
-        torch.cuda.synchronize()
-        dt = time.time() - t0
-        extras = {"vq_features_minibatch": {"batch_rows": mb_chunk, "steps": mb_steps, "final_assign_rows": n,
-                                            "wall_ms": dt * 1e3,
-                                            "rows_per_s": (mb_steps * mb_chunk + n) / dt,
-                                            "note": "host wall clock incl. the reference's per-step CPU torch.randint"}}
-
-        # SURVEY §8f ranks 1-2, the steps right after the clustering: join_features (5 % of the rows kept) and
-        # extract_rot_scale on a joined covariance table of n/4 rows; HBM-bound, reported against the copy peak
-        from c3dgs_b200 import _lib as ops2
-        pk = peaks()
-
-        def timed(fn, reps=5):
-            fn()
+    # pinned host -> device rate of this rank alone and of all ranks at once: what bounds e2e at N > 1
+    h2d_probe = None
+    if world > 1:
+        def h2d_once():
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
-            for _ in range(reps):
-                fn()
+            xd.copy_(xh, non_blocking=True)
             b.record()
             torch.cuda.synchronize()
-            return a.elapsed_time(b) / reps
+            return xh.numel() * 4 / a.elapsed_time(b) * 1e-6
+        h2d_once()
+        solo = torch.zeros(world, device=dev, dtype=torch.float64)
+        for r in range(world):
+            barrier()
+            if r == rank:
+                solo[r] = h2d_once()
+        barrier()
+        conc = torch.zeros(world, device=dev, dtype=torch.float64)
+        conc[rank] = h2d_once()
+        dist.all_reduce(solo)
+        dist.all_reduce(conc)
+        h2d_probe = {"bytes": int(xh.numel() * 4), "solo_gbs_per_rank": [round(v, 1) for v in solo.tolist()],
+                     "concurrent_gbs_per_rank": [round(v, 1) for v in conc.tolist()],
+                     "concurrent_aggregate_gbs": float(conc.sum()),
+                     "e2e_upload_floor_ms": float(xh.numel() * 4 / (conc.min().item() * 1e6)),
+                     "note": "pinned host -> device copy of this rank's rows: one rank at a time, then all ranks at once"}
+    del xh, wh, xd, wd, idxh
 
-        gen = torch.Generator(device=dev).manual_seed(5)
-        keep = torch.rand(n, device=dev, generator=gen) < 0.05
-        cbi = torch.randint(0, K, (int((~keep).sum()),), device=dev, generator=gen)
-        cbj = torch.randn(K, d, device=dev, generator=gen)
-        ms = timed(lambda: ops2.join_features(x, keep, cbj, cbi))
-        jbytes = n * (1 + 8) + int((~keep).sum()) * 8 + (K + int(keep.sum())) * d * 4 * 2
-        extras["join_features"] = {"rows": n, "kept_frac": 0.05, "ms": ms, "gbs": jbytes / ms * 1e-6,
-                                   "frac_of_hbm_peak": jbytes / ms * 1e-6 / pk["hbm_gbs"],
-                                   "note": "two kernels + one host sync for the kept count (output size is data dependent)"}
-        nr = n // 4
-        a6 = torch.randn(nr, 3, 3, device=dev, generator=gen)
-        a6 = a6 @ a6.transpose(-1, -2)
-        cov6 = torch.stack([a6[:, 0, 0], a6[:, 0, 1], a6[:, 0, 2], a6[:, 1, 1], a6[:, 1, 2], a6[:, 2, 2]], -1).contiguous()
-        ms = timed(lambda: ops2.extract_rot_scale(cov6))
-        rbytes = nr * (24 + 28)
-        ms_torch, n_torch = None, 0
-        for n_torch in (100_000, 32_768, 4_096):             # cuSOLVER's batched syev rejects large batches on some builds
-            sub = a6[:n_torch].contiguous()
-            try:
-                ms_torch = timed(lambda: torch.linalg.eigh(sub, UPLO="U"), reps=1)
-                break
-            except RuntimeError:
-                continue
-        extras["extract_rot_scale"] = {"rows": nr, "ms": ms, "gbs": rbytes / ms * 1e-6,
-                                       "frac_of_hbm_peak": rbytes / ms * 1e-6 / pk["hbm_gbs"],
-                                       "torch_eigh_ms": ms_torch, "torch_eigh_rows": n_torch,
-                                       "note": "torch.linalg.eigh (the reference's call, cuSOLVER batched) timed on "
-                                               "a slice for scale; it is not on the product path"}
-        xyz = torch.randn(n, 3, device=dev, generator=gen)
-        ms = timed(lambda: ops2.morton_order(xyz))
-        mbytes = n * 12 * 2 + 8 * n * (8 + 8 + 12 + 12)       # min/max + keys, then 8 radix passes of (hist read, scatter read+write)
-        ms_torch = timed(lambda: torch.sort(torch.randint(0, 2 ** 62, (n,), device=dev, generator=gen)), reps=2)
-        extras["morton_order"] = {"rows": n, "ms": ms, "gbs": mbytes / ms * 1e-6,
-                                  "frac_of_hbm_peak": mbytes / ms * 1e-6 / pk["hbm_gbs"],
-                                  "torch_sort_int64_ms": ms_torch,
-                                  "note": "keys + stable 8x8-bit LSD radix sort of (u64 key, u32 row); torch.sort (cub) "
-                                          "of n random int64 incl. their generation, timed beside it for scale"}
-        del keep, cbi, cbj, a6, cov6, sub, xyz
-        # the indexed-codebook decode, codebook[idx] -> [n, d] (8 B index in + 4 d B out per row)
-        idx_dec = torch.randint(0, K, (n,), device=dev, generator=gen)
-        cb_dec = torch.randn(K, d, device=dev, generator=gen)
-        ms = timed(lambda: ops2.gather(cb_dec, idx_dec))
-        gbytes = n * (8 + 4 * d)
-        extras["decode_gather"] = {"rows": n, "dim": d, "ms": ms, "gbs": gbytes / ms * 1e-6,
-                                   "frac_of_hbm_peak": gbytes / ms * 1e-6 / pk["hbm_gbs"]}
-        tab48 = torch.randn(K + n // 20, 16, 3, device=dev, generator=gen)
-        idx48 = torch.randint(0, tab48.shape[0], (n,), device=dev, generator=gen)
-        ms = timed(lambda: ops2.gather(tab48, idx48))
-        gbytes = n * (8 + 4 * 48)
-        extras["decode_gather_sh48"] = {"rows": n, "dim": 48, "table_rows": int(tab48.shape[0]), "ms": ms,
-                                        "gbs": gbytes / ms * 1e-6, "frac_of_hbm_peak": gbytes / ms * 1e-6 / pk["hbm_gbs"]}
-        del idx_dec, cb_dec, tab48, idx48
+    # ---- BASELINE configs[3]: 24 M rows split over the ranks (strong scaling), and the same rows on rank 0 alone ----
+    strong = None
+    if not args.no_extras and args.scaling == "weak" and not args.simt and world in (1, 2, 4, 8):
+        total, blocks = args.total_rows, 8
+        per = total // blocks
+        mine = range(rank * blocks // world, (rank + 1) * blocks // world)
+        parts = [synth(per, d, 5000 + b, device=dev) for b in mine]
+        xs, ws = torch.cat([p_[0] for p_ in parts]), torch.cat([p_[1] for p_ in parts])
+        del parts
+        cbs = init_codebook(xs, K, 99)
+        if world > 1:
+            dist.broadcast(cbs, src=0)
+        sj = Clustering(xs, ws, cbs, dev)
+        for _ in range(2):
+            sj.step(False)
+        barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(3):
+            sj.step(True)
+        b.record()
+        barrier()
+        ms_n = max_over_ranks(a.elapsed_time(b)) / 3
+        am, um = sj.kernel_ms()
+        ar_ms = float(np.mean([e[2].elapsed_time(e[3]) for e in sj.events]))
+        del sj, xs, ws
+        ms_1 = ms_n
+        if world > 1:
+            if rank == 0:
+                parts = [synth(per, d, 5000 + b, device=dev) for b in range(blocks)]
+                xa, wa = torch.cat([p_[0] for p_ in parts]), torch.cat([p_[1] for p_ in parts])
+                del parts
+                oj = Clustering(xa, wa, cbs, dev)
+                oj.vq._world = lambda: 1
+                for _ in range(2):
+                    oj.step(False)
+                torch.cuda.synchronize()
+                a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a.record()
+                for _ in range(3):
+                    oj.step(False)
+                b.record()
+                torch.cuda.synchronize()
+                ms_1 = a.elapsed_time(b) / 3
+                del oj, xa, wa
+            t = torch.tensor([ms_1], device=dev, dtype=torch.float64)
+            dist.broadcast(t, src=0)
+            ms_1 = float(t.item())
+        strong = {"workload": f"configs[3]: {total / 1e6:.0f}M Gaussians x {d}-D split over {world} GPU(s), K=4096, "
+                              "10 full-batch iterations per step, NCCL all-reduce of the sums per iteration",
+                  "total_rows": total, "rows_per_gpu": total // world, "n_gpus": world, "scaling": "strong",
+                  "ms_per_step": ms_n, "value": total * ITERS / (ms_n * 1e-3),
+                  "one_gpu_ms_per_step": ms_1, "speedup_vs_one_gpu": ms_1 / ms_n,
+                  "assign_ms_per_iteration": am, "update_ms_per_iteration": um, "allreduce_ms_per_iteration": ar_ms,
+                  "note": "the one-GPU time is measured in this run: rank 0 clusters all rows alone while the other ranks wait"}
+        torch.cuda.empty_cache()
 
-        # SURVEY §8f ranks 1 and 3, the formats either side of the path: normalised covariance, mask compaction,
-        # int8 scene-file quantisation (algorithmic bytes / time against the measured copy peak)
-        s3 = torch.rand(n, 3, device=dev, generator=gen) + 0.05
-        r4 = torch.randn(n, 4, device=dev, generator=gen)
-        ms = timed(lambda: ops2.build_covariance(s3, r4, activate=True))
-        extras["build_covariance"] = {"rows": n, "ms": ms, "gbs": n * 52 / ms * 1e-6,
-                                      "frac_of_hbm_peak": n * 52 / ms * 1e-6 / pk["hbm_gbs"]}
-        keep2 = torch.rand(n, device=dev, generator=gen) < 0.6
-        ms = timed(lambda: ops2.compact([x], keep2))
-        cbytes = n + int(keep2.sum()) * d * 4 * 2
-        extras["mask_splats_compact"] = {"rows": n, "kept_frac": 0.6, "row_bytes": d * 4, "ms": ms,
-                                         "gbs": cbytes / ms * 1e-6, "frac_of_hbm_peak": cbytes / ms * 1e-6 / pk["hbm_gbs"],
-                                         "note": "mask scan + host sync for the kept count + row move"}
-        ms = timed(lambda: ops2.quantize_i8(x, 0.03125, 3))
-        ms_t = timed(lambda: torch.quantize_per_tensor(x, 0.03125, 3, torch.qint8).int_repr())
-        extras["quantize_i8"] = {"elements": x.numel(), "ms": ms, "gbs": x.numel() * 5 / ms * 1e-6,
-                                 "frac_of_hbm_peak": x.numel() * 5 / ms * 1e-6 / pk["hbm_gbs"],
-                                 "torch_quantize_per_tensor_ms": ms_t,
-                                 "note": "bit-exact with torch's CUDA quantiser (fp64 division there; fp32 fast path "
-                                         "with an exact fp64 slow path here), timed beside it"}
-        del s3, r4, keep2
-
-        # BASELINE configs[4]: the full compress pipeline on a synthetic 6M-Gaussian scene — prune, thresholds, both
-        # codebooks with the reference's default schedule shape (mini-batches), join, rotation/scaling extraction,
-        # decode of every attribute, Morton order + int8 scene tensors (file IO itself excluded: host numpy/zlib)
-        from c3dgs_b200 import CompressionSettings, SplatScene, compress_gaussians
-        npipe = 6_000_000
-        feats = torch.randn(npipe, 16, 3, device=dev, generator=gen)
-        scene = SplatScene(torch.randn(npipe, 3, device=dev, generator=gen), feats[:, :1].contiguous(),
-                           feats[:, 1:].contiguous(), torch.randn(npipe, 1, device=dev, generator=gen),
-                           torch.rand(npipe, 3, device=dev, generator=gen) + 0.05,
-                           torch.randn(npipe, 4, device=dev, generator=gen),
-                           torch.randn(npipe, 1, device=dev, generator=gen) - 3)
-        del feats
-        cimp = torch.rand(npipe, device=dev, generator=gen) ** 4
-        gimp = torch.rand(npipe, device=dev, generator=gen) ** 4
-        p_steps, p_batch = 100, 2 ** 18
-        cc = CompressionSettings(K, 0.0, 0.6, 0.9, p_steps, DECAY, p_batch)
-        gc_ = CompressionSettings(K, 0.0, 0.3, 0.9, p_steps, DECAY, p_batch)
-        torch.cuda.synchronize()
-        t0 = time.time()
-        compress_gaussians(scene, cimp, gimp, cc, gc_, color_compress_non_dir=True, prune_threshold=1e-8, silent=True)
-        torch.cuda.synchronize()
-        t1 = time.time()
-        from c3dgs_b200.decode import decode_gaussians
-        sdec, rdec, fdec = decode_gaussians(scene._scaling, scene._rotation,
-                                            torch.cat((scene._features_dc, scene._features_rest), 1),
-                                            scene._gaussian_indices, scene._feature_indices)
-        torch.cuda.synchronize()
-        t2 = time.time()
-        scene._sort_morton()
-        qbytes = 0
-        for name in ("features_dc", "features_rest", "opacity", "scaling", "scaling_factor", "rotation"):
-            t = scene._stored(name)
-            qbytes += ops2.quantize_i8(t, 0.01, 0).numel()
-        half = ops2.convert(scene._xyz, torch.float16)
-        i32 = ops2.convert(scene._feature_indices, torch.int32)
-        torch.cuda.synchronize()
-        t3 = time.time()
-        extras["compress_pipeline"] = {
-            "workload": "configs[4]: synthetic 6M-Gaussian scene, SH 48-D + shape 6-D codebooks (K=4096, "
-                        f"{p_steps} mini-batch steps of {p_batch} rows each + final full assignment), join, "
-                        "rot/scale, decode gather, Morton order, int8/fp16/int32 scene tensors",
-            "gaussians": npipe, "after_prune": int(scene._xyz.shape[0]),
-            "color_table_rows": int(scene._features_dc.shape[0]), "shape_table_rows": int(scene._rotation.shape[0]),
-            "compress_gaussians_ms": (t1 - t0) * 1e3, "decode_ms": (t2 - t1) * 1e3,
-            "morton_and_wire_ms": (t3 - t2) * 1e3, "total_ms": (t3 - t0) * 1e3,
-            "decoded_bytes": int(sdec.numel() + rdec.numel() + fdec.numel()) * 4, "int8_bytes": int(qbytes),
-            "note": "host wall clock, single run, includes workspace allocation and the host syncs the data-dependent "
-                    "output sizes need"}
-        # the indexed rasteriser's per-Gaussian preprocess on the compressed scene just built
-        sys.path.insert(0, os.path.join(ROOT, "tests"))
-        from preprocess_scene import camera
-        cam = camera(width=1297, height=840, fovx=0.9)
-        camt = {k_: torch.from_numpy(v_).to(dev) for k_, v_ in cam.items() if hasattr(v_, "dtype")}
-        table = torch.cat((scene._features_dc, scene._features_rest), 1).contiguous()
-        npre = scene._xyz.shape[0]
-        pre = {}
-
-        def run_pre():
-            pre.update(ops2.preprocess_indexed(scene._xyz, scene._scaling, torch.exp(scene._scaling_factor), scene._rotation,
-                                               torch.sigmoid(scene._opacity), table, scene._feature_indices,
-                                               scene._gaussian_indices, camt["viewmatrix"], camt["projmatrix"],
-                                               camt["cam_pos"], cam["width"], cam["height"], cam["tan_fovx"],
-                                               cam["tan_fovy"]))
-        ms = timed(run_pre)
-        nvis = int((pre["radii"] > 0).sum())
-        pbytes = npre * 36 + nvis * (52 + 192 + 51)
-        extras["preprocess_indexed"] = {"gaussians": npre, "visible": nvis, "ms": ms, "gbs": pbytes / ms * 1e-6,
-                                        "frac_of_hbm_peak": pbytes / ms * 1e-6 / pk["hbm_gbs"],
-                                        "note": "incl. the activations (exp, sigmoid: torch) and zero-filling the outputs"}
-        del table, pre
-        del scene, cimp, gimp, sdec, rdec, fdec, half, i32
+    extras = None
+    if world == 1 and not args.simt and not args.no_extras:
+        extras = single_gpu_extras(x, w, wn, cb0, n, d, dev, pk, tf32)
+    if strong is not None:
+        extras = extras or {}
+        extras["strong_24M"] = strong
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -558,17 +660,262 @@ def main():
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": warm,
-            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": ms_per_step, "ms_per_step_median": float(np.median(per_step)), "higher_is_better": True,
+            "scaling": args.scaling, "vs_baseline": None,
             "dtype": "f32 (tf32 tensor-core screening + exact fp32 re-rank)" if not args.simt else "f32",
             "data": "synthetic",
-            "config": workload_config(n, d, world, "simt-exact" if args.simt else "tcgen05-tf32+rerank",
-                                      "atomic" if args.simt else args.sums),
-            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
-            "clocks": clocks, "extras": extras,
+            "config": workload_config(n, d, world, args.scaling),
+            "implementation": {"assignment": "simt-exact" if args.simt else "tcgen05-tf32+rerank",
+                               "sums": "atomic" if args.simt else args.sums},
+            "roofline": roofline, "roofline_update": roofline_update, "roofline_gather": roofline_gather,
+            "assign_stats": {"rows": stats_rows, "candidates_per_row": stats_cands / max(stats_rows, 1),
+                             "fallback_rows": stats_fb, "of": "the last assignment of the timed region"},
+            "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+            "parity": parity, "h2d_probe": h2d_probe, "extras": extras,
         }
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def single_gpu_extras(x, w, wn, cb0, n, d, dev, pk, tf32):
+    """The other BASELINE configurations and the stages either side of the path, on one GPU (rank 0, N = 1)."""
+    from c3dgs_b200 import _lib as ops2
+    extras = {}
+    gen = torch.Generator(device=dev).manual_seed(5)
+
+    # ---- the other north-star configurations, each a 10-iteration full-batch clustering of 5.8 M rows ----
+    x7, w7 = synth(n, 7, 77, device=dev)
+    extras["shape7"] = run_config("configs[2]: shape codebook clustering, 5.8M x 7-D (scale + rotation)", x7, w7, dev,
+                                  pk=pk, tf32=tf32)
+    del x7, w7
+    s3 = torch.nn.functional.normalize(torch.rand(n, 3, device=dev, generator=gen) + 0.05)
+    r4 = torch.randn(n, 4, device=dev, generator=gen)
+    cov = ops2.build_covariance(s3, r4)
+    extras["cov6_trace_normalised"] = run_config(
+        "configs[2], fork reality: 5.8M normalised covariances x 6-D with the trace normalisation after every step "
+        "(vq.py:76-77)", cov, w, dev, scale_normalize=True, pk=pk, tf32=tf32)
+    extras["cov6_trace_normalised"]["fallback_rows_limit"] = n // 50
+    del s3, r4, cov
+    x48, w48 = synth(n, 48, 48, device=dev)
+    extras["sh48"] = run_config("configs[1], fork reality: 5.8M x 48-D (DC + 15 SH coefficients x 3)", x48, w48, dev,
+                                pk=pk, tf32=tf32)
+    del x48, w48
+    xi, wi = synth(n, d, 45, device=dev, kind="iid")
+    cbi = xi[torch.randint(0, n, (K,), device=dev, generator=gen)].clone()
+    extras["iid45"] = run_config("5.8M iid N(0,1) rows x 45-D, initial codebook sampled from the rows (every codeword in use)",
+                                 xi, wi, dev, cb0=cbi, pk=pk, tf32=tf32)
+    del xi, wi, cbi
+
+    # ---- the "before" number (SURVEY §8d last row, BASELINE.md §4 row 3): the reference's own weighted_distance.cu
+    # compiled unmodified (oracle/_ref) + index_add_ for torch_scatter, one iteration on the bench's own rows ----
+    ref_dir = os.path.join(ROOT, "oracle", "_ref")
+    if os.path.exists(os.path.join(ref_dir, "weighted_distance_ref", "_C.so")):
+        sys.path.insert(0, ref_dir)
+        try:
+            from weighted_distance_ref import _C as ref
+            cb, ei = cb0.clone(), torch.zeros(K, device=dev)
+
+            def ref_update():
+                # compression/vq.py:28-35 with the reference kernel and index_add_ standing in for torch_scatter
+                _, idx = ref.weightedDistance(x, cb)
+                acc_w = torch.zeros(K, device=dev).index_add_(0, idx, wn)
+                ei.mul_(DECAY).add_(acc_w, alpha=1 - DECAY)
+                acc_x = torch.zeros(K, d, device=dev).index_add_(0, idx, x * wn[:, None])
+                cb.mul_(DECAY).add_(acc_x / (acc_w[:, None] + EPS), alpha=1 - DECAY)
+
+            ref.weightedDistance(x[:4096], cb)                       # module load / first launch
+            torch.cuda.synchronize()
+            a, m, b = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+            a.record(torch.cuda.default_stream(dev))
+            _, idx_r = ref.weightedDistance(x, cb0)                    # legacy default stream (weighted_distance.cu:52)
+            m.record(torch.cuda.default_stream(dev))
+            torch.cuda.synchronize()
+            ms_assign = a.elapsed_time(m)
+            ms_update = timed(ref_update, reps=1)
+            _, idx_o = ops2.assign(x, cb0, return_dist=False)
+            extras["gpu_reference_kernel"] = {
+                "workload": f"one update iteration on the headline rows ({n} x {d}, K=4096, iteration-0 codebook)",
+                "assign_ms": ms_assign, "update_iteration_ms": ms_update,
+                "value": n / (ms_update * 1e-3), "unit": UNIT,
+                "assignments_equal_ours": bool(torch.equal(idx_r, idx_o)),
+                "note": "submodules/weighted_distance/weighted_distance.cu compiled unmodified for sm_100a "
+                        "(make -C oracle ref) + torch index_add_ for the two torch_scatter calls; same box, same rows"}
+            del idx_r, idx_o
+        except Exception as exc:  # noqa: BLE001
+            extras["gpu_reference_kernel"] = {"unavailable": repr(exc)}
+        finally:
+            sys.path.remove(ref_dir)
+    else:
+        extras["gpu_reference_kernel"] = {"unavailable": "oracle/_ref/weighted_distance_ref/_C.so not built"}
+
+    # SURVEY §8d (ii): the reference's real default, mini-batch mode, through the drop-in vq_features
+    # (CPU randint batches with replacement, 100 x 2^18 rows, then the final full assignment); reported, not the metric
+    from c3dgs_b200.vq import vq_features
+    mb_steps, mb_chunk = 100, 2 ** 18
+    vq_features(x, w, K, vq_chunk=mb_chunk, steps=3, decay=DECAY, silent=True)      # warm-up
+    torch.cuda.synchronize()
+    t0 = time.time()
+    vq_features(x, w, K, vq_chunk=mb_chunk, steps=mb_steps, decay=DECAY, silent=True)
+    torch.cuda.synchronize()
+    dt = time.time() - t0
+    extras["vq_features_minibatch"] = {"batch_rows": mb_chunk, "steps": mb_steps, "final_assign_rows": n,
+                                       "wall_ms": dt * 1e3, "rows_per_s": (mb_steps * mb_chunk + n) / dt,
+                                       "note": "host wall clock incl. the reference's per-step CPU torch.randint"}
+
+    # SURVEY §8f ranks 1-2, the steps right after the clustering: join_features (5 % of the rows kept) and
+    # extract_rot_scale on a joined covariance table of n/4 rows; HBM-bound, reported against the copy peak
+    keep = torch.rand(n, device=dev, generator=gen) < 0.05
+    cbi = torch.randint(0, K, (int((~keep).sum()),), device=dev, generator=gen)
+    cbj = torch.randn(K, d, device=dev, generator=gen)
+    ms = timed(lambda: ops2.join_features(x, keep, cbj, cbi))
+    jbytes = n * (1 + 8) + int((~keep).sum()) * 8 + (K + int(keep.sum())) * d * 4 * 2
+    extras["join_features"] = {"rows": n, "kept_frac": 0.05, "ms": ms, "gbs": jbytes / ms * 1e-6,
+                               "frac_of_hbm_peak": jbytes / ms * 1e-6 / pk["hbm_gbs"],
+                               "note": "two kernels + one host sync for the kept count (output size is data dependent)"}
+    nr = n // 4
+    a6 = torch.randn(nr, 3, 3, device=dev, generator=gen)
+    a6 = a6 @ a6.transpose(-1, -2)
+    cov6 = torch.stack([a6[:, 0, 0], a6[:, 0, 1], a6[:, 0, 2], a6[:, 1, 1], a6[:, 1, 2], a6[:, 2, 2]], -1).contiguous()
+    ms = timed(lambda: ops2.extract_rot_scale(cov6))
+    rbytes = nr * (24 + 28)
+    ms_torch, n_torch = None, 0
+    for n_torch in (100_000, 32_768, 4_096):             # cuSOLVER's batched syev rejects large batches on some builds
+        sub = a6[:n_torch].contiguous()
+        try:
+            ms_torch = timed(lambda: torch.linalg.eigh(sub, UPLO="U"), reps=1)
+            break
+        except RuntimeError:
+            continue
+    extras["extract_rot_scale"] = {"rows": nr, "ms": ms, "gbs": rbytes / ms * 1e-6,
+                                   "frac_of_hbm_peak": rbytes / ms * 1e-6 / pk["hbm_gbs"],
+                                   "torch_eigh_ms": ms_torch, "torch_eigh_rows": n_torch,
+                                   "note": "torch.linalg.eigh (the reference's call, cuSOLVER batched) timed on "
+                                           "a slice for scale; it is not on the product path"}
+    xyz = torch.randn(n, 3, device=dev, generator=gen)
+    ms = timed(lambda: ops2.morton_order(xyz))
+    mbytes = n * 12 * 2 + 8 * n * (8 + 8 + 12 + 12)       # min/max + keys, then 8 radix passes of (hist read, scatter read+write)
+    ms_torch = timed(lambda: torch.sort(torch.randint(0, 2 ** 62, (n,), device=dev, generator=gen)), reps=2)
+    extras["morton_order"] = {"rows": n, "ms": ms, "gbs": mbytes / ms * 1e-6,
+                              "frac_of_hbm_peak": mbytes / ms * 1e-6 / pk["hbm_gbs"],
+                              "torch_sort_int64_ms": ms_torch,
+                              "note": "keys + stable LSD radix sort of (u64 key, u32 row); torch.sort (cub) "
+                                      "of n random int64 incl. their generation, timed beside it for scale"}
+    del keep, cbi, cbj, a6, cov6, sub, xyz
+    tab48 = torch.randn(K + n // 20, 16, 3, device=dev, generator=gen)
+    idx48 = torch.randint(0, tab48.shape[0], (n,), device=dev, generator=gen)
+    ms = timed(lambda: ops2.gather(tab48, idx48))
+    gbytes = n * (8 + 4 * 48)
+    extras["decode_gather_sh48"] = {"rows": n, "dim": 48, "table_rows": int(tab48.shape[0]), "ms": ms,
+                                    "gbs": gbytes / ms * 1e-6, "frac_of_hbm_peak": gbytes / ms * 1e-6 / pk["hbm_gbs"]}
+    del tab48, idx48
+
+    # SURVEY §8f ranks 1 and 3, the formats either side of the path: normalised covariance, mask compaction,
+    # int8 scene-file quantisation (algorithmic bytes / time against the measured copy peak)
+    s3 = torch.rand(n, 3, device=dev, generator=gen) + 0.05
+    r4 = torch.randn(n, 4, device=dev, generator=gen)
+    ms = timed(lambda: ops2.build_covariance(s3, r4, activate=True))
+    extras["build_covariance"] = {"rows": n, "ms": ms, "gbs": n * 52 / ms * 1e-6,
+                                  "frac_of_hbm_peak": n * 52 / ms * 1e-6 / pk["hbm_gbs"]}
+    keep2 = torch.rand(n, device=dev, generator=gen) < 0.6
+    ms = timed(lambda: ops2.compact([x], keep2))
+    cbytes = n + int(keep2.sum()) * d * 4 * 2
+    extras["mask_splats_compact"] = {"rows": n, "kept_frac": 0.6, "row_bytes": d * 4, "ms": ms,
+                                     "gbs": cbytes / ms * 1e-6, "frac_of_hbm_peak": cbytes / ms * 1e-6 / pk["hbm_gbs"],
+                                     "note": "mask scan + host sync for the kept count + row move"}
+    ms = timed(lambda: ops2.quantize_i8(x, 0.03125, 3))
+    ms_t = timed(lambda: torch.quantize_per_tensor(x, 0.03125, 3, torch.qint8).int_repr())
+    extras["quantize_i8"] = {"elements": x.numel(), "ms": ms, "gbs": x.numel() * 5 / ms * 1e-6,
+                             "frac_of_hbm_peak": x.numel() * 5 / ms * 1e-6 / pk["hbm_gbs"],
+                             "torch_quantize_per_tensor_ms": ms_t,
+                             "note": "bit-exact with torch's CUDA quantiser (fp64 division there; fp32 fast path "
+                                     "with an exact fp64 slow path here), timed beside it"}
+    del s3, r4, keep2
+
+    # BASELINE configs[4]: the full compress pipeline on a synthetic 6M-Gaussian scene — prune, thresholds, both
+    # codebooks with the reference's default schedule shape (mini-batches), join, rotation/scaling extraction,
+    # decode of every attribute, Morton order + int8 scene tensors (file IO itself excluded: host numpy/zlib)
+    from c3dgs_b200 import CompressionSettings, SplatScene, compress_gaussians
+    npipe = 6_000_000
+    feats = torch.randn(npipe, 16, 3, device=dev, generator=gen)
+    scene = SplatScene(torch.randn(npipe, 3, device=dev, generator=gen), feats[:, :1].contiguous(),
+                       feats[:, 1:].contiguous(), torch.randn(npipe, 1, device=dev, generator=gen),
+                       torch.rand(npipe, 3, device=dev, generator=gen) + 0.05,
+                       torch.randn(npipe, 4, device=dev, generator=gen),
+                       torch.randn(npipe, 1, device=dev, generator=gen) - 3)
+    del feats
+    cimp = torch.rand(npipe, device=dev, generator=gen) ** 4
+    gimp = torch.rand(npipe, device=dev, generator=gen) ** 4
+    p_steps, p_batch = 100, 2 ** 18
+    cc = CompressionSettings(K, 0.0, 0.6, 0.9, p_steps, DECAY, p_batch)
+    gc_ = CompressionSettings(K, 0.0, 0.3, 0.9, p_steps, DECAY, p_batch)
+    torch.cuda.synchronize()
+    t0 = time.time()
+    compress_gaussians(scene, cimp, gimp, cc, gc_, color_compress_non_dir=True, prune_threshold=1e-8, silent=True)
+    torch.cuda.synchronize()
+    t1 = time.time()
+    from c3dgs_b200.decode import decode_gaussians
+    sdec, rdec, fdec = decode_gaussians(scene._scaling, scene._rotation,
+                                        torch.cat((scene._features_dc, scene._features_rest), 1),
+                                        scene._gaussian_indices, scene._feature_indices)
+    torch.cuda.synchronize()
+    t2 = time.time()
+    scene._sort_morton()
+    qbytes = 0
+    for name in ("features_dc", "features_rest", "opacity", "scaling", "scaling_factor", "rotation"):
+        t = scene._stored(name)
+        qbytes += ops2.quantize_i8(t, 0.01, 0).numel()
+    half = ops2.convert(scene._xyz, torch.float16)
+    i32 = ops2.convert(scene._feature_indices, torch.int32)
+    torch.cuda.synchronize()
+    t3 = time.time()
+    extras["compress_pipeline"] = {
+        "workload": "configs[4]: synthetic 6M-Gaussian scene, SH 48-D + shape 6-D codebooks (K=4096, "
+                    f"{p_steps} mini-batch steps of {p_batch} rows each + final full assignment), join, "
+                    "rot/scale, decode gather, Morton order, int8/fp16/int32 scene tensors",
+        "gaussians": npipe, "after_prune": int(scene._xyz.shape[0]),
+        "color_table_rows": int(scene._features_dc.shape[0]), "shape_table_rows": int(scene._rotation.shape[0]),
+        "compress_gaussians_ms": (t1 - t0) * 1e3, "decode_ms": (t2 - t1) * 1e3,
+        "morton_and_wire_ms": (t3 - t2) * 1e3, "total_ms": (t3 - t0) * 1e3,
+        "decoded_bytes": int(sdec.numel() + rdec.numel() + fdec.numel()) * 4, "int8_bytes": int(qbytes),
+        "note": "host wall clock, single run, includes workspace allocation and the host syncs the data-dependent "
+                "output sizes need"}
+    # SURVEY §8f rank 4: the indexed rasteriser's per-Gaussian preprocess on the compressed scene just built,
+    # forward and backward (the backward is where finetuning writes gradients into the two codebooks)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from preprocess_scene import camera
+    cam = camera(width=1297, height=840, fovx=0.9)
+    camt = {k_: torch.from_numpy(v_).to(dev) for k_, v_ in cam.items() if hasattr(v_, "dtype")}
+    table = torch.cat((scene._features_dc, scene._features_rest), 1).contiguous()
+    npre = scene._xyz.shape[0]
+    pre = {}
+    factors, opac = torch.exp(scene._scaling_factor), torch.sigmoid(scene._opacity)
+
+    def run_pre():
+        pre.update(ops2.preprocess_indexed(scene._xyz, scene._scaling, factors, scene._rotation, opac, table,
+                                           scene._feature_indices, scene._gaussian_indices, camt["viewmatrix"],
+                                           camt["projmatrix"], camt["cam_pos"], cam["width"], cam["height"],
+                                           cam["tan_fovx"], cam["tan_fovy"]))
+    ms = timed(run_pre)
+    nvis = int((pre["radii"] > 0).sum())
+    pbytes = npre * 36 + nvis * (52 + 192 + 51)
+    extras["preprocess_indexed"] = {"gaussians": npre, "visible": nvis, "ms": ms, "gbs": pbytes / ms * 1e-6,
+                                    "frac_of_hbm_peak": pbytes / ms * 1e-6 / pk["hbm_gbs"],
+                                    "note": "forward; zero-filling of the culled rows included"}
+    g2d = torch.randn(npre, 3, device=dev, generator=gen)
+    gcon = torch.randn(npre, 2, 2, device=dev, generator=gen)
+    gcol = torch.randn(npre, 3, device=dev, generator=gen)
+    ms = timed(lambda: ops2.preprocess_indexed_backward(
+        scene._xyz, pre["radii"], table, pre["clamped"], scene._scaling, factors, scene._rotation, pre["cov3d"],
+        camt["viewmatrix"], camt["projmatrix"], camt["cam_pos"], cam["width"], cam["height"], cam["tan_fovx"],
+        cam["tan_fovy"], g2d, gcon, gcol, scene._feature_indices, scene._gaussian_indices))
+    bbytes = npre * 4 + nvis * (12 + 24 + 16 + 12 + 12 + 3 + 4 + 16 + 28 + 192) + npre * (12 + 24 + 4) + nvis * (192 + 28)
+    extras["preprocess_indexed_backward"] = {
+        "gaussians": npre, "visible": nvis, "ms": ms, "gbs": bbytes / ms * 1e-6,
+        "frac_of_hbm_peak": bbytes / ms * 1e-6 / pk["hbm_gbs"],
+        "note": "one kernel (the reference launches two) + zero-filling of the three table gradients; bytes = inputs "
+                "read + per-Gaussian gradients written + table rows read and reduced into"}
+    return extras
 
 
 if __name__ == "__main__":

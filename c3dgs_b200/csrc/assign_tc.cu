@@ -34,6 +34,9 @@
 //               tile, then the A operand of both row tiles)
 // A pass is 256 rows x all K codes.  Each row tile owns two accumulator slots, so the MMA warp fills one while
 // the tile's 256 drain threads read the other: MMA, drain and re-rank all overlap.
+#include <cuda_fp16.h>
+#include <cstdlib>
+
 #include "common.cuh"
 #include "tc_ptx.cuh"
 
@@ -76,6 +79,12 @@ constexpr uint32_t TC_SBO = 128;
 constexpr float TC_BIG = 8.507059173023462e37f;  // 2^126: score of dead / padding codes
 constexpr float TC_HUGE2 = 1.2676506002282294e30f;  // 2^100: squared-norm limit of the error model
 constexpr int TC_SMEM_LIMIT = 227 * 1024;
+// fp16 screening (kind::f16, twice the tensor rate of kind::tf32 at the same 2^-11 unit roundoff): operands are
+// scaled by gamma = 2^g so that gamma * max |c'_j| < 2^7; the norm pieces ride against a constant 256 in A so that
+// three pieces of 65504 mark a dead / padding code far above every real score of a row inside the range limit
+constexpr float TC_F16_ACONST = 256.f;
+constexpr float TC_F16_DEAD = 3.f * 65504.f * 256.f;     // 5.03e7
+constexpr float TC_F16_XLIM = 1073741824.f;             // 2^30: limit of gamma^2 |x'|^2 (every element below 2^15)
 
 // Workspace header (device memory, zeroed per call).
 struct TcHeader {
@@ -92,10 +101,12 @@ struct TcHeader {
     int excl_gap_bits;              // 0x7f800000 - float bits of min |c'_j| over the finite outlier codes (0: none)
     unsigned int exp_hist[256];     // exponent histogram of |c_j|^2 over the finite codes (k_tc_prep_hist)
     unsigned long long prof[32];    // developer build (C3VQ_TC_PROF): cycle counters per role/phase
+    int g_exp;                      // fp16 screening: operands are scaled by 2^g_exp (k_tc_prep_mean)
 };
 
-__host__ __device__ inline int tc_dp(int d) { return (d + 2 + 7) & ~7; }          // padded K extent
-__host__ __device__ inline int tc_nc(int d) { int r = tc_dp(d) - d; return r < 3 ? r : 3; }  // norm columns
+// padded K extent: tf32 steps of 8 with at least two norm columns, fp16 steps of 16 with three
+__host__ __device__ inline int tc_dp(int d, bool f16 = false) { return f16 ? ((d + 3 + 15) & ~15) : ((d + 2 + 7) & ~7); }
+__host__ __device__ inline int tc_nc(int d, bool f16 = false) { int r = tc_dp(d, f16) - d; return r < 3 ? r : 3; }  // norm columns
 
 struct TcParams {
     const float *x;
@@ -104,7 +115,7 @@ struct TcParams {
     int64_t n;
     int d, k, nsteps, nstages;
     int64_t npairs;
-    const float *bimg;      // [k_pad/128][dp/4][128][4] tf32 image of -2c' and the norm pieces
+    const float *bimg;      // [k_pad/bn][dp*esize/16][bn][16 bytes]: tf32 (or scaled fp16) image of -2c' and the norm pieces
     const float *cbp;       // [k][dpc] raw codebook, zero padded to a multiple of 4 columns
     int dpc;
     const float *mu;        // [d] centre
@@ -202,7 +213,14 @@ __global__ void __launch_bounds__(256) k_tc_prep_mean(const float *__restrict__ 
 #ifdef C3VQ_TC_NO_OUTLIERS
         sthr = 254;                  // developer build: every finite code is regular (the behaviour before r1q)
 #endif
-        if (blockIdx.x == 0) hdr->thr_exp = sthr;
+        if (blockIdx.x == 0) {
+            hdr->thr_exp = sthr;
+            // fp16 screening: gamma = 2^g with gamma * |c'_j| < 2^7 for every regular code (|c_j|^2 < 2^(E+1) and
+            // |mu| <= max |c_j| give |c'_j| < 2^((E+3)/2)); the sampled data scale is folded in so that ordinary
+            // rows stay far below the range limit as well
+            const int es = max(sthr, min(ex + 1, 254));
+            hdr->g_exp = 7 - ((es - 127 + 4) >> 1);
+        }
     }
     __syncthreads();
     const int thr = sthr;
@@ -231,7 +249,7 @@ __global__ void __launch_bounds__(256) k_tc_prep_mean(const float *__restrict__ 
 
 // prep 2: one thread per (padded) code: centre, norms, TF32 image, padded raw copy, Cmax
 __global__ void k_tc_prep_image(const float *__restrict__ cb, int k, int k_pad, int d, int dp, int nc, int dpc,
-                                int bn, TcHeader *hdr, float *__restrict__ mu_out, float *__restrict__ bimg,
+                                int bn, int f16, TcHeader *hdr, float *__restrict__ mu_out, float *__restrict__ bimg,
                                 float *__restrict__ cbp)
 {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
@@ -239,6 +257,9 @@ __global__ void k_tc_prep_image(const float *__restrict__ cb, int k, int k_pad, 
     const int live = hdr->live;
     const float inv = live > 0 ? 1.f / (float)live : 0.f;
     float *img = bimg + (size_t)(j / bn) * (bn * dp) + (size_t)(j % bn) * 4;   // + chunk*BN*4 + (kk&3)
+    // fp16 image: 16-byte chunks of 8 elements, + chunk*BN*8 + (kk&7)
+    __half *img16 = reinterpret_cast<__half *>(bimg) + (size_t)(j / bn) * (bn * dp) + (size_t)(j % bn) * 8;
+    const int g = hdr->g_exp;
     bool fin = j < k;
     double n2 = 0.0;
     float raw2 = 0.f;
@@ -270,6 +291,30 @@ __global__ void k_tc_prep_image(const float *__restrict__ cb, int k, int k_pad, 
         const int cb_bits = __reduce_max_sync(0xffffffffu, fin ? __float_as_int(sqrtf(nf)) : 0);
         if ((threadIdx.x & 31) == 0 && cb_bits) atomicMax(&hdr->cmax_bits, cb_bits);
     }
+    if (f16) {
+        // scaled fp16 operands: -2 gamma c' and gamma^2 |c'|^2 / 256 in three pieces (exact splits: every
+        // remainder fits the next piece unless it falls below the fp16 subnormal step, 2^-25 absolute)
+        const float vq = ldexpf(nf, 2 * g - 8);
+        const __half h1 = __float2half_rn(vq);
+        const float r1 = vq - __half2float(h1);
+        const __half h2 = __float2half_rn(r1);
+        const __half h3 = __float2half_rn(r1 - __half2float(h2));
+        for (int c = 0; c < dp; c++) {
+            __half v = __float2half_rn(0.f);
+            if (fin && nf < TC_HUGE2) {
+                if (c < d) {
+                    const float cc = cb[(size_t)j * d + c] - hdr->mu_sum[c] * inv;
+                    v = __float2half_rn(ldexpf(-2.f * cc, g));
+                } else if (c < d + 3) {
+                    v = (c == d) ? h1 : (c == d + 1) ? h2 : h3;
+                }
+            } else if (c < d + 3 && c >= d) {
+                v = __float2half_rn(65504.f);   // dead or padding code: score 3 * 65504 * 256, never inside any band
+            }
+            img16[(size_t)(c >> 3) * (bn * 8) + (c & 7)] = v;
+        }
+        return;
+    }
     for (int c = 0; c < dp; c++) {
         float v = 0.f;
         if (fin && nf < TC_HUGE2) {
@@ -292,14 +337,16 @@ __global__ void k_tc_prep_image(const float *__restrict__ cb, int k, int k_pad, 
 
 // ------------------------------------------------------------------------------------------------
 // Shared-memory plan of k_assign_tc (bytes; every region 16-byte aligned, sB/sA 128-byte aligned)
-template <int DP>
+template <int DP, bool F16>
 struct TcSmem {
-    static constexpr int KSTEPS = DP / 8;
-    static constexpr int BN = tc_bn(DP);                                   // codes per stage / per MMA
+    static constexpr int KSTEPS = F16 ? DP / 16 : DP / 8;                  // MMAs per stage (K = 16 fp16 or 8 tf32 each)
+    static constexpr int BN = F16 ? 96 : tc_bn(DP);                        // codes per stage / per MMA
+    static constexpr int ESIZE = F16 ? 2 : 4;                              // bytes per operand element
+    static constexpr int ACOLS = F16 ? DP / 2 : DP;                        // TMEM columns of one row tile's A operand
     static constexpr int NG = BN / 8;                                      // groups of 4 codes per drain thread and job
     static constexpr int LCAP = tc_lcap(DP);
     static constexpr uint32_t LBO_B = BN * 16;
-    static constexpr uint32_t BSTAGE = BN * DP * 4;
+    static constexpr uint32_t BSTAGE = BN * DP * ESIZE;
     // staged row stride in floats: rows are 16-byte aligned (bulk reduce source) and XS / 4 is odd, which keeps the
     // lane <-> row accesses at 4-way bank conflicts (lane <-> column accesses are conflict free)
     static constexpr int XS = DP + 4;
@@ -310,7 +357,7 @@ struct TcSmem {
     static constexpr int SPT = tc_spt(DP);
     static constexpr int NSLOT = 2 * SPT;
     static constexpr uint32_t ACOL = NSLOT * BN;
-    static_assert(ACOL + 2 * DP <= 512, "TMEM budget");
+    static_assert(ACOL + 2 * ACOLS <= 512, "TMEM budget");
     static constexpr uint32_t LIST_BYTES = 2u * TC_DT * LCAP * 4;          // score words + payload words
     static constexpr uint32_t QUEUE_BYTES = 2u * TC_QCAP * 4;              // two passes in flight
     static constexpr uint32_t BEST_BYTES = TC_PR * 8;
@@ -336,11 +383,12 @@ __device__ __forceinline__ float min4(uint32_t a, uint32_t b, uint32_t c, uint32
 // row status handed from the drain warps to the re-rank warps
 constexpr uint8_t ROW_OK = 0, ROW_FALLBACK = 1, ROW_SKIP = 2;
 
-// DCONST > 0: feature width known at compile time (6, 7, 45, 48); DCONST == 0: runtime width p.d <= DP - 2.
-template <int DP, int DCONST, bool DBG>
+// DCONST > 0: feature width known at compile time (6, 7, 45, 48); DCONST == 0: runtime width p.d <= DP - 2 (- 3).
+// F16: screening with kind::f16 on scaled fp16 operands instead of kind::tf32 (same unit roundoff, twice the rate).
+template <int DP, int DCONST, bool DBG, bool F16>
 __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
 {
-    using L = TcSmem<DP>;
+    using L = TcSmem<DP, F16>;
     constexpr int KSTEPS = L::KSTEPS;
     constexpr int BN = L::BN;
     extern __shared__ __align__(128) uint8_t smem_raw[];
@@ -418,8 +466,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             const uint32_t sb0 = smem_u32(sB);
             PROF_DECL;
             for (int64_t pair = blockIdx.x; pair < p.npairs; pair += gridDim.x) {
-                const float *src = p.bimg;
-                for (int s = 0; s < nsteps; s++, src += BN * DP) {
+                const char *src = reinterpret_cast<const char *>(p.bimg);
+                for (int s = 0; s < nsteps; s++, src += L::BSTAGE) {
                     PROF(0);
                     mbar_wait_backoff(B_EMPTY(stage), phase);
                     PROF(1);   // prof[1]: TMA wait B_EMPTY
@@ -445,11 +493,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             // owns all 512 columns; checked after the allocation), and the B descriptor of (stage, ks) is the
             // stage's low word plus ks * DLO_KS under a constant high word.
             const int t = warp - (TC_MISC_WARP0 + 1);                                 // row tile of this warp
-            constexpr uint32_t IDESC = idesc_tf32(TC_BM, BN);
+            constexpr uint32_t IDESC = F16 ? idesc_f16(TC_BM, BN) : idesc_tf32(TC_BM, BN);
             constexpr uint32_t DHI = ((TC_SBO >> 4) & 0x3FFFu) | (1u << 14);          // SBO, descriptor version 1
             constexpr uint32_t DLO_KS = (2 * L::LBO_B) >> 4, DLO_STAGE = L::BSTAGE >> 4;
             const uint32_t dlo0 = ((smem_u32(sB) & 0x3FFFFu) >> 4) | (((L::LBO_B >> 4) & 0x3FFFu) << 16);
-            const uint32_t a_col = L::ACOL + t * DP;
+            const uint32_t a_col = L::ACOL + t * L::ACOLS;
             uint32_t pi = 0, stage = 0, phase = 0, dlo = dlo0;
             uint32_t sk = 0, sph = 1;                 // slot of the tile used by this step, parity of its ACC_EMPTY wait
             PROF_DECL;
@@ -471,7 +519,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
 #pragma unroll
                         for (int ks = 0; ks < KSTEPS; ks++) {
                             const uint64_t bd = ((uint64_t)DHI << 32) | (uint64_t)(dlo + ks * DLO_KS);
-                            umma_tf32_ts(sl * BN, a_col + ks * 8, bd, IDESC, ks > 0 ? 1u : 0u);
+                            if (F16) umma_f16_ts(sl * BN, a_col + ks * 8, bd, IDESC, ks > 0 ? 1u : 0u);
+                            else umma_tf32_ts(sl * BN, a_col + ks * 8, bd, IDESC, ks > 0 ? 1u : 0u);
                         }
                         umma_commit(ACC_FULL(sl));
                         umma_commit(B_EMPTY(stage));      // second arrival comes from the other tile's warp
@@ -539,8 +588,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
         };
         // warp pw owns rows pw*32..+31 of the pass in both mappings: lane <-> column for the global loads and the
         // staging stores, lane <-> row (= TMEM lane, this warp's quarter pw & 3 of tile pw >> 2) for the A operand
-        const uint32_t a_tmem = *(volatile uint32_t *)sTmem + ((uint32_t)((pw & 3) * 32) << 16) + L::ACOL + (pw >> 2) * DP;
-        const float cmax = __int_as_float(p.hdr->cmax_bits);
+        const uint32_t a_tmem = *(volatile uint32_t *)sTmem + ((uint32_t)((pw & 3) * 32) << 16) + L::ACOL + (pw >> 2) * L::ACOLS;
+        // fp16 screening works in units scaled by gam = 2^g (scores and bands by gam^2): exact powers of two
+        const float gam = F16 ? ldexpf(1.f, p.hdr->g_exp) : 1.f;
+        const float ginv = F16 ? ldexpf(1.f, -p.hdr->g_exp) : 1.f;
+        const float cmax = __int_as_float(p.hdr->cmax_bits) * gam;
         const float cexcl = __int_as_float(0x7f800000 - p.hdr->excl_gap_bits);   // nearest outlier code (inf: none)
         const bool has_outliers = p.hdr->excl_gap_bits != 0;
         // constants of the band formula below (C1, C2): 2 C2 Cmax^2 and 1 / (2 C1 Cmax)
@@ -623,7 +675,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                     // if that bound clears the winner's exact distance with room for every rounding involved
                     // |x'| from the row's band (sBand, written when the row was staged): band >= 1.01 * 2 * (C1 |x'| Cmax +
                     // C2 Cmax^2), so the quotient below is an upper bound of |x'|, tight to a fraction of a percent
-                    const float sx = (sBand[qb * TC_PR + lr] * (1.f / 1.01f) - outl_c2) * outl_inv;
+                    const float sx = (sBand[qb * TC_PR + lr] * (1.f / 1.01f) - outl_c2) * outl_inv * ginv;
                     const float gap = cexcl - 1.001f * sx;
                     const float lim = gap > 0.f ? 0.98f * gap * gap : 0.f;
                     if (!(__uint_as_float((unsigned int)(best >> 32)) < lim)) status = ROW_FALLBACK;
@@ -695,30 +747,49 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             }
             sW[(pi & 1) * TC_PR + ptid] = wr;
             __syncwarp();
-            uint32_t av[DP];
-            float X = 0.f;                       // |x'|^2 of the rounded, centred row -> error band
+            uint32_t av[L::ACOLS];
+            float X = 0.f;                       // |x'|^2 of the rounded, centred row (scaled by gam^2) -> error band
+            if (F16) {
 #pragma unroll
-            for (int kk = 0; kk < DP; kk++) {
-                float v = (kk < D + NC) ? 1.0f : 0.f;        // 1.0 against the norm pieces, 0 beyond
-                if (kk < D) {
-                    v = __uint_as_float(to_tf32(xs_w[lane * L::XS + kk] - sMu[kk]));
-                    X = fmaf(v, v, X);
+                for (int kk = 0; kk < DP; kk++) {
+                    // 256 against the three norm pieces, 0 beyond; two elements per 32-bit column, even K in the low half
+                    uint32_t hb = (kk < D + 3) ? 0x5C00u : 0u;
+                    if (kk < D) {
+                        const __half h = __float2half_rn((xs_w[lane * L::XS + kk] - sMu[kk]) * gam);
+                        const float v = __half2float(h);
+                        X = fmaf(v, v, X);
+                        hb = (uint32_t)__half_as_ushort(h);
+                    }
+                    if (kk & 1) av[kk >> 1] |= hb << 16; else av[kk >> 1] = hb;
                 }
-                av[kk] = __float_as_uint(v);
+            } else {
+#pragma unroll
+                for (int kk = 0; kk < DP; kk++) {
+                    float v = (kk < D + NC) ? 1.0f : 0.f;        // 1.0 against the norm pieces, 0 beyond
+                    if (kk < D) {
+                        v = __uint_as_float(to_tf32(xs_w[lane * L::XS + kk] - sMu[kk]));
+                        X = fmaf(v, v, X);
+                    }
+                    av[kk] = __float_as_uint(v);
+                }
             }
             {
                 const int64_t gi = pair * TC_PR + ptid;
                 // E bounds |score + X - true distance| for every code
                 const float C1 = 1.002f * 0.001953125f + 7.62939453125e-6f;   // 2^-9 * 1.002 + 2^-17
                 const float C2 = 3.814697265625e-6f + 4.76837158203125e-7f;   // 2^-18 + 2^-21
-                const float E = C1 * sqrtf(X) * cmax + C2 * cmax * cmax;
+                float E = C1 * sqrtf(X) * cmax + C2 * cmax * cmax;
+                // fp16 only: elements below 2^-14 round with 2^-25 absolute error (against |B| <= 2 gam Cmax, resp.
+                // |A| summing to <= sqrt(D X)), and the three norm pieces leave at most 3 * 2^-25 * 256
+                if (F16) E += 6.0e-8f * (float)D * cmax + 3.0e-8f * sqrtf((float)D * X) + 3.1e-5f;
                 float band = 1.01f * (2.f * E + p.gamma2 * X) + 3.0e-36f;
-                if (!(X < TC_HUGE2 * 0.0625f) || force_fb || !(band < TC_BIG))
+                if (!(X < (F16 ? TC_F16_XLIM : TC_HUGE2 * 0.0625f)) || force_fb ||
+                    !(band < (F16 ? 0.25f * TC_F16_DEAD : TC_BIG)))
                     band = __int_as_float(0x7fc00000);                        // NaN: exact fallback
                 if (gi >= p.n) band = -1.f;
                 if (DBG && gi < p.n) {
-                    p.dbg_norm2[gi] = X;
-                    p.dbg_band[gi] = band;
+                    p.dbg_norm2[gi] = X * ginv * ginv;
+                    p.dbg_band[gi] = band * ginv * ginv;
                 }
                 sBand[(pi & 1) * TC_PR + ptid] = band;
             }
@@ -727,7 +798,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             PROF(1);   // prof[16+1]: producer wait A_EMPTY
             tc_fence_after();
 #pragma unroll
-            for (int c8 = 0; c8 < DP / 8; c8++) {
+            for (int c8 = 0; c8 < L::ACOLS / 8; c8++) {
                 const uint32_t r8[8] = {av[c8 * 8 + 0], av[c8 * 8 + 1], av[c8 * 8 + 2], av[c8 * 8 + 3],
                                         av[c8 * 8 + 4], av[c8 * 8 + 5], av[c8 * 8 + 6], av[c8 * 8 + 7]};
                 tmem_st8(a_tmem + c8 * 8, r8);
@@ -788,7 +859,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             float band = sBand[(pi & 1) * TC_PR + lr];            // computed by the producer of this row
             float m = 3.0e38f;
             // valid rows start at 2^124: above every real score, below the 2^126 of dead / padding codes
-            float thr = (band >= 0.f) ? 0.25f * TC_BIG : __int_as_float(0xff800000);
+            float thr = (band >= 0.f) ? (F16 ? 0.5f * TC_F16_DEAD : 0.25f * TC_BIG) : __int_as_float(0xff800000);
             uint32_t cnt_off = 0;                       // byte offset of the next free list entry
             PROF(2);       // prof[24+2]: drain band
 
@@ -843,11 +914,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                     }
                 }
             };
-            auto dump = [&](const uint32_t (&a)[16], int code0) {   // debug build of the kernel only
+            auto dump = [&](const uint32_t (&a)[16], int code0) {   // debug build of the kernel only (unscaled scores)
+                const float g2inv = F16 ? ldexpf(1.f, -2 * p.hdr->g_exp) : 1.f;
 #pragma unroll
                 for (int jj = 0; jj < 16; jj++)
                     if (pair * TC_PR + lr < p.n && code0 + jj < p.k)
-                        p.dbg_scores[(pair * TC_PR + lr) * p.k + code0 + jj] = __uint_as_float(a[jj]);
+                        p.dbg_scores[(pair * TC_PR + lr) * p.k + code0 + jj] = __uint_as_float(a[jj]) * g2inv;
             };
 
             for (int s = 0; s < nsteps; s++) {
@@ -1064,20 +1136,28 @@ struct TcLayout {
     int dp, nc, dpc, k_pad, bn;
 };
 
-static TcLayout tc_layout(int64_t n, int d, int k)
+// Screening arithmetic: fp16 operands (kind::f16) by default, C3VQ_SCREEN=tf32 selects kind::tf32 (developer A/B knob;
+// the results are identical, both are followed by the exact re-rank).
+static bool screen_f16()
+{
+    static const int v = [] { const char *e = getenv("C3VQ_SCREEN"); return (e && (e[0] == 't' || e[0] == 'T')) ? 0 : 1; }();
+    return v != 0;
+}
+
+static TcLayout tc_layout(int64_t n, int d, int k, bool f16)
 {
     TcLayout l;
-    l.dp = tc_dp(d);
-    l.nc = tc_nc(d);
+    l.dp = tc_dp(d, f16);
+    l.nc = tc_nc(d, f16);
     l.dpc = (d + 3) & ~3;
-    l.bn = tc_bn(l.dp);
+    l.bn = f16 ? 96 : tc_bn(l.dp);
     l.k_pad = (k + l.bn - 1) / l.bn * l.bn;
     if (l.k_pad == 0) l.k_pad = l.bn;
     size_t o = al256(sizeof(TcHeader));
     l.off_mu = o;
     o += al256(80 * sizeof(float));
     l.off_bimg = o;
-    o += al256((size_t)l.k_pad * l.dp * sizeof(float));
+    o += al256((size_t)l.k_pad * l.dp * sizeof(float));      // sized for tf32 elements; the fp16 image needs half
     l.off_cbp = o;
     o += al256((size_t)(k > 0 ? k : 1) * l.dpc * sizeof(float));
     l.off_fb = o;
@@ -1091,14 +1171,15 @@ static TcLayout tc_layout(int64_t n, int d, int k)
 size_t tc_workspace_bytes(int64_t n, int d, int k)
 {
     if (n < 0 || d < 1 || d > C3VQ_MAX_DIM || k < 0) return 256;
-    return tc_layout(n, d, k).total;
+    const size_t a = tc_layout(n, d, k, false).total, b = tc_layout(n, d, k, true).total;
+    return a > b ? a : b;
 }
 
-template <int DP, int DCONST, bool DBG = false>
+template <int DP, int DCONST, bool F16, bool DBG = false>
 static int launch_tc_t(const TcParams &p, int grid, cudaStream_t s)
 {
-    if (!DBG && DCONST == 0 && p.dbg_scores != nullptr) return launch_tc_t<DP, 0, true>(p, grid, s);
-    using L = TcSmem<DP>;
+    if (!DBG && DCONST == 0 && p.dbg_scores != nullptr) return launch_tc_t<DP, 0, F16, true>(p, grid, s);
+    using L = TcSmem<DP, F16>;
     TcParams q = p;
     q.nstages = L::stages();
     if (q.nstages < 1) {
@@ -1106,8 +1187,8 @@ static int launch_tc_t(const TcParams &p, int grid, cudaStream_t s)
         return C3VQ_EINVAL;
     }
     const size_t smem = L::bytes(q.nstages);
-    C3VQ_CUDA(cudaFuncSetAttribute(k_assign_tc<DP, DCONST, DBG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_assign_tc<DP, DCONST, DBG><<<grid, TC_THREADS, smem, s>>>(q);
+    C3VQ_CUDA(cudaFuncSetAttribute(k_assign_tc<DP, DCONST, DBG, F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_assign_tc<DP, DCONST, DBG, F16><<<grid, TC_THREADS, smem, s>>>(q);
     C3VQ_LAUNCH_CHECK("k_assign_tc");
     return C3VQ_OK;
 }
@@ -1119,7 +1200,8 @@ int launch_assign_tc(const float *x, const float *w, const int64_t *rows, int64_
     if (n == 0) return C3VQ_OK;
     if (k == 0) return launch_assign_exact(x, rows, n, d, codebook, k, out_dist, out_idx, s);   // defaults only
     C3VQ_CHECK_ARG(n < 0xffffffffLL, "n=%lld too large for the fallback list", (long long)n);
-    const TcLayout l = tc_layout(n, d, k);
+    const bool f16 = screen_f16();
+    const TcLayout l = tc_layout(n, d, k, f16);
     if (ws == nullptr || ws_bytes < l.total) {
         set_error("workspace too small: %zu < %zu", ws_bytes, l.total);
         return C3VQ_EWORKSPACE;
@@ -1137,8 +1219,8 @@ int launch_assign_tc(const float *x, const float *w, const int64_t *rows, int64_
     C3VQ_LAUNCH_CHECK("k_tc_prep_hist");
     k_tc_prep_mean<<<(k + TC_PREP_CODES - 1) / TC_PREP_CODES, 256, 0, s>>>(codebook, k, d, hdr);
     C3VQ_LAUNCH_CHECK("k_tc_prep_mean");
-    k_tc_prep_image<<<(l.k_pad + 127) / 128, 128, 0, s>>>(codebook, k, l.k_pad, d, l.dp, l.nc, l.dpc, l.bn, hdr, mu,
-                                                        bimg, cbp);
+    k_tc_prep_image<<<(l.k_pad + 127) / 128, 128, 0, s>>>(codebook, k, l.k_pad, d, l.dp, l.nc, l.dpc, l.bn, f16 ? 1 : 0,
+                                                        hdr, mu, bimg, cbp);
     C3VQ_LAUNCH_CHECK("k_tc_prep_image");
 
     TcParams p{};
@@ -1156,25 +1238,44 @@ int launch_assign_tc(const float *x, const float *w, const int64_t *rows, int64_
 
     int rc;
 #ifdef C3VQ_TC_SINGLE   // developer build: one instantiation only (fast compile, SASS inspection)
-    rc = launch_tc_t<48, 45>(p, grid, s);
+    rc = launch_tc_t<48, 45, true>(p, grid, s);
 #else
-    switch (dbg_scores ? -1 : d) {      // the debug build of the kernel exists for the generic widths only
-        case 6: rc = launch_tc_t<8, 6>(p, grid, s); break;
-        case 7: rc = launch_tc_t<16, 7>(p, grid, s); break;
-        case 45: rc = launch_tc_t<48, 45>(p, grid, s); break;
-        case 48: rc = launch_tc_t<56, 48>(p, grid, s); break;
-        default: {
-            // generic widths: the image is laid out for DP = tc_dp(d); kernels exist for every multiple of 8
-            switch (l.dp) {
-                case 8: rc = launch_tc_t<8, 0>(p, grid, s); break;
-                case 16: rc = launch_tc_t<16, 0>(p, grid, s); break;
-                case 24: rc = launch_tc_t<24, 0>(p, grid, s); break;
-                case 32: rc = launch_tc_t<32, 0>(p, grid, s); break;
-                case 40: rc = launch_tc_t<40, 0>(p, grid, s); break;
-                case 48: rc = launch_tc_t<48, 0>(p, grid, s); break;
-                case 56: rc = launch_tc_t<56, 0>(p, grid, s); break;
-                case 64: rc = launch_tc_t<64, 0>(p, grid, s); break;
-                default: rc = launch_tc_t<72, 0>(p, grid, s); break;
+    if (f16) {
+        switch (dbg_scores ? -1 : d) {  // the debug build of the kernel exists for the generic widths only
+            case 6: rc = launch_tc_t<16, 6, true>(p, grid, s); break;
+            case 7: rc = launch_tc_t<16, 7, true>(p, grid, s); break;
+            case 45: rc = launch_tc_t<48, 45, true>(p, grid, s); break;
+            case 48: rc = launch_tc_t<64, 48, true>(p, grid, s); break;
+            default: {
+                // generic widths: the image is laid out for DP = tc_dp(d, true); kernels exist for every multiple of 16
+                switch (l.dp) {
+                    case 16: rc = launch_tc_t<16, 0, true>(p, grid, s); break;
+                    case 32: rc = launch_tc_t<32, 0, true>(p, grid, s); break;
+                    case 48: rc = launch_tc_t<48, 0, true>(p, grid, s); break;
+                    case 64: rc = launch_tc_t<64, 0, true>(p, grid, s); break;
+                    default: rc = launch_tc_t<80, 0, true>(p, grid, s); break;
+                }
+            }
+        }
+    } else {
+        switch (dbg_scores ? -1 : d) {
+            case 6: rc = launch_tc_t<8, 6, false>(p, grid, s); break;
+            case 7: rc = launch_tc_t<16, 7, false>(p, grid, s); break;
+            case 45: rc = launch_tc_t<48, 45, false>(p, grid, s); break;
+            case 48: rc = launch_tc_t<56, 48, false>(p, grid, s); break;
+            default: {
+                // generic widths: the image is laid out for DP = tc_dp(d); kernels exist for every multiple of 8
+                switch (l.dp) {
+                    case 8: rc = launch_tc_t<8, 0, false>(p, grid, s); break;
+                    case 16: rc = launch_tc_t<16, 0, false>(p, grid, s); break;
+                    case 24: rc = launch_tc_t<24, 0, false>(p, grid, s); break;
+                    case 32: rc = launch_tc_t<32, 0, false>(p, grid, s); break;
+                    case 40: rc = launch_tc_t<40, 0, false>(p, grid, s); break;
+                    case 48: rc = launch_tc_t<48, 0, false>(p, grid, s); break;
+                    case 56: rc = launch_tc_t<56, 0, false>(p, grid, s); break;
+                    case 64: rc = launch_tc_t<64, 0, false>(p, grid, s); break;
+                    default: rc = launch_tc_t<72, 0, false>(p, grid, s); break;
+                }
             }
         }
     }

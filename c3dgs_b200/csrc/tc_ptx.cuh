@@ -159,6 +159,18 @@ __device__ __forceinline__ void umma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, u
         "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// kind::f16 (fp16 operands, fp32 accumulators), A operand in tensor memory: row i = lane i, one 32-bit column holds
+// the two consecutive K elements 2c (low half) and 2c + 1 (high half); K = 16 per instruction = 8 columns.
+__device__ __forceinline__ void umma_f16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc,
+                                            uint32_t accumulate)
+{
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(d_tmem),
+        "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
 // registers -> TMEM: this warp's 32 lanes x 8 consecutive 32-bit columns (one row per thread)
 __device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t (&r)[8])
 {
@@ -232,6 +244,13 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo_bytes,
 __host__ __device__ constexpr uint32_t idesc_tf32(int m, int n)
 {
     return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+
+// Instruction descriptor for kind::f16 with fp16 operands: D = F32 (bits [4,6) = 1), A = B = F16 (format 0),
+// both K-major, N>>3 at [17,23), M>>4 at [24,29).
+__host__ __device__ constexpr uint32_t idesc_f16(int m, int n)
+{
+    return (1u << 4) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
 
 __device__ __forceinline__ uint32_t to_tf32(float v)

@@ -32,7 +32,7 @@ for it in range(3):
     b.record()
     torch.cuda.synchronize()
     ws = _lib._workspace.get(dev, 256)
-    prof = ws[328:328 + 256].view(torch.int64).cpu().tolist()
+    prof = ws[1368:1368 + 256].view(torch.int64).cpu().tolist()
     ms = a.elapsed_time(b)
     npairs = (n + 255) // 256
     ctas = min(148, npairs)
