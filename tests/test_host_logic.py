@@ -63,7 +63,8 @@ class _RecordingModel:
     def uniform_init(self, x):
         pass
 
-    def update_indexed(self, features, importance, batch, scale_normalize=False):
+    def update_indexed(self, features, importance, batch, scale_normalize=False, batch_checked=False):
+        assert batch_checked                    # the loop vouches for its own randint(0, n) draws: no per-step host sync
         if self.fail_at is not None and len(self.batches) == self.fail_at:
             raise ValueError("boom")
         self.batches.append(batch)
