@@ -265,7 +265,7 @@ class Clustering:
         self.n, self.d = x.shape
         self.scale_normalize = scale_normalize
         self.ops = CudaOps()
-        self.ops.tensor_cores = False if simt else ("fused" if sums == "fused" else True)
+        self.ops.tensor_cores = False if simt else sums          # "sorted" / "fused": explicit, whatever the default
         self.split = (not simt) and sums == "sorted"
         self.vq = ShardedVectorQuantize(self.d, K, DECAY, device=dev, ops=self.ops)
         self.events = []           # per iteration (e0, e1, e2, e3, e4)
@@ -299,10 +299,35 @@ class Clustering:
                 self.events.append(ev)
 
     def kernel_ms(self):
-        """(assignment ms, update ms) per iteration, averaged over the recorded iterations."""
+        """(assignment ms, update ms) per iteration, averaged over the recorded iterations.  With the sums fused into
+        the assignment kernel the first figure holds both and the second only the EMA; `fused_split` separates them."""
         a = float(np.mean([e[0].elapsed_time(e[1]) for e in self.events]))
         u = float(np.mean([e[1].elapsed_time(e[2]) + e[3].elapsed_time(e[4]) for e in self.events]))
         return a, u
+
+    def fused_split(self):
+        """Fused mode only: one more 10-iteration job in which every iteration's codebook is first assigned WITHOUT
+        the sums (timed), then with them (timed): (assignment alone ms, increment for the sums ms) per iteration."""
+        vq, L = self.vq, self.L
+        vq.codebook.copy_(self.cb0)
+        vq.entry_importance.zero_()
+        alone, fused = [], []
+        for _ in range(ITERS):
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+            vq._acc.zero_()
+            ev[0].record()
+            L.assign(self.x, vq.codebook, return_dist=False)
+            ev[1].record()
+            self.ops.assign_accumulate(self.x, self.wn, vq.codebook, vq._acc)
+            ev[2].record()
+            vq._all_reduce(vq._acc)
+            self.ops.ema(vq.codebook, vq.entry_importance, vq._acc, DECAY, EPS, self.scale_normalize)
+            alone.append(ev[:2])
+            fused.append(ev[1:])
+        torch.cuda.synchronize()
+        a = float(np.mean([e[0].elapsed_time(e[1]) for e in alone]))
+        f = float(np.mean([e[0].elapsed_time(e[1]) for e in fused]))
+        return a, f - a
 
 
 def timed(fn, reps=5):
@@ -316,43 +341,62 @@ def timed(fn, reps=5):
     return a.elapsed_time(b) / reps
 
 
+def screening_pipe():
+    """Which tensor pipe the screening GEMM runs on (libc3vq reads C3VQ_SCREEN per call; default fp16 operands)."""
+    return "tf32" if os.environ.get("C3VQ_SCREEN", "f16").lower().startswith("t") else "f16"
+
+
 def assignment_roofline(n, d, kern_ms, share, pk, tf32, simt, split):
     """Tensor roofline for the wide rows, the score-drain (TMEM read) roofline for D <= 8 (that width
-    is compare-rate bound, the MMA is a single k-step)."""
+    is compare-rate bound, the MMA is a single k-step).  `peak` is the measured sustained rate of the tensor pipe
+    the kernel actually issues to: cuBLAS TF32 measured in this run for kind::tf32, MEASURED_PEAKS.json's bf16 figure
+    for kind::f16 (fp16 and bf16 share the pipe and the rate).  The north star words its target against the TF32
+    peak whatever the pipe, so that fraction is printed beside it."""
     flops = 2.0 * K * d * n                               # SURVEY §8d: assign flops = 2*K*D per Gaussian*iteration
+    pipe = screening_pipe()
     kernel = ("k_assign_exact (SIMT)" if simt else
-              ("k_tc_prep_* + k_assign_tc + k_assign_fallback_* (assignment; sums by the sorted segmented-sum kernels)"
-               if split else "k_assign_tc (fused assign+sums)"))
+              (f"k_tc_prep_* + k_assign_tc (kind::{pipe}) + k_assign_fallback_* (assignment alone)"
+               if split else f"k_assign_tc (kind::{pipe}) with the centroid sums fused in + prep + fallback"))
+    drain_peak = 148 * 4 * 64 * 1.965e9 / 4 / 1e12        # 1e12 scores/s: 64 B/clk per SM sub-partition, 4 B per score
+    drain = {"achieved_tscore_s": n * K / (kern_ms * 1e-3) / 1e12, "peak_tscore_s": drain_peak,
+             "frac": n * K / (kern_ms * 1e-3) / 1e12 / drain_peak,
+             "note": "every one of the n*K fp32 scores leaves TMEM once: 64 B/clk per SM sub-partition x 592 x 1.965 GHz"}
     if d > 8:
         achieved = flops / (kern_ms * 1e-3) / 1e12
-        peak = tf32["tf32_tflops_sustained"]
+        if pipe == "tf32" or simt:
+            peak, src = tf32["tf32_tflops_sustained"], ("measured in this run: cuBLAS TF32 matmul 8192^3, sustained "
+                                                         "(kernel timed inside a long step)")
+        else:
+            peak, src = pk["bf16_tflops_sustained"], (f"{pk['source']}: MEASURED_PEAKS.json bf16_tflops_sustained "
+                                                      "(the kind::f16 pipe; kernel timed inside a long step)")
         return {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
                 "traffic": None,
-                "traffic_source": "not measured in this run; ncu dram__bytes of one k_assign_tc<48,45> launch at 5.8M x 45: "
-                                  "profiles/r1q_ncu_assign_tc_summary.txt (1.094 GB = the algorithmic bytes)",
-                "kernel": kernel, "kernel_ms": kern_ms, "kernel_share_of_step": share,
-                "peak_source": "measured in this run: cuBLAS TF32 matmul 8192^3, sustained (kernel timed inside a long step)",
-                "frac_vs_tf32_burst": achieved / tf32["tf32_tflops"],
+                "traffic_source": "not measured in this run; ncu dram__bytes of one k_assign_tc launch at 5.8M x 45 under "
+                                  "profiles/ (1.09 GB = the algorithmic bytes)",
+                "kernel": kernel, "kernel_ms": kern_ms, "kernel_share_of_step": share, "pipe": "kind::" + pipe,
+                "peak_source": src,
+                "frac_vs_tf32_sustained_measured": achieved / tf32["tf32_tflops_sustained"],
+                "frac_vs_tf32_burst_measured": achieved / tf32["tf32_tflops"],
                 "frac_vs_half_bf16_sustained": achieved / (pk["bf16_tflops_sustained"] / 2.0),
-                "frac_vs_spec_1125": achieved / TF32_SPEC_TFLOPS,
-                "tf32_peak_measured": tf32, "algorithmic_flops_per_launch": flops}
-    # every one of the n*K scores is read from TMEM once: 4 B each at 64 B/clk per SM sub-partition (4 per SM)
-    sm_clk = 1.965e9
-    peak = 148 * 4 * 64 * sm_clk / 4 / 1e12               # 1e12 scores/s
-    achieved = n * K / (kern_ms * 1e-3) / 1e12
-    return {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "Tscore/s", "frac": achieved / peak,
-            "traffic": None, "kernel": kernel, "kernel_ms": kern_ms, "kernel_share_of_step": share,
-            "peak_source": "score-drain roofline for D <= 8 (SURVEY §8d: compare-rate bound): n*K fp32 scores read from "
-                           "TMEM at 64 B/clk per SM sub-partition x 592 sub-partitions x 1.965 GHz max clock",
+                "frac_vs_tf32_spec_1125": achieved / TF32_SPEC_TFLOPS,
+                "tf32_peak_measured": tf32, "score_drain": drain, "algorithmic_flops_per_launch": flops,
+                "note": "the kernel is bound by the score drain (TMEM read + min reduction), not by the MMA: see score_drain"}
+    return {"bound": "tensor", "achieved": drain["achieved_tscore_s"], "peak": drain_peak, "unit": "Tscore/s",
+            "frac": drain["frac"], "traffic": None, "kernel": kernel, "kernel_ms": kern_ms,
+            "kernel_share_of_step": share, "pipe": "kind::" + pipe,
+            "peak_source": "score-drain roofline for D <= 8 (SURVEY §8d: compare-rate bound): " + drain["note"],
             "tensor_tflops": flops / (kern_ms * 1e-3) / 1e12,
             "hbm_floor_ms": n * (4 * d + 12) / pk["hbm_gbs"] * 1e-6, "algorithmic_scores_per_launch": float(n) * K}
 
 
-def update_roofline(n, d, upd_ms, share, pk):
+def update_roofline(n, d, upd_ms, share, pk, fused=False):
     nbytes = float(n) * (4 * d + 4 + 8)                   # SURVEY §8d: update bytes = 4*D + 4 (w) + 8 (idx) per row
     achieved = nbytes / (upd_ms * 1e-3) / 1e9
+    kernel = ("what the centroid sums add to k_assign_tc when fused in (rows read from HBM once per iteration; timed as "
+              "fused launch minus assignment alone on the same codebooks) + k_ema" if fused else
+              "k_seg_hist + k_seg_scan + k_seg_scatter + k_seg_sum + k_ema (sorted centroid sums + EMA)")
     return {"bound": "hbm", "achieved": achieved, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": achieved / pk["hbm_gbs"],
-            "traffic": None, "kernel": "k_wseg_rank + k_wseg_scan + k_wseg_place + k_wseg_sum + k_ema (centroid sums + EMA)",
+            "traffic": None, "kernel": kernel,
             "kernel_ms": upd_ms, "kernel_share_of_step": share, "algorithmic_bytes_per_launch": nbytes,
             "peak_source": f"{pk['source']}: MEASURED_PEAKS.json hbm_gbs (copy bandwidth)"}
 
@@ -363,7 +407,7 @@ def run_config(name, x, w, dev, steps=3, scale_normalize=False, cb0=None, pk=Non
     n, d = x.shape
     wn = (w / w.max()).contiguous()
     cb0 = init_codebook(x, K, 99) if cb0 is None else cb0
-    job = Clustering(x, wn, cb0, dev, scale_normalize=scale_normalize)
+    job = Clustering(x, wn, cb0, dev, sums=_lib.default_sums(), scale_normalize=scale_normalize)
     for _ in range(2):
         job.step(False)
     torch.cuda.synchronize()
@@ -376,10 +420,14 @@ def run_config(name, x, w, dev, steps=3, scale_normalize=False, cb0=None, pk=Non
     ms = a.elapsed_time(b) / steps
     rows, cands, fb = _lib.assign_stats(dev)              # last iteration's assignment
     am, um = job.kernel_ms()
+    fused = not job.split
+    if fused:
+        alone, incr = job.fused_split()
+        um = max(incr, 0.0) + um
     out = {"workload": name, "rows": n, "dim": d, "ms_per_step": ms, "value": n * ITERS / (ms * 1e-3),
            "assign_ms": am, "update_ms": um, "candidates_per_row": cands / max(rows, 1), "fallback_rows": fb,
-           "roofline": assignment_roofline(n, d, am, am * ITERS / ms, pk, tf32, False, True),
-           "roofline_update": update_roofline(n, d, um, um * ITERS / ms, pk)}
+           "roofline": assignment_roofline(n, d, am, am * ITERS / ms, pk, tf32, False, job.split),
+           "roofline_update": update_roofline(n, d, um, um * ITERS / ms, pk, fused=fused)}
     return out
 
 
@@ -394,8 +442,9 @@ def main():
     ap.add_argument("--scaling", default="weak", choices=["weak", "strong"])
     ap.add_argument("--total-rows", type=int, default=24_000_000, help="--scaling strong: rows split over the ranks")
     ap.add_argument("--simt", action="store_true", help="use the SIMT exact assignment instead of tensor cores")
-    ap.add_argument("--sums", default="sorted", choices=["sorted", "fused"],
-                    help="centroid sums: sorted segmented sum after the assignment (default) or fused bulk reduce-adds")
+    ap.add_argument("--sums", default=None, choices=["sorted", "fused"],
+                    help="centroid sums: fused into the assignment kernel (one bulk reduce-add per distinct codeword of "
+                         "a warp; rows read once) or the sorted segmented sum after it; default: the library's default")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true")
     args = ap.parse_args()
@@ -433,6 +482,8 @@ def main():
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    if args.sums is None:
+        args.sums = _lib.default_sums()
     d = args.dim
     n = args.rows if args.scaling == "weak" else args.total_rows // world
     warm = max(3, args.warmup)
@@ -476,8 +527,17 @@ def main():
     replica_hash = int(vq.codebook.view(torch.int32).to(torch.int64).sum().item()) & 0xFFFFFFFFFFFF
 
     assign_ms, update_ms = job.kernel_ms()
-    roofline = assignment_roofline(n, d, assign_ms, assign_ms * ITERS / ms_per_step, pk, tf32, args.simt, job.split)
-    roofline_update = update_roofline(n, d, update_ms, update_ms * ITERS / ms_per_step, pk) if job.split else None
+    if job.split or args.simt:
+        roofline = assignment_roofline(n, d, assign_ms, assign_ms * ITERS / ms_per_step, pk, tf32, args.simt, job.split)
+        roofline_update = update_roofline(n, d, update_ms, update_ms * ITERS / ms_per_step, pk) if job.split else None
+    else:
+        # sums fused into the assignment kernel: the launch is timed as one; a second job splits it per iteration
+        alone_ms, incr_ms = job.fused_split()
+        roofline = assignment_roofline(n, d, assign_ms, assign_ms * ITERS / ms_per_step, pk, tf32, False, False)
+        roofline["assignment_alone_ms"] = alone_ms
+        upd = max(incr_ms, 0.0) + update_ms                     # update_ms holds only the EMA here
+        roofline_update = update_roofline(n, d, upd, upd * ITERS / ms_per_step, pk, fused=True)
+        roofline_update["sums_increment_ms"], roofline_update["ema_ms"] = incr_ms, update_ms
 
     # decode gather: codebook[idx] -> [n, d], 8 B index in + 4 d B out per row
     gen = torch.Generator(device=dev).manual_seed(5 + rank)

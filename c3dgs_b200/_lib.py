@@ -18,6 +18,7 @@ LIB_PATH = os.environ.get("C3VQ_LIB") or os.path.join(_HERE, "libc3vq.so")   # C
 
 _lib = None
 _lock = threading.Lock()
+DEFAULT_SUMS = "sorted"
 
 
 def default_tensor_cores() -> bool:
@@ -26,15 +27,25 @@ def default_tensor_cores() -> bool:
     return os.environ.get("C3VQ_ASSIGN", "tc").lower() != "simt"
 
 
+def default_sums() -> str:
+    """Centroid sums after / inside the tensor-core assignment: "sorted" (counting sort by codeword + segmented sum,
+    second pass over x) or "fused" (one bulk reduce-add per distinct codeword of a warp from the rows staged in
+    shared memory; x read once).  C3VQ_SUMS overrides the default."""
+    v = os.environ.get("C3VQ_SUMS", DEFAULT_SUMS).lower()
+    return "fused" if v == "fused" else "sorted"
+
+
 def _tc_mode(tensor_cores) -> int:
     """use_tensor_cores argument of c3vq_update / c3vq_assign_accumulate: 0 = SIMT exact assignment + atomic sums,
     1 = tcgen05 assignment + sorted segmented sums (default), 2 = tcgen05 assignment with the sums fused into
     the kernel (one bulk reduce-add per row; x read once).  C3VQ_SUMS=fused selects 2 wherever True is passed."""
-    if tensor_cores == "fused" or tensor_cores == 2:
+    if tensor_cores == "fused" or (tensor_cores == 2 and tensor_cores is not True):
         return 2
+    if tensor_cores == "sorted":
+        return 1
     if not tensor_cores:
         return 0
-    return 2 if os.environ.get("C3VQ_SUMS", "sorted").lower() == "fused" else 1
+    return 2 if default_sums() == "fused" else 1
 
 
 _c_f32p = ctypes.c_void_p
@@ -157,10 +168,12 @@ class Workspace:
         self._buf = {}
         self._lock = threading.Lock()
 
-    def get(self, device: torch.device, nbytes: int) -> torch.Tensor:
+    def get(self, device: torch.device, nbytes: int, tag: str = "assign") -> torch.Tensor:
+        """`tag` separates scratch areas with different layouts: "assign" starts with the assignment's stats
+        header (read back by assign_stats), "sums" is the sorted-sum tables of a stand-alone accumulate."""
         index = device.index if device.index is not None else torch.cuda.current_device()
         dev = torch.device("cuda", index)
-        key = (index, torch.cuda.current_stream(dev).cuda_stream)
+        key = (index, torch.cuda.current_stream(dev).cuda_stream, tag)
         with self._lock:
             buf = self._buf.get(key)
             if buf is None or buf.numel() < nbytes:
@@ -317,7 +330,7 @@ def accumulate(x, w, idx, k: int, acc: torch.Tensor | None = None, rows=None, so
             raise RuntimeError(f"acc must be a contiguous [{k}, {stride}] float32 tensor")
         if sorted_path:
             nbytes = L.c3vq_accumulate_sorted_workspace_bytes(n, k)
-            ws = _workspace.get(x.device, nbytes)
+            ws = _workspace.get(x.device, nbytes, "sums")
             rc = L.c3vq_accumulate_sorted(_ptr(x), _ptr(w), _ptr(rows), _ptr(idx), n, d, k, _ptr(acc), _ptr(ws),
                                           nbytes, _stream(x))
         else:

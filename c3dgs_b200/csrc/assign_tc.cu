@@ -216,10 +216,11 @@ __global__ void __launch_bounds__(256) k_tc_prep_mean(const float *__restrict__ 
         if (blockIdx.x == 0) {
             hdr->thr_exp = sthr;
             // fp16 screening: gamma = 2^g with gamma * |c'_j| < 2^7 for every regular code (|c_j|^2 < 2^(E+1) and
-            // |mu| <= max |c_j| give |c'_j| < 2^((E+3)/2)); the sampled data scale is folded in so that ordinary
-            // rows stay far below the range limit as well
-            const int es = max(sthr, min(ex + 1, 254));
-            hdr->g_exp = 7 - ((es - 127 + 4) >> 1);
+            // |mu| <= max |c_j| give |c'_j| < 2^((E+3)/2)).  The scale follows the regular codes only (sthr is a
+            // percentile of the codebook, at most 8 binades above it): a single far-away ROW must not shrink gamma,
+            // or every ordinary operand would sink into the fp16 subnormals.  Rows more than 2^8 above that scale
+            // exceed the range limit and take the exact scan.
+            hdr->g_exp = 7 - ((sthr - 127 + 4) >> 1);
         }
     }
     __syncthreads();
@@ -694,24 +695,31 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
 #ifndef C3VQ_TC_EXP_NORED
                 if (p.acc) {
                     // scale this warp's 32 staged rows in place (lane <-> column): [w*x (D) | w | 0 ...] = one
-                    // accumulator row, then ONE bulk reduce-add per row (TMA engine, f32 adds at the L2)
+                    // accumulator row, then ONE bulk reduce-add per DISTINCT codeword of the warp (TMA engine, f32
+                    // adds at the L2): rows that share a codeword are summed into the first of them here.  While a
+                    // few codewords own most rows (the first iterations from a uniform-box codebook) this cuts the
+                    // reductions on their table rows, which the L2 performs one after the other, by up to 32x.
                     float *xw = sX + (qb * TC_PR + pw * 32) * L::XS;
                     const float *ww = sW + qb * TC_PR + pw * 32;
+                    const unsigned int key = status == ROW_OK ? (unsigned int)bj : 0x80000000u + (unsigned int)lane;
+                    const int leader = __ffs(__match_any_sync(0xffffffffu, key)) - 1;   // lowest lane with this codeword
 #pragma unroll 8
                     for (int r = 0; r < 32; r++) {
                         const float wv = ww[r];
+                        const int dst = __shfl_sync(0xffffffffu, leader, r);          // <= r, warp-uniform
 #pragma unroll
                         for (int h = 0; h < NH; h++) {
                             const int col = lane + 32 * h;
                             if (col < p.acc_stride) {
                                 const float v = col < D ? __fmul_rn(xw[r * L::XS + col], wv) : (col == D ? wv : 0.f);
-                                xw[r * L::XS + col] = v;
+                                if (dst == r) xw[r * L::XS + col] = v;
+                                else xw[dst * L::XS + col] = __fadd_rn(xw[dst * L::XS + col], v);
                             }
                         }
                     }
                     fence_proxy_async_smem();
                     __syncwarp();
-                    if (status == ROW_OK)
+                    if (status == ROW_OK && leader == lane)
                         bulk_reduce_add_f32(p.acc + (size_t)bj * p.acc_stride, smem_u32(xw + lane * L::XS),
                                             (uint32_t)p.acc_stride * 4u);
                     bulk_commit_group();
@@ -1140,8 +1148,8 @@ struct TcLayout {
 // the results are identical, both are followed by the exact re-rank).
 static bool screen_f16()
 {
-    static const int v = [] { const char *e = getenv("C3VQ_SCREEN"); return (e && (e[0] == 't' || e[0] == 'T')) ? 0 : 1; }();
-    return v != 0;
+    const char *e = getenv("C3VQ_SCREEN");               // read per call: tests and A/B tools flip it in-process
+    return !(e && (e[0] == 't' || e[0] == 'T'));
 }
 
 static TcLayout tc_layout(int64_t n, int d, int k, bool f16)

@@ -346,11 +346,12 @@ size_t wseg_workspace_bytes(int64_t n, int k);
 int launch_accumulate_windowed(const float *x, const float *w, const int64_t *idx, int64_t n, int d, int k, float *acc,
                                int stride, int wcol, void *ws, size_t ws_bytes, cudaStream_t s);
 
-// developer knob: C3VQ_SUMS_WINDOWED=0 keeps the plain codeword-sorted gather also for rows in storage order
+// developer knob: C3VQ_SUMS_WINDOWED=1 selects the windowed sort for rows in storage order (default: the plain
+// codeword-sorted gather, which measured faster: profiles/r2a_sums_probe_*.txt)
 static bool use_windowed()
 {
-    static const int v = [] { const char *e = getenv("C3VQ_SUMS_WINDOWED"); return (e && e[0] == '0') ? 0 : 1; }();
-    return v != 0;
+    const char *e = getenv("C3VQ_SUMS_WINDOWED");       // read per call: tests and A/B tools flip it in-process
+    return e && e[0] == '1';
 }
 
 size_t seg_workspace_bytes(int64_t n, int k)
@@ -427,17 +428,15 @@ int launch_accumulate_sorted(const float *x, const float *w, const int64_t *rows
 constexpr int WSEG_WIN_LOG = 16;
 constexpr int WSEG_WIN = 1 << WSEG_WIN_LOG;
 #ifndef C3VQ_WSEG_U
-#define C3VQ_WSEG_U 16
+#define C3VQ_WSEG_U 8
 #endif
-#ifndef C3VQ_WSEG_CTAS
-#define C3VQ_WSEG_CTAS 1
-#endif
-constexpr int WSEG_CH = 64;            // sorted positions per warp work item (two perm entries per lane)
+constexpr int WSEG_CH = 32;            // sorted positions per warp work item (one perm entry per lane)
 constexpr int WSEG_U = C3VQ_WSEG_U;    // rows whose loads are in flight per warp (divides 32)
 constexpr int WSEG_SUM_THREADS = 512;
-// CTAs per SM of the sum kernel.  The band of rows the grid works on at a time is warps x WSEG_CH rows and the next
-// band is being prefetched meanwhile: 148 x 16 warps x 64 rows x 180 B = 27 MB per band at d = 45, two bands in the L2
-constexpr int WSEG_CTAS_PER_SM = C3VQ_WSEG_CTAS;
+// Two CTAs per SM: 148 x 32 warps x 32 rows = 151 k rows = 27 MB at d = 45 is the band the grid works on at a time;
+// each chunk pulls the storage rows of the chunk WSEG windows-ahead of it into the L2, far enough that a window is
+// resident before the first warp of the grid reaches its sorted positions (band + one window).
+constexpr int WSEG_CTAS_PER_SM = 2;
 
 __global__ void __launch_bounds__(256)
 k_wseg_rank(const int64_t *__restrict__ idx, int64_t n, int k, unsigned int *__restrict__ hist,
@@ -503,7 +502,7 @@ k_wseg_place(const unsigned int *__restrict__ slot, const float *__restrict__ w,
 }
 
 template <int NH>
-__global__ void __launch_bounds__(WSEG_SUM_THREADS)
+__global__ void __launch_bounds__(WSEG_SUM_THREADS, WSEG_CTAS_PER_SM)
 k_wseg_sum(const float *__restrict__ x, const uint2 *__restrict__ perm, const unsigned int *__restrict__ wlen,
            int64_t n, int d, float *__restrict__ acc, int stride, int wcol)
 {
@@ -511,18 +510,19 @@ k_wseg_sum(const float *__restrict__ x, const uint2 *__restrict__ perm, const un
     const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
     const int64_t nchunks = (n + WSEG_CH - 1) / WSEG_CH;            // windows are multiples of the chunk
+    constexpr int64_t CPW = WSEG_WIN / WSEG_CH;                     // chunks per window
+    const int64_t ahead = ((nwarps + CPW - 1) / CPW + 1) * CPW;     // prefetch distance in chunks: the band + one window
     const bool c0 = lane < d, c1 = NH == 2 && lane + 32 < d;
     const size_t row_bytes = (size_t)d * 4;
     for (int64_t g = warp; g < nchunks; g += nwarps) {
-        // pull the storage rows of this warp's NEXT chunk range into the L2 (sequential in memory; the sorted
-        // positions of a window are a permutation of its own storage rows, so the union over the grid is the band
-        // of windows the grid reaches one trip later)
+        // pull the storage rows [gn * CH, gn * CH + CH) into the L2, sequentially in memory: chunk g of window v
+        // fetches the same slice of window v + ahead / CPW, so every window is fetched exactly once, by the
+        // chunks of the window `ahead` before it (the first windows are cold)
         {
-            const int64_t gn = g + nwarps;
+            const int64_t gn = g + ahead;
             if (gn < nchunks) {
                 const char *pb = reinterpret_cast<const char *>(x) + (size_t)gn * WSEG_CH * row_bytes;
-                const size_t rows_here = (size_t)min((int64_t)WSEG_CH, n - gn * WSEG_CH);
-                const size_t bytes = rows_here * row_bytes;
+                const size_t bytes = (size_t)min((int64_t)WSEG_CH, n - gn * WSEG_CH) * row_bytes;
                 for (size_t o = (size_t)lane * 128; o < bytes; o += 32 * 128)
                     asm volatile("prefetch.global.L2 [%0];" ::"l"(pb + o));
             }
@@ -534,8 +534,7 @@ k_wseg_sum(const float *__restrict__ x, const uint2 *__restrict__ perm, const un
         if (in_win >= len) continue;                                 // rows with invalid codes left a gap at the window's end
         const int cnt = (int)min((unsigned int)WSEG_CH, len - in_win);
         const float *xw = x + (size_t)v * WSEG_WIN * d + lane;
-        const uint2 e0 = lane < cnt ? perm[p0 + lane] : make_uint2(0u, 0u);
-        const uint2 e1 = lane + 32 < cnt ? perm[p0 + 32 + lane] : make_uint2(0u, 0u);
+        const uint2 e = lane < cnt ? perm[p0 + lane] : make_uint2(0u, 0u);
         int cur = -1;
         float a0 = 0.f, a1 = 0.f, aw = 0.f;
         auto flush = [&]() {
@@ -551,12 +550,10 @@ k_wseg_sum(const float *__restrict__ x, const uint2 *__restrict__ perm, const un
             unsigned int key[WSEG_U], wb[WSEG_U];
 #pragma unroll
             for (int u = 0; u < WSEG_U; u++) {
-                const int r = r0 + u;                                // r0 is a multiple of WSEG_U, WSEG_U divides 32
-                const uint2 e = (r0 < 32) ? e0 : e1;
-                key[u] = __shfl_sync(0xffffffffu, e.x, r & 31);
-                wb[u] = __shfl_sync(0xffffffffu, e.y, r & 31);
+                key[u] = __shfl_sync(0xffffffffu, e.x, r0 + u);
+                wb[u] = __shfl_sync(0xffffffffu, e.y, r0 + u);
                 const float *xp = xw + (size_t)(key[u] & 0xffffu) * d;
-                const bool live = r < cnt;
+                const bool live = r0 + u < cnt;
                 v0[u] = (live && c0) ? xp[0] : 0.f;
                 v1[u] = (live && c1) ? xp[32] : 0.f;
             }

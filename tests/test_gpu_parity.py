@@ -241,11 +241,12 @@ def test_accumulate_sorted_vs_oracle(L, oracle, d, skew):
 
 
 @pytest.mark.parametrize("d,k", [(45, 4096), (6, 33), (48, 1)])
-def test_accumulate_windowed_vs_oracle(L, oracle, d, k):
+def test_accumulate_windowed_vs_oracle(L, oracle, monkeypatch, d, k):
     """Rows in storage order take the windowed sort (key = (window of 65536 rows, codeword)): several windows, a
     ragged last one, rows with out-of-range codes (they leave gaps at the end of their window's range), a codeword
     that owns most of one window only, unit weights."""
     n = 3 * 65536 + 777
+    monkeypatch.setenv("C3VQ_SUMS_WINDOWED", "1")             # developer knob, read per call
     x, w, _ = _synth(n, d, max(k, 2), seed=300 + d)
     g = torch.Generator().manual_seed(k)
     idx = torch.randint(0, k, (n,), generator=g)

@@ -287,3 +287,67 @@ def test_scene_file_round_trip_and_format(L, oracle, quantization, tmp_path):
         assert torch.equal(back._xyz, scene._xyz)
         assert torch.equal(back._features_rest, scene._features_rest)
         assert torch.equal(back._rotation, scene._rotation.half().float())
+
+
+# ---------------------------------------------------------------- reference-side interop of the scene file -----------
+# tests/golden/scene_interop.npz was made by oracle/make_scene_golden.py, which imports the reference's own
+# scene/gaussian_model.py on CPU and runs ITS save_npz (:505-623), load_npz (:625-740) and decode properties
+# (:213-257) on a small indexed, quantisation-aware model.
+def _interop():
+    return np.load(os.path.join(ROOT, "tests", "golden", "scene_interop.npz"))
+
+
+def _subfile(g, prefix):
+    return {k[len(prefix):]: g[k] for k in g.files if k.startswith(prefix)}
+
+
+def test_reference_written_scene_file_loads_into_the_same_tensors(L, tmp_path):
+    """A file written by the reference's save_npz, read by SplatScene.load_npz: every tensor equals what the
+    reference's own load_npz produced from it; then the indexed decode sites (get_features / get_rotation /
+    get_scaling, gaussian_model.py:213-257) equal the reference's on that model."""
+    from c3dgs_b200 import SplatScene
+    g = _interop()
+    path = str(tmp_path / "ref_written.npz")
+    np.savez_compressed(path, **_subfile(g, "fileA/"))
+    sc = SplatScene.load_npz(path, device=DEV)
+    for name in ("xyz", "features_dc", "features_rest", "scaling", "scaling_factor", "rotation"):
+        got, want = getattr(sc, "_" + name).cpu().numpy(), g["loaded/" + name]
+        assert got.shape == want.shape and got.dtype == want.dtype
+        assert np.array_equal(got, want), name                        # (q - zero_point) * scale in float32: exact
+    assert np.allclose(sc._opacity.cpu().numpy(), g["loaded/opacity"], rtol=3e-6, atol=1e-6)   # logit: libm vs CUDA log
+    for name in ("feature_indices", "gaussian_indices"):
+        got = getattr(sc, "_" + name)
+        assert got.dtype == torch.int64 and np.array_equal(got.cpu().numpy(), g["loaded/" + name])
+    assert sc.quantization and sc.is_color_indexed and sc.is_gaussian_indexed
+    assert np.array_equal(sc.get_features.cpu().numpy(), g["decoded/features"])                 # pure gather
+    assert np.allclose(sc.get_rotation.cpu().numpy(), g["decoded/rotation"], rtol=2e-6, atol=1e-7)
+    scaling = torch.exp(sc._scaling_factor) * sc.get_scaling_normalized                         # :213-222
+    assert np.allclose(scaling.cpu().numpy(), g["decoded/scaling"], rtol=4e-6, atol=1e-9)
+
+
+@pytest.mark.parametrize("sort_morton", [False, True])
+def test_scene_file_written_here_holds_the_reference_files_arrays(L, tmp_path, sort_morton):
+    """The other direction: SplatScene.save_npz from the same tensors and (scale, zero_point) pairs writes the same
+    keys, dtypes, shapes and values as the reference's save_npz did (so the reference's load_npz, pinned above on
+    its own file, reads it the same way).  The int8 values go through sigmoid / normalize evaluated on the GPU here
+    and on the CPU there, so a value on a rounding boundary may land one step apart (bounded at 0.5 % of a tensor)."""
+    from c3dgs_b200 import SplatScene
+    g = _interop()
+    want = _subfile(g, "fileB/" if sort_morton else "fileA/")
+    t = {k[3:]: torch.from_numpy(g[k]).to(DEV) for k in g.files if k.startswith("in/") and not k.endswith(("_scale", "_zero_point"))}
+    qp = {n: (float(g[f"in/{n}_scale"][0]), int(g[f"in/{n}_zero_point"][0]))
+          for n in ("features_dc", "features_rest", "opacity", "scaling", "scaling_factor", "rotation")}
+    sc = SplatScene(t["xyz"], t["features_dc"], t["features_rest"], t["opacity"], t["scaling"], t["rotation"],
+                    scaling_factor=t["scaling_factor"], quantization=True, qparams=qp)
+    sc._feature_indices, sc._gaussian_indices = t["feature_indices"], t["gaussian_indices"]
+    path = str(tmp_path / "ours.npz")
+    sc.save_npz(path, sort_morton=sort_morton)
+    got = dict(np.load(path))
+    assert sorted(got) == sorted(want)
+    for k in sorted(want):
+        assert got[k].dtype == want[k].dtype and got[k].shape == want[k].shape, (k, got[k].dtype, got[k].shape)
+        if want[k].dtype == np.int8:
+            diff = np.abs(got[k].astype(np.int32) - want[k].astype(np.int32))
+            assert diff.max() <= 1 and (diff != 0).mean() <= 5e-3, (k, int(diff.max()), float((diff != 0).mean()))
+        else:
+            assert np.array_equal(got[k], want[k]), k

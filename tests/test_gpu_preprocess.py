@@ -180,7 +180,7 @@ def _run_bwd(L, sc, cam, fwd, gr, deg=3, mod=1.0):
         t["scales"], t["scale_factors"], t["rotations"], torch.from_numpy(fwd["cov3d"]).to(DEV), c["viewmatrix"],
         c["projmatrix"], c["cam_pos"], cam["width"], cam["height"], cam["tan_fovx"], cam["tan_fovy"], t["dl_dmean2d"],
         t["dl_dconic"], t["dl_dcolor"], t["sh_indices"], t["g_indices"], sh_degree=deg, scale_modifier=mod)
-    return {k: v.cpu().numpy().reshape(v.shape[0], -1) for k, v in out.items()}
+    return {k: v.cpu().numpy().reshape(v.shape[0], int(np.prod(v.shape[1:]))) for k, v in out.items()}
 
 
 def _run_bwd_reference(sc, cam, fwd, gr, deg=3, mod=1.0):
@@ -208,7 +208,7 @@ def _run_bwd_reference(sc, cam, fwd, gr, deg=3, mod=1.0):
         out["scale_factors"].data_ptr(), out["rotations"].data_ptr(), t["sh_indices"].data_ptr(),
         t["g_indices"].data_ptr())
     assert rc == 0
-    return {k: v.cpu().numpy().reshape(v.shape[0], -1) for k, v in out.items()}
+    return {k: v.cpu().numpy().reshape(v.shape[0], int(np.prod(v.shape[1:]))) for k, v in out.items()}
 
 
 def _oracle_bwd(oracle, sc, cam, fwd, gr, deg=3, mod=1.0, dtype=np.float32):
@@ -217,7 +217,7 @@ def _oracle_bwd(oracle, sc, cam, fwd, gr, deg=3, mod=1.0, dtype=np.float32):
         fwd["cov3d"], cam["viewmatrix"], cam["projmatrix"], cam["cam_pos"], cam["width"], cam["height"],
         cam["tan_fovx"], cam["tan_fovy"], gr["dl_dmean2d"], gr["dl_dconic"], gr["dl_dcolor"], sc["sh_indices"],
         sc["g_indices"], sh_degree=deg, scale_modifier=mod, dtype=dtype)
-    return {k: np.asarray(v).reshape(len(v), -1) for k, v in out.items()}
+    return {k: np.asarray(v).reshape(len(v), int(np.prod(np.asarray(v).shape[1:]))) for k, v in out.items()}
 
 
 def _compare_bwd(a, b, what):

@@ -353,3 +353,25 @@ def test_oracle_preprocess_backward_matches_finite_differences(oracle):
                 lm = loss(s2)
                 num, ana = (lp - lm) / (2 * eps), bw[key][ix]
                 assert abs(num - ana) <= 5e-5 * (abs(num) + abs(ana)) + 1e-9, (deg, key, ix, num, ana)
+
+
+def test_scene_interop_fixture_pins_the_oracle_quantiser(oracle):
+    """tests/golden/scene_interop.npz holds a file the reference's own save_npz wrote and what its load_npz read back
+    (oracle/make_scene_golden.py).  The oracle's quantiser / dequantiser restate those two: the int8 arrays of the file
+    from the recorded inputs (torch's CPU quantiser multiplies by a float32 reciprocal, so a value on a rounding
+    boundary may differ by one step: bounded), the loaded tensors from the file bit for bit."""
+    g = np.load(os.path.join(ROOT, "tests", "golden", "scene_interop.npz"))
+    assert bool(g["fileA/quantization"]) and g["fileA/xyz"].dtype == np.float16
+    assert g["fileA/feature_indices"].dtype == np.int32 and g["loaded/feature_indices"].dtype == np.int64
+    assert np.array_equal(g["fileA/xyz"], g["in/xyz"].astype(np.float16))
+    for name in ("features_dc", "features_rest", "scaling_factor"):        # stored without an activation
+        scale, zp = float(g[f"in/{name}_scale"][0]), int(g[f"in/{name}_zero_point"][0])
+        q = oracle.quantize_i8(g["in/" + name], scale, zp)
+        diff = np.abs(q.astype(np.int32) - g["fileA/" + name].astype(np.int32))
+        assert diff.max() <= 1 and (diff != 0).mean() <= 2e-3, name
+    for name in ("features_dc", "features_rest", "scaling", "scaling_factor", "rotation"):
+        scale, zp = g[f"fileA/{name}_scale"][0], int(g[f"fileA/{name}_zero_point"][0])
+        assert np.array_equal(oracle.dequantize_i8(g["fileA/" + name], scale, zp), g["loaded/" + name]), name
+    # Morton-sorted file: same multiset of positions, a permutation of the per-Gaussian arrays only
+    assert np.array_equal(np.sort(g["fileB/xyz"].view(np.uint16), axis=0), np.sort(g["fileA/xyz"].view(np.uint16), axis=0))
+    assert np.array_equal(g["fileB/rotation"], g["fileA/rotation"])
