@@ -60,14 +60,55 @@ k_gather32(const T *__restrict__ table, int64_t table_rows, int dv, const int64_
 }
 
 // Rows that are not a multiple of 16 bytes (45 floats = 180 B is the SH width): a warp takes 32 consecutive output rows,
-// i.e. one contiguous, 16-byte aligned span of 32*d floats, reads its 32 indices with one coalesced load, parks them in
-// shared memory and writes the span as float4 — one integer division and one 16-byte store per four elements instead
-// of a division, an index load and a 4-byte store per element.
+// i.e. one contiguous, 16-byte aligned span of 32*d floats.  It reads its 32 indices with one coalesced load, copies
+// the 32 table rows into shared memory with lanes over columns (two coalesced 4-byte loads per row, eight rows in
+// flight, no index arithmetic per element) and writes the span out as float4.  ~150 warp instructions per 32 rows
+// where the element-wise formulation needed ~600 (a division and four scalar loads per float4).
 __global__ void __launch_bounds__(256)
 k_gather_span(const float *__restrict__ table, int64_t table_rows, int d, const int64_t *__restrict__ idx, int64_t n,
               float *__restrict__ out)
 {
-    __shared__ const float *sj[8][32];                               // source row of each output row (null: zeros)
+    extern __shared__ __align__(16) float stage[];                   // [8 warps][32 rows][d]
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    float *st = stage + (size_t)wib * 32 * d;
+    const int64_t nwarps = (int64_t)gridDim.x * 8;
+    for (int64_t r0 = ((int64_t)blockIdx.x * 8 + wib) * 32; r0 < n; r0 += nwarps * 32) {
+        const int rows_here = (int)min((int64_t)32, n - r0);
+        long long j = -1;
+        if (lane < rows_here) {
+            j = idx[r0 + lane];
+            if ((uint64_t)j >= (uint64_t)table_rows) j = -1;          // out of range: zeros
+        }
+        __syncwarp();                                                 // the previous span has left the staging rows
+#pragma unroll 8
+        for (int r = 0; r < 32; r++) {
+            const long long jr = __shfl_sync(0xffffffffu, j, r);
+            if (r < rows_here) {
+                const float *src = table + jr * d;
+                for (int c = lane; c < d; c += 32) st[r * d + c] = jr >= 0 ? __ldg(src + c) : 0.f;
+            }
+        }
+        __syncwarp();
+        float *dst = out + r0 * d;                                    // 32 * d * 4 bytes per span: 16-byte aligned
+        const int total = rows_here * d;
+        for (int e = lane * 4; e < total; e += 128) {
+            if (e + 3 < total) {
+                *reinterpret_cast<float4 *>(dst + e) = *reinterpret_cast<const float4 *>(st + e);
+            } else {
+                for (int t = 0; t < 4 && e + t < total; t++) dst[e + t] = st[e + t];
+            }
+        }
+    }
+}
+
+// Rows of whole float4 (d % 4 == 0; 48 floats = the fork's colour rows): the same span organisation without the
+// staging — the 32 * dv float4 of a span are copied lane-linear, four loads in flight per lane, the row of element e
+// by a multiply-shift (exact for e < 32 * dv, dv < 128) against row pointers parked in shared memory.
+__global__ void __launch_bounds__(256)
+k_gather_span4(const float4 *__restrict__ table, int64_t table_rows, int dv, unsigned int inv,
+               const int64_t *__restrict__ idx, int64_t n, float4 *__restrict__ out)
+{
+    __shared__ const float4 *sj[8][32];                              // source row of each output row (null: zeros)
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int64_t nwarps = (int64_t)gridDim.x * 8;
     for (int64_t r0 = ((int64_t)blockIdx.x * 8 + wib) * 32; r0 < n; r0 += nwarps * 32) {
@@ -75,29 +116,29 @@ k_gather_span(const float *__restrict__ table, int64_t table_rows, int d, const 
         long long j = -1;
         if (lane < rows_here) {
             j = idx[r0 + lane];
-            if ((uint64_t)j >= (uint64_t)table_rows) j = -1;          // out of range: zeros, as before
+            if ((uint64_t)j >= (uint64_t)table_rows) j = -1;
         }
         __syncwarp();
-        sj[wib][lane] = j >= 0 ? table + j * d : nullptr;
+        sj[wib][lane] = j >= 0 ? table + j * dv : nullptr;
         __syncwarp();
-        float *dst = out + r0 * d;                                    // 32 * d * 4 bytes per span: 16-byte aligned
-        const unsigned int total = (unsigned int)rows_here * (unsigned int)d;
-        for (unsigned int e = lane * 4; e < total; e += 128) {
-            unsigned int r = e / (unsigned int)d, c = e - r * (unsigned int)d;
-            float v[4];
+        float4 *dst = out + r0 * dv;
+        const unsigned int total = (unsigned int)rows_here * (unsigned int)dv;
+        for (unsigned int e0 = lane; e0 < total; e0 += 128) {
+            float4 v[4];
 #pragma unroll
-            for (int t = 0; t < 4; t++) {
-                v[t] = 0.f;
-                if (e + t < total) {
-                    const float *src = sj[wib][r];
-                    if (src != nullptr) v[t] = __ldg(src + c);
-                    if (++c == (unsigned int)d) c = 0, r++;
+            for (int u = 0; u < 4; u++) {
+                const unsigned int e = e0 + 32 * u;
+                v[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (e < total) {
+                    const unsigned int r = (e * inv) >> 20;
+                    const float4 *src = sj[wib][r];
+                    if (src != nullptr) v[u] = __ldg(src + (e - r * (unsigned int)dv));
                 }
             }
-            if (e + 3 < total) {
-                *reinterpret_cast<float4 *>(dst + e) = make_float4(v[0], v[1], v[2], v[3]);
-            } else {
-                for (int t = 0; t < 4 && e + t < total; t++) dst[e + t] = v[t];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const unsigned int e = e0 + 32 * u;
+                if (e < total) dst[e] = v[u];
             }
         }
     }
@@ -125,14 +166,23 @@ int launch_gather(const float *table, int64_t table_rows, int d, const int64_t *
     if (n == 0 || d == 0) return C3VQ_OK;
     const bool v4 = (d % 4 == 0) && ((reinterpret_cast<uintptr_t>(table) & 15) == 0) &&
                     ((reinterpret_cast<uintptr_t>(out) & 15) == 0);
+    int64_t blocks = (n + 255) / 256;                             // 8 warps x 32 rows per block and round
+    const int64_t cap = (int64_t)sm_count() * 16;
+    if (blocks > cap) blocks = cap;
+    if (v4 && d / 4 < 128) {
+        const int dv = d / 4;
+        k_gather_span4<<<(unsigned)blocks, 256, 0, s>>>(reinterpret_cast<const float4 *>(table), table_rows, dv,
+                                                        ((1u << 20) + dv - 1) / dv, idx, n,
+                                                        reinterpret_cast<float4 *>(out));
+        C3VQ_LAUNCH_CHECK("k_gather_span4");
+        return C3VQ_OK;
+    }
     if (v4)
         return launch_gather_t<float4>(reinterpret_cast<const float4 *>(table), table_rows, d / 4, idx, n,
                                        reinterpret_cast<float4 *>(out), s);
-    if ((reinterpret_cast<uintptr_t>(out) & 15) == 0 && d < (1 << 24)) {
-        int64_t blocks = (n + 255) / 256;                         // 8 warps x 32 rows per block and round
-        const int64_t cap = (int64_t)sm_count() * 16;
-        if (blocks > cap) blocks = cap;
-        k_gather_span<<<(unsigned)blocks, 256, 0, s>>>(table, table_rows, d, idx, n, out);
+    if ((reinterpret_cast<uintptr_t>(out) & 15) == 0 && (size_t)d * 1024 <= 48 * 1024) {
+        if (blocks > (int64_t)sm_count() * 4) blocks = (int64_t)sm_count() * 4;   // 1 KB x d of staging per block
+        k_gather_span<<<(unsigned)blocks, 256, (size_t)d * 1024, s>>>(table, table_rows, d, idx, n, out);
         C3VQ_LAUNCH_CHECK("k_gather_span");
         return C3VQ_OK;
     }

@@ -126,12 +126,23 @@ class SplatScene:
         for n, t in zip(names, outs):
             setattr(self, n, t)
 
+    @staticmethod
+    def _check_indices(indices: torch.Tensor, rows: int, what: str) -> None:
+        """The decode gathers read table rows unchecked (an out-of-range index decodes to a row of zeros where torch
+        indexing would raise), so index arrays are validated once, where they enter the scene."""
+        if indices.numel():
+            lo, hi = (int(v) for v in torch.aminmax(indices))
+            if lo < 0 or hi >= rows:
+                raise IndexError(f"{what} must lie in [0, {rows}), got [{lo}, {hi}]")
+
     def set_color_indexed(self, features: torch.Tensor, indices: torch.Tensor) -> None:
+        self._check_indices(indices, features.shape[0], "feature indices")
         self._feature_indices = indices
         self._features_dc = features[:, :1].detach()
         self._features_rest = features[:, 1:].detach()
 
     def set_gaussian_indexed(self, rotation: torch.Tensor, scaling: torch.Tensor, indices: torch.Tensor) -> None:
+        self._check_indices(indices, rotation.shape[0], "gaussian indices")
         self._gaussian_indices = indices.detach()
         self._rotation = rotation.detach()
         self._scaling = scaling.detach()
@@ -235,6 +246,8 @@ class SplatScene:
         scene.qparams = qparams
         if "gaussian_indices" in sd.files:
             scene._gaussian_indices = _lib.convert(dev_t("gaussian_indices"), torch.int64)
+            cls._check_indices(scene._gaussian_indices, rotation.shape[0], "gaussian_indices of " + str(path))
         if "feature_indices" in sd.files:
             scene._feature_indices = _lib.convert(dev_t("feature_indices"), torch.int64)
+            cls._check_indices(scene._feature_indices, scene._features_dc.shape[0], "feature_indices of " + str(path))
         return scene

@@ -351,3 +351,28 @@ def test_scene_file_written_here_holds_the_reference_files_arrays(L, tmp_path, s
             assert diff.max() <= 1 and (diff != 0).mean() <= 5e-3, (k, int(diff.max()), float((diff != 0).mean()))
         else:
             assert np.array_equal(got[k], want[k]), k
+
+
+def test_out_of_range_index_arrays_are_rejected_where_they_enter_the_scene(L, tmp_path):
+    """The decode gathers do not check indices (an out-of-range one would decode to zeros where torch indexing
+    raises): SplatScene validates index arrays once, in set_*_indexed and load_npz."""
+    from c3dgs_b200 import SplatScene
+    g = _interop()
+    t = {k[3:]: torch.from_numpy(g[k]).to(DEV) for k in g.files if k.startswith("in/") and not k.endswith(("_scale", "_zero_point"))}
+    sc = SplatScene(t["xyz"], t["features_dc"], t["features_rest"], t["opacity"], t["scaling"], t["rotation"],
+                    scaling_factor=t["scaling_factor"])
+    bad = t["feature_indices"].clone()
+    bad[3] = t["features_dc"].shape[0]
+    with pytest.raises(IndexError):
+        sc.set_color_indexed(torch.cat((t["features_dc"], t["features_rest"]), 1), bad)
+    bad = t["gaussian_indices"].clone()
+    bad[0] = -1
+    with pytest.raises(IndexError):
+        sc.set_gaussian_indexed(t["rotation"], t["scaling"], bad)
+    corrupt = _subfile(g, "fileA/")
+    corrupt["gaussian_indices"] = corrupt["gaussian_indices"].copy()
+    corrupt["gaussian_indices"][5] = 10_000
+    path = str(tmp_path / "corrupt.npz")
+    np.savez_compressed(path, **corrupt)
+    with pytest.raises(IndexError, match="gaussian_indices"):
+        SplatScene.load_npz(path, device=DEV)
