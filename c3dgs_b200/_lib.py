@@ -18,7 +18,7 @@ LIB_PATH = os.environ.get("C3VQ_LIB") or os.path.join(_HERE, "libc3vq.so")   # C
 
 _lib = None
 _lock = threading.Lock()
-DEFAULT_SUMS = "sorted"
+DEFAULT_SUMS = "fused"
 
 
 def default_tensor_cores() -> bool:
@@ -37,8 +37,9 @@ def default_sums() -> str:
 
 def _tc_mode(tensor_cores) -> int:
     """use_tensor_cores argument of c3vq_update / c3vq_assign_accumulate: 0 = SIMT exact assignment + atomic sums,
-    1 = tcgen05 assignment + sorted segmented sums (default), 2 = tcgen05 assignment with the sums fused into
-    the kernel (one bulk reduce-add per row; x read once).  C3VQ_SUMS=fused selects 2 wherever True is passed."""
+    1 = tcgen05 assignment + sorted segmented sums (second pass over x), 2 = tcgen05 assignment with the sums fused
+    into the kernel (one bulk reduce-add per distinct codeword of a warp; x read once: the default).  True selects the
+    default (C3VQ_SUMS=sorted|fused overrides it), "sorted" / "fused" select explicitly."""
     if tensor_cores == "fused" or (tensor_cores == 2 and tensor_cores is not True):
         return 2
     if tensor_cores == "sorted":
@@ -268,7 +269,8 @@ def update(x: torch.Tensor, w: torch.Tensor, codebook: torch.Tensor, entry_impor
 
 
 def assign_accumulate(x, w, codebook, acc: torch.Tensor | None = None, rows=None, tensor_cores: bool = True,
-                      return_dist: bool = False, return_idx: bool = True, rows_checked: bool = False):
+                      return_dist: bool = False, return_idx: bool = True, rows_checked: bool = False,
+                      out_idx: torch.Tensor | None = None):
     """Assignment + weighted sums added into acc, no EMA (multi-GPU building block).  c3vq_assign_accumulate."""
     _check(x, torch.float32, "x", 2)
     _check(w, torch.float32, "importance", 1)
@@ -290,7 +292,13 @@ def assign_accumulate(x, w, codebook, acc: torch.Tensor | None = None, rows=None
         elif acc.shape != (k, stride) or not acc.is_contiguous():
             raise RuntimeError(f"acc must be a contiguous [{k}, {stride}] float32 tensor")
         dist = torch.empty(n, dtype=torch.float32, device=x.device) if return_dist else None
-        idx = torch.empty(n, dtype=torch.int64, device=x.device) if return_idx else None
+        if out_idx is not None:
+            _check(out_idx, torch.int64, "out_idx", 1)
+            if out_idx.numel() != n or not out_idx.is_contiguous() or out_idx.device != x.device:
+                raise RuntimeError("out_idx must be a contiguous int64 tensor with one entry per row on x's device")
+            idx = out_idx
+        else:
+            idx = torch.empty(n, dtype=torch.int64, device=x.device) if return_idx else None
         nbytes = L.c3vq_update_workspace_bytes(n, d, k)
         ws = _workspace.get(x.device, nbytes)
         rc = L.c3vq_assign_accumulate(_ptr(x), _ptr(w), _ptr(rows), n, d, _ptr(codebook), k, _tc_mode(tensor_cores),

@@ -12,8 +12,6 @@
 // vectorised red.global.add.v4.f32 per 16-byte accumulator chunk when the row can be
 // loaded as float4 (d % 4 == 0), else one scalar red per element issued by consecutive
 // lanes onto consecutive addresses.
-#include <cstdlib>
-
 #include "common.cuh"
 
 namespace c3vq {
@@ -120,6 +118,10 @@ int launch_accumulate(const float *x, const float *w, const int64_t *rows, const
 // histogram, one scan, one scatter of row ids + weights), then each warp sums a contiguous run of the
 // sorted order in registers and touches the table only at segment boundaries.
 //   hist [k], offs [k+1], cursor [k] u32; perm [n] u32 (source row); wperm [n] f32 (its weight)
+// Tried in round 2 and dropped (profiles/r2a_sums_probe_*, r2b_sums_probe_windowed.txt): sorting by (window of 65536
+// rows, codeword) with sequential L2 prefetch of the coming windows, so that DRAM sees one sequential pass and the
+// gathers hit the L2 — 0.83-0.88 ms against 0.50-0.62 ms for this kernel (twice the sort traffic, four times the
+// segment flushes).  What replaced the second pass over x altogether is the fused mode of assign_tc.cu.
 constexpr int SEG_CH = 128;         // sorted positions per warp work item
 
 __global__ void __launch_bounds__(1024)
@@ -342,24 +344,10 @@ k_seg_sum(const float *__restrict__ x, const unsigned int *__restrict__ perm, co
     if (jf_prev >= 0) flush_table(jf_prev);
 }
 
-size_t wseg_workspace_bytes(int64_t n, int k);
-int launch_accumulate_windowed(const float *x, const float *w, const int64_t *idx, int64_t n, int d, int k, float *acc,
-                               int stride, int wcol, void *ws, size_t ws_bytes, cudaStream_t s);
-
-// developer knob: C3VQ_SUMS_WINDOWED=1 selects the windowed sort for rows in storage order (default: the plain
-// codeword-sorted gather, which measured faster: profiles/r2a_sums_probe_*.txt)
-static bool use_windowed()
-{
-    const char *e = getenv("C3VQ_SUMS_WINDOWED");       // read per call: tests and A/B tools flip it in-process
-    return e && e[0] == '1';
-}
-
 size_t seg_workspace_bytes(int64_t n, int k)
 {
     auto al = [](size_t v) { return (v + 255) & ~(size_t)255; };
-    const size_t plain = al((size_t)(k + 1) * 4) * 3 + al((size_t)(n > 0 ? n : 1) * 4) * 2;
-    const size_t win = wseg_workspace_bytes(n, k);
-    return plain > win ? plain : win;
+    return al((size_t)(k + 1) * 4) * 3 + al((size_t)(n > 0 ? n : 1) * 4) * 2;
 }
 
 int launch_accumulate_sorted(const float *x, const float *w, const int64_t *rows, const int64_t *idx, int64_t n, int d,
@@ -367,8 +355,6 @@ int launch_accumulate_sorted(const float *x, const float *w, const int64_t *rows
 {
     if (n == 0 || k == 0) return C3VQ_OK;
     C3VQ_CHECK_ARG(n < 0xffffffffLL, "n=%lld too large for 32-bit row ids", (long long)n);
-    if (rows == nullptr && k <= 65536 && use_windowed())
-        return launch_accumulate_windowed(x, w, idx, n, d, k, acc, stride, wcol, ws, ws_bytes, s);
     if (ws == nullptr || ws_bytes < seg_workspace_bytes(n, k)) {
         set_error("workspace too small: %zu < %zu", ws_bytes, seg_workspace_bytes(n, k));
         return C3VQ_EWORKSPACE;
@@ -406,220 +392,6 @@ int launch_accumulate_sorted(const float *x, const float *w, const int64_t *rows
     else
         k_seg_sum<2><<<(unsigned)gb, 256, 0, s>>>(x, perm, wperm, offs, d, k, acc, stride, wcol);
     C3VQ_LAUNCH_CHECK("k_seg_sum");
-    return C3VQ_OK;
-}
-
-// ------------------------------------------------------------------------------------------------
-// Windowed variant of the sorted sums (rows == nullptr: x is consumed in storage order).
-//
-// The codeword-sorted gather above reads 4*d-byte rows from all over x: DRAM moves 64-byte granules and opens a new
-// page for almost every row, so it runs at 39 % of the DRAM rate while moving 1.42x the algorithmic bytes.  Here the
-// sort key is (window, codeword) with windows of WSEG_WIN = 65536 consecutive rows (11.8 MB at d = 45): the sorted
-// order visits the input window by window, the whole grid works inside a band of a few windows at any time, and the
-// rows of the band after the current one are pulled into the L2 by sequential prefetches in storage order.  DRAM
-// therefore sees one sequential pass over x (traffic = algorithmic bytes) and the row gathers hit the L2.
-//   k_wseg_rank   rank of every row inside its (window, codeword) bucket: one warp-aggregated atomicAdd with return
-//                 on the bucket counter (which so becomes the histogram); slot[i] = code << 16 | rank
-//   k_wseg_scan   per window (independent: window v owns sorted positions [v * WIN, v * WIN + rows of v)):
-//                 exclusive scan of its K counters
-//   k_wseg_place  perm[offs[bucket] + rank] = (code << 16 | row in window, weight bits): no atomics
-//   k_wseg_sum    warps take chunks of WSEG_CH sorted positions in grid-stride order, WSEG_U row loads in flight,
-//                 partial sums in registers, one reduction into the table per codeword change
-constexpr int WSEG_WIN_LOG = 16;
-constexpr int WSEG_WIN = 1 << WSEG_WIN_LOG;
-#ifndef C3VQ_WSEG_U
-#define C3VQ_WSEG_U 8
-#endif
-constexpr int WSEG_CH = 32;            // sorted positions per warp work item (one perm entry per lane)
-constexpr int WSEG_U = C3VQ_WSEG_U;    // rows whose loads are in flight per warp (divides 32)
-constexpr int WSEG_SUM_THREADS = 512;
-// Two CTAs per SM: 148 x 32 warps x 32 rows = 151 k rows = 27 MB at d = 45 is the band the grid works on at a time;
-// each chunk pulls the storage rows of the chunk WSEG windows-ahead of it into the L2, far enough that a window is
-// resident before the first warp of the grid reaches its sorted positions (band + one window).
-constexpr int WSEG_CTAS_PER_SM = 2;
-
-__global__ void __launch_bounds__(256)
-k_wseg_rank(const int64_t *__restrict__ idx, int64_t n, int k, unsigned int *__restrict__ hist,
-            unsigned int *__restrict__ slot)
-{
-    const int lane = threadIdx.x & 31;
-    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-    for (int64_t i0 = warp * 32; i0 < n; i0 += nwarps * 32) {      // warp-uniform trip count
-        const int64_t i = i0 + lane;
-        const int64_t j = i < n ? idx[i] : -1;
-        const bool valid = (uint64_t)j < (uint64_t)k;              // out-of-range code: the row is ignored
-        // rows of one warp share a window (i0 is a multiple of 32): the codeword alone tells buckets apart
-        const unsigned int key = valid ? (unsigned int)j : 0x80000000u + (unsigned int)lane;
-        const unsigned int peers = __match_any_sync(0xffffffffu, key);
-        const int leader = __ffs(peers) - 1;
-        unsigned int base = 0;
-        if (valid && lane == leader)
-            base = atomicAdd(&hist[(size_t)(i0 >> WSEG_WIN_LOG) * k + (unsigned int)j], (unsigned int)__popc(peers));
-        base = __shfl_sync(0xffffffffu, base, leader);
-        if (i < n) slot[i] = valid ? (((unsigned int)j << 16) | (base + __popc(peers & ((1u << lane) - 1u)))) : 0xffffffffu;
-    }
-}
-
-// one CTA per window: offs[v][c] = v * WIN + sum_{c' < c} hist[v][c'], wlen[v] = rows of the window with a valid code
-__global__ void __launch_bounds__(1024)
-k_wseg_scan(const unsigned int *__restrict__ hist, int k, unsigned int *__restrict__ offs, unsigned int *__restrict__ wlen)
-{
-    __shared__ unsigned int part[1024];
-    const unsigned int *h = hist + (size_t)blockIdx.x * k;
-    unsigned int *o = offs + (size_t)blockIdx.x * k;
-    const int per = (k + 1023) / 1024;
-    const int j0 = threadIdx.x * per;
-    unsigned int sum = 0;
-    for (int j = j0; j < min(k, j0 + per); j++) sum += h[j];
-    part[threadIdx.x] = sum;
-    __syncthreads();
-    for (int st = 1; st < 1024; st <<= 1) {
-        const unsigned int v = threadIdx.x >= st ? part[threadIdx.x - st] : 0u;
-        __syncthreads();
-        part[threadIdx.x] += v;
-        __syncthreads();
-    }
-    unsigned int run = blockIdx.x * (unsigned int)WSEG_WIN + part[threadIdx.x] - sum;
-    for (int j = j0; j < min(k, j0 + per); j++) {
-        o[j] = run;
-        run += h[j];
-    }
-    if (threadIdx.x == 1023) wlen[blockIdx.x] = part[1023];
-}
-
-__global__ void __launch_bounds__(256)
-k_wseg_place(const unsigned int *__restrict__ slot, const float *__restrict__ w, int64_t n, int k,
-             const unsigned int *__restrict__ offs, uint2 *__restrict__ perm)
-{
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-        const unsigned int sl = slot[i];
-        if (sl == 0xffffffffu) continue;
-        const unsigned int code = sl >> 16;
-        const unsigned int pos = offs[(size_t)(i >> WSEG_WIN_LOG) * k + code] + (sl & 0xffffu);
-        perm[pos] = make_uint2((code << 16) | (unsigned int)(i & (WSEG_WIN - 1)), __float_as_uint(w ? w[i] : 1.f));
-    }
-}
-
-template <int NH>
-__global__ void __launch_bounds__(WSEG_SUM_THREADS, WSEG_CTAS_PER_SM)
-k_wseg_sum(const float *__restrict__ x, const uint2 *__restrict__ perm, const unsigned int *__restrict__ wlen,
-           int64_t n, int d, float *__restrict__ acc, int stride, int wcol)
-{
-    const int lane = threadIdx.x & 31;
-    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-    const int64_t nchunks = (n + WSEG_CH - 1) / WSEG_CH;            // windows are multiples of the chunk
-    constexpr int64_t CPW = WSEG_WIN / WSEG_CH;                     // chunks per window
-    const int64_t ahead = ((nwarps + CPW - 1) / CPW + 1) * CPW;     // prefetch distance in chunks: the band + one window
-    const bool c0 = lane < d, c1 = NH == 2 && lane + 32 < d;
-    const size_t row_bytes = (size_t)d * 4;
-    for (int64_t g = warp; g < nchunks; g += nwarps) {
-        // pull the storage rows [gn * CH, gn * CH + CH) into the L2, sequentially in memory: chunk g of window v
-        // fetches the same slice of window v + ahead / CPW, so every window is fetched exactly once, by the
-        // chunks of the window `ahead` before it (the first windows are cold)
-        {
-            const int64_t gn = g + ahead;
-            if (gn < nchunks) {
-                const char *pb = reinterpret_cast<const char *>(x) + (size_t)gn * WSEG_CH * row_bytes;
-                const size_t bytes = (size_t)min((int64_t)WSEG_CH, n - gn * WSEG_CH) * row_bytes;
-                for (size_t o = (size_t)lane * 128; o < bytes; o += 32 * 128)
-                    asm volatile("prefetch.global.L2 [%0];" ::"l"(pb + o));
-            }
-        }
-        const int64_t p0 = g * WSEG_CH;
-        const unsigned int v = (unsigned int)(p0 >> WSEG_WIN_LOG);
-        const unsigned int in_win = (unsigned int)(p0 & (WSEG_WIN - 1));
-        const unsigned int len = wlen[v];
-        if (in_win >= len) continue;                                 // rows with invalid codes left a gap at the window's end
-        const int cnt = (int)min((unsigned int)WSEG_CH, len - in_win);
-        const float *xw = x + (size_t)v * WSEG_WIN * d + lane;
-        const uint2 e = lane < cnt ? perm[p0 + lane] : make_uint2(0u, 0u);
-        int cur = -1;
-        float a0 = 0.f, a1 = 0.f, aw = 0.f;
-        auto flush = [&]() {
-            float *ap = acc + (size_t)cur * stride;
-            if (c0) atomicAdd(ap + lane, a0);
-            if (c1) atomicAdd(ap + lane + 32, a1);
-            if (lane == 0 && wcol >= 0) atomicAdd(ap + wcol, aw);
-            a0 = a1 = aw = 0.f;
-        };
-#pragma unroll 1
-        for (int r0 = 0; r0 < cnt; r0 += WSEG_U) {
-            float v0[WSEG_U], v1[WSEG_U];
-            unsigned int key[WSEG_U], wb[WSEG_U];
-#pragma unroll
-            for (int u = 0; u < WSEG_U; u++) {
-                key[u] = __shfl_sync(0xffffffffu, e.x, r0 + u);
-                wb[u] = __shfl_sync(0xffffffffu, e.y, r0 + u);
-                const float *xp = xw + (size_t)(key[u] & 0xffffu) * d;
-                const bool live = r0 + u < cnt;
-                v0[u] = (live && c0) ? xp[0] : 0.f;
-                v1[u] = (live && c1) ? xp[32] : 0.f;
-            }
-#pragma unroll
-            for (int u = 0; u < WSEG_U; u++) {
-                if (r0 + u < cnt) {                                  // warp-uniform
-                    const int code = (int)(key[u] >> 16);
-                    if (code != cur) {
-                        if (cur >= 0) flush();
-                        cur = code;
-                    }
-                    const float wv = __uint_as_float(wb[u]);
-                    a0 = __fadd_rn(a0, __fmul_rn(v0[u], wv));        // product rounded first (the reference's x*w temporary)
-                    a1 = __fadd_rn(a1, __fmul_rn(v1[u], wv));
-                    aw = __fadd_rn(aw, wv);
-                }
-            }
-        }
-        if (cur >= 0) flush();
-    }
-}
-
-static inline size_t wseg_al(size_t v) { return (v + 255) & ~(size_t)255; }
-
-size_t wseg_workspace_bytes(int64_t n, int k)
-{
-    const size_t nw = (size_t)((n + WSEG_WIN - 1) >> WSEG_WIN_LOG) + 1;
-    return 2 * wseg_al(nw * (size_t)k * 4) + wseg_al(nw * 4) + wseg_al((size_t)(n > 0 ? n : 1) * 4) +
-           wseg_al((size_t)(n > 0 ? n : 1) * 8);
-}
-
-int launch_accumulate_windowed(const float *x, const float *w, const int64_t *idx, int64_t n, int d, int k, float *acc,
-                               int stride, int wcol, void *ws, size_t ws_bytes, cudaStream_t s)
-{
-    if (n == 0 || k == 0) return C3VQ_OK;
-    C3VQ_CHECK_ARG(k <= 65536, "k=%d does not fit the 16-bit code field", k);
-    C3VQ_CHECK_ARG(n < 0xffffffffLL, "n=%lld too large for 32-bit positions", (long long)n);
-    if (ws == nullptr || ws_bytes < wseg_workspace_bytes(n, k)) {
-        set_error("workspace too small: %zu < %zu", ws_bytes, wseg_workspace_bytes(n, k));
-        return C3VQ_EWORKSPACE;
-    }
-    const size_t nw = (size_t)((n + WSEG_WIN - 1) >> WSEG_WIN_LOG);
-    char *p = (char *)ws;
-    unsigned int *hist = (unsigned int *)p; p += wseg_al((nw + 1) * (size_t)k * 4);
-    unsigned int *offs = (unsigned int *)p; p += wseg_al((nw + 1) * (size_t)k * 4);
-    unsigned int *wlen = (unsigned int *)p; p += wseg_al((nw + 1) * 4);
-    unsigned int *slot = (unsigned int *)p; p += wseg_al((size_t)n * 4);
-    uint2 *perm = (uint2 *)p;
-    const int sms = sm_count();
-    C3VQ_CUDA(cudaMemsetAsync(hist, 0, nw * (size_t)k * 4, s));
-    int64_t rb = (n + 255) / 256;
-    if (rb > (int64_t)sms * 16) rb = (int64_t)sms * 16;
-    k_wseg_rank<<<(unsigned)rb, 256, 0, s>>>(idx, n, k, hist, slot);
-    C3VQ_LAUNCH_CHECK("k_wseg_rank");
-    k_wseg_scan<<<(unsigned)nw, 1024, 0, s>>>(hist, k, offs, wlen);
-    C3VQ_LAUNCH_CHECK("k_wseg_scan");
-    k_wseg_place<<<(unsigned)rb, 256, 0, s>>>(slot, w, n, k, offs, perm);
-    C3VQ_LAUNCH_CHECK("k_wseg_place");
-    const int64_t nchunks = (n + WSEG_CH - 1) / WSEG_CH;
-    int64_t gb = (nchunks + WSEG_SUM_THREADS / 32 - 1) / (WSEG_SUM_THREADS / 32);
-    if (gb > (int64_t)sms * WSEG_CTAS_PER_SM) gb = (int64_t)sms * WSEG_CTAS_PER_SM;
-    if (d <= 32)
-        k_wseg_sum<1><<<(unsigned)gb, WSEG_SUM_THREADS, 0, s>>>(x, perm, wlen, n, d, acc, stride, wcol);
-    else
-        k_wseg_sum<2><<<(unsigned)gb, WSEG_SUM_THREADS, 0, s>>>(x, perm, wlen, n, d, acc, stride, wcol);
-    C3VQ_LAUNCH_CHECK("k_wseg_sum");
     return C3VQ_OK;
 }
 

@@ -84,6 +84,11 @@ class CudaOps:
     def accumulate(self, x, w, idx, acc):
         _lib.accumulate(x, w, idx, acc.size(0), acc=acc, sorted_path=bool(self.tensor_cores))
 
+    def assign_accumulate_chunk(self, x, w, codebook, acc, out_idx):
+        """Assignment of a chunk of rows into `out_idx` (a slice of the caller's index array) with the chunk's
+        weighted sums added into acc (update_from_host)."""
+        _lib.assign_accumulate(x, w, codebook, acc=acc, tensor_cores=self.tensor_cores, return_idx=True, out_idx=out_idx)
+
 
 class ShardedVectorQuantize:
     """VectorQuantize (compression/vq.py:15-42) with rows sharded over a process group."""
@@ -151,18 +156,27 @@ class ShardedVectorQuantize:
         copy.wait_stream(main)                                   # earlier work may still read x_dev
         idx = torch.empty(n, dtype=torch.int64, device=dev)
         self._acc.zero_()
+        fused = getattr(self.ops, "assign_accumulate_chunk", None) is not None
+        if fused:
+            with torch.cuda.stream(copy):                        # 4 bytes per row: ahead of the rows themselves
+                importance_dev.copy_(importance_host, non_blocking=True)
         for lo in range(0, n, chunk_rows):
             hi = min(lo + chunk_rows, n)
             with torch.cuda.stream(copy):
                 x_dev[lo:hi].copy_(x_host[lo:hi], non_blocking=True)
                 landed = copy.record_event()
             main.wait_event(landed)
-            self.ops.assign(x_dev[lo:hi], self.codebook, out_idx=idx[lo:hi])
-        with torch.cuda.stream(copy):
-            importance_dev.copy_(importance_host, non_blocking=True)
-            landed = copy.record_event()
-        main.wait_event(landed)
-        self.ops.accumulate(x_dev, importance_dev, idx, self._acc)
+            if fused:       # assignment with the chunk's weighted sums added into acc by the same kernel
+                self.ops.assign_accumulate_chunk(x_dev[lo:hi], importance_dev[lo:hi], self.codebook, self._acc,
+                                                 idx[lo:hi])
+            else:
+                self.ops.assign(x_dev[lo:hi], self.codebook, out_idx=idx[lo:hi])
+        if not fused:
+            with torch.cuda.stream(copy):
+                importance_dev.copy_(importance_host, non_blocking=True)
+                landed = copy.record_event()
+            main.wait_event(landed)
+            self.ops.accumulate(x_dev, importance_dev, idx, self._acc)
         self._all_reduce(self._acc)
         self.ops.ema(self.codebook, self.entry_importance, self._acc, self.decay, self.eps, scale_normalize)
         return idx

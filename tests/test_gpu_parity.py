@@ -241,12 +241,10 @@ def test_accumulate_sorted_vs_oracle(L, oracle, d, skew):
 
 
 @pytest.mark.parametrize("d,k", [(45, 4096), (6, 33), (48, 1)])
-def test_accumulate_windowed_vs_oracle(L, oracle, monkeypatch, d, k):
-    """Rows in storage order take the windowed sort (key = (window of 65536 rows, codeword)): several windows, a
-    ragged last one, rows with out-of-range codes (they leave gaps at the end of their window's range), a codeword
-    that owns most of one window only, unit weights."""
+def test_accumulate_sorted_large_and_invalid_codes(L, oracle, d, k):
+    """The sorted sums on 200 k rows in storage order: rows with out-of-range codes (ignored), a codeword that owns
+    most of one stretch of the input only, a one-codeword table, unit weights."""
     n = 3 * 65536 + 777
-    monkeypatch.setenv("C3VQ_SUMS_WINDOWED", "1")             # developer knob, read per call
     x, w, _ = _synth(n, d, max(k, 2), seed=300 + d)
     g = torch.Generator().manual_seed(k)
     idx = torch.randint(0, k, (n,), generator=g)
@@ -435,8 +433,10 @@ def test_update_from_host_equals_update(L):
     torch.cuda.synchronize()
     assert torch.equal(idx_a, idx_b)
     assert torch.equal(xd.cpu(), xh) and torch.equal(wd.cpu(), wh)
-    assert torch.allclose(a.codebook, b.codebook, rtol=1e-6, atol=1e-7)
-    assert torch.allclose(a.entry_importance, b.entry_importance, rtol=1e-6, atol=1e-7)
+    # the sums are fp32 reductions in whatever order the chunks and warps deliver them: north-star tolerance
+    scale = a.codebook.abs().max(1, keepdim=True).values + 1e-30
+    assert float(((a.codebook - b.codebook).abs() / scale).max()) < CB_RTOL
+    assert torch.allclose(a.entry_importance, b.entry_importance, rtol=1e-5, atol=1e-7)
 
 
 # ---------------------------------------------------------------- extract_rot_scale --
