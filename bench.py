@@ -268,6 +268,9 @@ class Clustering:
         self.ops.tensor_cores = False if simt else sums          # "sorted" / "fused": explicit, whatever the default
         self.split = (not simt) and sums == "sorted"
         self.vq = ShardedVectorQuantize(self.d, K, DECAY, device=dev, ops=self.ops)
+        # the assignments land in one buffer for the whole job: a fresh 8 n-byte tensor per iteration makes the caching
+        # allocator return and re-request blocks at 12-24 M rows, and cudaFree waits for the device
+        self.idx = torch.empty(self.n, dtype=torch.int64, device=dev)
         self.events = []           # per iteration (e0, e1, e2, e3, e4)
 
     def step(self, record: bool):
@@ -280,12 +283,13 @@ class Clustering:
             if record:
                 ev[0].record()
             if self.split:
-                idx = L.assign(self.x, vq.codebook, return_dist=False)[1]
+                L.assign(self.x, vq.codebook, return_dist=False, out_idx=self.idx)
                 if record:
                     ev[1].record()
-                L.accumulate(self.x, self.wn, idx, K, acc=vq._acc, sorted_path=True)
+                L.accumulate(self.x, self.wn, self.idx, K, acc=vq._acc, sorted_path=True)
             else:
-                self.ops.assign_accumulate(self.x, self.wn, vq.codebook, vq._acc)
+                L.assign_accumulate(self.x, self.wn, vq.codebook, acc=vq._acc, tensor_cores=self.ops.tensor_cores,
+                                    out_idx=self.idx)
                 if record:
                     ev[1].record()
             if record:
@@ -316,9 +320,10 @@ class Clustering:
             ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
             vq._acc.zero_()
             ev[0].record()
-            L.assign(self.x, vq.codebook, return_dist=False)
+            L.assign(self.x, vq.codebook, return_dist=False, out_idx=self.idx)
             ev[1].record()
-            self.ops.assign_accumulate(self.x, self.wn, vq.codebook, vq._acc)
+            L.assign_accumulate(self.x, self.wn, vq.codebook, acc=vq._acc, tensor_cores=self.ops.tensor_cores,
+                                out_idx=self.idx)
             ev[2].record()
             vq._all_reduce(vq._acc)
             self.ops.ema(vq.codebook, vq.entry_importance, vq._acc, DECAY, EPS, self.scale_normalize)
@@ -679,6 +684,7 @@ def main():
         ms_n = max_over_ranks(a.elapsed_time(b)) / 3
         am, um = sj.kernel_ms()
         ar_ms = float(np.mean([e[2].elapsed_time(e[3]) for e in sj.events]))
+        intervals = [float(np.mean([e[i].elapsed_time(e[i + 1]) for e in sj.events])) for i in range(4)]
         del sj, xs, ws
         ms_1 = ms_n
         if world > 1:
@@ -708,6 +714,7 @@ def main():
                   "ms_per_step": ms_n, "value": total * ITERS / (ms_n * 1e-3),
                   "one_gpu_ms_per_step": ms_1, "speedup_vs_one_gpu": ms_1 / ms_n,
                   "assign_ms_per_iteration": am, "update_ms_per_iteration": um, "allreduce_ms_per_iteration": ar_ms,
+                  "intervals_ms": dict(zip(("assign+sums", "gap", "allreduce", "ema"), intervals)),
                   "note": "the one-GPU time is measured in this run: rank 0 clusters all rows alone while the other ranks wait"}
         torch.cuda.empty_cache()
 
@@ -727,10 +734,11 @@ def main():
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": warm,
             "ms_per_step": ms_per_step, "ms_per_step_median": float(np.median(per_step)), "higher_is_better": True,
             "scaling": args.scaling, "vs_baseline": None,
-            "dtype": "f32 (tf32 tensor-core screening + exact fp32 re-rank)" if not args.simt else "f32",
+            "dtype": (f"f32 ({screening_pipe()} tensor-core screening + exact fp32 re-rank: results bit-identical to the "
+                      "fp32 reference)") if not args.simt else "f32",
             "data": "synthetic",
             "config": workload_config(n, d, world, args.scaling),
-            "implementation": {"assignment": "simt-exact" if args.simt else "tcgen05-tf32+rerank",
+            "implementation": {"assignment": "simt-exact" if args.simt else f"tcgen05-{screening_pipe()}+rerank",
                                "sums": "atomic" if args.simt else args.sums},
             "roofline": roofline, "roofline_update": roofline_update, "roofline_gather": roofline_gather,
             "assign_stats": {"rows": stats_rows, "candidates_per_row": stats_cands / max(stats_rows, 1),

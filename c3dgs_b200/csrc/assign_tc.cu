@@ -82,6 +82,11 @@ constexpr int TC_SMEM_LIMIT = 227 * 1024;
 // fp16 screening (kind::f16, twice the tensor rate of kind::tf32 at the same 2^-11 unit roundoff): operands are
 // scaled by gamma = 2^g so that gamma * max |c'_j| < 2^7; the norm pieces ride against a constant 256 in A so that
 // three pieces of 65504 mark a dead / padding code far above every real score of a row inside the range limit
+// Fused sums, large inputs: the CTAs add into TC_ACC_PARTS partial tables that are folded pairwise afterwards.  A
+// table row that owns 10^5-10^6 rows would otherwise be the end of as long a chain of fp32 additions at the L2
+// (2.5e-5 of centroid error against float64 at 5.8 M rows; 3e-6 with 32 partial tables, profiles/r2f_sums_probe.txt).
+constexpr int TC_ACC_PARTS = 32;
+constexpr int64_t TC_ACC_PARTS_MIN_ROWS = 1 << 20;
 constexpr float TC_F16_ACONST = 256.f;
 constexpr float TC_F16_DEAD = 3.f * 65504.f * 256.f;     // 5.03e7
 constexpr float TC_F16_XLIM = 1073741824.f;             // 2^30: limit of gamma^2 |x'|^2 (every element below 2^15)
@@ -122,8 +127,10 @@ struct TcParams {
     TcHeader *hdr;
     float *out_dist;
     int64_t *out_idx;
-    float *acc;
+    float *acc;             // fused sums: table (or acc_parts partial tables of acc_part_elems floats each)
     int acc_stride;
+    int acc_parts;          // CTA b adds into partial table b % acc_parts
+    size_t acc_part_elems;
     unsigned int *fb_list;
     unsigned long long *fb_best;   // per fallback row: running (distance bits, code) minimum
     float *dbg_scores, *dbg_norm2, *dbg_band;
@@ -720,8 +727,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                     fence_proxy_async_smem();
                     __syncwarp();
                     if (status == ROW_OK && leader == lane)
-                        bulk_reduce_add_f32(p.acc + (size_t)bj * p.acc_stride, smem_u32(xw + lane * L::XS),
-                                            (uint32_t)p.acc_stride * 4u);
+                        bulk_reduce_add_f32(p.acc + (size_t)(blockIdx.x % p.acc_parts) * p.acc_part_elems +
+                                                (size_t)bj * p.acc_stride,
+                                            smem_u32(xw + lane * L::XS), (uint32_t)p.acc_stride * 4u);
                     bulk_commit_group();
                 }
 #endif
@@ -1140,7 +1148,7 @@ k_assign_fallback_finish(const float *__restrict__ x, const float *__restrict__ 
 static inline size_t al256(size_t v) { return (v + 255) & ~(size_t)255; }
 
 struct TcLayout {
-    size_t off_mu, off_bimg, off_cbp, off_fb, off_fbbest, total;
+    size_t off_mu, off_bimg, off_cbp, off_fb, off_fbbest, off_parts, total;
     int dp, nc, dpc, k_pad, bn;
 };
 
@@ -1172,6 +1180,8 @@ static TcLayout tc_layout(int64_t n, int d, int k, bool f16)
     o += al256((size_t)(n > 0 ? n : 1) * sizeof(unsigned int));
     l.off_fbbest = o;
     o += al256((size_t)(n > 0 ? n : 1) * sizeof(unsigned long long));
+    l.off_parts = o;
+    if (n >= TC_ACC_PARTS_MIN_ROWS) o += al256((size_t)TC_ACC_PARTS * (size_t)(k > 0 ? k : 1) * acc_stride(d) * sizeof(float));
     l.total = o;
     return l;
 }
@@ -1199,6 +1209,21 @@ static int launch_tc_t(const TcParams &p, int grid, cudaStream_t s)
     k_assign_tc<DP, DCONST, DBG, F16><<<grid, TC_THREADS, smem, s>>>(q);
     C3VQ_LAUNCH_CHECK("k_assign_tc");
     return C3VQ_OK;
+}
+
+// acc[i] += pairwise sum over the partial tables (one thread per table element, coalesced over i)
+__global__ void __launch_bounds__(256) k_acc_fold(const float *__restrict__ parts, size_t elems, float *__restrict__ acc)
+{
+    const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (i >= elems) return;
+    float v[TC_ACC_PARTS];
+#pragma unroll
+    for (int c = 0; c < TC_ACC_PARTS; c++) v[c] = parts[(size_t)c * elems + i];
+#pragma unroll
+    for (int st = 1; st < TC_ACC_PARTS; st <<= 1)
+#pragma unroll
+        for (int c = 0; c < TC_ACC_PARTS; c += 2 * st) v[c] = __fadd_rn(v[c], v[c + st]);
+    acc[i] = __fadd_rn(acc[i], v[0]);
 }
 
 int launch_assign_tc(const float *x, const float *w, const int64_t *rows, int64_t n, int d, const float *codebook,
@@ -1237,6 +1262,14 @@ int launch_assign_tc(const float *x, const float *w, const int64_t *rows, int64_
     p.npairs = (n + TC_PR - 1) / TC_PR;
     p.bimg = bimg; p.cbp = cbp; p.dpc = l.dpc; p.mu = mu; p.hdr = hdr;
     p.out_dist = out_dist; p.out_idx = out_idx; p.acc = acc; p.acc_stride = acc_stride(d);
+    p.acc_parts = 1; p.acc_part_elems = 0;
+    float *parts = nullptr;
+    const size_t acc_elems = (size_t)k * acc_stride(d);
+    if (acc != nullptr && n >= TC_ACC_PARTS_MIN_ROWS) {
+        parts = (float *)(base + l.off_parts);
+        C3VQ_CUDA(cudaMemsetAsync(parts, 0, (size_t)TC_ACC_PARTS * acc_elems * sizeof(float), s));
+        p.acc = parts; p.acc_parts = TC_ACC_PARTS; p.acc_part_elems = acc_elems;
+    }
     p.fb_list = fb;
     p.fb_best = (unsigned long long *)(base + l.off_fbbest);
     p.dbg_scores = dbg_scores; p.dbg_norm2 = dbg_norm2; p.dbg_band = dbg_band;
@@ -1295,6 +1328,10 @@ int launch_assign_tc(const float *x, const float *w, const int64_t *rows, int64_
         k_assign_fallback_finish<<<sms, 128, 0, s>>>(x, w, rows, d, hdr, fb, p.fb_best, out_dist, out_idx, acc,
                                                      acc_stride(d));
         C3VQ_LAUNCH_CHECK("k_assign_fallback_finish");
+    }
+    if (parts != nullptr) {
+        k_acc_fold<<<(unsigned)((acc_elems + 255) / 256), 256, 0, s>>>(parts, acc_elems, acc);
+        C3VQ_LAUNCH_CHECK("k_acc_fold");
     }
     return C3VQ_OK;
 }

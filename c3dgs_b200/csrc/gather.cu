@@ -60,54 +60,53 @@ k_gather32(const T *__restrict__ table, int64_t table_rows, int dv, const int64_
 }
 
 // Rows that are not a multiple of 16 bytes (45 floats = 180 B is the SH width): a warp takes 32 consecutive output rows,
-// i.e. one contiguous, 16-byte aligned span of 32*d floats.  It reads its 32 indices with one coalesced load, copies
-// the 32 table rows into shared memory with lanes over columns (two coalesced 4-byte loads per row against row
-// pointers parked in shared memory, eight rows in flight, no index arithmetic per element) and writes the span out as
-// float4.  The element-wise formulation needed ~600 warp instructions per 32 rows (a division and four scalar loads
-// per float4) and was issue bound at 0.64 of the copy peak.
-template <int NH>                                                    // column groups of 32 per row (d <= 32 * NH)
+// i.e. one contiguous, 16-byte aligned span of 32*d floats, reads its 32 indices with one coalesced load, parks them in
+// shared memory and writes the span as float4 — one multiply-shift and one 16-byte store per four elements instead
+// of a division, an index load and a 4-byte store per element.
 __global__ void __launch_bounds__(256)
-k_gather_span(const float *__restrict__ table, int64_t table_rows, int d, const int64_t *__restrict__ idx, int64_t n,
-              float *__restrict__ out)
+k_gather_span(const float *__restrict__ table, int64_t table_rows, int d, unsigned int inv,
+              const int64_t *__restrict__ idx, int64_t n, float *__restrict__ out)
 {
-    extern __shared__ __align__(16) float stage[];                   // [8 warps][32 rows][d]
     __shared__ const float *sj[8][32];                               // source row of each output row (null: zeros)
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-    float *st = stage + (size_t)wib * 32 * d + lane;
     const int64_t nwarps = (int64_t)gridDim.x * 8;
-    bool col[NH];
-#pragma unroll
-    for (int h = 0; h < NH; h++) col[h] = lane + 32 * h < d;
     for (int64_t r0 = ((int64_t)blockIdx.x * 8 + wib) * 32; r0 < n; r0 += nwarps * 32) {
         const int rows_here = (int)min((int64_t)32, n - r0);
         long long j = -1;
         if (lane < rows_here) {
             j = idx[r0 + lane];
-            if ((uint64_t)j >= (uint64_t)table_rows) j = -1;          // out of range: zeros
+            if ((uint64_t)j >= (uint64_t)table_rows) j = -1;          // out of range: zeros, as before
         }
-        __syncwarp();                                                 // the previous span has left the staging rows
-        sj[wib][lane] = j >= 0 ? table + j * d + lane : nullptr;      // this lane's column of the row
         __syncwarp();
-#pragma unroll 8
-        for (int r = 0; r < 32; r++) {                                // rows beyond rows_here hold null: zeros, unused
-            const float *src = sj[wib][r];                            // broadcast read
-#pragma unroll
-            for (int h = 0; h < NH; h++)
-                if (col[h]) st[r * d + 32 * h] = src ? __ldg(src + 32 * h) : 0.f;
-        }
+        sj[wib][lane] = j >= 0 ? table + j * d : nullptr;
         __syncwarp();
         float *dst = out + r0 * d;                                    // 32 * d * 4 bytes per span: 16-byte aligned
-        const float *stw = stage + (size_t)wib * 32 * d;
-        const int total = rows_here * d;
-        for (int e = lane * 4; e < total; e += 128) {
+        const unsigned int total = (unsigned int)rows_here * (unsigned int)d;
+        for (unsigned int e = lane * 4; e < total; e += 128) {
+            // row of element e: multiply-shift (inv = ceil(2^20 / d), exact for e < 32 d while d < 181), else divide
+            unsigned int r = inv ? (e * inv) >> 20 : e / (unsigned int)d, c = e - r * (unsigned int)d;
+            float v[4];
+#pragma unroll
+            for (int t = 0; t < 4; t++) {
+                v[t] = 0.f;
+                if (e + t < total) {
+                    const float *src = sj[wib][r];
+                    if (src != nullptr) v[t] = __ldg(src + c);
+                    if (++c == (unsigned int)d) c = 0, r++;
+                }
+            }
             if (e + 3 < total) {
-                *reinterpret_cast<float4 *>(dst + e) = *reinterpret_cast<const float4 *>(stw + e);
+                *reinterpret_cast<float4 *>(dst + e) = make_float4(v[0], v[1], v[2], v[3]);
             } else {
-                for (int t = 0; t < 4 && e + t < total; t++) dst[e + t] = stw[e + t];
+                for (int t = 0; t < 4 && e + t < total; t++) dst[e + t] = v[t];
             }
         }
     }
 }
+
+// (Round 2 tried staging the 32 rows in shared memory with lanes over columns and writing the span out from there:
+// a quarter of the instructions, but 0.57 ms against 0.26 ms for this version — the extra shared-memory round trip and
+// its warp syncs cost more than the index arithmetic they remove; profiles/r2f_bench.json vs r1x_bench.json.)
 
 // Rows of whole float4 (d % 4 == 0; 48 floats = the fork's colour rows): the same span organisation without the
 // staging — the 32 * dv float4 of a span are copied lane-linear, four loads in flight per lane, the row of element e
@@ -188,12 +187,9 @@ int launch_gather(const float *table, int64_t table_rows, int d, const int64_t *
     if (v4)
         return launch_gather_t<float4>(reinterpret_cast<const float4 *>(table), table_rows, d / 4, idx, n,
                                        reinterpret_cast<float4 *>(out), s);
-    if ((reinterpret_cast<uintptr_t>(out) & 15) == 0 && (size_t)d * 1024 <= 48 * 1024) {
-        if (blocks > (int64_t)sm_count() * 4) blocks = (int64_t)sm_count() * 4;   // 1 KB x d of staging per block
-        if (d <= 32)
-            k_gather_span<1><<<(unsigned)blocks, 256, (size_t)d * 1024, s>>>(table, table_rows, d, idx, n, out);
-        else
-            k_gather_span<2><<<(unsigned)blocks, 256, (size_t)d * 1024, s>>>(table, table_rows, d, idx, n, out);
+    if ((reinterpret_cast<uintptr_t>(out) & 15) == 0 && d < (1 << 24)) {
+        k_gather_span<<<(unsigned)blocks, 256, 0, s>>>(table, table_rows, d, d < 181 ? ((1u << 20) + d - 1) / d : 0u,
+                                                       idx, n, out);
         C3VQ_LAUNCH_CHECK("k_gather_span");
         return C3VQ_OK;
     }

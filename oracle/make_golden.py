@@ -11,7 +11,7 @@ The reference module is imported unchanged through oracle/ref_loader.py.  Its
     recorders, so the fixture holds every random draw and every intermediate state.
 The fixtures pin the Python half of the path (weight normalisation, batch draw,
 update algebra, EMA order, eps, trace normalisation, final assignment).  The CUDA
-half (weighted_distance.cu) is pinned on the GPU box by oracle/make_golden_gpu.py.
+half (weighted_distance.cu) is pinned on the GPU box by oracle/Makefile (target `ref`).
 """
 from __future__ import annotations
 

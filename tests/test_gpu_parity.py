@@ -587,6 +587,31 @@ def test_full_size_reference_kernel_bit_exact(L):
         del dist_r, idx_r, dist, idx
 
 
+@pytest.mark.parametrize("book", ["uniform-box", "sampled"])
+def test_full_size_fused_sums_within_tolerance(L, book):
+    """BASELINE configs[1] at full size: the centroid sums the assignment kernel forms itself (default mode; warp
+    combining + 32 partial tables folded pairwise) against float64 accumulation of the same float32 products, as
+    centroids sum_x / (sum_w + eps), within the north star's 1e-5 (row-normalised).  The uniform-box codebook is the
+    hard case: four codewords own 88 % of the rows (a plain fp32 atomic scatter, the reference's torch_scatter, is off
+    by 2e-3 there: profiles/r2e_sums_probe.txt)."""
+    sys.path.insert(0, ROOT)
+    from bench import init_codebook, synth
+    n, d, k = 5_800_000, 45, 4096
+    x, w = synth(n, d, 1234, device=torch.device(DEV))
+    wn = (w / w.max()).contiguous()
+    g = torch.Generator(device=DEV).manual_seed(3)
+    cb = init_codebook(x, k, 99) if book == "uniform-box" else x[torch.randint(0, n, (k,), device=DEV, generator=g)].clone()
+    acc, _, idx = L.assign_accumulate(x, wn, cb, tensor_cores="fused")
+    ref_x = torch.zeros(k, d, device=DEV, dtype=torch.float64).index_add_(0, idx, (x * wn[:, None]).double())
+    ref_w = torch.zeros(k, device=DEV, dtype=torch.float64).index_add_(0, idx, wn.double())
+    ref_c = ref_x / (ref_w[:, None] + 1e-5)
+    got_c = acc[:, :d].double() / (acc[:, d].double()[:, None] + 1e-5)
+    err = (got_c - ref_c).abs().max(1).values / (ref_c.abs().max(1).values + 1e-30)
+    assert float(err[ref_w > 0].max()) < CB_RTOL, f"centroid error {float(err[ref_w > 0].max()):.2e}"
+    assert torch.allclose(acc[:, d].double(), ref_w, rtol=1e-5, atol=1e-9)
+    assert not acc[:, d + 1:].any()
+
+
 # ---------------------------------------------------------------- outlier codewords ----------------
 @pytest.mark.parametrize("d", [6, 45, 48])
 def test_assign_outlier_codewords_stay_exact_and_off_the_fallback(L, oracle, d):

@@ -58,6 +58,27 @@ for name, book in books.items():
             acc.zero_()
             _lib.assign_accumulate(x, wn, book, acc=acc, tensor_cores=mode)
         res[label] = timed(run)
+    # accuracy of the sums (as centroids sum_x / (sum_w + eps), row-normalised) against float64 accumulation of the
+    # same float32 products: fused bulk reduce-adds with warp combining, sorted segmented sum, plain atomics
+    prod = (x * wn[:, None]).double()
+    ref_x = torch.zeros(K, d, device=dev, dtype=torch.float64).index_add_(0, idx, prod)
+    ref_w = torch.zeros(K, device=dev, dtype=torch.float64).index_add_(0, idx, wn.double())
+    del prod
+    ref_c = ref_x / (ref_w[:, None] + 1e-5)
+    errs = {}
+    for label, fn in (("fused", lambda: _lib.assign_accumulate(x, wn, book, acc=acc, tensor_cores="fused")),
+                      ("sorted", lambda: _lib.accumulate(x, wn, idx, K, acc=acc, sorted_path=True)),
+                      ("atomic", lambda: _lib.accumulate(x, wn, idx, K, acc=acc, sorted_path=False))):
+        acc.zero_()
+        fn()
+        c = acc[:, :d].double() / (acc[:, d].double()[:, None] + 1e-5)
+        e = (c - ref_c).abs().max(1).values / (ref_c.abs().max(1).values + 1e-30)
+        live = ref_w > 0
+        errs[label] = float(e[live].max())
+        worst = int(torch.argmax(torch.where(live, e, torch.zeros_like(e))))
+        errs[label + "_rows_of_worst"] = int((idx == worst).sum())
+    print("   centroid error vs float64 (row-normalised max): " + ", ".join(
+        f"{k} {errs[k]:.2e} (worst codeword owns {errs[k + '_rows_of_worst']} rows)" for k in ("fused", "sorted", "atomic")))
     t_atomic = timed(lambda: _lib.accumulate(x, wn, idx, K, acc=acc, sorted_path=False), reps=2)
     t_sorted = timed(lambda: _lib.accumulate(x, wn, idx, K, acc=acc, sorted_path=True))
     print(f"   assign {t_assign:.3f} ms | assign+sorted sums {res['sorted']:.3f} ms (+{res['sorted'] - t_assign:.3f}) | "
