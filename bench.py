@@ -258,7 +258,7 @@ class Clustering:
     calls so that the assignment (prep + k_assign_tc + fallback scan) and the update (sums + EMA) can be bracketed
     by CUDA events on their own; the all-reduce of the sums sits between the two halves of the update."""
 
-    def __init__(self, x, wn, cb0, dev, simt=False, sums="sorted", scale_normalize=False):
+    def __init__(self, x, wn, cb0, dev, simt=False, sums="fused", scale_normalize=False):
         from c3dgs_b200 import _lib
         from c3dgs_b200.sharded import CudaOps, ShardedVectorQuantize
         self.L, self.x, self.wn, self.cb0 = _lib, x, wn, cb0
@@ -567,7 +567,7 @@ def main():
         dist.all_gather_object(hashes, replica_hash)
         sub = 262_144                                     # rows per rank in the reduced problem
         xs, ws = x[:sub].contiguous(), wn[:sub].contiguous()
-        pj = Clustering(xs, ws, cb0, dev)
+        pj = Clustering(xs, ws, cb0, dev, sums=args.sums)
         pj.step(False)                                    # sharded: all ranks, NCCL all-reduce per iteration
         cb_sharded = pj.vq.codebook.clone()
         gx = [torch.empty_like(xs) for _ in range(world)] if rank == 0 else None
@@ -576,7 +576,7 @@ def main():
         dist.gather(ws, gw, dst=0)
         if rank == 0:
             xa, wa = torch.cat(gx), torch.cat(gw)
-            one = Clustering(xa, wa, cb0, dev)
+            one = Clustering(xa, wa, cb0, dev, sums=args.sums)
             one.vq._world = lambda: 1                     # no collectives: the same rows on one GPU
             one.step(False)
             scale = one.vq.codebook.abs().max(1, keepdim=True).values + 1e-30
@@ -671,7 +671,7 @@ def main():
         cbs = init_codebook(xs, K, 99)
         if world > 1:
             dist.broadcast(cbs, src=0)
-        sj = Clustering(xs, ws, cbs, dev)
+        sj = Clustering(xs, ws, cbs, dev, sums=args.sums)
         for _ in range(2):
             sj.step(False)
         barrier()
@@ -692,7 +692,7 @@ def main():
                 parts = [synth(per, d, 5000 + b, device=dev) for b in range(blocks)]
                 xa, wa = torch.cat([p_[0] for p_ in parts]), torch.cat([p_[1] for p_ in parts])
                 del parts
-                oj = Clustering(xa, wa, cbs, dev)
+                oj = Clustering(xa, wa, cbs, dev, sums=args.sums)
                 oj.vq._world = lambda: 1
                 for _ in range(2):
                     oj.step(False)
@@ -714,7 +714,7 @@ def main():
                   "ms_per_step": ms_n, "value": total * ITERS / (ms_n * 1e-3),
                   "one_gpu_ms_per_step": ms_1, "speedup_vs_one_gpu": ms_1 / ms_n,
                   "assign_ms_per_iteration": am, "update_ms_per_iteration": um, "allreduce_ms_per_iteration": ar_ms,
-                  "intervals_ms": dict(zip(("assign+sums", "gap", "allreduce", "ema"), intervals)),
+                  "intervals_ms": dict(zip(("assign (+ fused sums)", "separate sums kernels", "allreduce", "ema"), intervals)),
                   "note": "the one-GPU time is measured in this run: rank 0 clusters all rows alone while the other ranks wait"}
         torch.cuda.empty_cache()
 

@@ -86,7 +86,8 @@ constexpr int TC_SMEM_LIMIT = 227 * 1024;
 // table row that owns 10^5-10^6 rows would otherwise be the end of as long a chain of fp32 additions at the L2
 // (2.5e-5 of centroid error against float64 at 5.8 M rows; 3e-6 with 32 partial tables, profiles/r2f_sums_probe.txt).
 constexpr int TC_ACC_PARTS = 32;
-constexpr int64_t TC_ACC_PARTS_MIN_ROWS = 1 << 20;
+constexpr int64_t TC_ACC_PARTS_MIN_ROWS = (1 << 18) + 1;   // above the reference's colour mini-batch (2^18 rows): there
+                                                           // the chains are short and the fold's ~12 us would show
 constexpr float TC_F16_ACONST = 256.f;
 constexpr float TC_F16_DEAD = 3.f * 65504.f * 256.f;     // 5.03e7
 constexpr float TC_F16_XLIM = 1073741824.f;             // 2^30: limit of gamma^2 |x'|^2 (every element below 2^15)

@@ -86,13 +86,16 @@ k_gather_span(const float *__restrict__ table, int64_t table_rows, int d, unsign
             // row of element e: multiply-shift (inv = ceil(2^20 / d), exact for e < 32 d while d < 181), else divide
             unsigned int r = inv ? (e * inv) >> 20 : e / (unsigned int)d, c = e - r * (unsigned int)d;
             float v[4];
+            const float *src = sj[wib][r];                            // reloaded only where the float4 crosses a row end
 #pragma unroll
             for (int t = 0; t < 4; t++) {
                 v[t] = 0.f;
                 if (e + t < total) {
-                    const float *src = sj[wib][r];
                     if (src != nullptr) v[t] = __ldg(src + c);
-                    if (++c == (unsigned int)d) c = 0, r++;
+                    if (++c == (unsigned int)d) {
+                        c = 0;
+                        src = sj[wib][(++r) & 31];
+                    }
                 }
             }
             if (e + 3 < total) {

@@ -109,7 +109,11 @@ int c3vq_ema(float *codebook, float *entry_importance, const float *acc,
  * (either may be null).  ws: c3vq_update_workspace_bytes(n, d, k) bytes.
  * use_tensor_cores: 0 = SIMT exact assignment + atomic sums; 1 = tensor-core assignment, then the sorted
  * segmented sums (second pass over x, no per-row atomics); 2 = tensor-core assignment with the sums fused
- * into the kernel (x read once, one bulk reduce-add per row: bounded by the L2's fp32 reduction rate).
+ * into the kernel (x read from HBM once: rows of a warp that share a codeword are combined in shared memory, one
+ * bulk reduce-add per distinct codeword, into 32 partial tables that are folded pairwise when n > 2^18; the host's
+ * default).  The tensor-core screening runs on fp16 operands scaled by a power of two (kind::f16; environment
+ * C3VQ_SCREEN=tf32 selects kind::tf32); either way the results are the exact fp32 re-rank's, bit-identical to the
+ * reference kernel.
  * n == 0 is not a no-op: like the reference's update on an empty batch (vq.py:31-34: nothing scattered, both EMAs
  * applied) every codeword and entry_importance decay by `decay`.  `rows`, when given, must lie in [0, rows of x):
  * the kernels do not check them (the Python host does unless the caller vouches for them).

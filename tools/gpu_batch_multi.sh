@@ -8,7 +8,7 @@ run bench.py --gpus $N --steps 2 --warmup 1 --impl reference > $O/${T}_bench_${N
 run tools/nccl_check.py > $O/${T}_nccl_check_${N}gpu.txt 2>&1
 python - <<PY
 import json
-j = json.load(open("$O/${T}_bench_${N}gpu.json"))
+j = [json.loads(l) for l in open("$O/${T}_bench_${N}gpu.json") if l.startswith("{")][-1]
 print("n_gpus", j["n_gpus"], "ms/step", round(j["ms_per_step"], 2), "value", round(j["value"] / 1e9, 3), "G; e2e ms", round(j["e2e"]["ms_per_step"], 2))
 print("parity", j["parity"])
 print("h2d", j["h2d_probe"])
