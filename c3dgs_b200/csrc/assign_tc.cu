@@ -942,14 +942,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                         p.dbg_scores[(pair * TC_PR + lr) * p.k + code0 + jj] = __uint_as_float(a[jj]) * g2inv;
             };
 
-            // The barrier of the NEXT step's slot is probed as soon as this step's slot has been handed back: the
-            // tensor core is usually a step ahead, and a try_wait that succeeds still takes ~90 cycles to say so, which
-            // then hide behind the min reduction instead of opening every step (ncu: 26 % of the drain warps' samples)
-            bool ready = false;
+            // Tried and dropped (round 2, A/B at 5.8 M x 45, fused sums, mean of iterations 1-7): probing the NEXT
+            // step's barrier with a try_wait right after handing this step's slot back, to hide the ~90 cycles a
+            // successful wait takes behind the min reduction: 3.63 ms per iteration against 3.46 ms without the probe
+            // (the extra try_wait + predicate per step cost more issue slots than the hidden latency gave back)
             for (int s = 0; s < nsteps; s++) {
                 const uint32_t acc_full = acc_full0 + 8u * par, tsrc = tsrc0 + par * BN;
                 PROF(4);   // prof[24+4]: drain (LDTM + min + lists)
-                if (!ready) mbar_wait_hint(acc_full, wph);
+                mbar_wait_hint(acc_full, wph);
                 PROF(3);   // prof[24+3]: drain wait ACC_FULL
                 tc_fence_after();
                 const int code_s = s * BN + h * (BN / 2);
@@ -971,11 +971,6 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                 tmem_wait_ld16(vb);
                 if (DBG) { dump(va, code_s); dump(vb, code_s + 16); }
                 groups(va, gv);
-                uint32_t par_n = par + 1, wph_n = wph;
-                if (par_n == (uint32_t)L::SPT) {
-                    par_n = 0;
-                    wph_n ^= 1u;
-                }
                 if (BN == 96) {
                     tmem_ld16_async(tsrc + 32, va);
                     groups(vb, gv + 4);
@@ -983,19 +978,19 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                     tc_fence_before();                  // this half of the slot is read: hand it back to the MMA warp
                     __syncwarp();
                     if (lane == 0) mbar_arrive(acc_full + ACC_E_OFF);
-                    ready = s + 1 < nsteps && mbar_try_wait(acc_full0 + 8u * par_n, wph_n);
                     if (DBG) dump(va, code_s + 32);
                     groups(va, gv + 8);
                 } else {                                // BN == 64: 32 columns per thread
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(acc_full + ACC_E_OFF);
-                    ready = s + 1 < nsteps && mbar_try_wait(acc_full0 + 8u * par_n, wph_n);
                     groups(vb, gv + 4);
                 }
                 process(gv, (uint32_t)(2 * s + h));
-                par = par_n;
-                wph = wph_n;
+                if (++par == (uint32_t)L::SPT) {
+                    par = 0;
+                    wph ^= 1u;
+                }
             }
             const int cnt = (int)(cnt_off / LIST_STRIDE);
             PROF(4);
