@@ -64,6 +64,7 @@ SIGNATURES = {
     "c3vq_assign_workspace_bytes": (_c_sz, [_c_i64, _c_int, _c_int]),
     "c3vq_assign": (_c_int, [_c_vp, _c_vp, _c_i64, _c_int, _c_vp, _c_int, _c_vp, _c_vp, _c_vp, _c_sz, _c_vp]),
     "c3vq_assign_exact": (_c_int, [_c_vp, _c_vp, _c_i64, _c_int, _c_vp, _c_int, _c_vp, _c_vp, _c_vp]),
+    "c3vq_assign_static": (_c_int, [_c_vp, _c_vp, _c_i64, _c_int, _c_vp, _c_int, _c_vp, _c_vp, _c_vp]),
     "c3vq_acc_stride": (_c_int, [_c_int]),
     "c3vq_accumulate": (_c_int, [_c_vp, _c_vp, _c_vp, _c_vp, _c_i64, _c_int, _c_int, _c_vp, _c_vp]),
     "c3vq_accumulate_sorted_workspace_bytes": (_c_sz, [_c_i64, _c_int]),
@@ -227,6 +228,28 @@ def assign(x: torch.Tensor, codebook: torch.Tensor, rows: torch.Tensor | None = 
     if rc:
         raise _err(rc)
     return dist, idx
+
+
+STATIC_SCRATCH_BYTES = 4 << 20      # C3VQ_STATIC_SCRATCH_BYTES of include/c3vq.h
+
+
+def assign_static(x: torch.Tensor, codebook: torch.Tensor, dist: torch.Tensor | None, idx: torch.Tensor,
+                  rows: torch.Tensor | None = None) -> None:
+    """c3vq_assign_static: nearest codeword per row into the caller's `idx` (int64 [n]) and optional `dist`
+    (float32 [n]); the scratch is the library's fixed device array, nothing is allocated here or in the library.
+    No counterpart in the reference (added for callers that cannot allocate); tensors must already be contiguous."""
+    for t, dt, nm in ((x, torch.float32, "coefs"), (codebook, torch.float32, "codebook"), (idx, torch.int64, "idx")):
+        _check(t, dt, nm)
+        if not t.is_contiguous():
+            raise RuntimeError(f"{nm} must be contiguous (assign_static makes no copies)")
+    n = rows.numel() if rows is not None else x.size(0)
+    if idx.numel() != n or (dist is not None and (dist.numel() != n or dist.dtype != torch.float32)):
+        raise RuntimeError("idx / dist must hold one entry per row")
+    with torch.cuda.device(x.device):
+        rc = load().c3vq_assign_static(_ptr(x), _ptr(rows), n, x.size(1), _ptr(codebook), codebook.size(0),
+                                       _ptr(dist), _ptr(idx), _stream(x))
+    if rc:
+        raise _err(rc)
 
 
 def update(x: torch.Tensor, w: torch.Tensor, codebook: torch.Tensor, entry_importance: torch.Tensor,

@@ -78,6 +78,16 @@ int c3vq_assign(const float *x, const int64_t *rows, int64_t n, int d, const flo
                             nullptr, ws, ws_bytes, (cudaStream_t)stream);
 }
 
+int c3vq_assign_static(const float *x, const int64_t *rows, int64_t n, int d, const float *codebook, int k,
+                       float *out_dist, int64_t *out_idx, c3vq_stream_t stream)
+{
+    int rc = check_common(x, n, d, codebook, k);
+    if (rc) return rc;
+    C3VQ_CHECK_ARG(n == 0 || out_idx != nullptr, "out_idx is null");
+    if (n == 0) return C3VQ_OK;
+    return launch_assign_tc_static(x, rows, n, d, codebook, k, out_dist, out_idx, (cudaStream_t)stream);
+}
+
 int c3vq_assign_exact(const float *x, const int64_t *rows, int64_t n, int d, const float *codebook, int k,
                       float *out_dist, int64_t *out_idx, c3vq_stream_t stream)
 {

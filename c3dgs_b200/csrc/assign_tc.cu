@@ -36,6 +36,7 @@
 // the tile's 256 drain threads read the other: MMA, drain and re-rank all overlap.
 #include <cuda_fp16.h>
 #include <cstdlib>
+#include <mutex>
 
 #include "common.cuh"
 #include "tc_ptx.cuh"
@@ -1353,6 +1354,55 @@ int tc_stats(void *ws, int64_t out[3], cudaStream_t s)
     out[1] = (int64_t)h.cands;
     out[2] = (int64_t)h.fb_rows;
     return C3VQ_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// c3vq_assign_static: the same search with its scratch (header, codebook image, fallback lists) in a fixed device
+// array instead of a caller-provided workspace, for callers that cannot allocate device memory (CUDA graph capture,
+// serving loops, harnesses that forbid cudaMalloc).  Every GPU that loads the library holds the array until exit.
+// g_static_scratch names the array in DEVICE code only; on the host the symbol is a stand-in, so the launcher asks
+// the runtime for the device address (once per device, with that device current) and hands that to the kernels.
+__device__ __align__(256) unsigned char g_static_scratch[C3VQ_STATIC_SCRATCH_BYTES];
+
+constexpr int STATIC_MAX_DEVICES = 64;
+static void *g_static_ptr[STATIC_MAX_DEVICES];           // device address of g_static_scratch, per device ordinal
+static std::mutex g_static_mutex;
+
+static int static_scratch_ptr(void **out)
+{
+    int dev = -1;
+    C3VQ_CUDA(cudaGetDevice(&dev));
+    C3VQ_CHECK_ARG(dev >= 0 && dev < STATIC_MAX_DEVICES, "device ordinal %d outside [0, %d)", dev, STATIC_MAX_DEVICES);
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    if (g_static_ptr[dev] == nullptr) {
+        void *ptr = nullptr;
+        C3VQ_CUDA(cudaGetSymbolAddress(&ptr, g_static_scratch));
+        C3VQ_CHECK_ARG(ptr != nullptr && (reinterpret_cast<uintptr_t>(ptr) & 255) == 0,
+                       "static scratch address %p is null or misaligned", ptr);
+        g_static_ptr[dev] = ptr;
+    }
+    *out = g_static_ptr[dev];
+    return C3VQ_OK;
+}
+
+int launch_assign_tc_static(const float *x, const int64_t *rows, int64_t n, int d, const float *codebook, int k,
+                            float *out_dist, int64_t *out_idx, cudaStream_t s)
+{
+    if (n == 0) return C3VQ_OK;
+    const size_t need = tc_workspace_bytes(n, d, k);
+    if (need > (size_t)C3VQ_STATIC_SCRATCH_BYTES) {
+        set_error("c3vq_assign_static: n=%lld, d=%d, k=%d needs %zu bytes of scratch, the static array holds %zu "
+                  "(use c3vq_assign with a caller-provided workspace)", (long long)n, d, k, need,
+                  (size_t)C3VQ_STATIC_SCRATCH_BYTES);
+        return C3VQ_EWORKSPACE;
+    }
+    void *ws = nullptr;
+    const int rc = static_scratch_ptr(&ws);
+    if (rc) return rc;
+    // nothing in the array has to survive or start at zero beyond what launch_assign_tc clears itself on every call
+    // (the header with its counters; lists and images are rewritten before they are read)
+    return launch_assign_tc(x, nullptr, rows, n, d, codebook, k, out_dist, out_idx, nullptr, nullptr, nullptr, nullptr,
+                            ws, (size_t)C3VQ_STATIC_SCRATCH_BYTES, s);
 }
 
 }  // namespace c3vq

@@ -114,5 +114,7 @@ int launch_assign_tc(const float *x, const float *w, const int64_t *rows, int64_
                      float *dbg_scores, float *dbg_norm2, float *dbg_band, void *ws, size_t ws_bytes,
                      cudaStream_t s);
 int tc_stats(void *ws, int64_t out[3], cudaStream_t s);
+int launch_assign_tc_static(const float *x, const int64_t *rows, int64_t n, int d, const float *codebook, int k,
+                            float *out_dist, int64_t *out_idx, cudaStream_t s);
 
 }  // namespace c3vq

@@ -69,6 +69,28 @@ int c3vq_assign_exact(const float *x, const int64_t *rows, int64_t n, int d,
                       float *out_dist, int64_t *out_idx, c3vq_stream_t stream);
 
 /*
+ * c3vq_assign without any device allocation on either side of the call.  No
+ * counterpart in the reference: added for
+ * callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same search, same bit-exact results as c3vq_assign;
+ * the scratch lives in a fixed __device__ array of C3VQ_STATIC_SCRATCH_BYTES that
+ * every GPU which loads the library holds until the process exits.  The call
+ * itself runs no cudaMalloc / cudaFree / allocating library routine.
+ * Limit: c3vq_assign_workspace_bytes(n, d, k) <= C3VQ_STATIC_SCRATCH_BYTES, which
+ * covers n <= 65536 rows against k <= 4096 codewords at every d <= C3VQ_MAX_DIM
+ * (more rows at smaller d or k); beyond it the call returns C3VQ_EWORKSPACE with
+ * a message that names the sizes, and nothing is launched.
+ * All calls on a device share the one array: calls that overlap on the GPU
+ * (different streams, or threads that do not order their launches) race.  Calls
+ * on one stream are ordered and safe; the array needs no clearing between calls
+ * (each call resets the counters it reads).
+ */
+#define C3VQ_STATIC_SCRATCH_BYTES (4 << 20)
+int c3vq_assign_static(const float *x, const int64_t *rows, int64_t n, int d,
+                       const float *codebook, int k,
+                       float *out_dist, int64_t *out_idx, c3vq_stream_t stream);
+
+/*
  * Sensitivity-weighted centroid sums.  acc is [k][c3vq_acc_stride(d)] fp32:
  * columns 0..d-1 accumulate w_i * x_i, column d accumulates w_i, the rest is
  * padding.  The call ADDS into acc (zero it first; a multi-GPU caller all-reduces
