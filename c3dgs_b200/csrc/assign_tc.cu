@@ -65,6 +65,16 @@ __host__ __device__ constexpr int tc_spt(int dp) { return dp <= 48 ? 3 : 2; }
 __host__ __device__ constexpr int tc_bn(int dp) { return dp <= 64 ? 96 : 64; }
 __host__ __device__ constexpr int tc_spt(int dp) { return 2; }   // accumulator slots per row tile
 #endif
+// fp16 screening: the A operand takes half the TMEM columns, which would leave room for 112 codes per MMA (4 x 112 +
+// 2 x DP/2 <= 512 up to DP = 64): 37 steps per pass over 4096 codewords instead of 43.  Built, bit-exact (full GPU
+// suite green) and measured in round 2 (5.8 M rows, fused sums, mean of iterations 1-7): 3.61 / 3.78 / 3.19 ms at
+// D = 45 / 48 / 7 against 3.43 / 3.70 / 3.15 ms with 96 -- the 56 columns a drain thread then holds per step spill
+// (72 registers at 896 threads), which costs more than the saved barrier waits.  Kept behind C3VQ_TC_F16_BN112.
+#ifdef C3VQ_TC_F16_BN112
+__host__ __device__ constexpr int tc_bn_f16(int dp) { return dp <= 64 ? 112 : 96; }
+#else
+__host__ __device__ constexpr int tc_bn_f16(int dp) { return 96; }
+#endif
 #ifndef C3VQ_TC_LCAP
 #define C3VQ_TC_LCAP 6
 #endif
@@ -300,8 +310,9 @@ __global__ void k_tc_prep_image(const float *__restrict__ cb, int k, int k_pad, 
     if (fin && !(nf < TC_HUGE2)) {      // finite code outside the error model: everything goes exact
         atomicOr(&hdr->force_fallback, 1u);
     }
-    {   // Cmax: one atomic per warp instead of one per code (k_pad is a multiple of 32: whole warps are here)
-        const int cb_bits = __reduce_max_sync(0xffffffffu, fin ? __float_as_int(sqrtf(nf)) : 0);
+    {   // Cmax: one atomic per warp instead of one per code (k_pad is a multiple of BN, which need not be a multiple of
+        // 32: the last warp may be partial, its lanes past k_pad have returned above)
+        const int cb_bits = __reduce_max_sync(__activemask(), fin ? __float_as_int(sqrtf(nf)) : 0);
         if ((threadIdx.x & 31) == 0 && cb_bits) atomicMax(&hdr->cmax_bits, cb_bits);
     }
     if (f16) {
@@ -353,7 +364,7 @@ __global__ void k_tc_prep_image(const float *__restrict__ cb, int k, int k_pad, 
 template <int DP, bool F16>
 struct TcSmem {
     static constexpr int KSTEPS = F16 ? DP / 16 : DP / 8;                  // MMAs per stage (K = 16 fp16 or 8 tf32 each)
-    static constexpr int BN = F16 ? 96 : tc_bn(DP);                        // codes per stage / per MMA
+    static constexpr int BN = F16 ? tc_bn_f16(DP) : tc_bn(DP);                       // codes per stage / per MMA
     static constexpr int ESIZE = F16 ? 2 : 4;                              // bytes per operand element
     static constexpr int ACOLS = F16 ? DP / 2 : DP;                        // TMEM columns of one row tile's A operand
     static constexpr int NG = BN / 8;                                      // groups of 4 codes per drain thread and job
@@ -857,7 +868,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
         // Warp (tile t, lane quarter q, column half h) reads its half of every accumulator slot of its tile: two
         // threads per row, so a slot is back with the MMA warp after two short tcgen05.ld round trips.
         if (TC_REGS_DRAIN < 72) setmaxnreg_dec<TC_REGS_DRAIN < 72 ? TC_REGS_DRAIN : 64>();
-        constexpr int NGH = BN / 8;                     // groups of 4 codes per half job (12 or 8)
+        constexpr int NGH = BN / 8;                     // groups of 4 codes per half job (14, 12 or 8)
         const int dw = warp - TC_DRAIN_WARP0;           // 0..15
         const int q = warp & 3;                         // TMEM lane quarter this warp may access
         const int t = (dw >> 2) & 1;                    // row tile
@@ -908,9 +919,19 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                         thr = m + p.gamma2 * fabsf(m) + band;
                         // group mask without the ALU pipe's compare + select: the sign bit of thr - gv[i] (FADD) is
                         // shifted in by one funnel shift per group; group i ends up at bit NGH-1-i, set = candidate
+#ifdef C3VQ_TC_ONE_CHAIN
                         uint32_t ng = 0;
 #pragma unroll
                         for (int i = 0; i < NGH; i++) ng = __funnelshift_l(__float_as_uint(thr - gv[i]), ng, 1);
+#else                   // two independent chains of NGH / 2 dependent shifts each, joined by one more
+                        uint32_t ng0 = 0, ng1 = 0;
+#pragma unroll
+                        for (int i = 0; i < NGH / 2; i++) {
+                            ng0 = __funnelshift_l(__float_as_uint(thr - gv[i]), ng0, 1);
+                            ng1 = __funnelshift_l(__float_as_uint(thr - gv[NGH / 2 + i]), ng1, 1);
+                        }
+                        const uint32_t ng = (ng0 << (NGH / 2)) | ng1;
+#endif
                         const uint32_t gm = ~ng & ((1u << NGH) - 1u);
                         if (cnt_off == LIST_END) {      // full: drop entries the tighter threshold excludes
                             uint32_t wpos = 0;
@@ -926,7 +947,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                         }
                         if (cnt_off < LIST_END) {
                             st_shared_u32(lS + cnt_off, __float_as_uint(cm));
-                            st_shared_u32(lS + LIST_PLANE + cnt_off, (chunk << 12) | gm);
+                            st_shared_u32(lS + LIST_PLANE + cnt_off, (chunk << 16) | gm);
                             cnt_off += LIST_STRIDE;
                         } else {
                             band = __int_as_float(0x7fc00000);   // overflow: NaN band = exact fallback for this row
@@ -972,7 +993,28 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                 tmem_wait_ld16(vb);
                 if (DBG) { dump(va, code_s); dump(vb, code_s + 16); }
                 groups(va, gv);
-                if (BN == 96) {
+                if (BN == 112) {                        // 56 columns per thread: 16 + 16 + 16 + 8
+                    uint32_t vc[8];
+                    tmem_ld16_async(tsrc + 32, va);
+                    tmem_ld8_async(tsrc + 48, vc);
+                    groups(vb, gv + 4);
+                    tmem_wait_ld16(va);
+                    tmem_wait_ld8(vc);
+                    tc_fence_before();                  // this half of the slot is read: hand it back to the MMA warp
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(acc_full + ACC_E_OFF);
+                    if (DBG) {
+                        dump(va, code_s + 32);
+#pragma unroll
+                        for (int jj = 0; jj < 8; jj++)
+                            if (pair * TC_PR + lr < p.n && code_s + 48 + jj < p.k)
+                                p.dbg_scores[(pair * TC_PR + lr) * p.k + code_s + 48 + jj] =
+                                    __uint_as_float(vc[jj]) * (F16 ? ldexpf(1.f, -2 * p.hdr->g_exp) : 1.f);
+                    }
+                    groups(va, gv + 8);
+                    gv[12] = min4(vc[0], vc[1], vc[2], vc[3]);
+                    gv[13] = min4(vc[4], vc[5], vc[6], vc[7]);
+                } else if (BN == 96) {
                     tmem_ld16_async(tsrc + 32, va);
                     groups(vb, gv + 4);
                     tmem_wait_ld16(va);
@@ -1021,8 +1063,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                     const uint32_t es = ld_shared_u32(lS + e * LIST_STRIDE);
                     if (__uint_as_float(es) <= thr) {
                         const uint32_t ep = ld_shared_u32(lS + LIST_PLANE + e * LIST_STRIDE);
-                        uint32_t gm = ep & 0xFFFu;
-                        const uint32_t grp0 = (ep >> 12) * NGH;      // first group (code / 4) of the half job
+                        uint32_t gm = ep & 0xFFFFu;
+                        const uint32_t grp0 = (ep >> 16) * NGH;      // first group (code / 4) of the half job
                         if ((int)(grp0 + NGH) * 4 > p.k) {           // the chunk that holds the end of the codebook
                             uint32_t keep = 0;
                             for (int bit = 0; bit < NGH; bit++)
@@ -1175,7 +1217,7 @@ static TcLayout tc_layout(int64_t n, int d, int k, bool f16)
     l.dp = tc_dp(d, f16);
     l.nc = tc_nc(d, f16);
     l.dpc = (d + 3) & ~3;
-    l.bn = f16 ? 96 : tc_bn(l.dp);
+    l.bn = f16 ? tc_bn_f16(l.dp) : tc_bn(l.dp);
     l.k_pad = (k + l.bn - 1) / l.bn * l.bn;
     if (l.k_pad == 0) l.k_pad = l.bn;
     size_t o = al256(sizeof(TcHeader));

@@ -229,6 +229,23 @@ __device__ __forceinline__ void tmem_wait_ld16(uint32_t (&r)[16])
                  : "memory");
 }
 
+// 8-column variants (the tail of a 56-column half job when an MMA covers 112 codes)
+__device__ __forceinline__ void tmem_ld8_async(uint32_t taddr, uint32_t (&r)[8])
+{
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_wait_ld8(uint32_t (&r)[8])
+{
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]), "+r"(r[7])
+                 :
+                 : "memory");
+}
+
 // Shared-memory matrix descriptor, K-major, no swizzle (canonical "interleave" layout):
 // core matrix = 8 rows x 16 bytes stored as 128 contiguous bytes;
 //   LBO = byte distance between the two 16-byte K chunks of one K=8 (tf32) step,
