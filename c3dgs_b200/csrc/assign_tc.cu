@@ -75,6 +75,20 @@ __host__ __device__ constexpr int tc_bn_f16(int dp) { return dp <= 64 ? 112 : 96
 #else
 __host__ __device__ constexpr int tc_bn_f16(int dp) { return 96; }
 #endif
+// Candidate granularity: the drain records GROUPS of GS consecutive codes (one mask bit each) and the re-rank
+// evaluates every code of a recorded group exactly.  Larger groups mean fewer minima / mask instructions per score in
+// the drain (which bounds the kernel) and proportionally more exact distances in the re-rank (which has slack).
+#ifndef C3VQ_TC_GS
+#define C3VQ_TC_GS 4
+#endif
+#ifndef C3VQ_TC_GS_LOW
+#define C3VQ_TC_GS_LOW 16
+#endif
+#ifdef C3VQ_TC_F16_BN112
+__host__ __device__ constexpr int tc_gs(int dp) { return 4; }
+#else
+__host__ __device__ constexpr int tc_gs(int dp) { return dp <= 16 ? C3VQ_TC_GS_LOW : C3VQ_TC_GS; }
+#endif
 #ifndef C3VQ_TC_LCAP
 #define C3VQ_TC_LCAP 6
 #endif
@@ -136,8 +150,12 @@ struct TcParams {
     int d, k, nsteps, nstages;
     int64_t npairs;
     const float *bimg;      // [k_pad/bn][dp*esize/16][bn][16 bytes]: tf32 (or scaled fp16) image of -2c' and the norm pieces
-    const float *cbp;       // [k][dpc] raw codebook, zero padded to a multiple of 4 columns
-    int dpc;
+    // raw codebook for the exact distances, float4-column major: float4 c4 of code j at cbp4[c4 * kq + j] (columns
+    // zero padded to dpc, a multiple of 4; kq = k rounded up to 8).  The lanes that re-rank the consecutive codes of a
+    // group then read consecutive 16-byte pieces: one L1 wavefront per group and load instead of one per code (with
+    // row-major rows the re-rank's divergent loads were half of all L1 wavefronts of the kernel, r2r ncu capture)
+    const float *cbp;
+    int dpc, kq;
     const float *mu;        // [d] centre
     TcHeader *hdr;
     float *out_dist;
@@ -150,6 +168,12 @@ struct TcParams {
     unsigned long long *fb_best;   // per fallback row: running (distance bits, code) minimum
     float *dbg_scores, *dbg_norm2, *dbg_band;
     float gamma2;           // relative slack for the reference chain's own rounding
+    // Seeds (full-batch loops call again and again with the same rows): the winner of row i in the previous call on this
+    // workspace.  Its distance under the CURRENT codebook is an upper bound of the row's minimum, so the drain starts
+    // with a tight threshold instead of learning it chunk by chunk (far fewer trips through the list path).  Any value
+    // is safe: the bound is evaluated against the current codebook, stale or foreign entries only make it loose.
+    int *prev;              // [n] or null (rows indirection, debug build)
+    const uint8_t *reg;     // [k] 1 = regular code (has a real score in the screening)
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -273,7 +297,7 @@ __global__ void __launch_bounds__(256) k_tc_prep_mean(const float *__restrict__ 
 // prep 2: one thread per (padded) code: centre, norms, TF32 image, padded raw copy, Cmax
 __global__ void k_tc_prep_image(const float *__restrict__ cb, int k, int k_pad, int d, int dp, int nc, int dpc,
                                 int bn, int f16, TcHeader *hdr, float *__restrict__ mu_out, float *__restrict__ bimg,
-                                float *__restrict__ cbp)
+                                float *__restrict__ cbp, int kq, uint8_t *__restrict__ reg)
 {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= k_pad) return;
@@ -297,9 +321,9 @@ __global__ void k_tc_prep_image(const float *__restrict__ cb, int k, int k_pad, 
             const float cc = v - m;
             n2 += (double)cc * (double)cc;
             raw2 = fmaf(v, v, raw2);
-            cbp[(size_t)j * dpc + c] = v;
+            cbp[((size_t)(c >> 2) * kq + j) * 4 + (c & 3)] = v;
         }
-        for (int c = d; c < dpc; c++) cbp[(size_t)j * dpc + c] = 0.f;
+        for (int c = d; c < dpc; c++) cbp[((size_t)(c >> 2) * kq + j) * 4 + (c & 3)] = 0.f;
     }
     const float nf = (float)n2;
     if (fin && !(isfinite(raw2) && (int)((__float_as_uint(raw2) >> 23) & 0xff) <= hdr->thr_exp)) {
@@ -315,6 +339,7 @@ __global__ void k_tc_prep_image(const float *__restrict__ cb, int k, int k_pad, 
         const int cb_bits = __reduce_max_sync(__activemask(), fin ? __float_as_int(sqrtf(nf)) : 0);
         if ((threadIdx.x & 31) == 0 && cb_bits) atomicMax(&hdr->cmax_bits, cb_bits);
     }
+    if (j < k) reg[j] = (fin && nf < TC_HUGE2) ? 1 : 0;     // the code takes part in the screening with its real score
     if (f16) {
         // scaled fp16 operands: -2 gamma c' and gamma^2 |c'|^2 / 256 in three pieces (exact splits: every
         // remainder fits the next piece unless it falls below the fp16 subnormal step, 2^-25 absolute)
@@ -367,7 +392,15 @@ struct TcSmem {
     static constexpr int BN = F16 ? tc_bn_f16(DP) : tc_bn(DP);                       // codes per stage / per MMA
     static constexpr int ESIZE = F16 ? 2 : 4;                              // bytes per operand element
     static constexpr int ACOLS = F16 ? DP / 2 : DP;                        // TMEM columns of one row tile's A operand
-    static constexpr int NG = BN / 8;                                      // groups of 4 codes per drain thread and job
+    static constexpr int GS = tc_gs(DP);                                   // codes per candidate group (4, 8 or 16)
+    static constexpr int NG = BN / (2 * GS);                               // groups per drain thread and (half) job
+    static_assert(GS == 4 || GS == 8 || GS == 16, "group size");
+    // Tried for the groups of 16 and dropped (round 2): group r = the 16 columns r, r + 3, r + 6, ... so that every first
+    // minimum takes one column of each of the three TMEM loads and ptxas cannot sink a load below the reduction of the
+    // one before it (it does with contiguous groups of 8 and 16).  5.8 M x 7: 3.35 ms against 3.41 ms for groups of 4 on
+    // the same box, where contiguous groups of 16 with their serialised loads gain 6 % (3.05 vs 3.23 ms): the 48 live
+    // columns spill, and the drain is bound by issue slots, not by the TMEM latency.
+    static_assert((BN / 2) % GS == 0 && (BN != 112 || GS == 4), "group size must divide the half job");
     static constexpr int LCAP = tc_lcap(DP);
     static constexpr uint32_t LBO_B = BN * 16;
     static constexpr uint32_t BSTAGE = BN * DP * ESIZE;
@@ -377,6 +410,7 @@ struct TcSmem {
     static constexpr uint32_t XS_BYTES = 2u * TC_PR * XS * 4;              // raw rows, two passes in flight
     static constexpr uint32_t W_BYTES = 2u * TC_PR * 4;                    // row weights, two passes in flight
     static constexpr uint32_t BAND_BYTES = 2u * TC_PR * 4;                 // per-row error band, two passes in flight
+    static constexpr uint32_t SEED_BYTES = 2u * TC_PR * 4;                 // per-row initial running minimum, two passes
     // TMEM columns: NSLOT accumulator slots of BN (two per row tile), then the A operand of both row tiles
     static constexpr int SPT = tc_spt(DP);
     static constexpr int NSLOT = 2 * SPT;
@@ -388,7 +422,7 @@ struct TcSmem {
     static constexpr uint32_t FLAG_BYTES = 4u * TC_PR;                     // per-row, per-half status, two passes in flight
     static constexpr uint32_t XCHG_BYTES = 4u * TC_PR * 4;                 // running minima exchanged between column halves
     static constexpr uint32_t MISC_BYTES = 80 * 4 /*mu*/ + 64 /*counters, tmem ptr*/ + 40 * 8 /*barriers*/;
-    static constexpr uint32_t FIXED = XS_BYTES + W_BYTES + BAND_BYTES + LIST_BYTES + QUEUE_BYTES + BEST_BYTES + FLAG_BYTES +
+    static constexpr uint32_t FIXED = XS_BYTES + W_BYTES + BAND_BYTES + SEED_BYTES + LIST_BYTES + QUEUE_BYTES + BEST_BYTES + FLAG_BYTES +
                                       XCHG_BYTES + MISC_BYTES + 128 /*alignment*/;
     static int stages()
     {
@@ -402,6 +436,24 @@ struct TcSmem {
 __device__ __forceinline__ float min4(uint32_t a, uint32_t b, uint32_t c, uint32_t d)
 {
     return fminf(fminf(fminf(__uint_as_float(a), __uint_as_float(b)), __uint_as_float(c)), __uint_as_float(d));
+}
+__device__ __forceinline__ float min3f(float a, float b, float c) { return fminf(fminf(a, b), c); }
+// minimum of 8 consecutive scores: three FMNMX3 + one FMNMX, depth 3
+__device__ __forceinline__ float min8(const uint32_t *a)
+{
+    const float r0 = min3f(__uint_as_float(a[0]), __uint_as_float(a[1]), __uint_as_float(a[2]));
+    const float r1 = min3f(__uint_as_float(a[3]), __uint_as_float(a[4]), __uint_as_float(a[5]));
+    return fminf(min3f(r0, r1, __uint_as_float(a[6])), __uint_as_float(a[7]));
+}
+// minimum of 16 consecutive scores: seven FMNMX3 + one FMNMX, depth 3
+__device__ __forceinline__ float min16(const uint32_t *a)
+{
+    const float r0 = min3f(__uint_as_float(a[0]), __uint_as_float(a[1]), __uint_as_float(a[2]));
+    const float r1 = min3f(__uint_as_float(a[3]), __uint_as_float(a[4]), __uint_as_float(a[5]));
+    const float r2 = min3f(__uint_as_float(a[6]), __uint_as_float(a[7]), __uint_as_float(a[8]));
+    const float r3 = min3f(__uint_as_float(a[9]), __uint_as_float(a[10]), __uint_as_float(a[11]));
+    const float r4 = min3f(__uint_as_float(a[12]), __uint_as_float(a[13]), __uint_as_float(a[14]));
+    return fminf(min3f(r0, r1, r2), min3f(r3, r4, __uint_as_float(a[15])));
 }
 
 // row status handed from the drain warps to the re-rank warps
@@ -424,7 +476,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
     float *sX = reinterpret_cast<float *>(sB + (size_t)S * L::BSTAGE);     // [2][PR][XS] raw rows of two passes
     float *sW = sX + 2 * TC_PR * L::XS;                                     // [2][PR] row weights
     float *sBand = sW + 2 * TC_PR;                                          // [2][PR]
-    uint32_t *sListS = reinterpret_cast<uint32_t *>(sBand + 2 * TC_PR);     // [LCAP][DT] chunk-minimum score bits
+    float *sSeed = sBand + 2 * TC_PR;                                       // [2][PR]
+    uint32_t *sListS = reinterpret_cast<uint32_t *>(sSeed + 2 * TC_PR);     // [LCAP][DT] chunk-minimum score bits
     uint32_t *sListP = sListS + TC_DT * L::LCAP;                            // [LCAP][DT] (chunk << 12) | group mask
     uint32_t *sQueue = sListP + TC_DT * L::LCAP;                            // [2][QCAP] (row << 16) | group
     unsigned long long *sBest = reinterpret_cast<unsigned long long *>(sQueue + 2 * TC_QCAP);   // [PR]
@@ -581,8 +634,10 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
         const int pw = warp - TC_PROD_WARP0;
         float xr[32 * NH];
         float wr = 0.f;
+        int pj = -1;                                             // previous winner of this lane's row (seed), -1 = none
         auto prefetch = [&](int64_t pair) {
             const int64_t r0 = pair * TC_PR + pw * 32;
+            pj = (p.prev != nullptr && r0 + lane < p.n) ? p.prev[r0 + lane] : -1;
             if (p.rows == nullptr && r0 + 32 <= p.n) {
                 // common case: 32 contiguous full rows -> one base pointer, immediate offsets
                 const float *xp = p.x + r0 * D + lane;
@@ -633,28 +688,43 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             const float *xq = sX + qb * (TC_PR * L::XS);                    // the staged raw rows of that pass
             mbar_wait_backoff(Q_FULL(qb), (rp >> 1) & 1);
             PROF(6);   // prof[16+6]: re-rank wait Q_FULL
-            sBest[ptid] = ((unsigned long long)__float_as_uint(FLT_MAX)) << 32;      // (FLT_MAX, code 0)
-            named_bar_sync(1, TC_PR);
 #if defined(C3VQ_TC_EXP_NORERANK) || defined(C3VQ_TC_EXP_NOQUEUE)   // experiment: no exact re-rank (results are garbage)
             const uint32_t nq = 0;
 #else
             const uint32_t nq = min(sQCount[qb], (uint32_t)TC_QCAP);
 #endif
             const uint32_t *queue = sQueue + qb * TC_QCAP;
-            const uint32_t gmask = 0xFu << (lane & ~3);
-            for (uint32_t u = ptid >> 2; u < nq; u += TC_PR / 4) {
+            constexpr int GS = L::GS;                                       // lanes per queue item = codes per group
+            // the codebook rows come from the L2 (a microsecond under this kernel's load) and a round is a serial chain
+            // behind them: every thread asks for the row of its NEXT round's code while it works on this round's
+            auto fetch_ahead = [&](uint32_t u) {
+                if (u < nq) {
+                    const int code = (int)(queue[u] & 0xFFFFu) * GS + (lane & (GS - 1));
+                    if (code < p.k) {        // the lanes of a group share the lines: lane i asks for columns i, i + GS, ...
+                        const float4 *cp = reinterpret_cast<const float4 *>(p.cbp) + code;
+                        for (int c4 = lane & (GS - 1); c4 < p.dpc / 4; c4 += GS) prefetch_l1(cp + (size_t)c4 * p.kq);
+                    }
+                }
+            };
+            fetch_ahead(ptid / GS);
+            sBest[ptid] = ((unsigned long long)__float_as_uint(FLT_MAX)) << 32;      // (FLT_MAX, code 0)
+            named_bar_sync(1, TC_PR);
+            const uint32_t gmask = ((1u << GS) - 1u) << (lane & ~(GS - 1));
+            for (uint32_t u = ptid / GS; u < nq; u += TC_PR / GS) {
+                fetch_ahead(u + TC_PR / GS);
                 const uint32_t item = queue[u];
                 const int lr = item >> 16;
-                const int code = (int)(item & 0xFFFFu) * 4 + (lane & 3);
+                const int code = (int)(item & 0xFFFFu) * GS + (lane & (GS - 1));
                 const float *xg = xq + lr * L::XS;
                 unsigned long long key = ~0ull;
                 if (code < p.k) {
-                    const float4 *cp = reinterpret_cast<const float4 *>(p.cbp + (size_t)code * p.dpc);
+                    const float4 *cp = reinterpret_cast<const float4 *>(p.cbp) + code;
+                    const size_t kq = (size_t)p.kq;
                     float a = 0.f;
                     if (DCONST > 0) {
                         float4 cv[DCONST > 0 ? (DCONST + 3) / 4 : 1];
 #pragma unroll
-                        for (int c4 = 0; c4 < (DCONST + 3) / 4; c4++) cv[c4] = __ldg(cp + c4);
+                        for (int c4 = 0; c4 < (DCONST + 3) / 4; c4++) cv[c4] = __ldg(cp + c4 * kq);
 #pragma unroll
                         for (int c4 = 0; c4 < (DCONST + 3) / 4; c4++) {
                             float df;
@@ -665,7 +735,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                         }
                     } else {
                         for (int c4 = 0; c4 < p.dpc / 4; c4++) {
-                            const float4 cv = __ldg(cp + c4);
+                            const float4 cv = __ldg(cp + c4 * kq);
                             float df;
                             if (4 * c4 + 0 < D) { df = xg[4 * c4 + 0] - cv.x; a = fmaf(df, df, a); }
                             if (4 * c4 + 1 < D) { df = xg[4 * c4 + 1] - cv.y; a = fmaf(df, df, a); }
@@ -677,14 +747,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                     // smaller distance <=> smaller key, NaN/inf sort above FLT_MAX, ties -> lower code
                     key = ((unsigned long long)__float_as_uint(a) << 32) | (unsigned int)code;
                 }
-                unsigned long long o = __shfl_xor_sync(gmask, key, 1);
-                key = o < key ? o : key;
-                o = __shfl_xor_sync(gmask, key, 2);
-                key = o < key ? o : key;
-                if ((lane & 3) == 0) atomicMin(&sBest[lr], key);
+#pragma unroll
+                for (int sh = 1; sh < GS; sh <<= 1) {
+                    const unsigned long long o = __shfl_xor_sync(gmask, key, sh);
+                    key = o < key ? o : key;
+                }
+                if ((lane & (GS - 1)) == 0) atomicMin(&sBest[lr], key);
             }
             named_bar_sync(1, TC_PR);
-            st_cands += 4ull * nq;      // counted once per thread, divided out below
+            st_cands += (unsigned long long)GS * nq;      // counted once per thread, divided out below
             // ---- outputs (lane <-> row): idx / dist, fallback list, then the weighted row into the centroid sums ----
 #ifndef C3VQ_TC_EXP_NORERANK
             {
@@ -706,6 +777,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                 }
                 if (status == ROW_OK) {
                     st_rows++;
+                    if (p.prev) p.prev[gi] = bj;
                     if (p.out_idx) p.out_idx[gi] = bj;
                     if (need_dist) p.out_dist[gi] = __uint_as_float((unsigned int)(best >> 32));
                 } else if (status == ROW_FALLBACK) {
@@ -726,6 +798,29 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                     const float *ww = sW + qb * TC_PR + pw * 32;
                     const unsigned int key = status == ROW_OK ? (unsigned int)bj : 0x80000000u + (unsigned int)lane;
                     const int leader = __ffs(__match_any_sync(0xffffffffu, key)) - 1;   // lowest lane with this codeword
+                    if (__all_sync(0xffffffffu, leader == lane)) {
+                        // 32 distinct codewords (the usual case once the codebook is in use): nothing to combine, the
+                        // rows are scaled as float4 (an accumulator row = the first AS / 4 float4 of a staged row)
+                        const int AS4 = (DCONST > 0 ? ((DCONST + 4) & ~3) : p.acc_stride) >> 2;
+#pragma unroll 4
+                        for (int i = lane; i < 32 * AS4; i += 32) {
+                            const int r = i / AS4, c4 = i - r * AS4;
+                            float4 *q = reinterpret_cast<float4 *>(xw + r * L::XS) + c4;
+                            const float wv = ww[r];
+                            float4 v = *q;
+                            if (4 * c4 + 3 < D) {
+                                v.x = __fmul_rn(v.x, wv); v.y = __fmul_rn(v.y, wv);
+                                v.z = __fmul_rn(v.z, wv); v.w = __fmul_rn(v.w, wv);
+                            } else {
+                                const int c = 4 * c4;
+                                v.x = c + 0 < D ? __fmul_rn(v.x, wv) : (c + 0 == D ? wv : 0.f);
+                                v.y = c + 1 < D ? __fmul_rn(v.y, wv) : (c + 1 == D ? wv : 0.f);
+                                v.z = c + 2 < D ? __fmul_rn(v.z, wv) : (c + 2 == D ? wv : 0.f);
+                                v.w = c + 3 < D ? __fmul_rn(v.w, wv) : (c + 3 == D ? wv : 0.f);
+                            }
+                            *q = v;
+                        }
+                    } else
 #pragma unroll 8
                     for (int r = 0; r < 32; r++) {
                         const float wv = ww[r];
@@ -779,6 +874,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             }
             sW[(pi & 1) * TC_PR + ptid] = wr;
             __syncwarp();
+            // seed: the flag of the previous winner and its codebook row are requested now and used after the conversion
+            const bool seed_ok = (unsigned)pj < (unsigned)p.k;
+            const float4 *seed_row = reinterpret_cast<const float4 *>(p.cbp) + (seed_ok ? pj : 0);
+            uint8_t seed_reg = 0;
+            if (seed_ok) seed_reg = p.reg[pj];
             uint32_t av[L::ACOLS];
             float X = 0.f;                       // |x'|^2 of the rounded, centred row (scaled by gam^2) -> error band
             if (F16) {
@@ -824,6 +924,47 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                     p.dbg_band[gi] = band * ginv * ginv;
                 }
                 sBand[(pi & 1) * TC_PR + ptid] = band;
+                // seed of the running minimum: the score of the row's previous winner, evaluated in fp32 on the centred
+                // operands (|c'|^2 - 2 x'.c' = sum c'(c' - 2x')), bounds the row's minimum screened score from above once
+                // the screening error (<= E) and its own rounding (< E) are added: band >= 2.02 E covers both.  3e38 = none
+                float seed = 3.0e38f;
+                {
+                    if (seed_ok && seed_reg != 0 && gi < p.n) {
+                        const float4 *cp = seed_row;
+                        const size_t kq = (size_t)p.kq;
+                        const float *xg = xs_w + lane * L::XS;
+                        float a = 0.f;
+                        auto term = [&](int kk, float cvk) {
+                            if (kk < D) {
+                                const float mk = sMu[kk], cc = cvk - mk;
+                                a = fmaf(cc, cc - 2.f * (xg[kk] - mk), a);
+                            }
+                        };
+                        if (DCONST > 0) {
+                            float4 cv[DCONST > 0 ? (DCONST + 3) / 4 : 1];
+#pragma unroll
+                            for (int c4 = 0; c4 < (DCONST + 3) / 4; c4++) cv[c4] = __ldg(cp + c4 * kq);
+#pragma unroll
+                            for (int c4 = 0; c4 < (DCONST + 3) / 4; c4++) {
+                                term(4 * c4 + 0, cv[c4].x);
+                                term(4 * c4 + 1, cv[c4].y);
+                                term(4 * c4 + 2, cv[c4].z);
+                                term(4 * c4 + 3, cv[c4].w);
+                            }
+                        } else {
+                            for (int c4 = 0; c4 < p.dpc / 4; c4++) {
+                                const float4 cv = __ldg(cp + c4 * kq);
+                                term(4 * c4 + 0, cv.x);
+                                term(4 * c4 + 1, cv.y);
+                                term(4 * c4 + 2, cv.z);
+                                term(4 * c4 + 3, cv.w);
+                            }
+                        }
+                        const float sd = a * (gam * gam) + band;
+                        if (sd < 3.0e38f) seed = sd;             // NaN / inf: no seed
+                    }
+                }
+                sSeed[(pi & 1) * TC_PR + ptid] = seed;
             }
             PROF(2);   // prof[16+2]: producer stage + convert + band
             mbar_wait(A_EMPTY, (pi & 1) ^ 1);          // previous pass' MMAs no longer read the A operand in TMEM
@@ -868,7 +1009,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
         // Warp (tile t, lane quarter q, column half h) reads its half of every accumulator slot of its tile: two
         // threads per row, so a slot is back with the MMA warp after two short tcgen05.ld round trips.
         if (TC_REGS_DRAIN < 72) setmaxnreg_dec<TC_REGS_DRAIN < 72 ? TC_REGS_DRAIN : 64>();
-        constexpr int NGH = BN / 8;                     // groups of 4 codes per half job (14, 12 or 8)
+        constexpr int GS = L::GS;                       // codes per candidate group
+        constexpr int NGH = L::NG;                      // groups per half job (BN / 2 codes)
+        constexpr int GPC = 16 / GS;                    // groups per 16-column TMEM load
         const int dw = warp - TC_DRAIN_WARP0;           // 0..15
         const int q = warp & 3;                         // TMEM lane quarter this warp may access
         const int t = (dw >> 2) & 1;                    // row tile
@@ -889,24 +1032,32 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             mbar_wait(A_FULL, pi & 1);
             PROF(1);       // prof[24+1]: drain wait A_FULL
             float band = sBand[(pi & 1) * TC_PR + lr];            // computed by the producer of this row
-            float m = 3.0e38f;
-            // valid rows start at 2^124: above every real score, below the 2^126 of dead / padding codes
-            float thr = (band >= 0.f) ? (F16 ? 0.5f * TC_F16_DEAD : 0.25f * TC_BIG) : __int_as_float(0xff800000);
+            float m = sSeed[(pi & 1) * TC_PR + lr];               // 3e38, or an upper bound of the row's minimum score
+            // unseeded valid rows start at 2^124: above every real score, below the 2^126 of dead / padding codes
+            float thr = (band >= 0.f) ? fminf(F16 ? 0.5f * TC_F16_DEAD : 0.25f * TC_BIG, m + p.gamma2 * fabsf(m) + band)
+                                      : __int_as_float(0xff800000);
             uint32_t cnt_off = 0;                       // byte offset of the next free list entry
             PROF(2);       // prof[24+2]: drain band
 
             // group minima of a 16-column chunk (FMNMX3 + FMNMX per group)
             auto groups = [&](const uint32_t (&a)[16], float *gm) {
-                gm[0] = min4(a[0], a[1], a[2], a[3]);
-                gm[1] = min4(a[4], a[5], a[6], a[7]);
-                gm[2] = min4(a[8], a[9], a[10], a[11]);
-                gm[3] = min4(a[12], a[13], a[14], a[15]);
+                if (GS == 4) {
+                    gm[0] = min4(a[0], a[1], a[2], a[3]);
+                    gm[1] = min4(a[4], a[5], a[6], a[7]);
+                    gm[2] = min4(a[8], a[9], a[10], a[11]);
+                    gm[3] = min4(a[12], a[13], a[14], a[15]);
+                } else if (GS == 8) {
+                    gm[0] = min8(a);
+                    gm[1] = min8(a + 8);
+                } else {
+                    gm[0] = min16(a);
+                }
             };
             // half-job minimum against the running threshold; the append path is entered per WARP (uniform branch)
             auto process = [&](const float (&gv)[NGH], uint32_t chunk) {
-                float cm = fminf(fminf(gv[0], gv[1]), gv[2]);
+                float cm = gv[0];
 #pragma unroll
-                for (int i = 3; i + 1 < NGH; i += 2) cm = fminf(fminf(cm, gv[i]), gv[i + 1]);
+                for (int i = 1; i + 1 < NGH; i += 2) cm = fminf(fminf(cm, gv[i]), gv[i + 1]);
                 if (NGH % 2 == 0) cm = fminf(cm, gv[NGH - 1]);
 #ifdef C3VQ_TC_EXP_NOPROC     // experiment: running minimum only, no candidate lists (results are garbage)
                 m = fminf(m, cm);
@@ -919,19 +1070,20 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                         thr = m + p.gamma2 * fabsf(m) + band;
                         // group mask without the ALU pipe's compare + select: the sign bit of thr - gv[i] (FADD) is
                         // shifted in by one funnel shift per group; group i ends up at bit NGH-1-i, set = candidate
-#ifdef C3VQ_TC_ONE_CHAIN
-                        uint32_t ng = 0;
+                        uint32_t ng;
+                        if (NGH % 2 != 0 || NGH < 6) {  // few groups: one chain
+                            ng = 0;
 #pragma unroll
-                        for (int i = 0; i < NGH; i++) ng = __funnelshift_l(__float_as_uint(thr - gv[i]), ng, 1);
-#else                   // two independent chains of NGH / 2 dependent shifts each, joined by one more
-                        uint32_t ng0 = 0, ng1 = 0;
+                            for (int i = 0; i < NGH; i++) ng = __funnelshift_l(__float_as_uint(thr - gv[i]), ng, 1);
+                        } else {                        // two independent chains of NGH / 2 dependent shifts, joined by one more
+                            uint32_t ng0 = 0, ng1 = 0;
 #pragma unroll
-                        for (int i = 0; i < NGH / 2; i++) {
-                            ng0 = __funnelshift_l(__float_as_uint(thr - gv[i]), ng0, 1);
-                            ng1 = __funnelshift_l(__float_as_uint(thr - gv[NGH / 2 + i]), ng1, 1);
+                            for (int i = 0; i < NGH / 2; i++) {
+                                ng0 = __funnelshift_l(__float_as_uint(thr - gv[i]), ng0, 1);
+                                ng1 = __funnelshift_l(__float_as_uint(thr - gv[NGH / 2 + i]), ng1, 1);
+                            }
+                            ng = (ng0 << (NGH / 2)) | ng1;
                         }
-                        const uint32_t ng = (ng0 << (NGH / 2)) | ng1;
-#endif
                         const uint32_t gm = ~ng & ((1u << NGH) - 1u);
                         if (cnt_off == LIST_END) {      // full: drop entries the tighter threshold excludes
                             uint32_t wpos = 0;
@@ -987,6 +1139,31 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
 #endif
                 uint32_t va[16], vb[16];
                 float gv[NGH];
+                if (BN == 96) {
+                    // the three loads of the half job, the slot handed back as soon as they have landed, then the minima
+                    // (with groups of 4 ptxas keeps all 48 columns in flight; with groups of 8 / 16 it sinks each load
+                    // below the reduction of the one before it, which keeps fewer columns live and costs nothing: see TcSmem)
+                    uint32_t vc[16];
+                    tmem_ld16_async(tsrc, va);
+                    tmem_ld16_async(tsrc + 16, vb);
+                    tmem_ld16_async(tsrc + 32, vc);
+                    tmem_wait_ld16(va);
+                    tmem_wait_ld16(vb);
+                    tmem_wait_ld16(vc);
+                    tc_fence_before();                  // this half of the slot is read: hand it back to the MMA warp
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(acc_full + ACC_E_OFF);
+                    if (DBG) { dump(va, code_s); dump(vb, code_s + 16); dump(vc, code_s + 32); }
+                    groups(va, gv);
+                    groups(vb, gv + GPC);
+                    groups(vc, gv + 2 * GPC);
+                    process(gv, (uint32_t)(2 * s + h));
+                    if (++par == (uint32_t)L::SPT) {
+                        par = 0;
+                        wph ^= 1u;
+                    }
+                    continue;
+                }
                 tmem_ld16_async(tsrc, va);
                 tmem_ld16_async(tsrc + 16, vb);
                 tmem_wait_ld16(va);
@@ -997,7 +1174,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                     uint32_t vc[8];
                     tmem_ld16_async(tsrc + 32, va);
                     tmem_ld8_async(tsrc + 48, vc);
-                    groups(vb, gv + 4);
+                    groups(vb, gv + GPC);
                     tmem_wait_ld16(va);
                     tmem_wait_ld8(vc);
                     tc_fence_before();                  // this half of the slot is read: hand it back to the MMA warp
@@ -1011,23 +1188,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                                 p.dbg_scores[(pair * TC_PR + lr) * p.k + code_s + 48 + jj] =
                                     __uint_as_float(vc[jj]) * (F16 ? ldexpf(1.f, -2 * p.hdr->g_exp) : 1.f);
                     }
-                    groups(va, gv + 8);
+                    groups(va, gv + 2 * GPC);
                     gv[12] = min4(vc[0], vc[1], vc[2], vc[3]);
                     gv[13] = min4(vc[4], vc[5], vc[6], vc[7]);
-                } else if (BN == 96) {
-                    tmem_ld16_async(tsrc + 32, va);
-                    groups(vb, gv + 4);
-                    tmem_wait_ld16(va);
-                    tc_fence_before();                  // this half of the slot is read: hand it back to the MMA warp
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(acc_full + ACC_E_OFF);
-                    if (DBG) dump(va, code_s + 32);
-                    groups(va, gv + 8);
                 } else {                                // BN == 64: 32 columns per thread
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(acc_full + ACC_E_OFF);
-                    groups(vb, gv + 4);
+                    groups(vb, gv + GPC);
                 }
                 process(gv, (uint32_t)(2 * s + h));
                 if (++par == (uint32_t)L::SPT) {
@@ -1064,11 +1232,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                     if (__uint_as_float(es) <= thr) {
                         const uint32_t ep = ld_shared_u32(lS + LIST_PLANE + e * LIST_STRIDE);
                         uint32_t gm = ep & 0xFFFFu;
-                        const uint32_t grp0 = (ep >> 16) * NGH;      // first group (code / 4) of the half job
-                        if ((int)(grp0 + NGH) * 4 > p.k) {           // the chunk that holds the end of the codebook
+                        const uint32_t grp0 = (ep >> 16) * NGH;      // first group (code / GS) of the half job
+                        if ((int)(grp0 + NGH) * GS > p.k) {          // the chunk that holds the end of the codebook
                             uint32_t keep = 0;
                             for (int bit = 0; bit < NGH; bit++)
-                                if ((int)(grp0 + (NGH - 1 - bit)) * 4 < p.k) keep |= 1u << bit;
+                                if ((int)(grp0 + (NGH - 1 - bit)) * GS < p.k) keep |= 1u << bit;
                             gm &= keep;
                         }
                         mk[e] = gm;
@@ -1173,7 +1341,7 @@ __global__ void __launch_bounds__(128)
 k_assign_fallback_finish(const float *__restrict__ x, const float *__restrict__ w, const int64_t *__restrict__ rows,
                          int d, const TcHeader *hdr, const unsigned int *__restrict__ fb_list,
                          const unsigned long long *__restrict__ fb_best, float *__restrict__ out_dist,
-                         int64_t *__restrict__ out_idx, float *__restrict__ acc, int stride)
+                         int64_t *__restrict__ out_idx, float *__restrict__ acc, int stride, int *__restrict__ prev)
 {
     const int lane = threadIdx.x & 31;
     const unsigned int count = hdr->fb_count;
@@ -1185,6 +1353,7 @@ k_assign_fallback_finish(const float *__restrict__ x, const float *__restrict__ 
         if (lane == 0) {
             if (out_idx) out_idx[gi] = bj;
             if (out_dist) out_dist[gi] = __uint_as_float((unsigned int)(best >> 32));
+            if (prev) prev[gi] = bj;
         }
         if (acc) {
             const int64_t src = rows ? rows[gi] : gi;
@@ -1199,8 +1368,8 @@ k_assign_fallback_finish(const float *__restrict__ x, const float *__restrict__ 
 static inline size_t al256(size_t v) { return (v + 255) & ~(size_t)255; }
 
 struct TcLayout {
-    size_t off_mu, off_bimg, off_cbp, off_fb, off_fbbest, off_parts, total;
-    int dp, nc, dpc, k_pad, bn;
+    size_t off_mu, off_bimg, off_cbp, off_fb, off_fbbest, off_prev, off_reg, off_parts, total;
+    int dp, nc, dpc, kq, k_pad, bn;
 };
 
 // Screening arithmetic: fp16 operands (kind::f16) by default, C3VQ_SCREEN=tf32 selects kind::tf32 (developer A/B knob;
@@ -1211,12 +1380,20 @@ static bool screen_f16()
     return !(e && (e[0] == 't' || e[0] == 'T'));
 }
 
+// C3VQ_SEEDS=0: developer A/B knob, the running minima start unseeded (results are identical either way)
+static bool seeds_enabled()
+{
+    const char *e = getenv("C3VQ_SEEDS");
+    return !(e && e[0] == '0');
+}
+
 static TcLayout tc_layout(int64_t n, int d, int k, bool f16)
 {
     TcLayout l;
     l.dp = tc_dp(d, f16);
     l.nc = tc_nc(d, f16);
     l.dpc = (d + 3) & ~3;
+    l.kq = ((k > 0 ? k : 1) + 7) & ~7;
     l.bn = f16 ? tc_bn_f16(l.dp) : tc_bn(l.dp);
     l.k_pad = (k + l.bn - 1) / l.bn * l.bn;
     if (l.k_pad == 0) l.k_pad = l.bn;
@@ -1226,11 +1403,15 @@ static TcLayout tc_layout(int64_t n, int d, int k, bool f16)
     l.off_bimg = o;
     o += al256((size_t)l.k_pad * l.dp * sizeof(float));      // sized for tf32 elements; the fp16 image needs half
     l.off_cbp = o;
-    o += al256((size_t)(k > 0 ? k : 1) * l.dpc * sizeof(float));
+    o += al256((size_t)l.kq * l.dpc * sizeof(float));
     l.off_fb = o;
     o += al256((size_t)(n > 0 ? n : 1) * sizeof(unsigned int));
     l.off_fbbest = o;
     o += al256((size_t)(n > 0 ? n : 1) * sizeof(unsigned long long));
+    l.off_prev = o;
+    o += al256((size_t)(n > 0 ? n : 1) * sizeof(int));
+    l.off_reg = o;
+    o += al256((size_t)(k > 0 ? k : 1));
     l.off_parts = o;
     if (n >= TC_ACC_PARTS_MIN_ROWS) o += al256((size_t)TC_ACC_PARTS * (size_t)(k > 0 ? k : 1) * acc_stride(d) * sizeof(float));
     l.total = o;
@@ -1304,14 +1485,14 @@ int launch_assign_tc(const float *x, const float *w, const int64_t *rows, int64_
     k_tc_prep_mean<<<(k + TC_PREP_CODES - 1) / TC_PREP_CODES, 256, 0, s>>>(codebook, k, d, hdr);
     C3VQ_LAUNCH_CHECK("k_tc_prep_mean");
     k_tc_prep_image<<<(l.k_pad + 127) / 128, 128, 0, s>>>(codebook, k, l.k_pad, d, l.dp, l.nc, l.dpc, l.bn, f16 ? 1 : 0,
-                                                        hdr, mu, bimg, cbp);
+                                                        hdr, mu, bimg, cbp, l.kq, (uint8_t *)(base + l.off_reg));
     C3VQ_LAUNCH_CHECK("k_tc_prep_image");
 
     TcParams p{};
     p.x = x; p.w = w; p.rows = rows; p.n = n; p.d = d; p.k = k;
     p.nsteps = l.k_pad / l.bn;
     p.npairs = (n + TC_PR - 1) / TC_PR;
-    p.bimg = bimg; p.cbp = cbp; p.dpc = l.dpc; p.mu = mu; p.hdr = hdr;
+    p.bimg = bimg; p.cbp = cbp; p.dpc = l.dpc; p.kq = l.kq; p.mu = mu; p.hdr = hdr;
     p.out_dist = out_dist; p.out_idx = out_idx; p.acc = acc; p.acc_stride = acc_stride(d);
     p.acc_parts = 1; p.acc_part_elems = 0;
     float *parts = nullptr;
@@ -1324,12 +1505,17 @@ int launch_assign_tc(const float *x, const float *w, const int64_t *rows, int64_
     p.fb_list = fb;
     p.fb_best = (unsigned long long *)(base + l.off_fbbest);
     p.dbg_scores = dbg_scores; p.dbg_norm2 = dbg_norm2; p.dbg_band = dbg_band;
+    // widths of one fp16 K step (d <= 13) record groups of 16 codes: their list path is cheap, a seed would not pay
+    p.prev = (rows == nullptr && dbg_scores == nullptr && l.dp > 16 && seeds_enabled()) ? (int *)(base + l.off_prev) : nullptr;
+    p.reg = (const uint8_t *)(base + l.off_reg);
     p.gamma2 = 2.1f * (float)(d + 3) * 5.9604644775390625e-8f;      // 2.1 (d+3) 2^-24
     const int sms = sm_count();
     const int grid = (int)(p.npairs < sms ? p.npairs : sms);
 
     int rc;
-#ifdef C3VQ_TC_SINGLE   // developer build: one instantiation only (fast compile, SASS inspection)
+#if defined(C3VQ_TC_SINGLE_D7)   // developer build: one instantiation only (fast compile, SASS inspection)
+    rc = launch_tc_t<16, 7, true>(p, grid, s);
+#elif defined(C3VQ_TC_SINGLE)
     rc = launch_tc_t<48, 45, true>(p, grid, s);
 #else
     if (f16) {
@@ -1377,7 +1563,7 @@ int launch_assign_tc(const float *x, const float *w, const int64_t *rows, int64_
         k_assign_fallback_scan<<<sms * 4, 128, 0, s>>>(x, rows, d, codebook, k, hdr, fb, p.fb_best);
         C3VQ_LAUNCH_CHECK("k_assign_fallback_scan");
         k_assign_fallback_finish<<<sms, 128, 0, s>>>(x, w, rows, d, hdr, fb, p.fb_best, out_dist, out_idx, acc,
-                                                     acc_stride(d));
+                                                     acc_stride(d), p.prev);
         C3VQ_LAUNCH_CHECK("k_assign_fallback_finish");
     }
     if (parts != nullptr) {

@@ -76,6 +76,12 @@ __device__ __forceinline__ uint32_t ld_shared_u32(uint32_t addr)
     return v;
 }
 
+// L1 prefetch of a global line (the re-rank fetches its codebook rows one round ahead)
+__device__ __forceinline__ void prefetch_l1(const void *ptr)
+{
+    asm volatile("prefetch.global.L1 [%0];" ::"l"(ptr));
+}
+
 // for waiters that are not on the critical path (producers running ahead): do not burn issue slots
 __device__ __forceinline__ void mbar_wait_backoff(uint32_t bar, uint32_t parity)
 {

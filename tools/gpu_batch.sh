@@ -1,22 +1,16 @@
 #!/bin/bash
 mkdir -p gpurun_out
-T=${TAG:-r2m}
+T=${TAG:-r2s}
 O=gpurun_out
-timeout 300 python -m pytest tests/test_gpu_parity.py -x -q -m gpu -k "assign_bit_exact" > $O/${T}_pytest_first.log 2>&1
-echo "== first (BN=112 sanity): rc=$?"; tail -5 $O/${T}_pytest_first.log
-if tail -1 $O/${T}_pytest_first.log | grep -q passed; then
-  timeout 1800 python -m pytest tests -x -q -m gpu > $O/${T}_pytest_gpu.log 2>&1
-  echo "== pytest"; tail -6 $O/${T}_pytest_gpu.log
-  for d in 45 48 7; do timeout 300 python tools/tc_profile_run.py 5800000 $d 8 > $O/${T}_tc_run_d$d.txt 2>&1; echo "== main (BN112, two chains) d$d"; tail -8 $O/${T}_tc_run_d$d.txt; done
-  for d in 45 48 7; do C3VQ_LIB=c3dgs_b200/libc3vq_vA.so timeout 300 python tools/tc_profile_run.py 5800000 $d 8 > $O/${T}_tc_run_vA_d$d.txt 2>&1; echo "== vA (BN112, one chain) d$d"; tail -8 $O/${T}_tc_run_vA_d$d.txt; done
-  timeout 900 python bench.py --steps 5 --warmup 3 > $O/${T}_bench.json 2> $O/${T}_bench.err
-  python - <<PY
-import json
-j = json.load(open("gpurun_out/${T}_bench.json"))
-print("ms/step", round(j["ms_per_step"], 2), "assign", round(j["roofline"]["kernel_ms"], 3), "e2e", round(j["e2e"]["ms_per_step"], 2))
-for k in ("shape7", "cov6_trace_normalised", "sh48", "iid45"):
-    v = j["extras"][k]; print(k, round(v["ms_per_step"], 2), round(v["assign_ms"], 3))
-PY
-  tail -n 3 $O/${T}_bench.err
-fi
-for d in 45 48 7; do C3VQ_LIB=c3dgs_b200/libc3vq_vB.so timeout 300 python tools/tc_profile_run.py 5800000 $d 8 > $O/${T}_tc_run_vB_d$d.txt 2>&1; echo "== vB (BN96, two chains) d$d"; tail -8 $O/${T}_tc_run_vB_d$d.txt; done
+timeout 900 python -m pytest tests/test_gpu_parity.py -x -q -m gpu > $O/${T}_pytest_parity.log 2>&1
+echo "== parity rc=$?: $(tail -1 $O/${T}_pytest_parity.log)"
+for sd in 1 0; do
+  for d in 45 48 7; do
+    C3VQ_SEEDS=$sd timeout 300 python tools/tc_profile_run.py 5800000 $d 10 > $O/${T}_tc_run_seeds${sd}_d$d.txt 2>&1
+    echo "-- seeds=$sd d$d"; tail -9 $O/${T}_tc_run_seeds${sd}_d$d.txt | awk '{print $1,$2,$4}' | tr '\n' ' '; echo
+  done
+done
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_assign_tc -s 5 -c 1 -o $O/${T}_assign_tc python tools/tc_profile_run.py 5800000 45 7 > $O/${T}_ncu.log 2>&1
+echo "ncu rc=$?"
+ncu -i $O/${T}_assign_tc.ncu-rep --page source --csv > $O/${T}_assign_tc_source.csv 2>/dev/null
+ncu -i $O/${T}_assign_tc.ncu-rep --page raw --csv > $O/${T}_assign_tc_raw.csv 2>/dev/null
