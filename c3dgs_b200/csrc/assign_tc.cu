@@ -576,20 +576,24 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             const uint32_t dlo0 = ((smem_u32(sB) & 0x3FFFFu) >> 4) | (((L::LBO_B >> 4) & 0x3FFFu) << 16);
             const uint32_t a_col = L::ACOL + t * L::ACOLS;
             uint32_t pi = 0, stage = 0, phase = 0, dlo = dlo0;
-            uint32_t sk = 0, sph = 1;                 // slot of the tile used by this step, parity of its ACC_EMPTY wait
+            // every pass starts on the tile's first slot (the drain warps unroll their loop over the slots); with an odd
+            // number of steps the slots are used unequally often, so each keeps its own ACC_EMPTY phase bit (bit sk)
+            uint32_t sk = 0, sphm = (1u << L::SPT) - 1u;
             PROF_DECL;
             for (int64_t pair = blockIdx.x; pair < p.npairs; pair += gridDim.x, pi++) {
                 PROF(0);
                 mbar_wait(A_FULL, pi & 1);
                 PROF(1);   // prof[8+1]: MMA wait A_FULL
                 tc_fence_after();
+                sk = 0;
                 for (int s = 0; s < nsteps; s++) {
                     PROF(0);
                     mbar_wait(B_FULL(stage), phase);
                     PROF(2);   // prof[8+2]: MMA wait B_FULL
                     // the tile owns L::SPT consecutive slots and cycles through them step by step
                     const uint32_t sl = L::SPT * t + sk;
-                    mbar_wait(ACC_EMPTY(sl), sph);
+                    mbar_wait(ACC_EMPTY(sl), (sphm >> sk) & 1u);
+                    sphm ^= 1u << sk;
                     PROF(3);   // prof[8+3]: MMA wait ACC_EMPTY
                     tc_fence_after();
                     if (elect_one()) {
@@ -605,10 +609,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                     __syncwarp();
                     PROF(4);   // prof[8+4]: MMA issue of one job (KSTEPS instructions + commits)
                     dlo += DLO_STAGE;
-                    if (++sk == (uint32_t)L::SPT) {
-                        sk = 0;
-                        sph ^= 1u;
-                    }
+                    if (++sk == (uint32_t)L::SPT) sk = 0;
                     if (++stage == (uint32_t)S) {
                         stage = 0;
                         phase ^= 1;
@@ -695,64 +696,85 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
 #endif
             const uint32_t *queue = sQueue + qb * TC_QCAP;
             constexpr int GS = L::GS;                                       // lanes per queue item = codes per group
-            // the codebook rows come from the L2 (a microsecond under this kernel's load) and a round is a serial chain
-            // behind them: every thread asks for the row of its NEXT round's code while it works on this round's
+            // Four lanes per queue item, each with GS / 4 codes of the group (lane i: codes i, i + 4, ...: the four lanes
+            // read consecutive 16-byte pieces of the column-major copy).  With groups of 16 a lane runs four independent
+            // distance chains; one lane per code would make a round of the loop four times as many serial L2 round trips.
+            constexpr int CPL = GS / 4;
+            static_assert(CPL == 1 || DP <= 16, "several codes per lane only for the narrow widths (registers)");
+            // the codebook pieces come from the L2 (a microsecond under this kernel's load) and a round is a serial chain
+            // behind them: every thread asks for the lines of its NEXT round's item while it works on this round's
             auto fetch_ahead = [&](uint32_t u) {
                 if (u < nq) {
-                    const int code = (int)(queue[u] & 0xFFFFu) * GS + (lane & (GS - 1));
-                    if (code < p.k) {        // the lanes of a group share the lines: lane i asks for columns i, i + GS, ...
-                        const float4 *cp = reinterpret_cast<const float4 *>(p.cbp) + code;
-                        for (int c4 = lane & (GS - 1); c4 < p.dpc / 4; c4 += GS) prefetch_l1(cp + (size_t)c4 * p.kq);
+                    const int code = (int)(queue[u] & 0xFFFFu) * GS;
+                    const float4 *cp = reinterpret_cast<const float4 *>(p.cbp) + code;
+                    if (CPL == 1) {          // 64 bytes per column of four: lane i asks for columns i, i + 4, ...
+                        for (int c4 = lane & 3; c4 < p.dpc / 4; c4 += 4) prefetch_l1(cp + (size_t)c4 * p.kq);
+                    } else {                 // 16 * CPL bytes per column of four: one line per lane
+                        const int c4 = (lane & 3) / (CPL / 2), part = (lane & 3) % (CPL / 2);
+                        if (c4 < p.dpc / 4) prefetch_l1(cp + (size_t)c4 * p.kq + 8 * part);
                     }
                 }
             };
-            fetch_ahead(ptid / GS);
+            fetch_ahead(ptid >> 2);
             sBest[ptid] = ((unsigned long long)__float_as_uint(FLT_MAX)) << 32;      // (FLT_MAX, code 0)
             named_bar_sync(1, TC_PR);
-            const uint32_t gmask = ((1u << GS) - 1u) << (lane & ~(GS - 1));
-            for (uint32_t u = ptid / GS; u < nq; u += TC_PR / GS) {
-                fetch_ahead(u + TC_PR / GS);
+            const uint32_t gmask = 0xFu << (lane & ~3);
+            for (uint32_t u = ptid >> 2; u < nq; u += TC_PR / 4) {
+                fetch_ahead(u + TC_PR / 4);
                 const uint32_t item = queue[u];
                 const int lr = item >> 16;
-                const int code = (int)(item & 0xFFFFu) * GS + (lane & (GS - 1));
+                const int code0 = (int)(item & 0xFFFFu) * GS + (lane & 3);
                 const float *xg = xq + lr * L::XS;
+                const float4 *cp = reinterpret_cast<const float4 *>(p.cbp) + code0;
+                const size_t kq = (size_t)p.kq;
                 unsigned long long key = ~0ull;
-                if (code < p.k) {
-                    const float4 *cp = reinterpret_cast<const float4 *>(p.cbp) + code;
-                    const size_t kq = (size_t)p.kq;
-                    float a = 0.f;
-                    if (DCONST > 0) {
-                        float4 cv[DCONST > 0 ? (DCONST + 3) / 4 : 1];
+                float a[CPL];
 #pragma unroll
-                        for (int c4 = 0; c4 < (DCONST + 3) / 4; c4++) cv[c4] = __ldg(cp + c4 * kq);
+                for (int j = 0; j < CPL; j++) a[j] = 0.f;
+                if (DCONST > 0) {
+                    constexpr int NF4 = DCONST > 0 ? (DCONST + 3) / 4 : 1;
+                    float4 cv[CPL][NF4];
 #pragma unroll
-                        for (int c4 = 0; c4 < (DCONST + 3) / 4; c4++) {
+                    for (int j = 0; j < CPL; j++)
+#pragma unroll
+                        for (int c4 = 0; c4 < NF4; c4++)
+                            cv[j][c4] = code0 + 4 * j < p.k ? __ldg(cp + c4 * kq + 4 * j) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                    for (int c4 = 0; c4 < NF4; c4++) {
+#pragma unroll
+                        for (int j = 0; j < CPL; j++) {
                             float df;
-                            if (4 * c4 + 0 < D) { df = xg[4 * c4 + 0] - cv[c4].x; a = fmaf(df, df, a); }
-                            if (4 * c4 + 1 < D) { df = xg[4 * c4 + 1] - cv[c4].y; a = fmaf(df, df, a); }
-                            if (4 * c4 + 2 < D) { df = xg[4 * c4 + 2] - cv[c4].z; a = fmaf(df, df, a); }
-                            if (4 * c4 + 3 < D) { df = xg[4 * c4 + 3] - cv[c4].w; a = fmaf(df, df, a); }
-                        }
-                    } else {
-                        for (int c4 = 0; c4 < p.dpc / 4; c4++) {
-                            const float4 cv = __ldg(cp + c4 * kq);
-                            float df;
-                            if (4 * c4 + 0 < D) { df = xg[4 * c4 + 0] - cv.x; a = fmaf(df, df, a); }
-                            if (4 * c4 + 1 < D) { df = xg[4 * c4 + 1] - cv.y; a = fmaf(df, df, a); }
-                            if (4 * c4 + 2 < D) { df = xg[4 * c4 + 2] - cv.z; a = fmaf(df, df, a); }
-                            if (4 * c4 + 3 < D) { df = xg[4 * c4 + 3] - cv.w; a = fmaf(df, df, a); }
+                            if (4 * c4 + 0 < D) { df = xg[4 * c4 + 0] - cv[j][c4].x; a[j] = fmaf(df, df, a[j]); }
+                            if (4 * c4 + 1 < D) { df = xg[4 * c4 + 1] - cv[j][c4].y; a[j] = fmaf(df, df, a[j]); }
+                            if (4 * c4 + 2 < D) { df = xg[4 * c4 + 2] - cv[j][c4].z; a[j] = fmaf(df, df, a[j]); }
+                            if (4 * c4 + 3 < D) { df = xg[4 * c4 + 3] - cv[j][c4].w; a[j] = fmaf(df, df, a[j]); }
                         }
                     }
-                    // distances are sums of squares from +0: non-negative or NaN; as unsigned bit patterns
-                    // smaller distance <=> smaller key, NaN/inf sort above FLT_MAX, ties -> lower code
-                    key = ((unsigned long long)__float_as_uint(a) << 32) | (unsigned int)code;
-                }
+                } else {
+                    for (int c4 = 0; c4 < p.dpc / 4; c4++) {
 #pragma unroll
-                for (int sh = 1; sh < GS; sh <<= 1) {
-                    const unsigned long long o = __shfl_xor_sync(gmask, key, sh);
-                    key = o < key ? o : key;
+                        for (int j = 0; j < CPL; j++) {
+                            const float4 cv = code0 + 4 * j < p.k ? __ldg(cp + c4 * kq + 4 * j) : make_float4(0.f, 0.f, 0.f, 0.f);
+                            float df;
+                            if (4 * c4 + 0 < D) { df = xg[4 * c4 + 0] - cv.x; a[j] = fmaf(df, df, a[j]); }
+                            if (4 * c4 + 1 < D) { df = xg[4 * c4 + 1] - cv.y; a[j] = fmaf(df, df, a[j]); }
+                            if (4 * c4 + 2 < D) { df = xg[4 * c4 + 2] - cv.z; a[j] = fmaf(df, df, a[j]); }
+                            if (4 * c4 + 3 < D) { df = xg[4 * c4 + 3] - cv.w; a[j] = fmaf(df, df, a[j]); }
+                        }
+                    }
                 }
-                if ((lane & (GS - 1)) == 0) atomicMin(&sBest[lr], key);
+                // distances are sums of squares from +0: non-negative or NaN; as unsigned bit patterns
+                // smaller distance <=> smaller key, NaN/inf sort above FLT_MAX, ties -> lower code
+#pragma unroll
+                for (int j = 0; j < CPL; j++) {
+                    const unsigned long long kj = ((unsigned long long)__float_as_uint(a[j]) << 32) | (unsigned int)(code0 + 4 * j);
+                    if (code0 + 4 * j < p.k && kj < key) key = kj;
+                }
+                unsigned long long o = __shfl_xor_sync(gmask, key, 1);
+                key = o < key ? o : key;
+                o = __shfl_xor_sync(gmask, key, 2);
+                key = o < key ? o : key;
+                if ((lane & 3) == 0) atomicMin(&sBest[lr], key);
             }
             named_bar_sync(1, TC_PR);
             st_cands += (unsigned long long)GS * nq;      // counted once per thread, divided out below
@@ -1012,8 +1034,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
         constexpr int GS = L::GS;                       // codes per candidate group
         constexpr int NGH = L::NG;                      // groups per half job (BN / 2 codes)
         constexpr int GPC = 16 / GS;                    // groups per 16-column TMEM load
-        const int dw = warp - TC_DRAIN_WARP0;           // 0..15
-        const int q = warp & 3;                         // TMEM lane quarter this warp may access
+        // the warp index through a shuffle: the compiler then knows that everything derived from it (TMEM address,
+        // barrier addresses) is warp-uniform and keeps it in uniform registers instead of recomputing it per step
+        const int warp_u = __shfl_sync(0xffffffffu, warp, 0);
+        const int dw = warp_u - TC_DRAIN_WARP0;         // 0..15
+        const int q = warp_u & 3;                       // TMEM lane quarter this warp may access
         const int t = (dw >> 2) & 1;                    // row tile
         const int h = dw >> 3;                          // column half of every slot served by this warp
         const int lr = t * TC_BM + q * 32 + lane;       // local row 0..255 (shared with the other half's thread)
@@ -1025,7 +1050,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
         const uint32_t lS = smem_u32(listS);            // the payload plane is LIST_PLANE bytes further
         constexpr uint32_t LIST_STRIDE = TC_DT * 4, LIST_END = L::LCAP * LIST_STRIDE, LIST_PLANE = LIST_END;
         uint32_t pi = 0;
-        uint32_t par = 0, wph = 0;                      // slot of the tile read by this step, its phase parity
+        uint32_t wphm = 0;                              // phase parity of the tile's slots (bit = slot)
         PROF_DECL;
         for (int64_t pair = blockIdx.x; pair < p.npairs; pair += gridDim.x, pi++) {
             PROF(0);
@@ -1120,10 +1145,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             // step's barrier with a try_wait right after handing this step's slot back, to hide the ~90 cycles a
             // successful wait takes behind the min reduction: 3.63 ms per iteration against 3.46 ms without the probe
             // (the extra try_wait + predicate per step cost more issue slots than the hidden latency gave back)
-            for (int s = 0; s < nsteps; s++) {
+            // unrolled over the tile's slots: slot, TMEM address and barrier address of a step are constants of the body
+            for (int s0 = 0; s0 < nsteps; s0 += L::SPT) {
+#pragma unroll
+              for (int par = 0; par < L::SPT; par++) {
+                const int s = s0 + par;
+                if (s >= nsteps) break;
                 const uint32_t acc_full = acc_full0 + 8u * par, tsrc = tsrc0 + par * BN;
                 PROF(4);   // prof[24+4]: drain (LDTM + min + lists)
-                mbar_wait_hint(acc_full, wph);
+                mbar_wait_hint(acc_full, (wphm >> par) & 1u);
+                wphm ^= 1u << par;
                 PROF(3);   // prof[24+3]: drain wait ACC_FULL
                 tc_fence_after();
                 const int code_s = s * BN + h * (BN / 2);
@@ -1131,10 +1162,6 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(acc_full + ACC_E_OFF);
-                if (++par == (uint32_t)L::SPT) {
-                    par = 0;
-                    wph ^= 1u;
-                }
                 continue;
 #endif
                 uint32_t va[16], vb[16];
@@ -1158,10 +1185,6 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                     groups(vb, gv + GPC);
                     groups(vc, gv + 2 * GPC);
                     process(gv, (uint32_t)(2 * s + h));
-                    if (++par == (uint32_t)L::SPT) {
-                        par = 0;
-                        wph ^= 1u;
-                    }
                     continue;
                 }
                 tmem_ld16_async(tsrc, va);
@@ -1198,10 +1221,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                     groups(vb, gv + GPC);
                 }
                 process(gv, (uint32_t)(2 * s + h));
-                if (++par == (uint32_t)L::SPT) {
-                    par = 0;
-                    wph ^= 1u;
-                }
+              }
             }
             const int cnt = (int)(cnt_off / LIST_STRIDE);
             PROF(4);
