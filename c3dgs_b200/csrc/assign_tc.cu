@@ -743,13 +743,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                             cv[j][c4] = code0 + 4 * j < p.k ? __ldg(cp + c4 * kq + 4 * j) : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
                     for (int c4 = 0; c4 < NF4; c4++) {
+                        const float4 xv = reinterpret_cast<const float4 *>(xg)[c4];     // 16-byte aligned rows
 #pragma unroll
                         for (int j = 0; j < CPL; j++) {
                             float df;
-                            if (4 * c4 + 0 < D) { df = xg[4 * c4 + 0] - cv[j][c4].x; a[j] = fmaf(df, df, a[j]); }
-                            if (4 * c4 + 1 < D) { df = xg[4 * c4 + 1] - cv[j][c4].y; a[j] = fmaf(df, df, a[j]); }
-                            if (4 * c4 + 2 < D) { df = xg[4 * c4 + 2] - cv[j][c4].z; a[j] = fmaf(df, df, a[j]); }
-                            if (4 * c4 + 3 < D) { df = xg[4 * c4 + 3] - cv[j][c4].w; a[j] = fmaf(df, df, a[j]); }
+                            if (4 * c4 + 0 < D) { df = xv.x - cv[j][c4].x; a[j] = fmaf(df, df, a[j]); }
+                            if (4 * c4 + 1 < D) { df = xv.y - cv[j][c4].y; a[j] = fmaf(df, df, a[j]); }
+                            if (4 * c4 + 2 < D) { df = xv.z - cv[j][c4].z; a[j] = fmaf(df, df, a[j]); }
+                            if (4 * c4 + 3 < D) { df = xv.w - cv[j][c4].w; a[j] = fmaf(df, df, a[j]); }
                         }
                     }
                 } else {
@@ -821,10 +822,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                     float *xw = sX + (qb * TC_PR + pw * 32) * L::XS;
                     const float *ww = sW + qb * TC_PR + pw * 32;
                     const unsigned int key = status == ROW_OK ? (unsigned int)bj : 0x80000000u + (unsigned int)lane;
-                    const int leader = __ffs(__match_any_sync(0xffffffffu, key)) - 1;   // lowest lane with this codeword
-                    if (__all_sync(0xffffffffu, leader == lane)) {
-                        // 32 distinct codewords (the usual case once the codebook is in use): nothing to combine, the
-                        // rows are scaled as float4 (an accumulator row = the first AS / 4 float4 of a staged row)
+                    const unsigned int same = __match_any_sync(0xffffffffu, key);          // lanes (rows) with this codeword
+                    const int leader = __ffs(same) - 1;                                   // the lowest of them
+                    const unsigned int leaders = __ballot_sync(0xffffffffu, leader == lane);
+                    {
+                        // every row is scaled in place as float4 (an accumulator row = the first AS / 4 float4 of a staged
+                        // row): once the codebook is in use the 32 codewords of a warp are nearly always distinct and
+                        // this is all there is to do
                         const int AS4 = (DCONST > 0 ? ((DCONST + 4) & ~3) : p.acc_stride) >> 2;
 #pragma unroll 4
                         for (int i = lane; i < 32 * AS4; i += 32) {
@@ -844,18 +848,19 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                             }
                             *q = v;
                         }
-                    } else
-#pragma unroll 8
-                    for (int r = 0; r < 32; r++) {
-                        const float wv = ww[r];
-                        const int dst = __shfl_sync(0xffffffffu, leader, r);          // <= r, warp-uniform
+                        // rows that are not the first of their codeword are added into that first one, in row order
+                        // (lanes over columns; sources are never destinations)
+                        if (leaders != 0xffffffffu) {
+                            __syncwarp();
+                            for (unsigned int nl = ~leaders; nl; nl &= nl - 1) {
+                                const int r = __ffs(nl) - 1;
+                                const int dst = __shfl_sync(0xffffffffu, leader, r);
 #pragma unroll
-                        for (int h = 0; h < NH; h++) {
-                            const int col = lane + 32 * h;
-                            if (col < p.acc_stride) {
-                                const float v = col < D ? __fmul_rn(xw[r * L::XS + col], wv) : (col == D ? wv : 0.f);
-                                if (dst == r) xw[r * L::XS + col] = v;
-                                else xw[dst * L::XS + col] = __fadd_rn(xw[dst * L::XS + col], v);
+                                for (int h = 0; h < NH; h++) {
+                                    const int col = lane + 32 * h;
+                                    if (col < p.acc_stride)
+                                        xw[dst * L::XS + col] = __fadd_rn(xw[dst * L::XS + col], xw[r * L::XS + col]);
+                                }
                             }
                         }
                     }
@@ -905,28 +910,56 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             if (seed_ok) seed_reg = p.reg[pj];
             uint32_t av[L::ACOLS];
             float X = 0.f;                       // |x'|^2 of the rounded, centred row (scaled by gam^2) -> error band
-            if (F16) {
+            // The row and the centre are read as float4 (rows are 16-byte aligned, stride XS / 4 odd: conflict free).
+            // Known widths fuse the seed into the same pass over the row: sa = sum c'(c' - 2x') = |c'|^2 - 2 x'.c' in fp32
+            // on the centred operands, the score of the previous winner (see below); its codebook pieces were asked
+            // for before the loop.  Columns past D of the staged row hold leftovers of the previous sums and are masked.
+            constexpr int NF4 = DCONST > 0 ? (DCONST + 3) / 4 : 1;
+            constexpr bool SEED_FUSED = DCONST > 0;
+            float4 scv[NF4];
+            float sa = 0.f;
+            if (SEED_FUSED) {
 #pragma unroll
-                for (int kk = 0; kk < DP; kk++) {
-                    // 256 against the three norm pieces, 0 beyond; two elements per 32-bit column, even K in the low half
-                    uint32_t hb = (kk < D + 3) ? 0x5C00u : 0u;
-                    if (kk < D) {
-                        const __half h = __float2half_rn((xs_w[lane * L::XS + kk] - sMu[kk]) * gam);
-                        const float v = __half2float(h);
-                        X = fmaf(v, v, X);
-                        hb = (uint32_t)__half_as_ushort(h);
-                    }
-                    if (kk & 1) av[kk >> 1] |= hb << 16; else av[kk >> 1] = hb;
+                for (int c4 = 0; c4 < NF4; c4++)
+                    scv[c4] = seed_ok ? __ldg(seed_row + c4 * (size_t)p.kq) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+            const float4 *xrow4 = reinterpret_cast<const float4 *>(xs_w + lane * L::XS);
+            const float4 *mu4 = reinterpret_cast<const float4 *>(sMu);
+#pragma unroll
+            for (int c4 = 0; c4 < DP / 4; c4++) {
+                float xe[4] = {0.f, 0.f, 0.f, 0.f}, me[4] = {0.f, 0.f, 0.f, 0.f}, ce[4] = {0.f, 0.f, 0.f, 0.f};
+                if (4 * c4 < D) {
+                    const float4 xv = xrow4[c4], mv = mu4[c4];
+                    xe[0] = xv.x; xe[1] = xv.y; xe[2] = xv.z; xe[3] = xv.w;
+                    me[0] = mv.x; me[1] = mv.y; me[2] = mv.z; me[3] = mv.w;
+                    if (SEED_FUSED && c4 < NF4) { ce[0] = scv[c4 < NF4 ? c4 : 0].x; ce[1] = scv[c4 < NF4 ? c4 : 0].y;
+                                                  ce[2] = scv[c4 < NF4 ? c4 : 0].z; ce[3] = scv[c4 < NF4 ? c4 : 0].w; }
                 }
-            } else {
 #pragma unroll
-                for (int kk = 0; kk < DP; kk++) {
-                    float v = (kk < D + NC) ? 1.0f : 0.f;        // 1.0 against the norm pieces, 0 beyond
-                    if (kk < D) {
-                        v = __uint_as_float(to_tf32(xs_w[lane * L::XS + kk] - sMu[kk]));
-                        X = fmaf(v, v, X);
+                for (int e = 0; e < 4; e++) {
+                    const int kk = 4 * c4 + e;
+                    if (F16) {
+                        // 256 against the three norm pieces, 0 beyond; two elements per 32-bit column, even K in the low half
+                        uint32_t hb = (kk < D + 3) ? 0x5C00u : 0u;
+                        if (kk < D) {
+                            const float xc = xe[e] - me[e];
+                            const __half h = __float2half_rn(xc * gam);
+                            const float v = __half2float(h);
+                            X = fmaf(v, v, X);
+                            hb = (uint32_t)__half_as_ushort(h);
+                            if (SEED_FUSED) { const float cc = ce[e] - me[e]; sa = fmaf(cc, cc - 2.f * xc, sa); }
+                        }
+                        if (kk & 1) av[kk >> 1] |= hb << 16; else av[kk >> 1] = hb;
+                    } else {
+                        float v = (kk < D + NC) ? 1.0f : 0.f;        // 1.0 against the norm pieces, 0 beyond
+                        if (kk < D) {
+                            const float xc = xe[e] - me[e];
+                            v = __uint_as_float(to_tf32(xc));
+                            X = fmaf(v, v, X);
+                            if (SEED_FUSED) { const float cc = ce[e] - me[e]; sa = fmaf(cc, cc - 2.f * xc, sa); }
+                        }
+                        av[kk] = __float_as_uint(v);
                     }
-                    av[kk] = __float_as_uint(v);
                 }
             }
             {
@@ -957,25 +990,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                         const float4 *cp = seed_row;
                         const size_t kq = (size_t)p.kq;
                         const float *xg = xs_w + lane * L::XS;
-                        float a = 0.f;
+                        float a = sa;
                         auto term = [&](int kk, float cvk) {
                             if (kk < D) {
                                 const float mk = sMu[kk], cc = cvk - mk;
                                 a = fmaf(cc, cc - 2.f * (xg[kk] - mk), a);
                             }
                         };
-                        if (DCONST > 0) {
-                            float4 cv[DCONST > 0 ? (DCONST + 3) / 4 : 1];
-#pragma unroll
-                            for (int c4 = 0; c4 < (DCONST + 3) / 4; c4++) cv[c4] = __ldg(cp + c4 * kq);
-#pragma unroll
-                            for (int c4 = 0; c4 < (DCONST + 3) / 4; c4++) {
-                                term(4 * c4 + 0, cv[c4].x);
-                                term(4 * c4 + 1, cv[c4].y);
-                                term(4 * c4 + 2, cv[c4].z);
-                                term(4 * c4 + 3, cv[c4].w);
-                            }
-                        } else {
+                        if (!SEED_FUSED) {
                             for (int c4 = 0; c4 < p.dpc / 4; c4++) {
                                 const float4 cv = __ldg(cp + c4 * kq);
                                 term(4 * c4 + 0, cv.x);
