@@ -78,17 +78,20 @@ __host__ __device__ constexpr int tc_bn_f16(int dp) { return 96; }
 // Candidate granularity: the drain records GROUPS of GS consecutive codes (one mask bit each) and the re-rank
 // evaluates every code of a recorded group exactly.  Larger groups mean fewer minima / mask instructions per score in
 // the drain (which bounds the kernel) and proportionally more exact distances in the re-rank (which has slack).
+// Groups of 3 (the default for the wide rows): a group minimum is ONE three-input FMNMX3, so the 48 scores of a half job
+// cost 16 + 8 minimum instructions instead of 24 + 6 with groups of 4 -- the drain is bound by the ALU pipe these run on
+// -- and a candidate group costs three exact distances instead of four.
 #ifndef C3VQ_TC_GS
-#define C3VQ_TC_GS 4
+#define C3VQ_TC_GS 3
 #endif
 #ifndef C3VQ_TC_GS_LOW
 #define C3VQ_TC_GS_LOW 16
 #endif
-#ifdef C3VQ_TC_F16_BN112
-__host__ __device__ constexpr int tc_gs(int dp) { return 4; }
-#else
-__host__ __device__ constexpr int tc_gs(int dp) { return dp <= 16 ? C3VQ_TC_GS_LOW : C3VQ_TC_GS; }
-#endif
+// (groups of 3 need a half job of 48 codes: BN = 96)
+__host__ __device__ constexpr int tc_gs(int dp, int bn)
+{
+    return bn != 96 ? 4 : (dp <= 16 ? C3VQ_TC_GS_LOW : C3VQ_TC_GS);
+}
 #ifndef C3VQ_TC_LCAP
 #define C3VQ_TC_LCAP 6
 #endif
@@ -392,9 +395,11 @@ struct TcSmem {
     static constexpr int BN = F16 ? tc_bn_f16(DP) : tc_bn(DP);                       // codes per stage / per MMA
     static constexpr int ESIZE = F16 ? 2 : 4;                              // bytes per operand element
     static constexpr int ACOLS = F16 ? DP / 2 : DP;                        // TMEM columns of one row tile's A operand
-    static constexpr int GS = tc_gs(DP);                                   // codes per candidate group (4, 8 or 16)
+    static constexpr int GS = tc_gs(DP, BN);                               // codes per candidate group (3, 4, 8 or 16)
     static constexpr int NG = BN / (2 * GS);                               // groups per drain thread and (half) job
-    static_assert(GS == 4 || GS == 8 || GS == 16, "group size");
+    static_assert(GS == 3 || GS == 4 || GS == 8 || GS == 16, "group size");
+    static constexpr int LPI = GS == 3 ? 3 : 4;                            // re-rank lanes per queue item
+    static constexpr int CPL = GS == 3 ? 1 : GS / 4;                       // codes per re-rank lane
     // Tried for the groups of 16 and dropped (round 2): group r = the 16 columns r, r + 3, r + 6, ... so that every first
     // minimum takes one column of each of the three TMEM loads and ptxas cannot sink a load below the reduction of the
     // one before it (it does with contiguous groups of 8 and 16).  5.8 M x 7: 3.35 ms against 3.41 ms for groups of 4 on
@@ -701,31 +706,34 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             // Four lanes per queue item, each with GS / 4 codes of the group (lane i: codes i, i + 4, ...: the four lanes
             // read consecutive 16-byte pieces of the column-major copy).  With groups of 16 a lane runs four independent
             // distance chains; one lane per code would make a round of the loop four times as many serial L2 round trips.
-            constexpr int CPL = GS / 4;
+            constexpr int CPL = L::CPL, LPI = L::LPI;                       // groups of 3: three lanes per item, ten items per warp
+            constexpr int IPW = 32 / LPI;                                   // items per warp and round
             static_assert(CPL == 1 || DP <= 16, "several codes per lane only for the narrow widths (registers)");
+            const int li = lane / LPI, lj = lane - li * LPI;                // item slot of this lane, lane within the item
+            const bool lane_on = li < IPW;                                  // 32 = 10 * 3 + 2: two lanes sit out
             // the codebook pieces come from the L2 (a microsecond under this kernel's load) and a round is a serial chain
             // behind them: every thread asks for the lines of its NEXT round's item while it works on this round's
             auto fetch_ahead = [&](uint32_t u) {
-                if (u < nq) {
+                if (lane_on && u < nq) {
                     const int code = (int)(queue[u] & 0xFFFFu) * GS;
                     const float4 *cp = reinterpret_cast<const float4 *>(p.cbp) + code;
-                    if (CPL == 1) {          // 64 bytes per column of four: lane i asks for columns i, i + 4, ...
-                        for (int c4 = lane & 3; c4 < p.dpc / 4; c4 += 4) prefetch_l1(cp + (size_t)c4 * p.kq);
+                    if (CPL == 1) {          // 16 * GS bytes per column of four: lane i asks for columns i, i + LPI, ...
+                        for (int c4 = lj; c4 < p.dpc / 4; c4 += LPI) prefetch_l1(cp + (size_t)c4 * p.kq);
                     } else {                 // 16 * CPL bytes per column of four: one line per lane
-                        const int c4 = (lane & 3) / (CPL / 2), part = (lane & 3) % (CPL / 2);
+                        const int c4 = lj / (CPL / 2), part = lj % (CPL / 2);
                         if (c4 < p.dpc / 4) prefetch_l1(cp + (size_t)c4 * p.kq + 8 * part);
                     }
                 }
             };
-            fetch_ahead(ptid >> 2);
+            fetch_ahead(pw * IPW + li);
             sBest[ptid] = ((unsigned long long)__float_as_uint(FLT_MAX)) << 32;      // (FLT_MAX, code 0)
             named_bar_sync(1, TC_PR);
-            const uint32_t gmask = 0xFu << (lane & ~3);
-            for (uint32_t u = ptid >> 2; u < nq; u += TC_PR / 4) {
-                fetch_ahead(u + TC_PR / 4);
+            const uint32_t gmask = ((1u << LPI) - 1u) << (li * LPI);
+            for (uint32_t u = pw * IPW + li; lane_on && u < nq; u += 8 * IPW) {
+                fetch_ahead(u + 8 * IPW);
                 const uint32_t item = queue[u];
                 const int lr = item >> 16;
-                const int code0 = (int)(item & 0xFFFFu) * GS + (lane & 3);
+                const int code0 = (int)(item & 0xFFFFu) * GS + lj;
                 const float *xg = xq + lr * L::XS;
                 const float4 *cp = reinterpret_cast<const float4 *>(p.cbp) + code0;
                 const size_t kq = (size_t)p.kq;
@@ -740,7 +748,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                     for (int j = 0; j < CPL; j++)
 #pragma unroll
                         for (int c4 = 0; c4 < NF4; c4++)
-                            cv[j][c4] = code0 + 4 * j < p.k ? __ldg(cp + c4 * kq + 4 * j) : make_float4(0.f, 0.f, 0.f, 0.f);
+                            cv[j][c4] = code0 + LPI * j < p.k ? __ldg(cp + c4 * kq + LPI * j) : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
                     for (int c4 = 0; c4 < NF4; c4++) {
                         const float4 xv = reinterpret_cast<const float4 *>(xg)[c4];     // 16-byte aligned rows
@@ -757,7 +765,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                     for (int c4 = 0; c4 < p.dpc / 4; c4++) {
 #pragma unroll
                         for (int j = 0; j < CPL; j++) {
-                            const float4 cv = code0 + 4 * j < p.k ? __ldg(cp + c4 * kq + 4 * j) : make_float4(0.f, 0.f, 0.f, 0.f);
+                            const float4 cv = code0 + LPI * j < p.k ? __ldg(cp + c4 * kq + LPI * j) : make_float4(0.f, 0.f, 0.f, 0.f);
                             float df;
                             if (4 * c4 + 0 < D) { df = xg[4 * c4 + 0] - cv.x; a[j] = fmaf(df, df, a[j]); }
                             if (4 * c4 + 1 < D) { df = xg[4 * c4 + 1] - cv.y; a[j] = fmaf(df, df, a[j]); }
@@ -770,14 +778,22 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                 // smaller distance <=> smaller key, NaN/inf sort above FLT_MAX, ties -> lower code
 #pragma unroll
                 for (int j = 0; j < CPL; j++) {
-                    const unsigned long long kj = ((unsigned long long)__float_as_uint(a[j]) << 32) | (unsigned int)(code0 + 4 * j);
-                    if (code0 + 4 * j < p.k && kj < key) key = kj;
+                    const unsigned long long kj = ((unsigned long long)__float_as_uint(a[j]) << 32) | (unsigned int)(code0 + LPI * j);
+                    if (code0 + LPI * j < p.k && kj < key) key = kj;
                 }
-                unsigned long long o = __shfl_xor_sync(gmask, key, 1);
-                key = o < key ? o : key;
-                o = __shfl_xor_sync(gmask, key, 2);
-                key = o < key ? o : key;
-                if ((lane & 3) == 0) atomicMin(&sBest[lr], key);
+                if (LPI == 4) {
+                    unsigned long long o = __shfl_xor_sync(gmask, key, 1);
+                    key = o < key ? o : key;
+                    o = __shfl_xor_sync(gmask, key, 2);
+                    key = o < key ? o : key;
+                } else {                                      // three lanes: each takes the keys of the other two
+                    const int b0 = lane - lj;
+                    const unsigned long long o1 = __shfl_sync(gmask, key, b0 + (lj + 1) % 3);
+                    const unsigned long long o2 = __shfl_sync(gmask, key, b0 + (lj + 2) % 3);
+                    key = o1 < key ? o1 : key;
+                    key = o2 < key ? o2 : key;
+                }
+                if (lj == 0) atomicMin(&sBest[lr], key);
             }
             named_bar_sync(1, TC_PR);
             st_cands += (unsigned long long)GS * nq;      // counted once per thread, divided out below
@@ -1057,7 +1073,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
         if (TC_REGS_DRAIN < 72) setmaxnreg_dec<TC_REGS_DRAIN < 72 ? TC_REGS_DRAIN : 64>();
         constexpr int GS = L::GS;                       // codes per candidate group
         constexpr int NGH = L::NG;                      // groups per half job (BN / 2 codes)
-        constexpr int GPC = 16 / GS;                    // groups per 16-column TMEM load
+        constexpr int GPC = GS == 3 ? 0 : 16 / GS;      // groups per 16-column TMEM load (groups of 3 straddle the loads)
         // the warp index through a shuffle: the compiler then knows that everything derived from it (TMEM address,
         // barrier addresses) is warp-uniform and keeps it in uniform registers instead of recomputing it per step
         const int warp_u = __shfl_sync(0xffffffffu, warp, 0);
@@ -1205,9 +1221,17 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                     __syncwarp();
                     if (lane == 0) mbar_arrive(acc_full + ACC_E_OFF);
                     if (DBG) { dump(va, code_s); dump(vb, code_s + 16); dump(vc, code_s + 32); }
-                    groups(va, gv);
-                    groups(vb, gv + GPC);
-                    groups(vc, gv + 2 * GPC);
+                    if (GS == 3) {                      // a group = three consecutive columns = one FMNMX3
+                        auto colv = [&](int c) {
+                            return __uint_as_float(c < 16 ? va[c & 15] : (c < 32 ? vb[c & 15] : vc[c & 15]));
+                        };
+#pragma unroll
+                        for (int g = 0; g < 16; g++) gv[g] = min3f(colv(3 * g), colv(3 * g + 1), colv(3 * g + 2));
+                    } else {
+                        groups(va, gv);
+                        groups(vb, gv + GPC);
+                        groups(vc, gv + 2 * GPC);
+                    }
                     process(gv, (uint32_t)(2 * s + h));
                     continue;
                 }

@@ -41,11 +41,11 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity)
         : "memory");
     return ok != 0;
 }
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
-{
-    while (!mbar_try_wait(bar, parity)) {
-    }
-}
+__device__ __forceinline__ void mbar_wait_hint(uint32_t bar, uint32_t parity);
+// every wait parks the thread in hardware (try_wait with a suspend-time hint): a bare try_wait / branch loop executed a
+// quarter of all instructions of k_assign_tc (r2x ncu source page: 16 drain warps polling A_FULL at every pass start)
+// and took the issue slots of the warps it was waiting for
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) { mbar_wait_hint(bar, parity); }
 
 #ifndef C3VQ_WAIT_HINT_NS
 #define C3VQ_WAIT_HINT_NS 20000u
