@@ -64,6 +64,43 @@ def test_assign_bit_exact_vs_oracle(L, oracle, d, n, k, exact):
     assert np.array_equal(dist.cpu().numpy().view(np.uint32), dist_o.view(np.uint32))
 
 
+@pytest.mark.parametrize("d", [45, 48])
+def test_assign_seeded_running_minima_are_harmless(L, oracle, d, monkeypatch):
+    """The tensor-core kernel seeds every row's running minimum with the row's winner of the previous call on the same
+    workspace (evaluated against the current codebook).  Whatever that previous call was, the results are the oracle's:
+    (1) the same rows and codebook again (perfect seeds), (2) a moved codebook (the k-means case), (3) unrelated rows of
+    the same shape (stale seeds that point anywhere), (4) a smaller codebook (seeds beyond k), (5) outlier / non-finite
+    codewords as previous winners, (6) seeds switched off (C3VQ_SEEDS=0)."""
+    n, k = 20011, 1024
+    x1, _, cb1 = _synth(n, d, k, seed=11)
+    x2, _, cb2 = _synth(n, d, k, seed=12, clustered=False)
+
+    def check(x, cb):
+        dist_o, idx_o = oracle.assign(x.numpy(), cb.numpy())
+        dist, idx = L.assign(x.to(DEV), cb.to(DEV))
+        assert np.array_equal(idx.cpu().numpy(), idx_o)
+        assert np.array_equal(dist.cpu().numpy().view(np.uint32), dist_o.view(np.uint32))
+        return idx_o
+
+    idx1 = check(x1, cb1)
+    check(x1, cb1)                                             # (1)
+    g = torch.Generator().manual_seed(3)
+    check(x1, (cb1 + 0.05 * torch.randn(cb1.shape, generator=g)).contiguous())     # (2)
+    check(x2, cb2)                                             # (3)
+    check(x1, cb1[:100].contiguous())                          # (4)
+    check(x1, cb1)
+    cb_bad = cb1.clone()                                       # (5): the most popular previous winners leave the screening
+    top = np.bincount(idx1, minlength=k).argsort()[::-1][:8].copy()
+    cb_bad[torch.from_numpy(top[:4])] *= 1.0e4                 # finite outliers
+    cb_bad[int(top[4])] = float("nan")
+    cb_bad[int(top[5])] = float("inf")
+    check(x1, cb_bad)
+    check(x1, cb1)
+    monkeypatch.setenv("C3VQ_SEEDS", "0")                      # (6)
+    check(x1, cb1)
+    check(x2, cb2)
+
+
 @pytest.mark.parametrize("exact", [True, False])
 def test_assign_kats(L, oracle, exact):
     g = torch.Generator().manual_seed(5)

@@ -1,0 +1,17 @@
+#!/bin/bash
+mkdir -p gpurun_out
+T=${TAG:-r3b}
+O=gpurun_out
+timeout 1800 python -m pytest tests -x -q -m gpu > $O/${T}_pytest_gpu.txt 2>&1
+echo "== pytest rc=$?: $(tail -1 $O/${T}_pytest_gpu.txt)"
+timeout 1500 python bench.py --steps 5 --warmup 3 > $O/${T}_bench.json 2> $O/${T}_bench.err
+echo "== bench rc=$?"
+python - <<PY
+import json
+j = json.load(open("gpurun_out/${T}_bench.json"))
+print("ms/step", round(j["ms_per_step"], 2), "assign", round(j["roofline"]["kernel_ms"], 3), "frac", round(j["roofline"]["frac"],3), "vs tf32", round(j["roofline"]["frac_vs_tf32_sustained_measured"],3), "e2e", round(j["e2e"]["ms_per_step"], 2))
+for k in ("shape7", "cov6_trace_normalised", "sh48", "iid45"):
+    v = j["extras"][k]; print(k, round(v["ms_per_step"], 2), round(v["assign_ms"], 3), v.get("candidates_per_row"), v.get("fallback_rows"))
+print("strong_24M", j["extras"]["strong_24M"]["ms_per_step"])
+PY
+tail -n 3 $O/${T}_bench.err
