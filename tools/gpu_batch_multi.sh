@@ -4,7 +4,6 @@ N=$1; T=$2; O=gpurun_out
 mkdir -p $O
 run() { python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 "$@"; }
 run bench.py --gpus $N --steps 5 --warmup 3 > $O/${T}_bench_${N}gpu.json 2> $O/${T}_bench_${N}gpu.err
-run bench.py --gpus $N --steps 2 --warmup 1 --impl reference > $O/${T}_bench_${N}gpu_reference_arm.json 2> $O/${T}_bench_${N}gpu_reference_arm.err
 run tools/nccl_check.py > $O/${T}_nccl_check_${N}gpu.txt 2>&1
 python - <<PY
 import json
@@ -14,4 +13,4 @@ print("parity", j["parity"])
 print("h2d", j["h2d_probe"])
 print("strong", j["extras"]["strong_24M"] if j.get("extras") else None)
 PY
-tail -n 5 $O/${T}_bench_${N}gpu.err; tail -n 4 $O/${T}_nccl_check_${N}gpu.txt; tail -c 400 $O/${T}_bench_${N}gpu_reference_arm.json
+tail -n 5 $O/${T}_bench_${N}gpu.err; tail -n 4 $O/${T}_nccl_check_${N}gpu.txt
