@@ -189,6 +189,9 @@ def test_compress_gaussians_end_to_end(L, oracle, monkeypatch):
     real_extract = splats.extract_rot_scale
     monkeypatch.setattr(splats, "extract_rot_scale", lambda cov: (seen.append(cov.clone()), real_extract(cov))[1])
     n, k = 30_000, 256
+    # compress_gaussians draws from the global generators like the reference (uniform_init on the device, the batch
+    # indices on the CPU): seeded here so that the outcome does not depend on which tests ran before
+    torch.manual_seed(20250)
     scene, cimp, gimp = _scene(n)
     orig_feats = scene.get_features.clone()
     orig_cov = scene.get_normalized_covariance().clone()
@@ -221,7 +224,10 @@ def test_compress_gaussians_end_to_end(L, oracle, monkeypatch):
     assert table_g.shape == (k + int(keep_g.sum()), 6)
     assert torch.equal(table_g[k:], cov_a[keep_g]) and torch.equal(table_g[gi][keep_g], cov_a[keep_g])
     tr = table_g[:k, 0] + table_g[:k, 3] + table_g[:k, 5]
-    assert (tr - 1).abs().max() < 1e-5
+    # x / tr(x) has trace 1 up to the rounding of its three terms: an unused codeword keeps its uniform-box draw, whose
+    # diagonal can nearly cancel (seen once: 2e-4 off with |diag| sums 2000 times the trace)
+    mag = table_g[:k, 0].abs() + table_g[:k, 3].abs() + table_g[:k, 5].abs()
+    assert ((tr - 1).abs() <= 4e-7 * mag + 1e-6).all()
     _, idx_g = oracle.assign(cov_a[~keep_g].cpu().numpy(), table_g[:k].contiguous().cpu().numpy())
     assert np.array_equal(gi[~keep_g].cpu().numpy(), idx_g)
     rot, sc = L.extract_rot_scale(table_g)
