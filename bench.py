@@ -549,6 +549,12 @@ def main():
         roofline_update = update_roofline(n, d, upd, upd * ITERS / ms_per_step, pk, fused=True)
         roofline_update["sums_increment_ms"], roofline_update["ema_ms"] = incr_ms, update_ms
 
+    # write-only DRAM rate (cudaMemset-class fill of 1 GiB): the decode gather reads its rows out of the L2 and is a pure
+    # write stream to DRAM, so the copy peak (read + write bytes) is not what bounds it
+    fill = torch.empty(1 << 28, dtype=torch.float32, device=dev)
+    ms_fill = timed(lambda: fill.fill_(1.0))
+    write_peak_gbs = fill.numel() * 4 / ms_fill * 1e-6
+    del fill
     # decode gather: codebook[idx] -> [n, d], 8 B index in + 4 d B out per row
     gen = torch.Generator(device=dev).manual_seed(5 + rank)
     idx_dec = torch.randint(0, K, (n,), device=dev, generator=gen)
@@ -557,6 +563,10 @@ def main():
     roofline_gather = {"bound": "hbm", "achieved": gbytes / ms_g * 1e-6, "peak": pk["hbm_gbs"], "unit": "GB/s",
                        "frac": gbytes / ms_g * 1e-6 / pk["hbm_gbs"], "traffic": None, "kernel": "k_gather_span / k_gather32",
                        "kernel_ms": ms_g, "algorithmic_bytes_per_launch": gbytes,
+                       "write_only_peak_measured_gbs": write_peak_gbs,
+                       "frac_vs_write_only_peak": gbytes / ms_g * 1e-6 / write_peak_gbs,
+                       "note": "the table rows come out of the L2: DRAM sees the indices and the output rows, i.e. a "
+                               "write stream; write_only_peak = torch fill_ of 1 GiB timed in this run",
                        "peak_source": f"{pk['source']}: MEASURED_PEAKS.json hbm_gbs (copy bandwidth)"}
     del idx_dec
 
@@ -748,6 +758,7 @@ def main():
 
     extras = None
     if world == 1 and not args.simt and not args.no_extras:
+        pk["write_only_gbs"] = write_peak_gbs
         extras = single_gpu_extras(x, w, wn, cb0, n, d, dev, pk, tf32)
     if strong is not None:
         extras = extras or {}
@@ -900,7 +911,8 @@ def single_gpu_extras(x, w, wn, cb0, n, d, dev, pk, tf32):
     extras["morton_order"] = {"rows": n, "ms": ms, "gbs": mbytes / ms * 1e-6,
                               "frac_of_hbm_peak": mbytes / ms * 1e-6 / pk["hbm_gbs"],
                               "torch_sort_int64_ms": ms_torch,
-                              "note": "keys + stable LSD radix sort of (u64 key, u32 row); torch.sort (cub) "
+                              "note": "keys + stable LSD radix sort of (u64 key, u32 row), tiles digit-sorted in shared "
+                                      "memory before the write-out; torch.sort (cub) "
                                       "of n random int64 incl. their generation, timed beside it for scale"}
     del keep, cbi, cbj, a6, cov6, sub, xyz
     tab48 = torch.randn(K + n // 20, 16, 3, device=dev, generator=gen)
@@ -908,7 +920,9 @@ def single_gpu_extras(x, w, wn, cb0, n, d, dev, pk, tf32):
     ms = timed(lambda: ops2.gather(tab48, idx48))
     gbytes = n * (8 + 4 * 48)
     extras["decode_gather_sh48"] = {"rows": n, "dim": 48, "table_rows": int(tab48.shape[0]), "ms": ms,
-                                    "gbs": gbytes / ms * 1e-6, "frac_of_hbm_peak": gbytes / ms * 1e-6 / pk["hbm_gbs"]}
+                                    "gbs": gbytes / ms * 1e-6, "frac_of_hbm_peak": gbytes / ms * 1e-6 / pk["hbm_gbs"],
+                                    "frac_vs_write_only_peak": gbytes / ms * 1e-6 / pk["write_only_gbs"]
+                                    if pk.get("write_only_gbs") else None}
     del tab48, idx48
 
     # SURVEY §8f ranks 1 and 3, the formats either side of the path: normalised covariance, mask compaction,

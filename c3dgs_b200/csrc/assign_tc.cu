@@ -1368,33 +1368,52 @@ constexpr unsigned long long FB_INIT = ((unsigned long long)0x7f7fffffu) << 32; 
 
 __global__ void __launch_bounds__(128)
 k_assign_fallback_scan(const float *__restrict__ x, const int64_t *__restrict__ rows, int d,
-                       const float *__restrict__ cb, int k, const TcHeader *hdr,
+                       const float *__restrict__ cbp, int dpc, int kq, int k, const TcHeader *hdr,
                        const unsigned int *__restrict__ fb_list, unsigned long long *__restrict__ fb_best)
 {
-    __shared__ float xs[4][C3VQ_MAX_DIM];
+    // codes from the float4-column-major copy (TcParams::cbp): lane l takes the codes blk * 256 + l + 32 t, t = 0..7,
+    // eight independent distance chains whose loads are in flight together (each chain in column order, as the
+    // reference).  The row-major version walked them one after the other behind dependent loads: 268 us for the
+    // 14 k rows the trace-normalised shape codebook leaves undecided, now a fraction of that.
+    __shared__ __align__(16) float xs[4][C3VQ_MAX_DIM + 4];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const unsigned int count = hdr->fb_count;
     const unsigned int nblk = (unsigned int)((k + FB_CODES - 1) / FB_CODES);
     const unsigned long long items = (unsigned long long)count * nblk;
     const unsigned int nwarps = gridDim.x * 4;
+    const float4 *cb4 = reinterpret_cast<const float4 *>(cbp);
     for (unsigned long long w = blockIdx.x * 4 + wib; w < items; w += nwarps) {
         const unsigned int it = (unsigned int)(w / nblk), blk = (unsigned int)(w % nblk);
         const int64_t gi = fb_list[it];
         const int64_t src = rows ? rows[gi] : gi;
         __syncwarp();
-        for (int c = lane; c < d; c += 32) xs[wib][c] = x[src * d + c];
+        for (int c = lane; c < dpc; c += 32) xs[wib][c] = c < d ? x[src * d + c] : 0.f;
         __syncwarp();
-        unsigned long long key = ~0ull;
-        const int j1 = min(k, (int)(blk + 1) * FB_CODES);
-        for (int j = (int)blk * FB_CODES + lane; j < j1; j += 32) {
-            const float *cr = cb + (size_t)j * d;
-            float a = 0.f;
-            for (int c = 0; c < d; c++) {
-                const float df = xs[wib][c] - cr[c];
-                a = fmaf(df, df, a);
+        const int j0 = (int)blk * FB_CODES + lane;
+        float a[8];
+#pragma unroll
+        for (int t = 0; t < 8; t++) a[t] = 0.f;
+        for (int c4 = 0; c4 < dpc / 4; c4++) {
+            const float4 xv = reinterpret_cast<const float4 *>(xs[wib])[c4];
+            float4 cv[8];
+#pragma unroll
+            for (int t = 0; t < 8; t++)
+                cv[t] = j0 + 32 * t < k ? __ldg(cb4 + (size_t)c4 * kq + j0 + 32 * t) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int t = 0; t < 8; t++) {
+                float df;
+                if (4 * c4 + 0 < d) { df = xv.x - cv[t].x; a[t] = fmaf(df, df, a[t]); }
+                if (4 * c4 + 1 < d) { df = xv.y - cv[t].y; a[t] = fmaf(df, df, a[t]); }
+                if (4 * c4 + 2 < d) { df = xv.z - cv[t].z; a[t] = fmaf(df, df, a[t]); }
+                if (4 * c4 + 3 < d) { df = xv.w - cv[t].w; a[t] = fmaf(df, df, a[t]); }
             }
-            const unsigned long long kj = ((unsigned long long)__float_as_uint(a) << 32) | (unsigned int)j;
-            key = kj < key ? kj : key;
+        }
+        unsigned long long key = ~0ull;
+#pragma unroll
+        for (int t = 0; t < 8; t++) {
+            const int j = j0 + 32 * t;
+            const unsigned long long kj = ((unsigned long long)__float_as_uint(a[t]) << 32) | (unsigned int)j;
+            if (j < k && kj < key) key = kj;
         }
         for (int o = 16; o > 0; o >>= 1) {
             const unsigned long long ok = __shfl_xor_sync(0xffffffffu, key, o);
@@ -1628,7 +1647,7 @@ int launch_assign_tc(const float *x, const float *w, const int64_t *rows, int64_
 #endif
     if (rc) return rc;
     if (dbg_scores == nullptr) {
-        k_assign_fallback_scan<<<sms * 4, 128, 0, s>>>(x, rows, d, codebook, k, hdr, fb, p.fb_best);
+        k_assign_fallback_scan<<<sms * 4, 128, 0, s>>>(x, rows, d, cbp, l.dpc, l.kq, k, hdr, fb, p.fb_best);
         C3VQ_LAUNCH_CHECK("k_assign_fallback_scan");
         k_assign_fallback_finish<<<sms, 128, 0, s>>>(x, w, rows, d, hdr, fb, p.fb_best, out_dist, out_idx, acc,
                                                      acc_stride(d), p.prev);

@@ -22,7 +22,10 @@ namespace {
 
 constexpr int RS_THREADS = 512;                       // 16 warps
 constexpr int RS_WARPS = RS_THREADS / 32;
-constexpr int RS_ROUNDS = 8;                          // 32-key rounds per warp
+#ifndef C3VQ_RS_ROUNDS
+#define C3VQ_RS_ROUNDS 8
+#endif
+constexpr int RS_ROUNDS = C3VQ_RS_ROUNDS;             // 32-key rounds per warp
 constexpr int RS_TILE = RS_THREADS * RS_ROUNDS;       // 4096 keys per CTA
 
 // order-preserving float <-> unsigned maps for atomicMin / atomicMax
@@ -68,11 +71,23 @@ __global__ void __launch_bounds__(256) k_xyz_minmax(const float *__restrict__ xy
         lo[a] = __reduce_min_sync(0xffffffffu, lo[a]);
         hi[a] = __reduce_max_sync(0xffffffffu, hi[a]);
     }
+    // one set of atomics per CTA: tens of thousands of same-address atomics were most of this kernel's time
+    __shared__ unsigned int smm[6];
+    if (threadIdx.x < 6) smm[threadIdx.x] = threadIdx.x < 3 ? 0xffffffffu : 0u;
+    __syncthreads();
     if ((threadIdx.x & 31) == 0) {
 #pragma unroll
         for (int a = 0; a < 3; a++) {
-            atomicMin(&mm[a], lo[a]);
-            atomicMax(&mm[3 + a], hi[a]);
+            atomicMin(&smm[a], lo[a]);
+            atomicMax(&smm[3 + a], hi[a]);
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int a = 0; a < 3; a++) {
+            atomicMin(&mm[a], smm[a]);
+            atomicMax(&mm[3 + a], smm[3 + a]);
         }
     }
 }
