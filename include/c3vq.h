@@ -57,7 +57,11 @@ int64_t c3vq_launch_count(void);
  * c3vq_assign runs the tensor-core path (TF32 tcgen05 screening + exact fp32
  * re-rank of every candidate inside a proven error band); c3vq_assign_exact runs
  * the SIMT in-order kernel over all k codewords.  Both give the same output.
- * out_dist may be null.  ws: c3vq_assign_workspace_bytes(n, d, k) bytes.
+ * out_dist may be null.  ws: c3vq_assign_workspace_bytes(n, d, k) bytes; its
+ * contents need no initialisation.  The call leaves each row's winner in it and a
+ * later call on the same workspace uses that as a starting bound (re-evaluated
+ * against that call's codebook: whatever the workspace holds, the results are the
+ * same; reusing one workspace across the iterations of a clustering is faster).
  */
 size_t c3vq_assign_workspace_bytes(int64_t n, int d, int k);
 int c3vq_assign(const float *x, const int64_t *rows, int64_t n, int d,
