@@ -1592,8 +1592,10 @@ int launch_assign_tc(const float *x, const float *w, const int64_t *rows, int64_
     p.fb_list = fb;
     p.fb_best = (unsigned long long *)(base + l.off_fbbest);
     p.dbg_scores = dbg_scores; p.dbg_norm2 = dbg_norm2; p.dbg_band = dbg_band;
-    // widths of one fp16 K step (d <= 13) record groups of 16 codes: their list path is cheap, a seed would not pay
-    p.prev = (rows == nullptr && dbg_scores == nullptr && l.dp > 16 && seeds_enabled()) ? (int *)(base + l.off_prev) : nullptr;
+#ifndef C3VQ_SEEDS_MIN_DP
+#define C3VQ_SEEDS_MIN_DP 0
+#endif
+    p.prev = (rows == nullptr && dbg_scores == nullptr && l.dp > C3VQ_SEEDS_MIN_DP && seeds_enabled()) ? (int *)(base + l.off_prev) : nullptr;
     p.reg = (const uint8_t *)(base + l.off_reg);
     p.gamma2 = 2.1f * (float)(d + 3) * 5.9604644775390625e-8f;      // 2.1 (d+3) 2^-24
     const int sms = sm_count();
