@@ -111,6 +111,12 @@ k_gather_span(const float *__restrict__ table, int64_t table_rows, int d, unsign
 // a quarter of the instructions, but 0.57 ms against 0.26 ms for this version — the extra shared-memory round trip and
 // its warp syncs cost more than the index arithmetic they remove; profiles/r2f_bench.json vs r1x_bench.json.)
 
+// (Also measured in round 2, 5.8 M rows x 45 floats from a 4096-row table: lanes over the columns of one row at a time,
+// 4-byte coalesced loads and stores and no index arithmetic at all: 0.50 ms against 0.25 ms for the float4 stores above;
+// a branch for the float4 that do not cross a row end: 0.32 ms, the warp runs both paths.  From the same table with
+// 48-float rows, i.e. aligned float4 loads, the span copy below reaches 5.95 TB/s: what holds the 180-byte rows back is
+// that their source rows are only 4-byte aligned.)
+
 // Rows of whole float4 (d % 4 == 0; 48 floats = the fork's colour rows): the same span organisation without the
 // staging — the 32 * dv float4 of a span are copied lane-linear, four loads in flight per lane, the row of element e
 // by a multiply-shift (exact for e < 32 * dv, dv < 128) against row pointers parked in shared memory.

@@ -560,6 +560,18 @@ def test_morton_order_large_and_errors(L, oracle):
     o_or = np.argsort(k_or, kind="stable")
     assert np.array_equal(ks.cpu().numpy(), k_or[o_or])
     assert np.array_equal(o.cpu().numpy(), o_or)
+    # sizes around the 4096-key tile of the radix sort, an unaligned view (the vectorised min/max needs 16-byte alignment
+    # and must fall back), heavy ties: the permutation equals torch's stable sort of the same keys
+    for m in (1, 31, 4095, 4096, 4097, 12289, 70001):
+        g2 = torch.Generator().manual_seed(m)
+        base = torch.randn(m + 1, 3, generator=g2).to(DEV)
+        p3 = base.reshape(-1)[3:].reshape(m, 3)                                # starts 12 bytes into the storage
+        p3[m // 3:m // 3 + m // 4] = p3[:m // 4].clone()
+        o2, k2 = L.morton_order(p3, return_keys=True)
+        krow = torch.empty_like(k2)
+        krow[o2] = k2
+        assert np.array_equal(krow.cpu().numpy().astype(np.uint64), oracle.morton_keys(p3.cpu().numpy()))
+        assert torch.equal(o2, torch.sort(krow, stable=True).indices)
     assert L.morton_order(torch.empty(0, 3, device=DEV)).shape == (0,)
     with pytest.raises(RuntimeError):
         L.morton_order(torch.zeros(4, 2, device=DEV))
