@@ -104,8 +104,10 @@ constexpr int TC_DT = TC_NDRAIN * 32; // drain threads
 constexpr int TC_PROD_WARP0 = TC_DRAIN_WARP0 + TC_NDRAIN;
 constexpr int TC_MISC_WARP0 = TC_PROD_WARP0 + 8;        // TMA producer, MMA issuer, TMEM allocator, spare
 constexpr int TC_THREADS = (TC_MISC_WARP0 + 4) * 32;   // 896
-// register budgets per role (setmaxnreg): the CTA owns 896 * 72 = 64512 registers = 4*32*40 + 16*32*72 + 8*32*88
-constexpr int TC_REGS_MISC = 40, TC_REGS_DRAIN = 72, TC_REGS_PROD = 88;
+// register budgets per role (setmaxnreg): the CTA owns 896 * 72 = 64512 registers = 4*32*40 + 16*32*64 + 8*32*104.
+// The unrolled drain loop keeps its addresses in uniform registers and fits 64; the producers (12 float4 of a codebook
+// row plus the packed A operand) spilled at 88 (all 36 instantiations together: 3052 bytes of spill stores, 412 now)
+constexpr int TC_REGS_MISC = 40, TC_REGS_DRAIN = 64, TC_REGS_PROD = 104;
 constexpr uint32_t TC_SBO = 128;
 constexpr float TC_BIG = 8.507059173023462e37f;  // 2^126: score of dead / padding codes
 constexpr float TC_HUGE2 = 1.2676506002282294e30f;  // 2^100: squared-norm limit of the error model
