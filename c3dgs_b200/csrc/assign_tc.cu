@@ -713,31 +713,19 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             static_assert(CPL == 1 || DP <= 16, "several codes per lane only for the narrow widths (registers)");
             const int li = lane / LPI, lj = lane - li * LPI;                // item slot of this lane, lane within the item
             const bool lane_on = li < IPW;                                  // 32 = 10 * 3 + 2: two lanes sit out
-            // the codebook pieces come from the L2 (a microsecond under this kernel's load) and a round is a serial chain
-            // behind them: every thread asks for the lines of its NEXT round's item while it works on this round's
-            auto fetch_ahead = [&](uint32_t u) {
-                if (lane_on && u < nq) {
-                    const int code = (int)(queue[u] & 0xFFFFu) * GS;
-                    const float4 *cp = reinterpret_cast<const float4 *>(p.cbp) + code;
-                    if (CPL == 1) {          // 16 * GS bytes per column of four: lane i asks for columns i, i + LPI, ...
-                        for (int c4 = lj; c4 < p.dpc / 4; c4 += LPI) prefetch_l1(cp + (size_t)c4 * p.kq);
-                    } else {                 // 16 * CPL bytes per column of four: one line per lane
-                        const int c4 = lj / (CPL / 2), part = lj % (CPL / 2);
-                        if (c4 < p.dpc / 4) prefetch_l1(cp + (size_t)c4 * p.kq + 8 * part);
-                    }
-                }
-            };
-            fetch_ahead(pw * IPW + li);
+            // (an L1 prefetch of the next round's pieces was measured and removed: once the loads were one wavefront per
+            // item, its ~25 instructions per round cost 2.5 % of the kernel and hid nothing)
             sBest[ptid] = ((unsigned long long)__float_as_uint(FLT_MAX)) << 32;      // (FLT_MAX, code 0)
             named_bar_sync(1, TC_PR);
             const uint32_t gmask = ((1u << LPI) - 1u) << (li * LPI);
             for (uint32_t u = pw * IPW + li; lane_on && u < nq; u += 8 * IPW) {
-                fetch_ahead(u + 8 * IPW);
                 const uint32_t item = queue[u];
                 const int lr = item >> 16;
                 const int code0 = (int)(item & 0xFFFFu) * GS + lj;
                 const float *xg = xq + lr * L::XS;
-                const float4 *cp = reinterpret_cast<const float4 *>(p.cbp) + code0;
+                // codes past the end of the codebook (last group) read the last code instead and are dropped below:
+                // unconditional loads, no select per component
+                const float4 *cb4 = reinterpret_cast<const float4 *>(p.cbp);
                 const size_t kq = (size_t)p.kq;
                 unsigned long long key = ~0ull;
                 float a[CPL];
@@ -750,7 +738,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                     for (int j = 0; j < CPL; j++)
 #pragma unroll
                         for (int c4 = 0; c4 < NF4; c4++)
-                            cv[j][c4] = code0 + LPI * j < p.k ? __ldg(cp + c4 * kq + LPI * j) : make_float4(0.f, 0.f, 0.f, 0.f);
+                            cv[j][c4] = __ldg(cb4 + c4 * kq + min(code0 + LPI * j, p.k - 1));
 #pragma unroll
                     for (int c4 = 0; c4 < NF4; c4++) {
                         const float4 xv = reinterpret_cast<const float4 *>(xg)[c4];     // 16-byte aligned rows
@@ -767,7 +755,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                     for (int c4 = 0; c4 < p.dpc / 4; c4++) {
 #pragma unroll
                         for (int j = 0; j < CPL; j++) {
-                            const float4 cv = code0 + LPI * j < p.k ? __ldg(cp + c4 * kq + LPI * j) : make_float4(0.f, 0.f, 0.f, 0.f);
+                            const float4 cv = __ldg(cb4 + c4 * kq + min(code0 + LPI * j, p.k - 1));
                             float df;
                             if (4 * c4 + 0 < D) { df = xg[4 * c4 + 0] - cv.x; a[j] = fmaf(df, df, a[j]); }
                             if (4 * c4 + 1 < D) { df = xg[4 * c4 + 1] - cv.y; a[j] = fmaf(df, df, a[j]); }
@@ -923,7 +911,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             __syncwarp();
             // seed: the flag of the previous winner and its codebook row are requested now and used after the conversion
             const bool seed_ok = (unsigned)pj < (unsigned)p.k;
-            const float4 *seed_row = reinterpret_cast<const float4 *>(p.cbp) + (seed_ok ? pj : 0);
+            const float4 *seed_row = reinterpret_cast<const float4 *>(p.cbp) + (seed_ok ? pj : 0);   // code 0 when there is no seed
             uint8_t seed_reg = 0;
             if (seed_ok) seed_reg = p.reg[pj];
             uint32_t av[L::ACOLS];
@@ -939,7 +927,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             if (SEED_FUSED) {
 #pragma unroll
                 for (int c4 = 0; c4 < NF4; c4++)
-                    scv[c4] = seed_ok ? __ldg(seed_row + c4 * (size_t)p.kq) : make_float4(0.f, 0.f, 0.f, 0.f);
+                    scv[c4] = __ldg(seed_row + c4 * (size_t)p.kq);          // unconditional (k >= 1); unused without a seed
             }
             const float4 *xrow4 = reinterpret_cast<const float4 *>(xs_w + lane * L::XS);
             const float4 *mu4 = reinterpret_cast<const float4 *>(sMu);
