@@ -1,20 +1,8 @@
 #!/bin/bash
 mkdir -p gpurun_out
-T=${TAG:-r3p}
+T=${TAG:-r3v}
 O=gpurun_out
-timeout 1800 python -m pytest tests -x -q -m gpu > $O/${T}_pytest_gpu.txt 2>&1
-echo "== pytest rc=$?: $(tail -1 $O/${T}_pytest_gpu.txt)"
-timeout 300 python -m pytest tests/test_zz_no_alloc.py -x -q -m gpu > $O/${T}_pytest_no_alloc_alone.txt 2>&1
-echo "== no_alloc alone rc=$?: $(tail -1 $O/${T}_pytest_no_alloc_alone.txt)"
-timeout 300 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tail -1
-timeout 1500 python bench.py --steps 5 --warmup 3 > $O/${T}_bench.json 2> $O/${T}_bench.err
-echo "== bench rc=$?"
-python - <<PY
-import json
-j = json.load(open("gpurun_out/${T}_bench.json"))
-print("ms/step", round(j["ms_per_step"], 2), "assign", round(j["roofline"]["kernel_ms"], 3), "frac", round(j["roofline"]["frac"],3), "vs tf32", round(j["roofline"]["frac_vs_tf32_sustained_measured"],3), "e2e", round(j["e2e"]["ms_per_step"], 2))
-for k in ("shape7", "cov6_trace_normalised", "sh48", "iid45"):
-    v = j["extras"][k]; print(k, round(v["ms_per_step"], 2), round(v["assign_ms"], 3), v.get("candidates_per_row"), v.get("fallback_rows"))
-print("strong_24M", j["extras"]["strong_24M"]["ms_per_step"], "pipeline", j["extras"]["compress_pipeline"]["total_ms"], "minibatch", j["extras"]["vq_features_minibatch"]["wall_ms"])
-PY
-tail -n 3 $O/${T}_bench.err
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_assign_tc -s ${IT:-9} -c 1 -o $O/${T}_assign_tc python tools/tc_profile_run.py 5800000 ${D:-45} 10 > $O/${T}_ncu.log 2>&1
+echo "ncu rc=$?"
+ncu -i $O/${T}_assign_tc.ncu-rep --page source --csv > $O/${T}_assign_tc_source.csv 2>/dev/null
+ncu -i $O/${T}_assign_tc.ncu-rep --page raw --csv > $O/${T}_assign_tc_raw.csv 2>/dev/null
