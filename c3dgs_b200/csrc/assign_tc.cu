@@ -861,12 +861,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                             for (unsigned int nl = ~leaders; nl; nl &= nl - 1) {
                                 const int r = __ffs(nl) - 1;
                                 const int dst = __shfl_sync(0xffffffffu, leader, r);
-#pragma unroll
-                                for (int h = 0; h < NH; h++) {
-                                    const int col = lane + 32 * h;
-                                    if (col < p.acc_stride)
-                                        xw[dst * L::XS + col] = __fadd_rn(xw[dst * L::XS + col], xw[r * L::XS + col]);
-                                }
+                                // (acc_stride can exceed 64 columns: d = 61 ... 64)
+                                for (int col = lane; col < p.acc_stride; col += 32)
+                                    xw[dst * L::XS + col] = __fadd_rn(xw[dst * L::XS + col], xw[r * L::XS + col]);
                             }
                         }
                     }

@@ -64,6 +64,31 @@ def test_assign_bit_exact_vs_oracle(L, oracle, d, n, k, exact):
     assert np.array_equal(dist.cpu().numpy().view(np.uint32), dist_o.view(np.uint32))
 
 
+@pytest.mark.parametrize("screen", ["f16", "tf32"])
+@pytest.mark.parametrize("d", [1, 2, 3, 5, 13, 14, 16, 20, 29, 33, 44, 46, 50, 61, 62, 64])
+def test_assign_generic_widths_bit_exact(L, oracle, d, screen, monkeypatch):
+    """Widths without a specialised kernel (runtime d inside the DP = 16 ... 80 instantiations, both screenings): the
+    assignment twice in a row (unseeded, then seeded) and the fused sums against the oracle."""
+    monkeypatch.setenv("C3VQ_SCREEN", screen)
+    n, k = 3001, 300
+    x, w, cb = _synth(n, d, k, seed=500 + d)
+    dist_o, idx_o = oracle.assign(x.numpy(), cb.numpy())
+    xd, cbd = x.to(DEV), cb.to(DEV)
+    for _ in range(2):
+        dist, idx = L.assign(xd, cbd)
+        assert np.array_equal(idx.cpu().numpy(), idx_o)
+        assert np.array_equal(dist.cpu().numpy().view(np.uint32), dist_o.view(np.uint32))
+    wn = (w / w.max()).contiguous().to(DEV)
+    acc = torch.zeros(k, L.acc_stride(d), device=DEV)
+    _, _, idx2 = L.assign_accumulate(xd, wn, cbd, acc=acc, tensor_cores="fused")
+    assert np.array_equal(idx2.cpu().numpy(), idx_o)
+    sx64, sw64 = oracle.scatter_sum_f64(x.numpy(), wn.cpu().numpy(), idx_o, k)
+    a = acc.cpu().numpy().astype(np.float64)
+    scale = np.abs(sx64).max(1, keepdims=True) + 1e-30
+    assert (np.abs(a[:, :d] - sx64) / scale).max() <= 1e-5
+    assert np.abs(a[:, d] - sw64).max() <= 1e-5 * (np.abs(sw64).max() + 1e-30)
+
+
 @pytest.mark.parametrize("d", [45, 48])
 def test_assign_seeded_running_minima_are_harmless(L, oracle, d, monkeypatch):
     """The tensor-core kernel seeds every row's running minimum with the row's winner of the previous call on the same
