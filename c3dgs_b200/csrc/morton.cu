@@ -11,9 +11,11 @@
 // radix sort, 8 passes of 8 bits over (key u64, row u32) pairs: equal keys keep their row order (torch's sort makes no
 // promise for ties; its CUDA and CPU implementations both happen to be stable).
 //
-// Per pass: k_radix_hist (per-tile digit counts, digit-major table), k_radix_scan (one CTA per digit scans its row of
-// the table), k_radix_scatter (stable ranking: every warp owns a contiguous slice of the tile and walks it 32 keys at a
-// time with match.any, so ranks follow the input order without any atomics).  HBM-bound: 40 bytes per key and pass.
+// The key kernel also counts the digit totals of all eight passes; every pass is then ONE kernel
+// (k_radix_scatter): tiles by ticket, stable ranking of the tile's keys (every warp owns a contiguous slice and walks it
+// 32 keys at a time, digit peers by ballots, so ranks follow the input order without atomics), the tile sorted by digit
+// in shared memory, the per-digit offsets of earlier tiles by decoupled look-back, full-sector write-out.
+// HBM-bound: 24 bytes per key and pass.
 #include "common.cuh"
 
 namespace c3vq {
@@ -106,8 +108,14 @@ __device__ __forceinline__ unsigned long long split_by_3(unsigned long long a)
 
 __global__ void __launch_bounds__(256) k_morton_keys(const float *__restrict__ xyz, int64_t n,
                                                      const unsigned int *__restrict__ mm,
-                                                     unsigned long long *__restrict__ keys)
+                                                     unsigned long long *__restrict__ keys,
+                                                     unsigned int *__restrict__ totals)
 {
+    // totals[p * 256 + d] = number of keys whose digit of pass p is d, for all eight radix passes, counted while the keys
+    // are in registers (the multiset of keys does not change from pass to pass)
+    __shared__ unsigned int cnt[8 * 256];
+    for (int j = threadIdx.x; j < 8 * 256; j += blockDim.x) cnt[j] = 0;
+    __syncthreads();
     float mn[3], dp[3];
 #pragma unroll
     for (int a = 0; a < 3; a++) {
@@ -132,50 +140,12 @@ __global__ void __launch_bounds__(256) k_morton_keys(const float *__restrict__ x
             key |= split_by_3((unsigned long long)q) << rk[a];           // axis with the smallest extent -> bit 0
         }
         keys[i] = key;
-    }
-}
-
-// table[d * nb + tile] = number of keys of the tile whose digit is d
-__global__ void __launch_bounds__(RS_THREADS) k_radix_hist(const unsigned long long *__restrict__ keys, int64_t n, int shift,
-                                                           unsigned int *__restrict__ table, int nb)
-{
-    __shared__ unsigned int cnt[256];
-    if (threadIdx.x < 256) cnt[threadIdx.x] = 0;
-    __syncthreads();
-    const int64_t base = (int64_t)blockIdx.x * RS_TILE;
-#pragma unroll 4
-    for (int r = 0; r < RS_ROUNDS; r++) {
-        const int64_t i = base + (int64_t)r * RS_THREADS + threadIdx.x;
-        if (i < n) atomicAdd(&cnt[(unsigned int)(keys[i] >> shift) & 255u], 1u);
+#pragma unroll
+        for (int p = 0; p < 8; p++) atomicAdd(&cnt[p * 256 + ((unsigned int)(key >> (8 * p)) & 255u)], 1u);
     }
     __syncthreads();
-    if (threadIdx.x < 256) table[(size_t)threadIdx.x * nb + blockIdx.x] = cnt[threadIdx.x];
-}
-
-// CTA d: exclusive scan of table[d * nb .. d * nb + nb) in place, total[d] = sum
-__global__ void __launch_bounds__(1024) k_radix_scan(unsigned int *__restrict__ table, int nb, unsigned int *__restrict__ total)
-{
-    __shared__ unsigned int part[1024];
-    unsigned int *row = table + (size_t)blockIdx.x * nb;
-    const int per = (nb + 1023) / 1024;
-    const int j0 = threadIdx.x * per, j1 = min(nb, j0 + per);
-    unsigned int sum = 0;
-    for (int j = j0; j < j1; j++) sum += row[j];
-    part[threadIdx.x] = sum;
-    __syncthreads();
-    for (int o = 1; o < 1024; o <<= 1) {
-        const unsigned int v = threadIdx.x >= o ? part[threadIdx.x - o] : 0u;
-        __syncthreads();
-        part[threadIdx.x] += v;
-        __syncthreads();
-    }
-    unsigned int run = part[threadIdx.x] - sum;
-    for (int j = j0; j < j1; j++) {
-        const unsigned int c = row[j];
-        row[j] = run;
-        run += c;
-    }
-    if (threadIdx.x == 1023) total[blockIdx.x] = part[1023];
+    for (int j = threadIdx.x; j < 8 * 256; j += blockDim.x)
+        if (cnt[j]) atomicAdd(&totals[j], cnt[j]);
 }
 
 // lanes of `act` whose 8-bit digit equals this lane's: eight ballots.  match.any costs a trip per DISTINCT value of the
@@ -191,6 +161,14 @@ __device__ __forceinline__ unsigned int digit_peers(unsigned int act, unsigned i
     return peers;
 }
 
+// One kernel per pass ("one sweep"): a CTA takes the next tile by ticket, counts its digits, publishes the counts,
+// and gets the number of keys of each digit in all EARLIER tiles by decoupled look-back over the published words
+// (status[tile][digit] = count | AGGREGATE, later prefix-including-this-tile | INCLUSIVE): thread d walks back from
+// tile - 1 until it meets an INCLUSIVE word.  Tickets are handed out in tile order, so every tile a CTA waits for has
+// started: no deadlock, whatever the hardware's block scheduling order.  Round 2's first version needed a histogram
+// kernel, a scan kernel and the scatter per pass (17 + 7 + 75 us at 5.8 M keys).
+constexpr unsigned int RS_AGG = 1u << 30, RS_INC = 1u << 31, RS_CNT = RS_AGG - 1u;
+
 // FIRST: the row payload is the position itself (pass 0); LAST: write int64 rows (and optionally the sorted keys).
 // The tile is first sorted by digit INSIDE shared memory (stable: ranks follow the input order), then written out in
 // that order: consecutive threads then hold consecutive keys of one digit, whose global positions are consecutive, so
@@ -202,12 +180,19 @@ struct ScatterSmem {
     unsigned int wcnt[RS_WARPS][256];                  // per-warp digit counts, then per-warp running offsets (tile-local)
     unsigned int dbase[256];                           // global position of the tile's first key of each digit
     unsigned int dloc[256];                            // tile-local position of the first key of each digit
+    unsigned int tile;                                 // the ticket
 };
 
+// CTAs per SM the register allocation leaves room for (78 registers unbounded = one CTA of 16 warps per SM, a quarter
+// of the SM's warps, with five CTA-wide barriers and a look-back per tile: latency bound)
+#ifndef C3VQ_RS_MINBLOCKS
+#define C3VQ_RS_MINBLOCKS 2
+#endif
 template <bool FIRST, bool LAST>
-__global__ void __launch_bounds__(RS_THREADS)
+__global__ void __launch_bounds__(RS_THREADS, C3VQ_RS_MINBLOCKS)
 k_radix_scatter(const unsigned long long *__restrict__ keys_in, const unsigned int *__restrict__ rows_in, int64_t n,
-                int shift, const unsigned int *__restrict__ table, int nb, const unsigned int *__restrict__ total,
+                int shift, unsigned int *__restrict__ ticket, unsigned int *__restrict__ status,
+                const unsigned int *__restrict__ total,
                 unsigned long long *__restrict__ keys_out, unsigned int *__restrict__ rows_out,
                 int64_t *__restrict__ order_out)
 {
@@ -215,10 +200,12 @@ k_radix_scatter(const unsigned long long *__restrict__ keys_in, const unsigned i
     ScatterSmem &sm = *reinterpret_cast<ScatterSmem *>(scatter_smem);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const unsigned int lt = (1u << lane) - 1u;
+    if (threadIdx.x == 0) sm.tile = atomicAdd(ticket, 1u);
     for (int j = threadIdx.x; j < RS_WARPS * 256; j += RS_THREADS) (&sm.wcnt[0][0])[j] = 0;
     __syncthreads();
+    const unsigned int tile = sm.tile;
     // warp w owns keys [base + w * 32 * RS_ROUNDS, + 32 * RS_ROUNDS) of the tile, 32 consecutive keys per round
-    const int64_t tbase = (int64_t)blockIdx.x * RS_TILE;
+    const int64_t tbase = (int64_t)tile * RS_TILE;
     const int64_t wbase = tbase + (int64_t)warp * (32 * RS_ROUNDS);
     const int tile_n = (int)((n - tbase) < (int64_t)RS_TILE ? (n - tbase) : (int64_t)RS_TILE);
     unsigned long long key[RS_ROUNDS];
@@ -256,8 +243,10 @@ k_radix_scatter(const unsigned long long *__restrict__ keys_in, const unsigned i
             run += c;
         }
         dcount = run;
-        sm.dbase[dgt] = table[(size_t)dgt * nb + blockIdx.x];
         sm.dloc[dgt] = run;                                              // scanned below
+        // publish this tile's count now; the counts of the earlier tiles are collected after the local scatter
+        volatile unsigned int *st = status + (size_t)tile * 256 + dgt;
+        *st = dcount | (tile == 0 ? RS_INC : RS_AGG);
     }
     __syncthreads();
     if (threadIdx.x < 32) {
@@ -280,14 +269,33 @@ k_radix_scatter(const unsigned long long *__restrict__ keys_in, const unsigned i
         unsigned int run = incl - s, runc = inclc - sc;
 #pragma unroll
         for (int j = 0; j < 8; j++) {
-            sm.dbase[lane * 8 + j] += run;
+            sm.dbase[lane * 8 + j] = run;                                // + the keys of earlier tiles, below
             sm.dloc[lane * 8 + j] = runc;
             run += t[j];
             runc += c[j];
         }
     }
     __syncthreads();
-    (void)dcount;
+    // Decoupled look-back, as early as possible (the sooner a tile publishes its inclusive prefix, the shorter the walk of
+    // the tiles behind it): thread d adds up digit d's counts of the earlier tiles until it meets an inclusive prefix;
+    // the other half of the CTA goes on to the local scatter meanwhile (dbase is not needed before the write-out).
+    // Measured and dropped: a warp-parallel look-back (32 earlier tiles x 16 digits per warp and window, one warp
+    // reduction per digit): 208 us per pass against 91 us -- the nearest inclusive prefix is one to three tiles back, and
+    // the wide windows only multiply the polling traffic.
+    if (threadIdx.x < 256 && tile > 0) {
+        const int dgt = threadIdx.x;
+        unsigned int excl = 0;
+        for (int t = (int)tile - 1; t >= 0; t--) {
+            volatile unsigned int *pt = status + (size_t)t * 256 + dgt;
+            unsigned int v;
+            do { v = *pt; } while ((v & (RS_AGG | RS_INC)) == 0u);
+            excl += v & RS_CNT;
+            if (v & RS_INC) break;
+        }
+        volatile unsigned int *st = status + (size_t)tile * 256 + dgt;
+        *st = (excl + dcount) | RS_INC;
+        sm.dbase[dgt] += excl;
+    }
     // stable local scatter: tile-local position = start of the digit + keys of earlier warps + rank inside the warp
 #pragma unroll
     for (int r = 0; r < RS_ROUNDS; r++) {
@@ -320,7 +328,7 @@ k_radix_scatter(const unsigned long long *__restrict__ keys_in, const unsigned i
 }
 
 struct MortonLayout {
-    size_t off_mm, off_total, off_table, off_keys0, off_keys1, off_rows0, off_rows1, bytes;
+    size_t off_mm, off_total, off_ticket, off_status, off_keys0, off_keys1, off_rows0, off_rows1, bytes;
     int nb;
 };
 
@@ -332,8 +340,9 @@ MortonLayout morton_layout(int64_t n)
     auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
     size_t o = 0;
     l.off_mm = o, o += 256;
-    l.off_total = o, o += up(256 * 4);
-    l.off_table = o, o += up((size_t)256 * l.nb * 4);
+    l.off_total = o, o += up(8 * 256 * 4);                       // digit totals of the eight passes
+    l.off_ticket = o, o += 256;                                  // one ticket counter per pass
+    l.off_status = o, o += up((size_t)8 * 256 * l.nb * 4);       // look-back words [pass][tile][digit] (zeroed per call)
     l.off_keys0 = o, o += up((size_t)n * 8);
     l.off_keys1 = o, o += up((size_t)n * 8);
     l.off_rows0 = o, o += up((size_t)n * 4);
@@ -356,18 +365,21 @@ int launch_morton_order(const float *xyz, int64_t n, int64_t *out_order, uint64_
         return C3VQ_EWORKSPACE;
     }
     uint8_t *w = (uint8_t *)ws;
+    C3VQ_CHECK_ARG(n < (int64_t)RS_AGG, "n=%lld too large for the 30-bit look-back counters", (long long)n);
     unsigned int *mm = (unsigned int *)(w + l.off_mm), *total = (unsigned int *)(w + l.off_total);
-    unsigned int *table = (unsigned int *)(w + l.off_table);
+    unsigned int *ticket = (unsigned int *)(w + l.off_ticket), *status = (unsigned int *)(w + l.off_status);
     unsigned long long *keys[2] = {(unsigned long long *)(w + l.off_keys0), (unsigned long long *)(w + l.off_keys1)};
     unsigned int *rows[2] = {(unsigned int *)(w + l.off_rows0), (unsigned int *)(w + l.off_rows1)};
 
     const unsigned int mm_init[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0u, 0u, 0u};
     C3VQ_CUDA(cudaMemcpyAsync(mm, mm_init, sizeof(mm_init), cudaMemcpyHostToDevice, s));
+    // totals, tickets and look-back words are contiguous: one memset
+    C3VQ_CUDA(cudaMemsetAsync(total, 0, l.off_keys0 - l.off_total, s));
     int64_t gb = (n + 255) / 256;
     if (gb > (int64_t)sm_count() * 8) gb = (int64_t)sm_count() * 8;
     k_xyz_minmax<<<(unsigned)gb, 256, 0, s>>>(xyz, n, mm);
     C3VQ_LAUNCH_CHECK("k_xyz_minmax");
-    k_morton_keys<<<(unsigned)gb, 256, 0, s>>>(xyz, n, mm, keys[0]);
+    k_morton_keys<<<(unsigned)gb, 256, 0, s>>>(xyz, n, mm, keys[0], total);
     C3VQ_LAUNCH_CHECK("k_morton_keys");
     constexpr int PASSES = 8;
     const size_t ssm = sizeof(ScatterSmem);
@@ -376,18 +388,16 @@ int launch_morton_order(const float *xyz, int64_t n, int64_t *out_order, uint64_
     C3VQ_CUDA(cudaFuncSetAttribute(k_radix_scatter<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ssm));
     for (int p = 0; p < PASSES; p++) {
         const int in = p & 1, out = in ^ 1, shift = 8 * p;
-        k_radix_hist<<<l.nb, RS_THREADS, 0, s>>>(keys[in], n, shift, table, l.nb);
-        C3VQ_LAUNCH_CHECK("k_radix_hist");
-        k_radix_scan<<<256, 1024, 0, s>>>(table, l.nb, total);
-        C3VQ_LAUNCH_CHECK("k_radix_scan");
+        unsigned int *tk = ticket + p, *st = status + (size_t)p * 256 * l.nb;
+        const unsigned int *tot = total + p * 256;
         if (p == 0)
-            k_radix_scatter<true, false><<<l.nb, RS_THREADS, ssm, s>>>(keys[in], nullptr, n, shift, table, l.nb, total,
+            k_radix_scatter<true, false><<<l.nb, RS_THREADS, ssm, s>>>(keys[in], nullptr, n, shift, tk, st, tot,
                                                                     keys[out], rows[out], nullptr);
         else if (p == PASSES - 1)
-            k_radix_scatter<false, true><<<l.nb, RS_THREADS, ssm, s>>>(keys[in], rows[in], n, shift, table, l.nb, total,
+            k_radix_scatter<false, true><<<l.nb, RS_THREADS, ssm, s>>>(keys[in], rows[in], n, shift, tk, st, tot,
                                                                     (unsigned long long *)out_keys, nullptr, out_order);
         else
-            k_radix_scatter<false, false><<<l.nb, RS_THREADS, ssm, s>>>(keys[in], rows[in], n, shift, table, l.nb, total,
+            k_radix_scatter<false, false><<<l.nb, RS_THREADS, ssm, s>>>(keys[in], rows[in], n, shift, tk, st, tot,
                                                                      keys[out], rows[out], nullptr);
         C3VQ_LAUNCH_CHECK("k_radix_scatter");
     }
