@@ -400,6 +400,16 @@ struct TcSmem {
     static constexpr int GS = tc_gs(DP, BN);                               // codes per candidate group (3, 4, 8 or 16)
     static constexpr int NG = BN / (2 * GS);                               // groups per drain thread and (half) job
     static_assert(GS == 3 || GS == 4 || GS == 8 || GS == 16, "group size");
+    // Drain warps per (tile, lane quarter, SLOT) instead of (tile, lane quarter, column half): a warp takes every other
+    // step and reads all 96 columns of it in two batches, one wait and one hand-back per 96 columns instead of per 48.
+    // Measured (same box, 5.8 M rows, mean of iterations 1-9): D = 7 2.03 ms against 2.17 ms; D = 45 2.56 against 2.57,
+    // D = 48 2.79 against 2.79 -- the narrow widths, where the drain is all there is, take it; the wide rows stay on
+    // the column-half mapping (C3VQ_TC_SLOTWARPS_ALL switches them too).
+#ifdef C3VQ_TC_SLOTWARPS_ALL
+    static constexpr bool SLOTWARPS = BN == 96 && tc_spt(DP) == 2;
+#else
+    static constexpr bool SLOTWARPS = BN == 96 && tc_spt(DP) == 2 && DP <= 16;
+#endif
     static constexpr int LPI = GS == 3 ? 3 : 4;                            // re-rank lanes per queue item
     static constexpr int CPL = GS == 3 ? 1 : GS / 4;                       // codes per re-rank lane
     // Tried for the groups of 16 and dropped (round 2): group r = the 16 columns r, r + 3, r + 6, ... so that every first
@@ -519,7 +529,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
         mbar_init(A_EMPTY, 2);
         for (int sl = 0; sl < L::NSLOT; sl++) {
             mbar_init(ACC_FULL(sl), 1);
-            mbar_init(ACC_EMPTY(sl), 8);           // one arrival per drain warp of the tile
+            mbar_init(ACC_EMPTY(sl), L::SLOTWARPS ? 4 : 8);   // one arrival per drain warp of the tile (of the slot)
         }
         for (int b = 0; b < 2; b++) {
             mbar_init(Q_FULL(b), TC_NDRAIN);
@@ -594,7 +604,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
                 mbar_wait(A_FULL, pi & 1);
                 PROF(1);   // prof[8+1]: MMA wait A_FULL
                 tc_fence_after();
-                sk = 0;
+                if (!L::SLOTWARPS) sk = 0;
                 for (int s = 0; s < nsteps; s++) {
                     PROF(0);
                     mbar_wait(B_FULL(stage), phase);
@@ -1070,7 +1080,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
         const int h = dw >> 3;                          // column half of every slot served by this warp
         const int lr = t * TC_BM + q * 32 + lane;       // local row 0..255 (shared with the other half's thread)
         const int dl = dw * 32 + lane;                  // drain thread 0..511 (list column)
-        const uint32_t tsrc0 = ((uint32_t)(q * 32) << 16) + (L::SPT * t) * BN + h * (BN / 2);   // TMEM base is 0 (checked)
+        // (slot warps: h is the warp's slot, not its column half)
+        const uint32_t tsrc0 = ((uint32_t)(q * 32) << 16) + (L::SPT * t) * BN + (L::SLOTWARPS ? 0 : h * (BN / 2));   // TMEM base is 0 (checked)
+        uint32_t slot0 = 0;                             // slot warps: slot of the first step of the current pass
         const uint32_t acc_full0 = ACC_FULL(L::SPT * t);     // ACC_EMPTY of the same slot is NSLOT barriers further
         constexpr uint32_t ACC_E_OFF = 8u * L::NSLOT;
         uint32_t *listS = sListS + dl, *listP = sListP + dl;
@@ -1172,6 +1184,47 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_assign_tc(const TcParams p)
             // step's barrier with a try_wait right after handing this step's slot back, to hide the ~90 cycles a
             // successful wait takes behind the min reduction: 3.63 ms per iteration against 3.46 ms without the probe
             // (the extra try_wait + predicate per step cost more issue slots than the hidden latency gave back)
+            if (L::SLOTWARPS) {
+            // a drain warp per (tile, lane quarter, SLOT): it takes every other step and reads all 96 columns of it in two
+            // batches of 48 (TcSmem::SLOTWARPS).  The MMA warps keep cycling the slots across passes, so the slot of a
+            // pass' first step alternates when the step count is odd.
+            for (int s = (int)((h - slot0) & 1u); s < nsteps; s += 2) {
+                const uint32_t acc_full = acc_full0 + 8u * h, tsrc = tsrc0 + h * BN;
+                mbar_wait_hint(acc_full, wphm & 1u);
+                wphm ^= 1u;
+                tc_fence_after();
+#pragma unroll
+                for (int bt = 0; bt < 2; bt++) {
+                    uint32_t va[16], vb[16], vc[16];
+                    float gv[NGH];
+                    tmem_ld16_async(tsrc + bt * 48, va);
+                    tmem_ld16_async(tsrc + bt * 48 + 16, vb);
+                    tmem_ld16_async(tsrc + bt * 48 + 32, vc);
+                    tmem_wait_ld16(va);
+                    tmem_wait_ld16(vb);
+                    tmem_wait_ld16(vc);
+                    if (bt == 1) {                      // the whole slot is read: hand it back to the MMA warp
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(acc_full + ACC_E_OFF);
+                    }
+                    if (DBG) { dump(va, s * BN + bt * 48); dump(vb, s * BN + bt * 48 + 16); dump(vc, s * BN + bt * 48 + 32); }
+                    if (GS == 3) {
+                        auto colv = [&](int c) {
+                            return __uint_as_float(c < 16 ? va[c & 15] : (c < 32 ? vb[c & 15] : vc[c & 15]));
+                        };
+#pragma unroll
+                        for (int g = 0; g < 16; g++) gv[g] = min3f(colv(3 * g), colv(3 * g + 1), colv(3 * g + 2));
+                    } else {
+                        groups(va, gv);
+                        groups(vb, gv + GPC);
+                        groups(vc, gv + 2 * GPC);
+                    }
+                    process(gv, (uint32_t)(2 * s + bt));
+                }
+            }
+            slot0 = (slot0 + (uint32_t)nsteps) & 1u;
+            } else
             // unrolled over the tile's slots: slot, TMEM address and barrier address of a step are constants of the body
             for (int s0 = 0; s0 < nsteps; s0 += L::SPT) {
 #pragma unroll
