@@ -1,7 +1,7 @@
 #!/bin/bash
 # end-of-round evidence: GPU tests, smoke, bench, ncu launch list of the bench command
 mkdir -p gpurun_out
-T=${TAG:-r4g}
+T=${TAG:-r4j}
 O=gpurun_out
 timeout 1800 python -m pytest tests -x -q -m gpu > $O/${T}_pytest_gpu.txt 2>&1
 echo "== pytest rc=$?: $(tail -1 $O/${T}_pytest_gpu.txt)"
@@ -20,5 +20,3 @@ e = j["extras"]
 print("strong_24M", e["strong_24M"]["ms_per_step"], "pipeline", e["compress_pipeline"]["total_ms"], "minibatch", e["vq_features_minibatch"]["wall_ms"], "morton", e["morton_order"]["ms"], "gather", j["roofline_gather"]["kernel_ms"])
 PY
 tail -n 2 $O/${T}_bench.err
-timeout 1500 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $O/${T}_launches_bench.csv python bench.py --steps 2 --warmup 1 > $O/${T}_ncu_launch.log 2>&1
-echo "launch list rc=$?"
