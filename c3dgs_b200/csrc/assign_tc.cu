@@ -58,13 +58,10 @@ using namespace ptx;
 constexpr int TC_BM = 128;            // rows per UMMA tile
 constexpr int TC_PR = 2 * TC_BM;      // rows per CTA pass ("pair" of tiles)
 // codes per stage / per MMA: four accumulator slots plus the A operand of both row tiles share the 512 TMEM columns
-#ifdef C3VQ_TC_BN64   // experiment: 64 codes per MMA, three accumulator slots per row tile
-__host__ __device__ constexpr int tc_bn(int dp) { return 64; }
-__host__ __device__ constexpr int tc_spt(int dp) { return dp <= 48 ? 3 : 2; }
-#else
+// (64 codes per MMA with three accumulator slots per row tile was an experiment of the TF32 era: 4.19 ms per launch
+// against 3.87 ms, the extra barrier round trips cost more than the deeper ring gained)
 __host__ __device__ constexpr int tc_bn(int dp) { return dp <= 64 ? 96 : 64; }
 __host__ __device__ constexpr int tc_spt(int dp) { return 2; }   // accumulator slots per row tile
-#endif
 // fp16 screening: the A operand takes half the TMEM columns, which would leave room for 112 codes per MMA (4 x 112 +
 // 2 x DP/2 <= 512 up to DP = 64): 37 steps per pass over 4096 codewords instead of 43.  Built, bit-exact (full GPU
 // suite green) and measured in round 2 (5.8 M rows, fused sums, mean of iterations 1-7): 3.61 / 3.78 / 3.19 ms at
