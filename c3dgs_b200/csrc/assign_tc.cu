@@ -5,31 +5,31 @@
 // feature row from HBM exactly once per iteration.
 //
 // Method (results are bit-identical to the reference's fp32 argmin):
-//   1. SCREEN  s_ij = |c'_j|^2 - 2 x'_i . c'_j  with tcgen05.mma kind::tf32 into TMEM, where
-//      x' = x - mu, c' = c - mu (mu = codebook mean; a distance-preserving shift that shrinks the
-//      cancellation error).  Operands are rounded to TF32 by us (cvt.rna), |c'|^2 rides along as 2-3
-//      extra K columns (hi/mid/lo TF32 pieces against a 1.0 in the A operand), so the epilogue is a
-//      pure min: one FMNMX3 per two scores.
-//   2. BAND    every GROUP of 4 consecutive codes whose minimum score is within band_i of the running
-//      row minimum is recorded, where band_i = 2*E_i + slack bounds the worst-case screening error
-//      (TF32 input rounding 2^-11 per operand, tensor-core accumulation, norm split) plus the
-//      reference chain's own rounding; the fp32 argmin of the reference is therefore always inside a
-//      recorded group.
-//   3. RE-RANK all codes of the surviving groups with the reference arithmetic (in-order fma chain,
-//      first index wins ties).  Rows whose group list overflows, or whose magnitudes break the error
-//      model, go to an exact scan (k_assign_fallback_scan / _finish).
+//   1. SCREEN  s_ij = |c'_j|^2 - 2 x'_i . c'_j  with tcgen05.mma into TMEM (kind::f16 on operands scaled by a power
+//      of two, or kind::tf32), where x' = x - mu, c' = c - mu (mu = codebook mean; a distance-preserving shift that
+//      shrinks the cancellation error).  Operands are rounded by us, |c'|^2 rides along as three extra K columns
+//      (hi/mid/lo pieces against a constant in the A operand), so the epilogue is a pure min: one FMNMX3 per three scores.
+//   2. BAND    every GROUP of 3 consecutive codes (16 at the one-K-step widths) whose minimum score is within band_i of
+//      the running row minimum is recorded, where band_i = 2*E_i + slack bounds the worst-case screening error
+//      (input rounding 2^-11 per operand, tensor-core accumulation, norm split) plus the reference chain's own
+//      rounding; the fp32 argmin of the reference is therefore always inside a recorded group.  The
+//      running minimum starts from the score of the row's winner in the previous call on the same workspace,
+//      re-evaluated against the current codebook (an upper bound of the minimum whatever the workspace holds).
+//   3. RE-RANK all codes of the surviving groups with the reference arithmetic (in-order fma chain, first index wins
+//      ties).  Rows whose group list overflows, or whose magnitudes break the error model, go to an exact scan
+//      (k_assign_fallback_scan / _finish).
 //
 // Kernel organisation (persistent, one CTA per SM, 896 threads, warp specialised, setmaxnreg per role):
-//   warps 0-15  drain: tcgen05.ld 16 columns at a time, running min + group list per row; two threads per
-//               row (one per column half of every accumulator slot); at the end of a pass the halves
-//               exchange minima and push the surviving groups into a work queue
+//   warps 0-15  drain: three tcgen05.ld of 16 columns in flight, running min + group list per row; two threads per
+//               row (one per column half of every accumulator slot; one per slot at the narrow widths); at the end of a
+//               pass the two exchange minima and push the surviving groups into a work queue
 //   warps 16-23 feature producers AND re-rankers: stage the prefetched next 256 raw rows in shared memory
-//               (double buffered), write them centred + TF32-rounded into TMEM as the A operand; then,
-//               while the tensor core and the drain warps work on that pass, re-rank the previous pass'
-//               queue from the staged rows (4 lanes per group, shared-memory 64-bit atomicMin per row),
-//               write idx/dist, red.global.add.v4 the weighted rows; then prefetch.
+//               (double buffered), write them centred + rounded into TMEM as the A operand together with the row's
+//               band and seed; then, while the tensor core and the drain warps work on that pass, re-rank the previous
+//               pass' queue from the staged rows (a lane per code, shared-memory 64-bit atomicMin per row), write
+//               idx/dist, scale the rows by their weights and bulk-reduce them into the centroid sums; then prefetch.
 //   warp 24     bulk-copy (TMA engine, cp.async.bulk) producer: codebook image stages -> smem ring
-//   warps 25,26 MMA issuers, one per row tile: per stage KSTEPS tcgen05.mma (M=128, N=BN, K=8), commits to mbarriers;
+//   warps 25,26 MMA issuers, one per row tile: per stage KSTEPS tcgen05.mma (M=128, N=BN), commits to mbarriers;
 //               warp 26 also allocates the TMEM (512 columns: four 128 x BN fp32 accumulator slots, two per row
 //               tile, then the A operand of both row tiles)
 // A pass is 256 rows x all K codes.  Each row tile owns two accumulator slots, so the MMA warp fills one while
