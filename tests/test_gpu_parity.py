@@ -89,6 +89,22 @@ def test_assign_generic_widths_bit_exact(L, oracle, d, screen, monkeypatch):
     assert np.abs(a[:, d] - sw64).max() <= 1e-5 * (np.abs(sw64).max() + 1e-30)
 
 
+@pytest.mark.parametrize("d", [6, 7, 45])
+@pytest.mark.parametrize("k", [1, 64, 97, 150, 193, 300])
+def test_assign_many_passes_few_steps(L, d, k):
+    """Several 256-row passes per CTA against codebooks of one to four 96-code steps (odd and even step counts: the
+    accumulator slots alternate their role from pass to pass when the count is odd): tensor-core path == exact kernel,
+    twice (unseeded, seeded)."""
+    n = 300_007
+    x, _, cb = _synth(n, d, k, seed=7000 + 10 * d + k)
+    xd, cbd = x.to(DEV), cb.to(DEV)
+    dist_e, idx_e = L.assign(xd, cbd, exact=True)
+    for _ in range(2):
+        dist, idx = L.assign(xd, cbd)
+        assert torch.equal(idx, idx_e)
+        assert torch.equal(dist.view(torch.int32), dist_e.view(torch.int32))
+
+
 @pytest.mark.parametrize("d", [45, 48])
 def test_assign_seeded_running_minima_are_harmless(L, oracle, d, monkeypatch):
     """The tensor-core kernel seeds every row's running minimum with the row's winner of the previous call on the same
