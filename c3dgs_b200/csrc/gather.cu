@@ -117,6 +117,16 @@ k_gather_span(const float *__restrict__ table, int64_t table_rows, int d, unsign
 // 48-float rows, i.e. aligned float4 loads, the span copy below reaches 5.95 TB/s: what holds the 180-byte rows back is
 // that their source rows are only 4-byte aligned.)
 
+// (End of round 2, ncu on the three kernels at 5.8 M rows, profiles/r5a_ncu_gather_summary.txt: what bounds
+// k_gather_span is the L1 data pipe — l1tex__data_pipe_lsu_wavefronts at 89 % of its peak, ~350 wavefronts per span of
+// 32 rows (every 4-byte load instruction of a warp touches three or four source rows), where k_gather_span4 needs 171
+// and sits at 55 %.  Two more organisations measured against it on the same box, both bit-exact, both dropped:
+// (1) the two ALIGNED 16-byte granules around each output float4 loaded as float4 and shifted in registers by
+// (address / 4) & 3 with nine selects, the columns past a row end as scalar loads: 0.254 ms against 0.246 ms — half the
+// sectors, but each granule load still costs ~10 wavefronts (327 per span) and the instruction count stays ~80 per
+// float4; (2) the span assembled in shared memory by 4-byte loads with lanes over consecutive span elements and sent
+// out by one cp.async.bulk per span, double buffered per warp, 15 loads in flight per lane: 0.424 ms.)
+
 // Rows of whole float4 (d % 4 == 0; 48 floats = the fork's colour rows): the same span organisation without the
 // staging — the 32 * dv float4 of a span are copied lane-linear, four loads in flight per lane, the row of element e
 // by a multiply-shift (exact for e < 32 * dv, dv < 128) against row pointers parked in shared memory.

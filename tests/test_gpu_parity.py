@@ -439,6 +439,29 @@ def test_gather_bit_exact(L, oracle, shape):
     assert empty.shape == (0,) + tuple(shape[1:])
 
 
+@pytest.mark.parametrize("d", [1, 3, 5, 6, 7, 9, 13, 45, 47, 48, 63, 101, 179, 181])
+def test_gather_unaligned_rows_every_alignment(L, d):
+    """Rows that are not whole float4, or whose table is not 16-byte aligned (k_gather_span): every residue of d mod 4,
+    the table starting at each of the four 4-byte alignments, ragged row counts (the partial last span), the last table
+    row, and out-of-range indices, which decode to zeros (the unchecked decode's contract)."""
+    g = torch.Generator().manual_seed(1000 + d)
+    rows = 517
+    store = torch.randn(rows * d + 8, generator=g).to(DEV)
+    for shift in range(4):
+        table = store[shift:shift + rows * d].view(rows, d)
+        assert table.data_ptr() % 16 == (store.data_ptr() + 4 * shift) % 16
+        for n in (1, 31, 32, 33, 64, 4099, 100_003):
+            idx = torch.randint(0, rows, (n,), generator=g)
+            idx[::97] = rows - 1
+            idx[5::389] = 0
+            want = table.cpu()[idx]
+            if n > 40:
+                idx[7], idx[40] = -1, rows
+                want[7], want[40] = 0.0, 0.0
+            out = L.gather(table, idx.to(DEV))
+            assert torch.equal(out.cpu(), want), (d, shift, n)
+
+
 def test_indexed_decode_autograd_matches_torch_indexing(L):
     from c3dgs_b200 import indexed_decode
     g = torch.Generator().manual_seed(12)
