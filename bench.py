@@ -561,7 +561,9 @@ def main():
     ms_g = timed(lambda: _lib.gather(vq.codebook, idx_dec))
     gbytes = float(n) * (8 + 4 * d)
     roofline_gather = {"bound": "hbm", "achieved": gbytes / ms_g * 1e-6, "peak": pk["hbm_gbs"], "unit": "GB/s",
-                       "frac": gbytes / ms_g * 1e-6 / pk["hbm_gbs"], "traffic": None, "kernel": "k_gather_span / k_gather32",
+                       "frac": gbytes / ms_g * 1e-6 / pk["hbm_gbs"], "traffic": None,
+                       "kernel": "k_gather_pad_prep + k_gather_padded (c3vq_gather_ws: four padded copies of the "
+                                 "table, aligned 16-byte loads)" if d % 4 and d >= 12 else "k_gather_span4 / k_gather_span",
                        "kernel_ms": ms_g, "algorithmic_bytes_per_launch": gbytes,
                        "write_only_peak_measured_gbs": write_peak_gbs,
                        "frac_vs_write_only_peak": gbytes / ms_g * 1e-6 / write_peak_gbs,

@@ -76,6 +76,8 @@ SIGNATURES = {
     "c3vq_assign_accumulate": (_c_int, [_c_vp, _c_vp, _c_vp, _c_i64, _c_int, _c_vp, _c_int, _c_int, _c_vp, _c_vp,
                                         _c_vp, _c_vp, _c_sz, _c_vp]),
     "c3vq_gather": (_c_int, [_c_vp, _c_i64, _c_int, _c_vp, _c_i64, _c_vp, _c_vp]),
+    "c3vq_gather_workspace_bytes": (_c_sz, [_c_i64, _c_int, _c_i64]),
+    "c3vq_gather_ws": (_c_int, [_c_vp, _c_i64, _c_int, _c_vp, _c_i64, _c_vp, _c_vp, _c_sz, _c_vp]),
     "c3vq_scatter_add": (_c_int, [_c_vp, _c_vp, _c_i64, _c_int, _c_vp, _c_i64, _c_vp]),
     "c3vq_join_workspace_bytes": (_c_sz, [_c_i64]),
     "c3vq_join_count": (_c_int, [_c_vp, _c_i64, ctypes.POINTER(_c_i64), _c_vp, _c_sz, _c_vp]),
@@ -387,7 +389,7 @@ def ema(codebook, entry_importance, acc, decay: float, eps: float, scale_normali
 
 
 def gather(table: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
-    """out[i] = table[idx[i]] for a [R, ...] float32 table.  c3vq_gather."""
+    """out[i] = table[idx[i]] for a [R, ...] float32 table.  c3vq_gather / c3vq_gather_ws."""
     _check(table, torch.float32, "table")
     _check(idx, torch.int64, "idx", 1)
     if idx.device != table.device:
@@ -398,7 +400,13 @@ def gather(table: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
     n = idx.numel()
     with torch.cuda.device(table.device):
         out = torch.empty((n,) + tuple(table.shape[1:]), dtype=torch.float32, device=table.device)
-        rc = load().c3vq_gather(_ptr(table), rows, d, _ptr(idx), n, _ptr(out), _stream(table))
+        L = load()
+        nbytes = L.c3vq_gather_workspace_bytes(rows, d, n)     # > 0: 180-byte rows & co. decode from padded copies
+        if nbytes:
+            ws = _workspace.get(table.device, nbytes, "gather")
+            rc = L.c3vq_gather_ws(_ptr(table), rows, d, _ptr(idx), n, _ptr(out), _ptr(ws), ws.numel(), _stream(table))
+        else:
+            rc = L.c3vq_gather(_ptr(table), rows, d, _ptr(idx), n, _ptr(out), _stream(table))
     if rc:
         raise _err(rc)
     return out

@@ -228,6 +228,19 @@ int c3vq_gather(const float *table, int64_t table_rows, int d, const int64_t *id
     return launch_gather(table, table_rows, d, idx, n, out, (cudaStream_t)stream);
 }
 
+size_t c3vq_gather_workspace_bytes(int64_t table_rows, int d, int64_t n)
+{
+    return (table_rows < 0 || d < 0 || n < 0) ? 0 : gather_workspace_bytes(table_rows, d, n);
+}
+
+int c3vq_gather_ws(const float *table, int64_t table_rows, int d, const int64_t *idx, int64_t n, float *out, void *ws,
+                   size_t ws_bytes, c3vq_stream_t stream)
+{
+    C3VQ_CHECK_ARG(n >= 0 && d >= 0 && table_rows >= 0, "negative size");
+    C3VQ_CHECK_ARG(n == 0 || d == 0 || (table && idx && out), "null pointer");
+    return launch_gather_ws(table, table_rows, d, idx, n, out, ws, ws_bytes, (cudaStream_t)stream);
+}
+
 int c3vq_scatter_add(const float *grad_out, const int64_t *idx, int64_t n, int d, float *grad_table,
                      int64_t table_rows, c3vq_stream_t stream)
 {

@@ -64,6 +64,9 @@ int launch_ema(float *codebook, float *entry_importance, const float *acc, int k
                int scale_normalize, cudaStream_t s);
 int launch_gather(const float *table, int64_t table_rows, int d, const int64_t *idx, int64_t n, float *out,
                   cudaStream_t s);
+size_t gather_workspace_bytes(int64_t table_rows, int d, int64_t n);
+int launch_gather_ws(const float *table, int64_t table_rows, int d, const int64_t *idx, int64_t n, float *out,
+                     void *ws, size_t ws_bytes, cudaStream_t s);
 int launch_gather_rows(const float *x, const float *w, const int64_t *rows, int64_t n, int d, float *out_x,
                        float *out_w, cudaStream_t s);
 

@@ -5,7 +5,8 @@
 // `features[batch]` (compression/vq.py:70).  HBM bound: algorithmic bytes per output
 // row = 8 (idx, i64) + 4*d (row written); the table is L2 resident for codebooks.
 // Rows whose byte length is a multiple of 16 move as float4 with fully coalesced
-// stores; other widths are written as float4 too, a warp per span of 32 output rows (k_gather_span).
+// stores; other widths are written as float4 too, a warp per span of 32 output rows: from four padded copies of
+// the table when the caller lends scratch (k_gather_padded, c3vq_gather_ws), else with 4-byte loads (k_gather_span).
 #include "common.cuh"
 
 namespace c3vq {
@@ -168,6 +169,132 @@ k_gather_span4(const float4 *__restrict__ table, int64_t table_rows, int dv, uns
             }
         }
     }
+}
+
+// Rows that are not whole float4, from padded copies of the table (the caller lends scratch: c3vq_gather_ws).  What
+// bounds k_gather_span is the L1 data pipe: the source of an output float4 is only 4-byte aligned, so it takes four
+// 4-byte loads.  A float4 that starts at column c of its row needs a copy of the table in which column c is 16-byte
+// aligned, and c mod 4 takes four values: k_gather_pad_prep writes FOUR copies, copy q holding row j in a slot of P
+// floats (P % 4 == 0) behind a pad of (4 - q) & 3 floats, so that the columns c = q (mod 4) are aligned.  For a
+// 4096 x 45 codebook that is 3.4 MB, L2 resident.  Then an output float4 inside a row is ONE aligned 16-byte load from
+// copy c & 3; where it crosses the row end after m = d - c < 4 columns, the first columns of the next output row come
+// from that row's slot in copy 4 - m, whose pad is exactly m floats: the float4 at the slot start holds them at
+// positions m .. 3.  Two loads and three selects there, one load elsewhere — the load pattern of k_gather_span4.
+// (Writing the crossing float4 in a second sweep, one per lane, so that the main loop has no second load: 0.37 ms
+// against 0.23 ms — the output stream then has 16-byte holes that are filled later, and partial-line writes are what
+// the L2 / DRAM write path punishes most.)
+__global__ void __launch_bounds__(256)
+k_gather_pad_prep(const float *__restrict__ table, int rows, int d, int P, float *__restrict__ pad)
+{
+    const int total = 4 * rows * P;
+    for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < total; e += gridDim.x * blockDim.x) {
+        const int slot = e / P, p = e - slot * P;
+        const int q = slot / rows, j = slot - q * rows;
+        const int col = p - ((4 - q) & 3);
+        pad[e] = (col >= 0 && col < d) ? table[(int64_t)j * d + col] : 0.f;
+    }
+}
+
+// 16-byte load through the read-only path under a predicate (zeros where it is off): no branch around the load
+__device__ __forceinline__ float4 ldg_f4_if(const float4 *p, bool on)
+{
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %5, 0;\n\t"
+        "@p ld.global.nc.v4.f32 {%0, %1, %2, %3}, [%4];\n\t}"
+        : "+f"(v.x), "+f"(v.y), "+f"(v.z), "+f"(v.w)
+        : "l"(p), "r"((int)on)
+        : "memory");                                     // keeps the stores of a round behind all of its loads
+    return v;
+}
+
+__global__ void __launch_bounds__(256)
+k_gather_padded(const float *__restrict__ table, const float4 *__restrict__ pad, int rows, int d, int P4,
+                unsigned int inv, const int64_t *__restrict__ idx, int64_t n, float *__restrict__ out)
+{
+    __shared__ int sj[8][32];                                        // source row of each output row (-1: zeros)
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int64_t nwarps = (int64_t)gridDim.x * 8;
+    const unsigned int ud = (unsigned int)d;
+    for (int64_t r0 = ((int64_t)blockIdx.x * 8 + wib) * 32; r0 < n; r0 += nwarps * 32) {
+        const int rows_here = (int)min((int64_t)32, n - r0);
+        long long j = -1;
+        if (lane < rows_here) {
+            j = idx[r0 + lane];
+            if ((uint64_t)j >= (uint64_t)rows) j = -1;
+        }
+        __syncwarp();
+        sj[wib][lane] = (int)j;
+        __syncwarp();
+        float *dst = out + r0 * d;
+        const unsigned int total = (unsigned int)rows_here * ud;
+        if (rows_here == 32) {                                       // 32 d floats: whole float4, none crosses the span end
+            // four float4 per lane and round, every load issued (predicated, no branches) before the first select
+            for (unsigned int e0 = lane * 4; e0 < total; e0 += 512) {
+                float4 va[4], vb[4];
+                unsigned int m[4];
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const unsigned int e = min(e0 + 128u * u, total - 4u);       // past the end: a harmless repeat
+                    const unsigned int r = (e * inv) >> 20, c = e - r * ud, q = c & 3u;
+                    m[u] = ud - c;                                   // columns left in output row r (>= 1)
+                    const int ja = sj[wib][r], jb = sj[wib][(r + 1u) & 31u];
+                    va[u] = ldg_f4_if(pad + ((q * rows + ja) * P4 + ((((4u - q) & 3u) + c) >> 2)), ja >= 0);
+                    // columns m .. 3 open output row r + 1: the start of its slot in copy 4 - m
+                    vb[u] = ldg_f4_if(pad + (((4u - m[u]) & 3u) * rows + jb) * P4, m[u] < 4u && jb >= 0);
+                }
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const unsigned int e = e0 + 128u * u;
+                    if (e < total) {
+                        float4 v = va[u];
+                        if (m[u] <= 1u) v.y = vb[u].y;
+                        if (m[u] <= 2u) v.z = vb[u].z;
+                        if (m[u] <= 3u) v.w = vb[u].w;
+                        *reinterpret_cast<float4 *>(dst + e) = v;
+                    }
+                }
+            }
+        } else {                                                     // the last, partial span: from the table itself
+            for (unsigned int e = lane; e < total; e += 32) {
+                const unsigned int r = e / ud, c = e - r * ud;
+                const int js = sj[wib][r];
+                dst[e] = js >= 0 ? __ldg(table + (int64_t)js * d + c) : 0.f;
+            }
+        }
+    }
+}
+
+constexpr size_t GATHER_PAD_MAX_BYTES = 16u << 20;       // the four copies must stay L2 resident
+static inline int gather_pad_pitch(int d) { return (d + 9) & ~3; }   // pad (<= 3) + d + read-past (<= 3), whole float4
+
+size_t gather_workspace_bytes(int64_t table_rows, int d, int64_t n)
+{
+    if (d < 12 || d >= 181 || d % 4 == 0 || table_rows <= 0) return 0;   // narrow rows: k_gather_span is faster
+    const size_t bytes = (size_t)4 * (size_t)table_rows * gather_pad_pitch(d) * sizeof(float);
+    if (bytes > GATHER_PAD_MAX_BYTES || n < 8 * table_rows) return 0;   // the copies must pay for themselves
+    return bytes;
+}
+
+int launch_gather_ws(const float *table, int64_t table_rows, int d, const int64_t *idx, int64_t n, float *out,
+                     void *ws, size_t ws_bytes, cudaStream_t s)
+{
+    const size_t need = gather_workspace_bytes(table_rows, d, n);
+    if (need == 0 || ws == nullptr || ws_bytes < need || (reinterpret_cast<uintptr_t>(ws) & 15) != 0 ||
+        (reinterpret_cast<uintptr_t>(out) & 15) != 0)
+        return launch_gather(table, table_rows, d, idx, n, out, s);
+    const int rows = (int)table_rows, P = gather_pad_pitch(d);
+    const int total = 4 * rows * P;
+    k_gather_pad_prep<<<(total + 255) / 256, 256, 0, s>>>(table, rows, d, P, (float *)ws);
+    C3VQ_LAUNCH_CHECK("k_gather_pad_prep");
+    int64_t blocks = (n + 255) / 256;
+    const int64_t cap = (int64_t)sm_count() * 16;
+    if (blocks > cap) blocks = cap;
+    k_gather_padded<<<(unsigned)blocks, 256, 0, s>>>(table, (const float4 *)ws, rows, d, P / 4,
+                                                     ((1u << 20) + d - 1) / d, idx, n, out);
+    C3VQ_LAUNCH_CHECK("k_gather_padded");
+    return C3VQ_OK;
 }
 
 template <typename T>

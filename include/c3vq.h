@@ -16,6 +16,7 @@
  *   c3vq_update        <- VectorQuantize.update          compression/vq.py:28-35
  *   c3vq_assign_accumulate <- vq.py:30-31,33 (update without the EMAs; multi-GPU building block)
  *   c3vq_gather        <- codebook[idx] decode           compression/vq.py:40-42; scene/gaussian_model.py:220, :240, :257, :893-897
+ *   c3vq_gather_ws     <- the same decode with scratch   (aligned loads from padded copies of the table)
  *   c3vq_scatter_add   <- backward of that gather        (autograd index_put_(accumulate=True))
  *   c3vq_gather_rows   <- features[batch]                compression/vq.py:70
  */
@@ -166,6 +167,19 @@ int c3vq_assign_accumulate(const float *x, const float *w, const int64_t *rows, 
 /* Indexed-codebook decode: out[i,:] = table[idx[i],:], rows of d floats. */
 int c3vq_gather(const float *table, int64_t table_rows, int d,
                 const int64_t *idx, int64_t n, float *out, c3vq_stream_t stream);
+
+/*
+ * The same decode with scratch lent by the caller.  Rows that are not whole float4 (the 45-float SH rows) are only
+ * 4-byte aligned in the table, which costs the plain call four 4-byte loads per 16 bytes written; with
+ * c3vq_gather_workspace_bytes(table_rows, d, n) bytes of scratch (16-byte aligned) the call first writes four padded
+ * copies of the table, one per alignment, and then decodes with aligned 16-byte loads.  The size is 0 when the
+ * copies would not pay (whole-float4 rows, rows under 12 floats, tables above 16 MB of copies, n < 8 table_rows): then, and with ws null
+ * or too small, the call is c3vq_gather.  Same results bit for bit; out-of-range indices decode to zeros.
+ */
+size_t c3vq_gather_workspace_bytes(int64_t table_rows, int d, int64_t n);
+int c3vq_gather_ws(const float *table, int64_t table_rows, int d,
+                   const int64_t *idx, int64_t n, float *out,
+                   void *ws, size_t ws_bytes, c3vq_stream_t stream);
 
 /* Backward of the decode: grad_table[idx[i],:] += grad_out[i,:] (grad_table zeroed by caller). */
 int c3vq_scatter_add(const float *grad_out, const int64_t *idx, int64_t n, int d,

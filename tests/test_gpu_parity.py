@@ -441,16 +441,17 @@ def test_gather_bit_exact(L, oracle, shape):
 
 @pytest.mark.parametrize("d", [1, 3, 5, 6, 7, 9, 13, 45, 47, 48, 63, 101, 179, 181])
 def test_gather_unaligned_rows_every_alignment(L, d):
-    """Rows that are not whole float4, or whose table is not 16-byte aligned (k_gather_span): every residue of d mod 4,
-    the table starting at each of the four 4-byte alignments, ragged row counts (the partial last span), the last table
-    row, and out-of-range indices, which decode to zeros (the unchecked decode's contract)."""
+    """Rows that are not whole float4, or whose table is not 16-byte aligned (k_gather_span, and k_gather_padded from
+    the four padded copies once n >= 8 table rows): every residue of d mod 4, the table starting at each of the four
+    4-byte alignments, ragged row counts (the partial last span), the last table row, and out-of-range indices, which
+    decode to zeros (the unchecked decode's contract)."""
     g = torch.Generator().manual_seed(1000 + d)
     rows = 517
     store = torch.randn(rows * d + 8, generator=g).to(DEV)
     for shift in range(4):
         table = store[shift:shift + rows * d].view(rows, d)
         assert table.data_ptr() % 16 == (store.data_ptr() + 4 * shift) % 16
-        for n in (1, 31, 32, 33, 64, 4099, 100_003):
+        for n in (1, 31, 32, 33, 64, 4099, 4136, 4137, 100_003):
             idx = torch.randint(0, rows, (n,), generator=g)
             idx[::97] = rows - 1
             idx[5::389] = 0
@@ -458,8 +459,23 @@ def test_gather_unaligned_rows_every_alignment(L, d):
             if n > 40:
                 idx[7], idx[40] = -1, rows
                 want[7], want[40] = 0.0, 0.0
-            out = L.gather(table, idx.to(DEV))
+            dev_idx = idx.to(DEV)
+            out = L.gather(table, dev_idx)
             assert torch.equal(out.cpu(), want), (d, shift, n)
+            # the C entry points side by side: without scratch (c3vq_gather), and with scratch refused (null / short)
+            lib = L.load()
+            need = lib.c3vq_gather_workspace_bytes(rows, d, n)
+            assert (need > 0) == (d % 4 != 0 and 12 <= d < 181 and n >= 8 * rows), (d, n, need)
+            plain = torch.empty_like(out)
+            assert lib.c3vq_gather(table.data_ptr(), rows, d, dev_idx.data_ptr(), n, plain.data_ptr(), None) == 0
+            assert torch.equal(plain, out)
+            if need:
+                short = torch.empty(need - 16, dtype=torch.uint8, device=DEV)
+                for ws, nb in ((None, 0), (short, short.numel())):
+                    o2 = torch.full_like(out, float("nan"))
+                    assert lib.c3vq_gather_ws(table.data_ptr(), rows, d, dev_idx.data_ptr(), n, o2.data_ptr(),
+                                              ws.data_ptr() if ws is not None else None, nb, None) == 0
+                    assert torch.equal(o2, out)
 
 
 def test_indexed_decode_autograd_matches_torch_indexing(L):

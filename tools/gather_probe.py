@@ -24,7 +24,7 @@ def timed(fn, reps=10):
     return a.elapsed_time(b) / reps
 
 
-for d, rows in ((45, 4096), (48, 4096), (48, 294096), (7, 4096)):
+for d, rows in ((45, 4096), (45, 294096), (48, 4096), (48, 294096), (7, 4096), (6, 4096), (13, 4096), (27, 512)):
     tab = torch.randn(rows, d, device=dev, generator=g)
     idx = torch.randint(0, rows, (n,), device=dev, generator=g)
     out = _lib.gather(tab, idx)
@@ -32,4 +32,8 @@ for d, rows in ((45, 4096), (48, 4096), (48, 294096), (7, 4096)):
     t = timed(lambda: _lib.gather(tab, idx))
     t_ref = timed(lambda: tab[idx])
     gb = n * (8 + 4 * d) / 1e9
-    print(f"d={d} table rows {rows}: {t:.3f} ms = {gb / t:.2f} TB/s (torch indexing {t_ref:.3f} ms)")
+    lib = _lib.load()
+    t_plain = timed(lambda: lib.c3vq_gather(tab.data_ptr(), rows, d, idx.data_ptr(), n, out.data_ptr(), None))
+    ws = lib.c3vq_gather_workspace_bytes(rows, d, n)
+    print(f"d={d} table rows {rows}: {t:.3f} ms = {gb / t:.2f} TB/s (torch indexing {t_ref:.3f} ms; "
+          f"c3vq_gather without scratch {t_plain:.3f} ms; scratch {ws} B)")

@@ -11,7 +11,7 @@ dev = torch.device("cuda:0")
 g = torch.Generator(device=dev).manual_seed(0)
 n = 5_800_000
 idx = torch.randint(0, 4096, (n,), device=dev, generator=g)
-for d in (45, 48):
+for d in (45, 48, 27):
     cb = torch.randn(4096, d, device=dev, generator=g)
     for _ in range(3):
         out = _lib.gather(cb, idx)
