@@ -364,8 +364,8 @@ int c3vq_preprocess_indexed(int64_t p, int sh_degree, int sh_coeffs, const float
                               out_tiles_touched && out_clamped),
                    "null output pointer");
     C3VQ_CHECK_ARG(((uintptr_t)rotations & 15) == 0 && ((uintptr_t)out_conic_opacity & 15) == 0 &&
-                       ((uintptr_t)out_xy & 7) == 0,
-                   "rotations / out_conic_opacity must be 16-byte and out_xy 8-byte aligned");
+                       ((uintptr_t)out_xy & 7) == 0 && ((uintptr_t)out_cov3d & 7) == 0,
+                   "rotations / out_conic_opacity must be 16-byte and out_xy / out_cov3d 8-byte aligned");
     return launch_preprocess_indexed(p, sh_degree, sh_coeffs, means3d, scales, scale_factors, scale_modifier, rotations,
                                      opacities, shs, viewmatrix, projmatrix, cam_pos, width, height, focal_x, focal_y,
                                      tan_fovx, tan_fovy, prefiltered, sh_indices, g_indices, clamp_color, out_radii,

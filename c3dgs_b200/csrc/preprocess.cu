@@ -76,8 +76,8 @@ __global__ void __launch_bounds__(PRE_THREADS, 4) k_preprocess_indexed(const Pre
     const V3 pv = {sv[0] * px + sv[4] * py + sv[8] * pz + sv[12], sv[1] * px + sv[5] * py + sv[9] * pz + sv[13],
                    sv[2] * px + sv[6] * py + sv[10] * pz + sv[14]};
     if (!q.prefiltered && pv.z <= 0.01f) {
-        float *cz = q.cov3d + idx * 6;
-        cz[0] = 0.f, cz[1] = 0.f, cz[2] = 0.f, cz[3] = 0.f, cz[4] = 0.f, cz[5] = 0.f;
+        float2 *cz = reinterpret_cast<float2 *>(q.cov3d + idx * 6);    // 24-byte rows: 8-byte aligned
+        cz[0] = make_float2(0.f, 0.f), cz[1] = make_float2(0.f, 0.f), cz[2] = make_float2(0.f, 0.f);
         zero_rest();
         return;
     }
@@ -104,8 +104,8 @@ __global__ void __launch_bounds__(PRE_THREADS, 4) k_preprocess_indexed(const Pre
     const float c0 = m00 * m00 + m10 * m10 + m20 * m20, c1 = m00 * m01 + m10 * m11 + m20 * m21;
     const float c2 = m00 * m02 + m10 * m12 + m20 * m22, c3 = m01 * m01 + m11 * m11 + m21 * m21;
     const float c4 = m01 * m02 + m11 * m12 + m21 * m22, c5 = m02 * m02 + m12 * m12 + m22 * m22;
-    float *cov3 = q.cov3d + idx * 6;
-    cov3[0] = c0, cov3[1] = c1, cov3[2] = c2, cov3[3] = c3, cov3[4] = c4, cov3[5] = c5;
+    float2 *cov3 = reinterpret_cast<float2 *>(q.cov3d + idx * 6);     // 24-byte rows: 8-byte aligned
+    cov3[0] = make_float2(c0, c1), cov3[1] = make_float2(c2, c3), cov3[2] = make_float2(c4, c5);
 
     // EWA 2D covariance (forward_indexed.cu:79-121)
     const float limx = 1.3f * q.tan_fovx, limy = 1.3f * q.tan_fovy;
