@@ -281,7 +281,8 @@ int c3vq_compact_rows(const void *src, const uint8_t *keep_mask, int64_t n, int6
  * culled at the near plane (depth <= 0.01) gets zeros everywhere, one with a singular 2D covariance or no covered tile
  * gets its cov3d and zeros elsewhere (the reference leaves those rows untouched).
  * float32 throughout; agrees with the reference kernel to rounding (sum order inside the 3x3 products), see
- * tests/test_gpu_preprocess.py for the stated tolerances.
+ * tests/test_gpu_preprocess.py for the stated tolerances.  Alignment: rotations and out_conic_opacity 16 bytes,
+ * out_xy and out_cov3d 8 bytes (C3VQ_EINVAL otherwise).
  */
 int c3vq_preprocess_indexed(int64_t p, int sh_degree, int sh_coeffs, const float *means3d, const float *scales,
                             const float *scale_factors, float scale_modifier, const float *rotations,
