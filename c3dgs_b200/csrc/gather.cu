@@ -11,6 +11,14 @@
 
 namespace c3vq {
 
+// output rows are written once and not read by the kernel: streaming stores keep them from evicting the table rows
+// (the kept-rows table of a compressed scene is tens of MB and lives in the L2 between its reads)
+#ifdef C3VQ_GATHER_PLAIN_ST
+#define C3VQ_GATHER_ST(p, v) (*(p) = (v))
+#else
+#define C3VQ_GATHER_ST(p, v) __stcs((p), (v))
+#endif
+
 template <typename T>
 __global__ void __launch_bounds__(256)
 k_gather(const T *__restrict__ table, int64_t table_rows, int dv, const int64_t *__restrict__ idx, int64_t n,
@@ -100,7 +108,7 @@ k_gather_span(const float *__restrict__ table, int64_t table_rows, int d, unsign
                 }
             }
             if (e + 3 < total) {
-                *reinterpret_cast<float4 *>(dst + e) = make_float4(v[0], v[1], v[2], v[3]);
+                C3VQ_GATHER_ST(reinterpret_cast<float4 *>(dst + e), make_float4(v[0], v[1], v[2], v[3]));
             } else {
                 for (int t = 0; t < 4 && e + t < total; t++) dst[e + t] = v[t];
             }
@@ -165,7 +173,7 @@ k_gather_span4(const float4 *__restrict__ table, int64_t table_rows, int dv, uns
 #pragma unroll
             for (int u = 0; u < 4; u++) {
                 const unsigned int e = e0 + 32 * u;
-                if (e < total) dst[e] = v[u];
+                if (e < total) C3VQ_GATHER_ST(dst + e, v[u]);
             }
         }
     }
@@ -252,7 +260,7 @@ k_gather_padded(const float *__restrict__ table, const float4 *__restrict__ pad,
                         if (m[u] <= 1u) v.y = vb[u].y;
                         if (m[u] <= 2u) v.z = vb[u].z;
                         if (m[u] <= 3u) v.w = vb[u].w;
-                        *reinterpret_cast<float4 *>(dst + e) = v;
+                        C3VQ_GATHER_ST(reinterpret_cast<float4 *>(dst + e), v);
                     }
                 }
             }
