@@ -558,7 +558,7 @@ def main():
     # decode gather: codebook[idx] -> [n, d], 8 B index in + 4 d B out per row
     gen = torch.Generator(device=dev).manual_seed(5 + rank)
     idx_dec = torch.randint(0, K, (n,), device=dev, generator=gen)
-    ms_g = timed(lambda: _lib.gather(vq.codebook, idx_dec))
+    ms_g = timed(lambda: _lib.gather(vq.codebook, idx_dec), reps=20)
     gbytes = float(n) * (8 + 4 * d)
     roofline_gather = {"bound": "hbm", "achieved": gbytes / ms_g * 1e-6, "peak": pk["hbm_gbs"], "unit": "GB/s",
                        "frac": gbytes / ms_g * 1e-6 / pk["hbm_gbs"], "traffic": None,
